@@ -1,0 +1,738 @@
+// libaps: host side of the C ABI in include/aps.h.  Owns the HBM slab, the hash table and the scratch
+// buffers of one store, stages request arrays, launches the kernels in aps_kernels.cuh.
+// There is NO CPU fallback: every data-path entry point needs a CUDA device and fails with APS_ECUDA
+// when the runtime cannot provide one.
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <unordered_set>
+#include <vector>
+
+#include "aps_kernels.cuh"
+
+using namespace aps;
+
+namespace {
+
+thread_local char tl_cuda_error[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+#define CUDA_TRY(expr)                                                                                   \
+  do {                                                                                                   \
+    cudaError_t _e = (expr);                                                                             \
+    if (_e != cudaSuccess) {                                                                             \
+      snprintf(tl_cuda_error, sizeof(tl_cuda_error), "%s:%d %s -> %s", __FILE__, __LINE__, #expr,        \
+               cudaGetErrorString(_e));                                                                  \
+      return APS_ECUDA;                                                                                  \
+    }                                                                                                    \
+  } while (0)
+
+struct DeviceGuard {  // the library never leaves the caller's current device changed
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// ---- per-device constants: CRC tables and shift constants --------------------------------------
+uint32_t host_xpow8(uint64_t nbytes) {  // x^(8*nbytes) mod P by square and multiply
+  uint32_t r = 0x80000000u;  // x^0 (bit 31 is x^0)
+  uint32_t p = 0x00800000u;  // x^8
+  for (; nbytes; nbytes >>= 1) {
+    if (nbytes & 1) r = gf_mul(r, p);
+    p = gf_mul(p, p);
+  }
+  return r;
+}
+
+struct DeviceConsts {
+  bool ready = false;
+  CrcTables* d_tables = nullptr;
+  int num_sms = 0;
+};
+std::mutex g_dev_mu;
+DeviceConsts g_dev[64];
+
+struct HostCrcConsts {
+  CrcTables tables;
+  uint32_t xpow8[32];
+  uint32_t lane_shift[32];
+};
+// Pure host arithmetic: the GF(2) constants the copy kernel uses.
+const HostCrcConsts& host_crc_consts() {
+  static const HostCrcConsts* c = [] {
+    auto* h = new HostCrcConsts();
+    const uint32_t xrow = host_xpow8(kRowBytes), x4 = host_xpow8(4);
+    for (uint32_t j = 0; j < 4; ++j)
+      for (uint32_t b = 0; b < 256; ++b) {
+        h->tables.fold[j][b] = gf_mul(b << (8 * j), xrow);
+        h->tables.z4[j][b] = gf_mul(b << (8 * j), x4);
+      }
+    for (int k = 0; k < 32; ++k) h->xpow8[k] = host_xpow8(1ull << k);
+    // lane l holds bytes 16l..16l+15 of a 512-byte row; after the in-lane reduction its value
+    // still has 512 - 16l - 12 = 500 - 16l bytes of the row behind it
+    for (int l = 0; l < 32; ++l) h->lane_shift[l] = host_xpow8(500 - 16 * l);
+    return h;
+  }();
+  return *c;
+}
+
+int ensure_device_consts(int dev, DeviceConsts** out) {
+  std::lock_guard<std::mutex> lk(g_dev_mu);
+  if (dev < 0 || dev >= 64) return APS_EINVAL;
+  DeviceConsts& d = g_dev[dev];
+  if (!d.ready) {
+    const HostCrcConsts& h = host_crc_consts();
+    CUDA_TRY(cudaMalloc(&d.d_tables, sizeof(CrcTables)));
+    CUDA_TRY(cudaMemcpy(d.d_tables, &h.tables, sizeof(CrcTables), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpyToSymbol(c_xpow8, h.xpow8, sizeof(h.xpow8)));
+    CUDA_TRY(cudaMemcpyToSymbol(c_lane_shift, h.lane_shift, sizeof(h.lane_shift)));
+    CUDA_TRY(cudaFuncSetAttribute(copy_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+    CUDA_TRY(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    d.ready = true;
+  }
+  *out = &d;
+  return APS_OK;
+}
+
+uint64_t next_pow2(uint64_t v) {
+  uint64_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+}  // namespace
+
+struct aps_store {
+  std::mutex mu;
+  bool closed = false;
+  aps_config cfg{};
+  cudaStream_t stream = nullptr;
+  Table table{};
+  uint64_t slots = 0, n_entries = 0;
+  uint32_t chunks_per_page = 0;
+  DeviceConsts* dc = nullptr;
+  // scratch, sized for cfg.max_batch requests
+  Job* d_jobs = nullptr;
+  uint32_t* d_partials = nullptr;
+  uint32_t* d_done = nullptr;
+  int* d_error = nullptr;
+  void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
+  aps_result* d_res = nullptr;
+  uint8_t* h_stage = nullptr;   // pinned: requests, then results
+  uint8_t* h_bounce = nullptr;  // pinned: one page, for pageable single-page callers
+  uint32_t faults = 0;
+  std::atomic<uint64_t> launches{0};
+  // optional timing of the copy kernel (aps_profile_*): event pairs recorded around each launch
+  bool prof_on = false;
+  std::vector<cudaEvent_t> prof_events;
+  size_t prof_used = 0;
+};
+
+namespace {
+
+inline void count_launch(aps_store* s, uint64_t k = 1) {
+  g_launches += k;
+  if (s) s->launches += k;
+}
+
+int launch_copy(aps_store* s, uint32_t n, aps_result* d_res, uint32_t* d_crc_out, cudaStream_t st) {
+  const bool crc = (s->cfg.flags & APS_FLAG_CRC) != 0 || d_crc_out != nullptr;
+  CopyArgs a{};
+  a.jobs = s->d_jobs;
+  a.n_jobs = n;
+  a.chunks_per_job = s->chunks_per_page;
+  a.res = d_res;
+  a.crc_out = d_crc_out;
+  a.partials = s->d_partials;
+  a.done = s->d_done;
+  a.tables = s->dc->d_tables;
+  a.slot_crc = s->table.slot_crc;
+  a.counters = s->table.counters;
+  a.error_flag = s->d_error;
+  const uint64_t items = (uint64_t)n * s->chunks_per_page;
+  const uint32_t warps_per_block = kCopyThreads / 32;
+  uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, (items + warps_per_block - 1) / warps_per_block);
+  if (grid == 0) grid = 1;
+  const bool timed = s->prof_on && s->prof_used + 2 <= s->prof_events.size();
+  if (timed) CUDA_TRY(cudaEventRecord(s->prof_events[s->prof_used], st));
+  if (crc) copy_kernel<true><<<grid, kCopyThreads, kCopyDynSmem, st>>>(a);
+  else copy_kernel<false><<<grid, kCopyThreads, 0, st>>>(a);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  if (timed) {
+    CUDA_TRY(cudaEventRecord(s->prof_events[s->prof_used + 1], st));
+    s->prof_used += 2;
+  }
+  return APS_OK;
+}
+
+inline dim3 tile_grid(uint32_t n) { return dim3((n * 8 + 255) / 256); }
+
+int check_open(aps_store* s) {
+  if (!s) return APS_EINVAL;
+  if (s->closed) return APS_ECLOSED;
+  return APS_OK;
+}
+
+struct KeyHash {
+  size_t operator()(const aps_key& k) const { return (size_t)hash_key(k); }
+};
+struct KeyEq {
+  bool operator()(const aps_key& a, const aps_key& b) const {
+    return a.file_hi == b.file_hi && a.file_lo == b.file_lo && a.page_index == b.page_index;
+  }
+};
+
+template <class GetKey>
+bool distinct_keys(uint32_t n, GetKey key_of) {
+  std::unordered_set<aps_key, KeyHash, KeyEq> seen;
+  seen.reserve(n * 2);
+  for (uint32_t i = 0; i < n; ++i)
+    if (!seen.insert(key_of(i)).second) return false;
+  return true;
+}
+
+int check_device_error(aps_store* s, cudaStream_t st) {
+  int err = 0;
+  CUDA_TRY(cudaMemcpyAsync(&err, s->d_error, sizeof(int), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  if (err) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "copy kernel: shared-memory window not at the expected address");
+    return APS_ECUDA;
+  }
+  return APS_OK;
+}
+
+void free_store(aps_store* s) {
+  cudaFree(s->table.slab);
+  cudaFree(s->table.entries);
+  cudaFree(s->table.free_slots);
+  cudaFree(s->table.free_top);
+  cudaFree(s->table.slot_crc);
+  cudaFree(s->table.counters);
+  cudaFree(s->d_jobs);
+  cudaFree(s->d_partials);
+  cudaFree(s->d_done);
+  cudaFree(s->d_error);
+  cudaFree(s->d_reqs);
+  cudaFree(s->d_res);
+  for (cudaEvent_t e : s->prof_events) cudaEventDestroy(e);
+  s->prof_events.clear();
+  if (s->h_stage) cudaFreeHost(s->h_stage);
+  if (s->h_bounce) cudaFreeHost(s->h_bounce);
+  if (s->stream) cudaStreamDestroy(s->stream);
+}
+
+__global__ void corrupt_kernel(Table t, aps_key key, uint32_t off, int* found) {
+  const uint32_t sub = threadIdx.x & 7u;
+  Probe pr = tile_lookup(t, key, sub, 0);
+  if (sub == 0) {
+    *found = pr.meta != 0;
+    if (pr.meta && off < meta_len(pr.meta)) t.slab[(uint64_t)meta_slot(pr.meta) * t.page_size + off] ^= 0x5Au;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* aps_version(void) { return "libaps 0.1 (sm_100a)"; }
+
+int aps_debug_crc_constants(uint32_t* fold, uint32_t* z4, uint32_t* xpow8_out, uint32_t* lane_shift) {
+  const HostCrcConsts& h = host_crc_consts();
+  if (fold) memcpy(fold, h.tables.fold, sizeof(h.tables.fold));
+  if (z4) memcpy(z4, h.tables.z4, sizeof(h.tables.z4));
+  if (xpow8_out) memcpy(xpow8_out, h.xpow8, sizeof(h.xpow8));
+  if (lane_shift) memcpy(lane_shift, h.lane_shift, sizeof(h.lane_shift));
+  return APS_OK;
+}
+const char* aps_last_cuda_error(void) { return tl_cuda_error; }
+uint64_t aps_total_kernel_launches(void) { return g_launches.load(); }
+
+const char* aps_strerror(int code) {
+  switch (code) {
+    case APS_OK: return "ok";
+    case APS_ENOTFOUND: return "page not found";
+    case APS_EINVAL: return "invalid argument";
+    case APS_ENOSPC: return "no free slab slot or table entry";
+    case APS_ECUDA: return "CUDA call failed";
+    case APS_ECORRUPT: return "page CRC32C mismatch";
+    case APS_ECLOSED: return "store is closed";
+    case APS_ENOMEM: return "out of memory";
+    case APS_EFAULT: return "injected fault";
+    default: return "unknown error";
+  }
+}
+
+int aps_open(const aps_config* cfg, aps_store** out) {
+  if (!cfg || !out) return APS_EINVAL;
+  *out = nullptr;
+  if (cfg->page_size == 0 || (cfg->page_size & 15u) || cfg->page_size > (1u << 30)) return APS_EINVAL;
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (cfg->device < 0 || cfg->device >= ndev) return APS_EINVAL;
+  DeviceGuard g(cfg->device);
+  if (!g.ok) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "cudaSetDevice(%d) failed", cfg->device);
+    return APS_ECUDA;
+  }
+  DeviceConsts* dc = nullptr;
+  int rc = ensure_device_consts(cfg->device, &dc);
+  if (rc != APS_OK) return rc;
+
+  aps_store* s = new (std::nothrow) aps_store();
+  if (!s) return APS_ENOMEM;
+  s->cfg = *cfg;
+  s->dc = dc;
+  uint64_t slots = cfg->slab_slots;
+  if (slots == 0) {
+    uint64_t base = (cfg->cache_bytes + cfg->page_size - 1) / cfg->page_size;
+    slots = base + std::max<uint64_t>(64, base / 8);
+  }
+  if (slots >= (1ull << 31)) { delete s; return APS_EINVAL; }
+  uint64_t entries = cfg->table_capacity ? next_pow2(cfg->table_capacity) : std::max<uint64_t>(1024, next_pow2(2 * slots));
+  if (entries < kBucketEntries) entries = kBucketEntries;
+  if (s->cfg.max_batch == 0) s->cfg.max_batch = 4096;
+  s->slots = slots;
+  s->n_entries = entries;
+  s->chunks_per_page = (cfg->page_size + kChunkBytes - 1) / kChunkBytes;
+  const uint32_t mb = s->cfg.max_batch;
+
+#define OPEN_TRY(expr)                                                                                    \
+  do {                                                                                                    \
+    cudaError_t _e = (expr);                                                                              \
+    if (_e != cudaSuccess) {                                                                              \
+      snprintf(tl_cuda_error, sizeof(tl_cuda_error), "%s:%d %s -> %s", __FILE__, __LINE__, #expr,         \
+               cudaGetErrorString(_e));                                                                   \
+      free_store(s);                                                                                      \
+      delete s;                                                                                           \
+      return _e == cudaErrorMemoryAllocation ? APS_ENOMEM : APS_ECUDA;                                    \
+    }                                                                                                     \
+  } while (0)
+
+  OPEN_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  OPEN_TRY(cudaMalloc(&s->table.slab, slots * (uint64_t)cfg->page_size));
+  OPEN_TRY(cudaMalloc(&s->table.entries, entries * sizeof(Entry)));
+  OPEN_TRY(cudaMalloc(&s->table.free_slots, slots * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->table.free_top, sizeof(int32_t)));
+  OPEN_TRY(cudaMalloc(&s->table.slot_crc, slots * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->table.counters, kNumCounters * sizeof(unsigned long long)));
+  OPEN_TRY(cudaMalloc(&s->d_jobs, (uint64_t)mb * sizeof(Job)));
+  OPEN_TRY(cudaMalloc(&s->d_partials, (uint64_t)mb * s->chunks_per_page * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->d_done, (uint64_t)mb * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->d_error, sizeof(int)));
+  OPEN_TRY(cudaMalloc(&s->d_reqs, (uint64_t)mb * sizeof(aps_get_req)));
+  OPEN_TRY(cudaMalloc(&s->d_res, (uint64_t)mb * sizeof(aps_result)));
+  OPEN_TRY(cudaHostAlloc(&s->h_stage, (uint64_t)mb * (sizeof(aps_get_req) + sizeof(aps_result)), cudaHostAllocDefault));
+  OPEN_TRY(cudaHostAlloc(&s->h_bounce, cfg->page_size, cudaHostAllocDefault));
+  s->table.bucket_mask = entries / kBucketEntries - 1;
+  s->table.page_size = cfg->page_size;
+  const int32_t top = (int32_t)slots;
+  OPEN_TRY(cudaMemsetAsync(s->table.entries, 0, entries * sizeof(Entry), s->stream));
+  OPEN_TRY(cudaMemsetAsync(s->table.slot_crc, 0, slots * sizeof(uint32_t), s->stream));
+  OPEN_TRY(cudaMemsetAsync(s->table.counters, 0, kNumCounters * sizeof(unsigned long long), s->stream));
+  OPEN_TRY(cudaMemsetAsync(s->d_done, 0, (uint64_t)mb * sizeof(uint32_t), s->stream));
+  OPEN_TRY(cudaMemsetAsync(s->d_error, 0, sizeof(int), s->stream));
+  OPEN_TRY(cudaMemcpyAsync(s->table.free_top, &top, sizeof(top), cudaMemcpyHostToDevice, s->stream));
+  init_free_slots_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, s->stream>>>(s->table.free_slots, slots);
+  count_launch(s);
+  OPEN_TRY(cudaGetLastError());
+  OPEN_TRY(cudaStreamSynchronize(s->stream));
+#undef OPEN_TRY
+  *out = s;
+  return APS_OK;
+}
+
+int aps_close(aps_store* s) {
+  if (!s) return APS_EINVAL;
+  {
+    std::lock_guard<std::mutex> lk(s->mu);
+    if (s->closed) return APS_ECLOSED;
+    s->closed = true;
+    DeviceGuard g(s->cfg.device);
+    cudaStreamSynchronize(s->stream);
+    free_store(s);
+  }
+  delete s;
+  return APS_OK;
+}
+
+uint64_t aps_cache_size(const aps_store* s) { return s ? s->cfg.cache_bytes : 0; }
+
+int aps_set_faults(aps_store* s, uint32_t fault_mask) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  s->faults = fault_mask;
+  return APS_OK;
+}
+
+// ---------------------------------------------------------------- device-resident batched forms
+
+int aps_get_batch_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !d_reqs || !d_res) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  get_resolve_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  return launch_copy(s, n, d_res, nullptr, st);
+}
+
+int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_result* d_res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !d_reqs || !d_res) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  put_resolve_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  return launch_copy(s, n, d_res, nullptr, st);
+}
+
+int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, aps_result* d_res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (!d_keys || !d_res) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  delete_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_keys, n, d_res);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  return APS_OK;
+}
+
+int aps_lookup_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, int32_t* d_len, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (!d_keys || !d_len) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  lookup_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_keys, n, d_len);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  return APS_OK;
+}
+
+int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_data, const uint32_t* d_len, uint32_t* d_crc,
+                         aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !d_data || !d_len || !d_crc) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  crc_jobs_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_data, d_len, n, s->cfg.page_size, s->d_jobs, d_crc);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  return launch_copy(s, n, nullptr, d_crc, st);
+}
+
+// ---------------------------------------------------------------- host-array batched forms
+
+int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !reqs || !res) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  aps_get_req* h_reqs = reinterpret_cast<aps_get_req*>(s->h_stage);
+  aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_get_req));
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
+  rc = aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+  rc = check_device_error(s, st);  // also waits for the stream
+  if (rc) return rc;
+  memcpy(res, h_res, (size_t)n * sizeof(aps_result));
+  return APS_OK;
+}
+
+int aps_put_batch(aps_store* s, uint32_t n, const aps_put_req* reqs, aps_result* res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !reqs || !res) return APS_EINVAL;
+  if (!distinct_keys(n, [&](uint32_t i) { return reqs[i].key; })) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  aps_put_req* h_reqs = reinterpret_cast<aps_put_req*>(s->h_stage);
+  aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_put_req));
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_put_req), cudaMemcpyHostToDevice, st));
+  rc = aps_put_batch_dev(s, n, (const aps_put_req*)s->d_reqs, s->d_res, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+  rc = check_device_error(s, st);
+  if (rc) return rc;
+  memcpy(res, h_res, (size_t)n * sizeof(aps_result));
+  return APS_OK;
+}
+
+int aps_delete_batch(aps_store* s, uint32_t n, const aps_key* keys, aps_result* res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !keys || !res) return APS_EINVAL;
+  if (!distinct_keys(n, [&](uint32_t i) { return keys[i]; })) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  aps_key* h_keys = reinterpret_cast<aps_key*>(s->h_stage);
+  aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  memcpy(h_keys, keys, (size_t)n * sizeof(aps_key));
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_keys, (size_t)n * sizeof(aps_key), cudaMemcpyHostToDevice, st));
+  rc = aps_delete_batch_dev(s, n, (const aps_key*)s->d_reqs, s->d_res, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(cudaStreamSynchronize(st));
+  memcpy(res, h_res, (size_t)n * sizeof(aps_result));
+  return APS_OK;
+}
+
+// ---------------------------------------------------------------- single-page PageStore calls
+
+static bool is_device_accessible(const void* p) {
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged;
+}
+
+int aps_put(aps_store* s, const aps_key* key, const void* src, uint32_t len) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!key || (!src && len)) return APS_EINVAL;
+  if (len > s->cfg.page_size) return APS_EINVAL;
+  if (s->faults & APS_FAULT_PUT) return APS_EFAULT;
+  DeviceGuard g(s->cfg.device);
+  aps_put_req rq{*key, len, 0, src};
+  std::unique_lock<std::mutex> lk(s->mu);
+  if (len && !is_device_accessible(src)) {  // pageable caller memory: stage through the pinned page
+    memcpy(s->h_bounce, src, len);
+    rq.src = s->h_bounce;
+  }
+  aps_put_req* h_req = reinterpret_cast<aps_put_req*>(s->h_stage);
+  aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  *h_req = rq;
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
+  rc = aps_put_batch_dev(s, 1, (const aps_put_req*)s->d_reqs, s->d_res, s->stream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, sizeof(aps_result), cudaMemcpyDeviceToHost, s->stream));
+  rc = check_device_error(s, s->stream);
+  if (rc) return rc;
+  return h_res->len < 0 ? -h_res->len : APS_OK;
+}
+
+int aps_get(aps_store* s, const aps_key* key, uint32_t page_off, uint32_t bytes_to_read, void* dst, uint32_t dst_cap,
+            uint32_t* out_len, uint32_t* out_crc) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (out_len) *out_len = 0;
+  if (out_crc) *out_crc = 0;
+  if (!key) return APS_EINVAL;
+  const uint32_t want = std::min(bytes_to_read, dst_cap);
+  if (!dst && want) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::unique_lock<std::mutex> lk(s->mu);
+  const bool direct = want == 0 || is_device_accessible(dst);
+  aps_get_req rq{*key, page_off, std::min(want, s->cfg.page_size), direct ? dst : (void*)s->h_bounce};
+  aps_get_req* h_req = reinterpret_cast<aps_get_req*>(s->h_stage);
+  aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  *h_req = rq;
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
+  rc = aps_get_batch_dev(s, 1, (const aps_get_req*)s->d_reqs, s->d_res, s->stream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, sizeof(aps_result), cudaMemcpyDeviceToHost, s->stream));
+  rc = check_device_error(s, s->stream);
+  if (rc) return rc;
+  if (h_res->len < 0) return -h_res->len;
+  if (!direct && h_res->len > 0) memcpy(dst, s->h_bounce, (size_t)h_res->len);
+  if (out_len) *out_len = (uint32_t)h_res->len;
+  if (out_crc) *out_crc = h_res->crc;
+  return APS_OK;
+}
+
+int aps_delete(aps_store* s, const aps_key* key) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!key) return APS_EINVAL;
+  if (s->faults & APS_FAULT_DELETE) return APS_EFAULT;
+  aps_result r{0, 0};
+  rc = aps_delete_batch(s, 1, key, &r, nullptr);
+  if (rc) return rc;
+  return r.len < 0 ? -r.len : APS_OK;
+}
+
+int aps_iterate(aps_store* s, aps_iter_cb cb, void* user) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!cb) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::vector<Entry> host;
+  {
+    std::lock_guard<std::mutex> lk(s->mu);
+    host.resize(s->n_entries);
+    CUDA_TRY(cudaMemcpyAsync(host.data(), s->table.entries, s->n_entries * sizeof(Entry), cudaMemcpyDeviceToHost, s->stream));
+    CUDA_TRY(cudaStreamSynchronize(s->stream));
+  }
+  for (const Entry& e : host) {
+    if (!(e.meta >> 63)) continue;
+    aps_key k{e.k0, e.k1, e.k2};
+    if (cb(user, &k, meta_len(e.meta))) break;
+  }
+  return APS_OK;
+}
+
+int aps_stats(aps_store* s, aps_stats_t* out) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!out) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  unsigned long long c[kNumCounters];
+  int32_t top = 0;
+  CUDA_TRY(cudaMemcpyAsync(c, s->table.counters, sizeof(c), cudaMemcpyDeviceToHost, s->stream));
+  CUDA_TRY(cudaMemcpyAsync(&top, s->table.free_top, sizeof(top), cudaMemcpyDeviceToHost, s->stream));
+  CUDA_TRY(cudaStreamSynchronize(s->stream));
+  out->pages = c[kCtrPages];
+  out->bytes = c[kCtrBytes];
+  out->slots_free = (uint64_t)std::max(top, 0);
+  out->table_capacity = s->n_entries;
+  out->tombstones = c[kCtrTombs];
+  out->lookups = c[kCtrLookups];
+  out->probe_buckets = c[kCtrProbes];
+  out->bytes_copied = c[kCtrBytesCopied];
+  out->crc_mismatches = c[kCtrCrcMismatch];
+  out->kernel_launches = s->launches.load();
+  return APS_OK;
+}
+
+int aps_profile_begin(aps_store* s, uint32_t max_launches) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  while (s->prof_events.size() < (size_t)max_launches * 2) {
+    cudaEvent_t e;
+    CUDA_TRY(cudaEventCreate(&e));
+    s->prof_events.push_back(e);
+  }
+  s->prof_used = 0;
+  s->prof_on = true;
+  return APS_OK;
+}
+
+int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_launches) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  s->prof_on = false;
+  double total = 0;
+  for (size_t i = 0; i + 1 < s->prof_used; i += 2) {
+    CUDA_TRY(cudaEventSynchronize(s->prof_events[i + 1]));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, s->prof_events[i], s->prof_events[i + 1]));
+    total += ms;
+  }
+  if (copy_ms_total) *copy_ms_total = total;
+  if (copy_launches) *copy_launches = (uint32_t)(s->prof_used / 2);
+  s->prof_used = 0;
+  return APS_OK;
+}
+
+int aps_debug_corrupt(aps_store* s, const aps_key* key, uint32_t byte_offset) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!key) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  int found = 0;
+  corrupt_kernel<<<1, 8, 0, s->stream>>>(s->table, *key, byte_offset, s->d_error + 0);
+  count_launch(s);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpyAsync(&found, s->d_error, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+  CUDA_TRY(cudaMemsetAsync(s->d_error, 0, sizeof(int), s->stream));
+  CUDA_TRY(cudaStreamSynchronize(s->stream));
+  return found ? APS_OK : APS_ENOTFOUND;
+}
+
+// ---------------------------------------------------------------- stateless entry points
+
+int aps_fill_pages_dev(int32_t device, void* d_dst, uint64_t stride, uint32_t page_len, uint32_t n_pages,
+                       const uint64_t* d_files, const uint64_t* d_indices, uint64_t seed, aps_stream stream) {
+  if (!d_dst || !d_files || !d_indices) return APS_EINVAL;
+  if (n_pages == 0 || page_len == 0) return APS_OK;
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  const uint64_t total = (uint64_t)((page_len + 7) / 8) * n_pages;
+  const unsigned grid = (unsigned)std::min<uint64_t>((total + 255) / 256, 148ull * 32);
+  fill_pages_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((uint8_t*)d_dst, stride, page_len, n_pages, d_files, d_indices, seed);
+  count_launch(nullptr);
+  CUDA_TRY(cudaGetLastError());
+  return APS_OK;
+}
+
+int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
+                      uint8_t (*d_out)[16], aps_stream stream) {
+  if (n_files == 0) return APS_OK;
+  if (!d_data || !d_len || !d_out) return APS_EINVAL;
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out);
+  count_launch(nullptr);
+  CUDA_TRY(cudaGetLastError());
+  return APS_OK;
+}
+
+int aps_md5_batch(int32_t device, uint32_t n_files, const void* const* data, const uint64_t* len, uint8_t (*out)[16]) {
+  if (n_files == 0) return APS_OK;
+  if (!data || !len || !out) return APS_EINVAL;
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  void** d_data = nullptr;
+  uint64_t* d_len = nullptr;
+  uint8_t(*d_out)[16] = nullptr;
+  int rc = APS_OK;
+  cudaError_t e;
+  if ((e = cudaMalloc(&d_data, n_files * sizeof(void*))) != cudaSuccess ||
+      (e = cudaMalloc(&d_len, n_files * sizeof(uint64_t))) != cudaSuccess ||
+      (e = cudaMalloc(&d_out, n_files * 16)) != cudaSuccess ||
+      (e = cudaMemcpy(d_data, data, n_files * sizeof(void*), cudaMemcpyHostToDevice)) != cudaSuccess ||
+      (e = cudaMemcpy(d_len, len, n_files * sizeof(uint64_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "aps_md5_batch staging: %s", cudaGetErrorString(e));
+    rc = APS_ECUDA;
+  }
+  if (rc == APS_OK) rc = aps_md5_batch_dev(device, n_files, d_data, d_len, d_out, nullptr);
+  if (rc == APS_OK && (e = cudaMemcpy(out, d_out, n_files * 16, cudaMemcpyDeviceToHost)) != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "aps_md5_batch readback: %s", cudaGetErrorString(e));
+    rc = APS_ECUDA;
+  }
+  cudaFree(d_data);
+  cudaFree(d_len);
+  cudaFree(d_out);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,219 @@
+// Device-side building blocks of libaps: hash-table probing (K1) and GF(2) CRC32C arithmetic (K3).
+// sm_100a only.  See DESIGN.md for the layout and the roofline of each kernel.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/aps.h"
+
+namespace aps {
+
+// ------------------------------------------------------------------------------------------------
+// K1: hash table.  Open addressing over 256-byte buckets of eight 32-byte entries; one bucket is
+// read by a tile of eight lanes (one 32-byte sector each), keys compared with a tile ballot.
+// Replaces DefaultMetaStore.mPageMap (CACHE/DefaultMetaStore.java:36,52) and the path lookup in
+// LocalPageStore.getFilePath (CACHE/store/LocalPageStore.java:139-143).
+// ------------------------------------------------------------------------------------------------
+struct __align__(32) Entry {
+  uint64_t k0, k1, k2;  // file_hi, file_lo, page_index
+  uint64_t meta;        // EMPTY / TOMB / LOCKED, or VALID | slot << 32 | len
+};
+constexpr uint32_t kBucketEntries = 8;
+constexpr uint64_t kMetaEmpty = 0, kMetaTomb = 1, kMetaLocked = 2;
+constexpr uint64_t kMetaValid = 1ull << 63;
+constexpr uint32_t kNoSlot = 0xFFFFFFFFu;
+
+__host__ __device__ __forceinline__ uint64_t meta_make(uint32_t slot, uint32_t len) {
+  return kMetaValid | ((uint64_t)slot << 32) | len;
+}
+__host__ __device__ __forceinline__ uint32_t meta_slot(uint64_t m) { return (uint32_t)(m >> 32) & 0x7FFFFFFFu; }
+__host__ __device__ __forceinline__ uint32_t meta_len(uint64_t m) { return (uint32_t)m; }
+
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z) {
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__host__ __device__ __forceinline__ uint64_t hash_key(const aps_key& k) {
+  return mix64(k.file_hi ^ mix64(k.file_lo ^ mix64(k.page_index + 0x9E3779B97F4A7C15ull)));
+}
+
+enum Counter { kCtrPages = 0, kCtrBytes, kCtrTombs, kCtrLookups, kCtrProbes, kCtrBytesCopied, kCtrCrcMismatch, kNumCounters };
+
+struct Table {
+  Entry* entries;
+  uint64_t bucket_mask;  // buckets - 1 (power of two)
+  uint32_t* free_slots;  // stack of free slab slots
+  int32_t* free_top;     // number of entries on the stack
+  uint32_t* slot_crc;    // CRC32C recorded at put, per slab slot
+  unsigned long long* counters;
+  uint8_t* slab;
+  uint32_t page_size;
+};
+
+__device__ __forceinline__ void load_entry(const Entry* e, uint64_t& k0, uint64_t& k1, uint64_t& k2, uint64_t& meta) {
+  // .cg: always observe L2, entries are written by other SMs in earlier (or the same) launches
+  const ulonglong2* p = reinterpret_cast<const ulonglong2*>(e);
+  ulonglong2 a = __ldcg(p), b = __ldcg(p + 1);
+  k0 = a.x; k1 = a.y; k2 = b.x; meta = b.y;
+}
+
+struct Probe {
+  uint64_t meta;       // meta of the matching entry, 0 if absent
+  uint64_t entry_idx;  // index of the matching entry
+  uint32_t empties;    // bitmask of EMPTY entries in the bucket where the probe ended
+  uint32_t nbuckets;   // buckets read
+};
+
+// Tile-cooperative lookup.  `sub` = lane within the tile (0..7), `tshift` = first lane of the tile in
+// the warp.  All eight lanes of the tile must call it with the same key.
+__device__ __forceinline__ Probe tile_lookup(const Table& t, const aps_key& key, uint32_t sub, uint32_t tshift) {
+  const uint32_t tmask = 0xFFu << tshift;
+  uint64_t b = hash_key(key) & t.bucket_mask;
+  Probe r{0, 0, 0, 0};
+  for (uint64_t p = 0; p <= t.bucket_mask; ++p) {
+    uint64_t k0, k1, k2, meta;
+    load_entry(t.entries + b * kBucketEntries + sub, k0, k1, k2, meta);
+    r.nbuckets++;
+    bool match = (meta >> 63) && k0 == key.file_hi && k1 == key.file_lo && k2 == key.page_index;
+    uint32_t bm = (__ballot_sync(tmask, match) >> tshift) & 0xFFu;
+    uint32_t be = (__ballot_sync(tmask, meta == kMetaEmpty) >> tshift) & 0xFFu;
+    if (bm) {
+      uint32_t src = __ffs(bm) - 1;
+      r.meta = __shfl_sync(tmask, meta, tshift + src);
+      r.entry_idx = b * kBucketEntries + src;
+      r.empties = be;
+      return r;
+    }
+    if (be) {
+      r.empties = be;
+      return r;
+    }
+    b = (b + 1) & t.bucket_mask;
+  }
+  return r;
+}
+
+// Tile-cooperative insert-or-replace.  Returns APS_OK and the slot; *replaced_len >= 0 when the id was
+// already present (its slot is kept, PageStore.put overwrites).  Keys in one launch must be distinct.
+__device__ __forceinline__ int tile_insert(const Table& t, const aps_key& key, uint32_t len, uint32_t sub, uint32_t tshift,
+                                           uint32_t* slot_out) {
+  const uint32_t tmask = 0xFFu << tshift;
+  const uint64_t home = hash_key(key) & t.bucket_mask;
+  for (int attempt = 0; attempt < 64; ++attempt) {
+    uint64_t b = home;
+    uint64_t cand = ~0ull, cand_seen = 0;
+    bool ended = false;
+    for (uint64_t p = 0; p <= t.bucket_mask && !ended; ++p) {
+      uint64_t k0, k1, k2, meta;
+      load_entry(t.entries + b * kBucketEntries + sub, k0, k1, k2, meta);
+      bool match = (meta >> 63) && k0 == key.file_hi && k1 == key.file_lo && k2 == key.page_index;
+      uint32_t bm = (__ballot_sync(tmask, match) >> tshift) & 0xFFu;
+      uint32_t be = (__ballot_sync(tmask, meta == kMetaEmpty) >> tshift) & 0xFFu;
+      uint32_t bt = (__ballot_sync(tmask, meta == kMetaTomb) >> tshift) & 0xFFu;
+      if (bm) {  // replace in place: same slot, new length
+        uint32_t src = __ffs(bm) - 1;
+        uint64_t old = __shfl_sync(tmask, meta, tshift + src);
+        uint32_t slot = meta_slot(old);
+        if (sub == src) {
+          t.entries[b * kBucketEntries + src].meta = meta_make(slot, len);
+          atomicAdd(&t.counters[kCtrBytes], (unsigned long long)len - (unsigned long long)meta_len(old));
+        }
+        *slot_out = slot;
+        return APS_OK;
+      }
+      if (cand == ~0ull && (bt | be)) {  // keep EMPTY entries for chain termination: prefer a tombstone
+        uint32_t pick = bt ? (__ffs(bt) - 1) : (__ffs(be) - 1);
+        cand = b * kBucketEntries + pick;
+        cand_seen = bt ? kMetaTomb : kMetaEmpty;
+      }
+      if (be) ended = true;
+      b = (b + 1) & t.bucket_mask;
+    }
+    if (cand == ~0ull) return APS_ENOSPC;  // every bucket full
+    int ok = 0;
+    if (sub == 0)
+      ok = atomicCAS((unsigned long long*)&t.entries[cand].meta, (unsigned long long)cand_seen,
+                     (unsigned long long)kMetaLocked) == cand_seen;
+    ok = __shfl_sync(tmask, ok, tshift);
+    if (!ok) continue;  // another key took the entry first: rescan
+    uint32_t slot = kNoSlot;
+    if (sub == 0) {
+      int idx = atomicSub(t.free_top, 1) - 1;
+      if (idx < 0) atomicAdd(t.free_top, 1);
+      else slot = t.free_slots[idx];
+    }
+    slot = __shfl_sync(tmask, slot, tshift);
+    if (slot == kNoSlot) {
+      if (sub == 0) t.entries[cand].meta = cand_seen;  // give the entry back
+      return APS_ENOSPC;
+    }
+    if (sub == 0) {
+      Entry* e = t.entries + cand;
+      e->k0 = key.file_hi; e->k1 = key.file_lo; e->k2 = key.page_index;
+      __threadfence();
+      e->meta = meta_make(slot, len);
+      atomicAdd(&t.counters[kCtrPages], 1ull);
+      atomicAdd(&t.counters[kCtrBytes], (unsigned long long)len);
+      if (cand_seen == kMetaTomb) atomicAdd(&t.counters[kCtrTombs], ~0ull);
+    }
+    *slot_out = slot;
+    return APS_OK;
+  }
+  return APS_ENOSPC;
+}
+
+// Tile-cooperative erase.  An entry in a bucket that still has an EMPTY entry goes straight back to
+// EMPTY (no probe chain runs through such a bucket); otherwise it becomes a tombstone.
+__device__ __forceinline__ int tile_erase(const Table& t, const aps_key& key, uint32_t sub, uint32_t tshift) {
+  Probe pr = tile_lookup(t, key, sub, tshift);
+  if (!pr.meta) return APS_ENOTFOUND;
+  if (sub == 0) {
+    bool to_empty = pr.empties != 0;
+    t.entries[pr.entry_idx].meta = to_empty ? kMetaEmpty : kMetaTomb;
+    int idx = atomicAdd(t.free_top, 1);
+    t.free_slots[idx] = meta_slot(pr.meta);
+    atomicAdd(&t.counters[kCtrPages], ~0ull);
+    atomicAdd(&t.counters[kCtrBytes], 0ull - (unsigned long long)meta_len(pr.meta));
+    if (!to_empty) atomicAdd(&t.counters[kCtrTombs], 1ull);
+  }
+  return APS_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: CRC32C arithmetic.  Reflected CRC-32C register algebra: bit 31 is x^0, bit 0 is x^31.
+//   update(r, byte) = (r >> 8) ^ T[(r ^ byte) & 255];  Z_n = "advance the register by n zero bytes"
+//   is multiplication by x^(8n) mod P, and crc(A||B) = Z_|B|(crc(A)) ^ crc(B) for zero-init CRCs.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kCrcPoly = 0x82F63B78u;
+
+__host__ __device__ __forceinline__ uint32_t gf_mul(uint32_t a, uint32_t b) {  // a * b mod P
+  uint32_t r = 0;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    r ^= a & (0u - ((b >> (31 - i)) & 1u));
+    a = (a >> 1) ^ (kCrcPoly & (0u - (a & 1u)));
+  }
+  return r;
+}
+
+// x^(8 * 2^k) mod P for k = 0..31 (filled by the host at load time)
+__constant__ uint32_t c_xpow8[32];
+// per-lane constant of the 512-byte row reduction: x^(8 * (500 - 16 * lane))
+__constant__ uint32_t c_lane_shift[32];
+
+__device__ __forceinline__ uint32_t xpow8(uint32_t nbytes) {  // x^(8 * nbytes) mod P
+  uint32_t r = 0x80000000u;                                    // x^0
+  for (int k = 0; nbytes; ++k, nbytes >>= 1)
+    if (nbytes & 1u) r = gf_mul(r, c_xpow8[k]);
+  return r;
+}
+
+__device__ __forceinline__ uint32_t crc_byte_bitwise(uint32_t r, uint32_t byte) {
+  r ^= byte;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) r = (r >> 1) ^ (kCrcPoly & (0u - (r & 1u)));
+  return r;
+}
+
+}  // namespace aps

@@ -1,0 +1,519 @@
+// Kernels of libaps (sm_100a).  K1 table kernels, K2/K3 batched copy with fused CRC32C,
+// K4 many-file MD5, and the synthetic-page generator.  Host launch code is in aps_api.cu.
+#pragma once
+#include "aps_device.cuh"
+
+namespace aps {
+
+// ------------------------------------------------------------------------------------------------
+// Copy jobs: the resolve kernels turn requests into jobs, the copy kernel executes them.
+// ------------------------------------------------------------------------------------------------
+struct Job {
+  const uint8_t* src;
+  uint8_t* dst;  // nullptr: checksum only
+  uint32_t n;    // bytes to move; 0 = nothing to do
+  uint32_t slot;
+  uint32_t flags;
+  uint32_t pad;
+};
+constexpr uint32_t kJobVerify = 1u;  // whole-page get: compare with the CRC recorded at put
+constexpr uint32_t kJobRecord = 2u;  // put: record the CRC for the slot
+constexpr uint32_t kJobOutCrc = 4u;  // write the CRC to crc_out[job] (stand-alone checksum pass)
+
+constexpr uint32_t kChunkBytes = 16384;  // one warp-task: 32 rows of 512 bytes
+constexpr uint32_t kRowBytes = 512;      // one warp-wide 128-bit access
+constexpr uint32_t kCopyThreads = 1024;
+
+// Shared-memory map of the CRC copy kernel, as absolute shared-window addresses:
+//   0x0F000 .. 0x0FFFF  Z_4 tables  G[j][b], j = 0..3 (plain, 4 KiB)         -- row-state reduction
+//   0x10000 .. 0x2FFFF  Z_512 tables F[j][b], each entry replicated for the 32 lanes so that lane l
+//                       only ever touches bank l (conflict-free): address = 0x10000 + (j>>1)*0x10000
+//                       + b*256 + (j&1)*128 + lane*4.  The 64 KiB alignment lets one PRMT build the
+//                       address from a data byte (see fold_word).
+constexpr uint32_t kSmemG = 0x0F000u;
+constexpr uint32_t kSmemF = 0x10000u;
+constexpr uint32_t kSmemEnd = 0x30000u;
+constexpr uint32_t kCopyDynSmem = kSmemEnd;  // requested size; the window starts at <= 1 KiB
+
+struct CrcTables {      // device-global copy, built once on the host
+  uint32_t fold[4][256];  // F_j[b] = (b << 8j) * x^(8*512)
+  uint32_t z4[4][256];    // G_j[b] = (b << 8j) * x^32
+};
+
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// S * x^(8*512): four conflict-free table reads.  rb = 0x00010000 | lane*4.  PRMT picks byte j of S
+// into bits 8..15, lane*4 into bits 0..7 and 0x0001 into the upper half: one instruction per address.
+__device__ __forceinline__ uint32_t fold_word(uint32_t s, uint32_t rb) {
+  uint32_t a0, a1, a2, a3, v0, v1, v2, v3;
+  asm("prmt.b32 %0, %1, %2, 0x7604;" : "=r"(a0) : "r"(s), "r"(rb));
+  asm("prmt.b32 %0, %1, %2, 0x7614;" : "=r"(a1) : "r"(s), "r"(rb));
+  asm("prmt.b32 %0, %1, %2, 0x7624;" : "=r"(a2) : "r"(s), "r"(rb));
+  asm("prmt.b32 %0, %1, %2, 0x7634;" : "=r"(a3) : "r"(s), "r"(rb));
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v0) : "r"(a0));
+  asm volatile("ld.shared.u32 %0, [%1+128];" : "=r"(v1) : "r"(a1));
+  asm volatile("ld.shared.u32 %0, [%1+65536];" : "=r"(v2) : "r"(a2));
+  asm volatile("ld.shared.u32 %0, [%1+65664];" : "=r"(v3) : "r"(a3));
+  return v0 ^ v1 ^ v2 ^ v3;
+}
+
+// r * x^32 (advance the register over four zero bytes) from the plain tables.
+__device__ __forceinline__ uint32_t z4_word(uint32_t r) {
+  return lds_u32(kSmemG + (r & 0xFFu) * 4u) ^ lds_u32(kSmemG + 1024u + ((r >> 8) & 0xFFu) * 4u) ^
+         lds_u32(kSmemG + 2048u + ((r >> 16) & 0xFFu) * 4u) ^ lds_u32(kSmemG + 3072u + (r >> 24) * 4u);
+}
+
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void stg_stream(uint4* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ uint32_t warp_xor(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o; o >>= 1) v ^= __shfl_xor_sync(0xFFFFFFFFu, v, o);
+  return v;
+}
+
+// Aligned fast path: `rows` 512-byte rows, 16 bytes per lane per row, four rows in flight.
+// Returns the zero-init CRC of the rows (same value in every lane) when kCrc.
+template <bool kCrc>
+__device__ __forceinline__ uint32_t warp_rows(const uint8_t* src, uint8_t* dst, uint32_t rows, uint32_t lane) {
+  const uint4* s = reinterpret_cast<const uint4*>(src) + lane;
+  uint4* d = reinterpret_cast<uint4*>(dst) + lane;
+  const bool store = dst != nullptr;
+  const uint32_t rb = 0x00010000u | (lane << 2);
+  uint32_t S0 = 0, S1 = 0, S2 = 0, S3 = 0;
+  uint32_t r = 0;
+  for (; r + 4 <= rows; r += 4) {
+    uint4 w0 = ldg_stream(s + (r + 0) * 32), w1 = ldg_stream(s + (r + 1) * 32);
+    uint4 w2 = ldg_stream(s + (r + 2) * 32), w3 = ldg_stream(s + (r + 3) * 32);
+    if (store) {
+      stg_stream(d + (r + 0) * 32, w0);
+      stg_stream(d + (r + 1) * 32, w1);
+      stg_stream(d + (r + 2) * 32, w2);
+      stg_stream(d + (r + 3) * 32, w3);
+    }
+    if (kCrc) {
+      S0 = fold_word(S0, rb) ^ w0.x; S1 = fold_word(S1, rb) ^ w0.y; S2 = fold_word(S2, rb) ^ w0.z; S3 = fold_word(S3, rb) ^ w0.w;
+      S0 = fold_word(S0, rb) ^ w1.x; S1 = fold_word(S1, rb) ^ w1.y; S2 = fold_word(S2, rb) ^ w1.z; S3 = fold_word(S3, rb) ^ w1.w;
+      S0 = fold_word(S0, rb) ^ w2.x; S1 = fold_word(S1, rb) ^ w2.y; S2 = fold_word(S2, rb) ^ w2.z; S3 = fold_word(S3, rb) ^ w2.w;
+      S0 = fold_word(S0, rb) ^ w3.x; S1 = fold_word(S1, rb) ^ w3.y; S2 = fold_word(S2, rb) ^ w3.z; S3 = fold_word(S3, rb) ^ w3.w;
+    }
+  }
+  for (; r < rows; ++r) {
+    uint4 w = ldg_stream(s + r * 32);
+    if (store) stg_stream(d + r * 32, w);
+    if (kCrc) {
+      S0 = fold_word(S0, rb) ^ w.x; S1 = fold_word(S1, rb) ^ w.y; S2 = fold_word(S2, rb) ^ w.z; S3 = fold_word(S3, rb) ^ w.w;
+    }
+  }
+  if (!kCrc) return 0;
+  // lane words -> one register: t = Z4(Z4(Z4(S0)^S1)^S2)^S3, then shift to the end of the row
+  uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
+  return warp_xor(gf_mul(t, c_lane_shift[lane]));
+}
+
+// Generic path (tails, unaligned requests): lane l takes the l-th contiguous slice, one byte at a
+// time.  Returns the zero-init CRC of the n bytes (same value in every lane) when kCrc.
+template <bool kCrc>
+__device__ __forceinline__ uint32_t warp_bytes(const uint8_t* src, uint8_t* dst, uint32_t n, uint32_t lane) {
+  uint32_t per = (n + 31u) >> 5;
+  uint32_t lo = min(n, lane * per), hi = min(n, lo + per);
+  uint32_t r = 0;
+  for (uint32_t i = lo; i < hi; ++i) {
+    uint32_t b = src[i];
+    if (dst) dst[i] = (uint8_t)b;
+    if (kCrc) r = crc_byte_bitwise(r, b);
+  }
+  if (!kCrc) return 0;
+  return warp_xor(gf_mul(r, xpow8(n - hi)));
+}
+
+struct CopyArgs {
+  const Job* jobs;
+  uint32_t n_jobs;
+  uint32_t chunks_per_job;  // ceil(max job bytes / kChunkBytes)
+  aps_result* res;          // may be null
+  uint32_t* crc_out;        // for kJobOutCrc
+  uint32_t* partials;       // scratch: n_jobs * chunks_per_job zero-init chunk CRCs
+  uint32_t* done;           // scratch: per-job finished-chunk counters; zero on entry, reset by the finisher
+  const CrcTables* tables;
+  uint32_t* slot_crc;
+  unsigned long long* counters;
+  int* error_flag;  // set if the shared-memory window is not where the kernel needs it
+};
+
+// K2 + K3.  Persistent: one CTA per SM, every warp takes chunk-tasks round robin.  A task is one
+// 16 KiB chunk of one job: rows of 512 bytes are loaded and stored 128 bits per lane, and (kCrc)
+// folded into four per-lane CRC words; the warp reduces them to the chunk's zero-init CRC; the warp
+// that finishes the last chunk of a job combines the chunk CRCs (GF(2) shift by the bytes that
+// follow each chunk), applies init/xorout, and verifies or records the page CRC.
+template <bool kCrc>
+__global__ void __launch_bounds__(kCopyThreads, 1) copy_kernel(CopyArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  if (kCrc) {
+    uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    uint32_t dyn;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
+    if (base > kSmemG || base + dyn < kSmemEnd) {
+      if (threadIdx.x == 0) *a.error_flag = 1;
+      return;
+    }
+    for (uint32_t idx = warp; idx < 1024; idx += nwarps) {
+      uint32_t j = idx >> 8, b = idx & 255u;
+      sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, a.tables->fold[j][b]);
+    }
+    for (uint32_t idx = threadIdx.x; idx < 1024; idx += blockDim.x) sts_u32(kSmemG + idx * 4u, (&a.tables->z4[0][0])[idx]);
+    __syncthreads();
+  }
+  const uint32_t total_warps = gridDim.x * nwarps;
+  const uint32_t n_items = a.n_jobs * a.chunks_per_job;
+  for (uint32_t item = blockIdx.x * nwarps + warp; item < n_items; item += total_warps) {
+    const uint32_t job = item / a.chunks_per_job, c = item - job * a.chunks_per_job;
+    const Job j = a.jobs[job];
+    const uint32_t off = c * kChunkBytes;
+    if (off >= j.n) continue;
+    const uint32_t len = min(kChunkBytes, j.n - off);
+    const uint8_t* src = j.src + off;
+    uint8_t* dst = j.dst ? j.dst + off : nullptr;
+    const bool aligned = (((uintptr_t)src | (uintptr_t)dst) & 15u) == 0;
+    const uint32_t rows = aligned ? len / kRowBytes : 0;
+    const uint32_t tail = len - rows * kRowBytes;
+    uint32_t crc = 0;
+    if (rows) crc = warp_rows<kCrc>(src, dst, rows, lane);
+    if (tail) {
+      uint32_t ct = warp_bytes<kCrc>(src + rows * kRowBytes, dst ? dst + rows * kRowBytes : nullptr, tail, lane);
+      if (kCrc) crc = rows ? (gf_mul(crc, xpow8(tail)) ^ ct) : ct;
+    }
+    if (!kCrc) continue;
+    const uint32_t nchunks = (j.n + kChunkBytes - 1) / kChunkBytes;
+    uint32_t prev = 0;
+    if (lane == 0) {
+      a.partials[item] = crc;
+      __threadfence();
+      prev = atomicAdd(&a.done[job], 1u);
+    }
+    prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
+    if (prev != nchunks - 1) continue;
+    // last chunk of this job: combine
+    __threadfence();
+    uint32_t acc = 0;
+    for (uint32_t base = 0; base < nchunks; base += 32) {
+      uint32_t jj = base + lane;
+      if (jj < nchunks) {
+        uint32_t p = __ldcg(&a.partials[job * a.chunks_per_job + jj]);
+        uint32_t end = min(j.n, (jj + 1) * kChunkBytes);
+        acc ^= gf_mul(p, xpow8(j.n - end));
+      }
+    }
+    acc = warp_xor(acc);
+    if (lane == 0) {
+      uint32_t full = acc ^ gf_mul(0xFFFFFFFFu, xpow8(j.n)) ^ 0xFFFFFFFFu;
+      if (j.flags & kJobRecord) a.slot_crc[j.slot] = full;
+      if (a.res) a.res[job].crc = full;
+      if (j.flags & kJobOutCrc) a.crc_out[job] = full;
+      if ((j.flags & kJobVerify) && a.slot_crc[j.slot] != full) {
+        if (a.res) a.res[job].len = -APS_ECORRUPT;
+        atomicAdd(&a.counters[kCtrCrcMismatch], 1ull);
+      }
+      a.done[job] = 0;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1 kernels: eight lanes per request.
+// ------------------------------------------------------------------------------------------------
+__global__ void get_resolve_kernel(Table t, const aps_get_req* reqs, uint32_t n, Job* jobs, aps_result* res, int crc_on) {
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
+  if (i >= n) return;
+  const aps_get_req rq = reqs[i];
+  Probe pr = tile_lookup(t, rq.key, sub, tshift);
+  if (sub) return;
+  atomicAdd(&t.counters[kCtrLookups], 1ull);
+  atomicAdd(&t.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
+  Job jb{nullptr, nullptr, 0, 0, 0, 0};
+  aps_result rs{0, 0};
+  if (!pr.meta) {
+    rs.len = -APS_ENOTFOUND;
+  } else {
+    const uint32_t len = meta_len(pr.meta), slot = meta_slot(pr.meta);
+    if (rq.page_off > len) {  // LocalPageStore.java:99-100
+      rs.len = -APS_EINVAL;
+    } else {
+      const uint32_t nb = min(len - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
+      jb.src = t.slab + (uint64_t)slot * t.page_size + rq.page_off;
+      jb.dst = (uint8_t*)rq.dst;
+      jb.n = nb;
+      jb.slot = slot;
+      jb.flags = (crc_on && rq.page_off == 0 && nb == len && len > 0) ? kJobVerify : 0u;
+      rs.len = (int32_t)nb;
+      atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)nb);
+    }
+  }
+  jobs[i] = jb;
+  res[i] = rs;
+}
+
+__global__ void put_resolve_kernel(Table t, const aps_put_req* reqs, uint32_t n, Job* jobs, aps_result* res, int crc_on) {
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
+  if (i >= n) return;
+  const aps_put_req rq = reqs[i];
+  Job jb{nullptr, nullptr, 0, 0, 0, 0};
+  aps_result rs{0, 0};
+  if (rq.len > t.page_size) {
+    rs.len = -APS_EINVAL;
+  } else {
+    uint32_t slot = kNoSlot;
+    int st = tile_insert(t, rq.key, rq.len, sub, tshift, &slot);
+    if (st != APS_OK) {
+      rs.len = -st;
+    } else {
+      jb.src = (const uint8_t*)rq.src;
+      jb.dst = t.slab + (uint64_t)slot * t.page_size;
+      jb.n = rq.len;
+      jb.slot = slot;
+      jb.flags = crc_on ? kJobRecord : 0u;
+      rs.len = (int32_t)rq.len;
+      if (sub == 0) {
+        if (rq.len == 0) t.slot_crc[slot] = 0;  // CRC32C of the empty string
+        atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)rq.len);
+      }
+    }
+  }
+  if (sub) return;
+  jobs[i] = jb;
+  res[i] = rs;
+}
+
+__global__ void delete_kernel(Table t, const aps_key* keys, uint32_t n, aps_result* res) {
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
+  if (i >= n) return;
+  int st = tile_erase(t, keys[i], sub, tshift);
+  if (sub == 0) res[i] = aps_result{-st, 0};
+}
+
+__global__ void lookup_kernel(Table t, const aps_key* keys, uint32_t n, int32_t* len_out) {
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
+  if (i >= n) return;
+  Probe pr = tile_lookup(t, keys[i], sub, tshift);
+  if (sub) return;
+  atomicAdd(&t.counters[kCtrLookups], 1ull);
+  atomicAdd(&t.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
+  len_out[i] = pr.meta ? (int32_t)meta_len(pr.meta) : -1;
+}
+
+// jobs for the stand-alone checksum pass
+__global__ void crc_jobs_kernel(const void* const* data, const uint32_t* len, uint32_t n, uint32_t max_len, Job* jobs,
+                                uint32_t* crc_out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint32_t l = min(len[i], max_len);
+  jobs[i] = Job{(const uint8_t*)data[i], nullptr, l, 0, kJobOutCrc, 0};
+  if (l == 0) crc_out[i] = 0;
+}
+
+__global__ void init_free_slots_kernel(uint32_t* free_slots, uint64_t n) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) free_slots[i] = (uint32_t)(n - 1 - i);  // slot 0 is handed out first
+}
+
+// ------------------------------------------------------------------------------------------------
+// Synthetic pages: word k of page (file, index) = splitmix64 output k for the seed
+// seed ^ (file << 32) ^ index.  One 8-byte word per thread, grid-stride.
+// ------------------------------------------------------------------------------------------------
+__global__ void fill_pages_kernel(uint8_t* dst, uint64_t stride, uint32_t page_len, uint32_t n_pages, const uint64_t* files,
+                                  const uint64_t* indices, uint64_t seed) {
+  const uint64_t words_per_page = (page_len + 7u) / 8u;
+  const uint64_t total = words_per_page * n_pages;
+  for (uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t p = g / words_per_page, k = g - p * words_per_page;
+    const uint64_t s = seed ^ (files[p] << 32) ^ indices[p];
+    const uint64_t w = mix64(s + (k + 1) * 0x9E3779B97F4A7C15ull);
+    uint8_t* out = dst + p * stride + k * 8;
+    if (k * 8 + 8 <= page_len && (((uintptr_t)out) & 7u) == 0) {
+      *reinterpret_cast<uint64_t*>(out) = w;
+    } else {
+      for (uint32_t b = 0; b < 8 && k * 8 + b < page_len; ++b) out[b] = (uint8_t)(w >> (8 * b));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: MD5 of many files at once (RFC 1321).  One file per lane; the chain inside a file is serial,
+// so parallelism is across files only (ChecksumCommand.java:83-90 replaced file by file).  A warp
+// stages 512 bytes of each of its 32 files per step with 16-byte cp.async (coalesced per file) into
+// a padded shared tile (row stride 132 words, read back 128 bits at a time without bank conflicts).
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kMd5Seg = 512;
+constexpr uint32_t kMd5RowWords = kMd5Seg / 4 + 4;  // 528-byte rows: 16-byte aligned, and a quarter-warp of
+                                                    // 128-bit reads (lane f at f*528) covers all 32 banks
+
+__device__ __forceinline__ uint32_t rotl32(uint32_t x, int s) { return __funnelshift_l(x, x, s); }
+
+#define APS_MD5_STEP(f, a, b, c, d, m, k, s) \
+  a = b + rotl32(a + f(b, c, d) + (m) + (k), s)
+#define APS_F1(b, c, d) ((d) ^ ((b) & ((c) ^ (d))))
+#define APS_F2(b, c, d) ((c) ^ ((d) & ((b) ^ (c))))
+#define APS_F3(b, c, d) ((b) ^ (c) ^ (d))
+#define APS_F4(b, c, d) ((c) ^ ((b) | ~(d)))
+
+__device__ __forceinline__ void md5_block(uint32_t h[4], const uint32_t m[16]) {
+  uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+  APS_MD5_STEP(APS_F1, a, b, c, d, m[0], 0xd76aa478u, 7);  APS_MD5_STEP(APS_F1, d, a, b, c, m[1], 0xe8c7b756u, 12);
+  APS_MD5_STEP(APS_F1, c, d, a, b, m[2], 0x242070dbu, 17); APS_MD5_STEP(APS_F1, b, c, d, a, m[3], 0xc1bdceeeu, 22);
+  APS_MD5_STEP(APS_F1, a, b, c, d, m[4], 0xf57c0fafu, 7);  APS_MD5_STEP(APS_F1, d, a, b, c, m[5], 0x4787c62au, 12);
+  APS_MD5_STEP(APS_F1, c, d, a, b, m[6], 0xa8304613u, 17); APS_MD5_STEP(APS_F1, b, c, d, a, m[7], 0xfd469501u, 22);
+  APS_MD5_STEP(APS_F1, a, b, c, d, m[8], 0x698098d8u, 7);  APS_MD5_STEP(APS_F1, d, a, b, c, m[9], 0x8b44f7afu, 12);
+  APS_MD5_STEP(APS_F1, c, d, a, b, m[10], 0xffff5bb1u, 17); APS_MD5_STEP(APS_F1, b, c, d, a, m[11], 0x895cd7beu, 22);
+  APS_MD5_STEP(APS_F1, a, b, c, d, m[12], 0x6b901122u, 7);  APS_MD5_STEP(APS_F1, d, a, b, c, m[13], 0xfd987193u, 12);
+  APS_MD5_STEP(APS_F1, c, d, a, b, m[14], 0xa679438eu, 17); APS_MD5_STEP(APS_F1, b, c, d, a, m[15], 0x49b40821u, 22);
+  APS_MD5_STEP(APS_F2, a, b, c, d, m[1], 0xf61e2562u, 5);  APS_MD5_STEP(APS_F2, d, a, b, c, m[6], 0xc040b340u, 9);
+  APS_MD5_STEP(APS_F2, c, d, a, b, m[11], 0x265e5a51u, 14); APS_MD5_STEP(APS_F2, b, c, d, a, m[0], 0xe9b6c7aau, 20);
+  APS_MD5_STEP(APS_F2, a, b, c, d, m[5], 0xd62f105du, 5);  APS_MD5_STEP(APS_F2, d, a, b, c, m[10], 0x02441453u, 9);
+  APS_MD5_STEP(APS_F2, c, d, a, b, m[15], 0xd8a1e681u, 14); APS_MD5_STEP(APS_F2, b, c, d, a, m[4], 0xe7d3fbc8u, 20);
+  APS_MD5_STEP(APS_F2, a, b, c, d, m[9], 0x21e1cde6u, 5);  APS_MD5_STEP(APS_F2, d, a, b, c, m[14], 0xc33707d6u, 9);
+  APS_MD5_STEP(APS_F2, c, d, a, b, m[3], 0xf4d50d87u, 14); APS_MD5_STEP(APS_F2, b, c, d, a, m[8], 0x455a14edu, 20);
+  APS_MD5_STEP(APS_F2, a, b, c, d, m[13], 0xa9e3e905u, 5); APS_MD5_STEP(APS_F2, d, a, b, c, m[2], 0xfcefa3f8u, 9);
+  APS_MD5_STEP(APS_F2, c, d, a, b, m[7], 0x676f02d9u, 14); APS_MD5_STEP(APS_F2, b, c, d, a, m[12], 0x8d2a4c8au, 20);
+  APS_MD5_STEP(APS_F3, a, b, c, d, m[5], 0xfffa3942u, 4);  APS_MD5_STEP(APS_F3, d, a, b, c, m[8], 0x8771f681u, 11);
+  APS_MD5_STEP(APS_F3, c, d, a, b, m[11], 0x6d9d6122u, 16); APS_MD5_STEP(APS_F3, b, c, d, a, m[14], 0xfde5380cu, 23);
+  APS_MD5_STEP(APS_F3, a, b, c, d, m[1], 0xa4beea44u, 4);  APS_MD5_STEP(APS_F3, d, a, b, c, m[4], 0x4bdecfa9u, 11);
+  APS_MD5_STEP(APS_F3, c, d, a, b, m[7], 0xf6bb4b60u, 16); APS_MD5_STEP(APS_F3, b, c, d, a, m[10], 0xbebfbc70u, 23);
+  APS_MD5_STEP(APS_F3, a, b, c, d, m[13], 0x289b7ec6u, 4); APS_MD5_STEP(APS_F3, d, a, b, c, m[0], 0xeaa127fau, 11);
+  APS_MD5_STEP(APS_F3, c, d, a, b, m[3], 0xd4ef3085u, 16); APS_MD5_STEP(APS_F3, b, c, d, a, m[6], 0x04881d05u, 23);
+  APS_MD5_STEP(APS_F3, a, b, c, d, m[9], 0xd9d4d039u, 4);  APS_MD5_STEP(APS_F3, d, a, b, c, m[12], 0xe6db99e5u, 11);
+  APS_MD5_STEP(APS_F3, c, d, a, b, m[15], 0x1fa27cf8u, 16); APS_MD5_STEP(APS_F3, b, c, d, a, m[2], 0xc4ac5665u, 23);
+  APS_MD5_STEP(APS_F4, a, b, c, d, m[0], 0xf4292244u, 6);  APS_MD5_STEP(APS_F4, d, a, b, c, m[7], 0x432aff97u, 10);
+  APS_MD5_STEP(APS_F4, c, d, a, b, m[14], 0xab9423a7u, 15); APS_MD5_STEP(APS_F4, b, c, d, a, m[5], 0xfc93a039u, 21);
+  APS_MD5_STEP(APS_F4, a, b, c, d, m[12], 0x655b59c3u, 6); APS_MD5_STEP(APS_F4, d, a, b, c, m[3], 0x8f0ccc92u, 10);
+  APS_MD5_STEP(APS_F4, c, d, a, b, m[10], 0xffeff47du, 15); APS_MD5_STEP(APS_F4, b, c, d, a, m[1], 0x85845dd1u, 21);
+  APS_MD5_STEP(APS_F4, a, b, c, d, m[8], 0x6fa87e4fu, 6);  APS_MD5_STEP(APS_F4, d, a, b, c, m[15], 0xfe2ce6e0u, 10);
+  APS_MD5_STEP(APS_F4, c, d, a, b, m[6], 0xa3014314u, 15); APS_MD5_STEP(APS_F4, b, c, d, a, m[13], 0x4e0811a1u, 21);
+  APS_MD5_STEP(APS_F4, a, b, c, d, m[4], 0xf7537e82u, 6);  APS_MD5_STEP(APS_F4, d, a, b, c, m[11], 0xbd3af235u, 10);
+  APS_MD5_STEP(APS_F4, c, d, a, b, m[2], 0x2ad7d2bbu, 15); APS_MD5_STEP(APS_F4, b, c, d, a, m[9], 0xeb86d391u, 21);
+  h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void* gptr) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(gptr) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// One warp per block; lane f digests file blockIdx.x*32 + f.
+__global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* const* data, const uint64_t* len,
+                                                 uint8_t (*out)[16]) {
+  __shared__ __align__(16) uint32_t tile[2][32 * kMd5RowWords];
+  const uint32_t lane = threadIdx.x;
+  const uint32_t file = blockIdx.x * 32 + lane;
+  const bool have = file < n_files;
+  const uint8_t* my = have ? (const uint8_t*)data[file] : nullptr;
+  const uint64_t my_len = have ? len[file] : 0;
+  // staging needs a 16-byte aligned base; otherwise the lane reads its bytes straight from global
+  const bool my_aligned = (((uintptr_t)my) & 15u) == 0;
+  uint64_t max_len = my_len;
+#pragma unroll
+  for (int o = 16; o; o >>= 1) max_len = max(max_len, __shfl_xor_sync(0xFFFFFFFFu, max_len, o));
+  const uint64_t nseg = max_len / kMd5Seg;  // segments that are full for at least one file
+
+  uint32_t h[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+
+  auto stage = [&](uint64_t seg, int buf) {
+    // for each file of the warp: 32 lanes fetch its 512-byte segment, 16 bytes each
+    for (uint32_t f = 0; f < 32; ++f) {
+      const uint8_t* base = (const uint8_t*)__shfl_sync(0xFFFFFFFFu, (unsigned long long)my, f);
+      const uint64_t flen = __shfl_sync(0xFFFFFFFFu, (unsigned long long)my_len, f);
+      const bool fal = __shfl_sync(0xFFFFFFFFu, (int)my_aligned, f);
+      if (fal && (seg + 1) * kMd5Seg <= flen) {
+        const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&tile[buf][f * kMd5RowWords]);
+        cp_async16(sbase + lane * 16, base + seg * kMd5Seg + lane * 16);
+      }
+    }
+    cp_async_commit();
+  };
+
+  if (nseg) stage(0, 0);
+  for (uint64_t seg = 0; seg < nseg; ++seg) {
+    const int buf = (int)(seg & 1);
+    if (seg + 1 < nseg) { stage(seg + 1, buf ^ 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
+    __syncwarp();
+    if (have && (seg + 1) * kMd5Seg <= my_len) {
+      if (my_aligned) {
+        const uint4* row = reinterpret_cast<const uint4*>(&tile[buf][lane * kMd5RowWords]);
+#pragma unroll 1
+        for (int blk = 0; blk < 8; ++blk) {
+          uint32_t m[16];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 v = row[blk * 4 + j];
+            m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+          }
+          md5_block(h, m);
+        }
+      } else {
+        const uint8_t* g = my + seg * kMd5Seg;
+        for (int blk = 0; blk < 8; ++blk) {
+          uint32_t m[16];
+          for (int j = 0; j < 16; ++j) {
+            const uint8_t* q = g + blk * 64 + j * 4;
+            m[j] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+          }
+          md5_block(h, m);
+        }
+      }
+    }
+    __syncwarp();
+  }
+  if (!have) return;
+  // remainder (< 512 bytes) + padding, straight from global memory
+  uint64_t pos = (my_len / kMd5Seg) * kMd5Seg;
+  while (pos + 64 <= my_len) {
+    uint32_t m[16];
+    for (int j = 0; j < 16; ++j) {
+      const uint8_t* q = my + pos + j * 4;
+      m[j] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+    }
+    md5_block(h, m);
+    pos += 64;
+  }
+  uint8_t last[128];
+  uint32_t rem = (uint32_t)(my_len - pos);
+  for (uint32_t i = 0; i < rem; ++i) last[i] = my[pos + i];
+  last[rem] = 0x80;
+  const uint32_t total = rem < 56 ? 64 : 128;
+  for (uint32_t i = rem + 1; i < total - 8; ++i) last[i] = 0;
+  const uint64_t bits = my_len * 8;
+  for (int i = 0; i < 8; ++i) last[total - 8 + i] = (uint8_t)(bits >> (8 * i));
+  for (uint32_t o = 0; o < total; o += 64) {
+    uint32_t m[16];
+    for (int j = 0; j < 16; ++j)
+      m[j] = (uint32_t)last[o + j * 4] | ((uint32_t)last[o + j * 4 + 1] << 8) | ((uint32_t)last[o + j * 4 + 2] << 16) |
+             ((uint32_t)last[o + j * 4 + 3] << 24);
+    md5_block(h, m);
+  }
+  for (int i = 0; i < 4; ++i)
+    for (int k = 0; k < 4; ++k) out[file][4 * i + k] = (uint8_t)(h[i] >> (8 * k));
+}
+
+}  // namespace aps

@@ -1,0 +1,408 @@
+#!/usr/bin/env python
+"""Benchmark of the page-cache hot path (BASELINE.json configs[1]).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One step = one batched get of 256 x 1 MiB pages, drawn uniformly from a 64 GiB HBM-resident set,
+with the CRC32C integrity check fused into the copy.  `value` times the device-resident form
+(requests and destinations already in HBM) with CUDA events; `e2e` times the host-facing C-ABI call
+aps_get_batch() with host request arrays and PINNED HOST destinations, so every page crosses PCIe
+inside the timed region.  N > 1: one process per GPU (torchrun), one shard per GPU, no data-path
+collective (weak scaling).  `--impl reference` times the CPU restatement of the reference's
+LocalCacheManager + LocalPageStore on the host cores for the same workload.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import shutil
+import statistics
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MB = 1 << 20
+PAGE = MB
+BATCH = 256
+DATA_SEED = 0xA11C10
+METRIC = "batched_page_get_fused_crc32c_GBps"
+UNIT = "GB/s"
+
+
+def workload_name(resident_pages):
+    return ("GpuPageStore on 1 B200 per rank: 1 MiB pages, %d GiB resident in HBM, uniform random batched get of "
+            "%d pages with fused CRC32C (BASELINE configs[1])" % (resident_pages * PAGE >> 30, BATCH))
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+
+def cpu_sample_dir():
+    for base in ("/dev/shm", tempfile.gettempdir()):
+        try:
+            if shutil.disk_usage(base).free > 3 << 30:
+                return tempfile.mkdtemp(prefix="aps_cpu_", dir=base), base
+        except OSError:
+            pass
+    return tempfile.mkdtemp(prefix="aps_cpu_"), tempfile.gettempdir()
+
+
+def cpu_reference_run(steps, warmup, threads, sample_pages=2048, gets_per_step=BATCH):
+    """Reference CPU path (oracle port of LocalCacheManager.get -> LocalPageStore.get, one file per
+    page on a real directory) on `threads` host threads.  Returns (GB/s, ms_per_step, description)."""
+    from oracle import binding as orc
+    root, base = cpu_sample_dir()
+    try:
+        n_files = 16
+        ppf = sample_pages // n_files
+        orc.bench_local_get(root, PAGE, n_files, ppf, True, 64, DATA_SEED, 1, threads)  # populate + touch
+        for w in range(warmup):
+            orc.bench_local_get(root, PAGE, n_files, ppf, False, gets_per_step, DATA_SEED, 100 + w, threads)
+        secs, nbytes = 0.0, 0
+        for k in range(steps):
+            s, b = orc.bench_local_get(root, PAGE, n_files, ppf, False, gets_per_step, DATA_SEED, 1000 + k, threads)
+            secs += s
+            nbytes += b
+        desc = ("%d uniform random whole-page gets per step over a %d GiB file set (%d x 1 MiB page files under %s, "
+                "resident in the OS page cache: the reference's best case)" %
+                (gets_per_step, sample_pages * PAGE >> 30, sample_pages, base))
+        return nbytes / secs / 1e9, secs / max(1, steps) * 1e3, desc
+    finally:
+        shutil.rmtree(root, ignore_errors=True)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import binding as orc
+    orc.build()
+    threads = os.cpu_count() or 1
+    steps = max(1, min(args.steps, 200))
+    gbps, ms, desc = cpu_reference_run(steps, min(args.warmup, 5), threads)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": round(gbps, 3), "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": min(args.warmup, 5), "ms_per_step": round(ms, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(65536), "page_bytes": PAGE, "batch_pages": BATCH},
+        "cpu_baseline": {"value": round(gbps, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+        "e2e": {"value": round(gbps, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference is Java and cannot be built here (no JVM); this is the oracle's C++ port of "
+                "LocalCacheManager+LocalPageStore, CRC not included because the reference has none",
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every ~10 ms through NVML while running."""
+
+    def __init__(self, index, uuid=None):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._halt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)).encode()) if uuid else None
+            except Exception:  # noqa: BLE001
+                self.h = None
+            if self.h is None:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._halt.is_set():
+            try:
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:  # noqa: BLE001
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.samples.append((mhz, util))
+                for bit, name in names.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.01)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=2)
+        busy = [m for m, u in self.samples if u > 0] or [m for m, _ in self.samples]
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from alluxio_b200 import capi
+    from alluxio_b200 import build as build_mod
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the page store has no CPU fallback")
+    if rank == 0:
+        build_mod.build_libaps()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.barrier()
+    L = capi.lib()
+    dev = torch.device("cuda", local_rank)
+    K, W = args.steps, max(3, args.warmup)
+
+    resident = int(os.environ.get("APS_BENCH_PAGES", "65536"))
+    free_b, _ = torch.cuda.mem_get_info(dev)
+    while resident * PAGE + (6 << 30) > free_b and resident > 1024:
+        resident //= 2  # a smaller GPU slice: stated in config.workload
+    cfg = capi.aps_config(device=local_rank, page_size=PAGE, cache_bytes=resident * PAGE, slab_slots=resident,
+                          table_capacity=0, max_batch=BATCH, flags=capi.APS_FLAG_CRC)
+    h = C.c_void_p()
+    capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "aps_open")
+    stream = torch.cuda.current_stream(dev)
+    sp = C.c_void_p(stream.cuda_stream)
+
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from gpu_util import GET_REQ, PUT_REQ, RESULT
+
+    # ---- populate: generate pages on the device, put them 256 at a time (file = page // 1024)
+    stage = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
+    d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
+    file_base = rank << 20  # shards hold disjoint files
+    t_pop = time.time()
+    first_put_res = None
+    for b0 in range(0, resident, BATCH):
+        ids = np.arange(b0, b0 + BATCH, dtype=np.uint64)
+        files, idx = ids // 1024 + file_base, ids % 1024
+        d_files = torch.from_numpy(files.view(np.int64)).to(dev)
+        d_idx = torch.from_numpy(idx.view(np.int64)).to(dev)
+        capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, BATCH, d_files.data_ptr(),
+                                        d_idx.data_ptr(), DATA_SEED, sp), "fill")
+        reqs = np.zeros(BATCH, PUT_REQ)
+        reqs["file_lo"], reqs["page_index"], reqs["len"] = files, idx, PAGE
+        reqs["src"] = stage.data_ptr() + np.arange(BATCH, dtype=np.uint64) * PAGE
+        d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
+        capi.check(L.aps_put_batch_dev(h, BATCH, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
+        if b0 == 0:
+            torch.cuda.synchronize(dev)
+            first_put_res = d_res.cpu().numpy().view(RESULT).copy()
+    torch.cuda.synchronize(dev)
+    t_pop = time.time() - t_pop
+
+    # ---- parity spot check against the oracle (the checker; never the thing measured)
+    from oracle import binding as orc
+    for i in (0, 1, 255):
+        want = orc.crc32c(orc.fill_page(DATA_SEED, file_base + i // 1024, i % 1024, PAGE))
+        assert int(first_put_res[i]["crc"]) == want and int(first_put_res[i]["len"]) == PAGE, "put CRC differs from oracle"
+
+    # ---- request pool: uniform random page ids, seed 2 + rank
+    rng = np.random.default_rng(2 + rank)
+    pool = min(K + W, 512)
+    dst = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
+    picks = rng.integers(0, resident, size=(pool, BATCH)).astype(np.uint64)
+    reqs = np.zeros((pool, BATCH), GET_REQ)
+    reqs["file_lo"], reqs["page_index"] = picks // 1024 + file_base, picks % 1024
+    reqs["page_off"], reqs["nbytes"] = 0, PAGE
+    reqs["dst"] = dst.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
+    d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
+    d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
+    req_bytes = BATCH * GET_REQ.itemsize
+
+    def step_dev(k):
+        capi.check(L.aps_get_batch_dev(h, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+
+    for k in range(W):
+        step_dev(k)
+    torch.cuda.synchronize(dev)
+    # correctness of the last warm-up step, against the oracle, before anything is timed
+    res = d_res.cpu().numpy().view(RESULT)
+    k_last = (W - 1) % pool
+    for i in (0, 17, 255):
+        p = int(picks[k_last, i])
+        page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
+        assert int(res[i]["len"]) == PAGE and int(res[i]["crc"]) == orc.crc32c(page), "get CRC differs from oracle"
+        assert np.array_equal(dst[i * PAGE:(i + 1) * PAGE].cpu().numpy(), page), "get bytes differ from oracle"
+
+    sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None))
+    sampler.start()
+
+    # ---- timed region: device-resident batched get with fused CRC (value + roofline)
+    capi.check(L.aps_profile_begin(h, K), "profile_begin")
+    launches0 = L.aps_total_kernel_launches()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for k in range(K):
+        step_dev(W + k)
+    ev1.record(stream)
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = L.aps_total_kernel_launches() - launches0
+    copy_ms, copy_n = C.c_double(), C.c_uint32()
+    capi.check(L.aps_profile_end(h, C.byref(copy_ms), C.byref(copy_n)), "profile_end")
+    res = d_res.cpu().numpy().view(RESULT)
+    assert (res["len"] == PAGE).all(), "a timed get did not return a full page"
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+
+    # ---- end to end: host request arrays, pinned host destinations, results read back
+    e2e_steps = max(1, min(K, 100))
+    pinned = torch.empty(BATCH * PAGE, dtype=torch.uint8).pin_memory()
+    h_reqs = reqs.copy()
+    h_reqs["dst"] = pinned.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
+    h_res = np.zeros(BATCH, RESULT)
+
+    def step_host(k):
+        capi.check(L.aps_get_batch(h, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+
+    for k in range(3):
+        step_host(k)
+    p = int(picks[2 % pool, 5])
+    page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
+    assert np.array_equal(pinned.numpy()[5 * PAGE:6 * PAGE], page) and int(h_res[5]["crc"]) == orc.crc32c(page)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        step_host(3 + k)
+    torch.cuda.synchronize(dev)
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    assert (h_res["len"] == PAGE).all()
+
+    # ---- auxiliary numbers (not the headline): put with CRC
+    aux = {}
+    aux_steps = max(1, min(K, 50))
+    put_reqs = np.zeros(BATCH, PUT_REQ)
+    ids = np.arange(BATCH, dtype=np.uint64)
+    put_reqs["file_lo"], put_reqs["page_index"], put_reqs["len"] = ids // 1024 + file_base, ids % 1024, PAGE
+    put_reqs["src"] = stage.data_ptr() + ids * PAGE  # stage still holds the last populated batch: rewrite ids 0..255
+    files0 = torch.from_numpy((ids // 1024 + file_base).view(np.int64)).to(dev)
+    idx0 = torch.from_numpy((ids % 1024).view(np.int64)).to(dev)
+    capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, BATCH, files0.data_ptr(), idx0.data_ptr(),
+                                    DATA_SEED, sp), "fill")
+    d_put = torch.from_numpy(put_reqs.view(np.uint8).reshape(-1)).to(dev)
+    for _ in range(3):
+        capi.check(L.aps_put_batch_dev(h, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
+    torch.cuda.synchronize(dev)
+    ev0.record(stream)
+    for _ in range(aux_steps):
+        capi.check(L.aps_put_batch_dev(h, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
+    ev1.record(stream)
+    torch.cuda.synchronize(dev)
+    aux["put_fused_crc32c_GBps"] = round(aux_steps * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
+    aux["put_note"] = "re-puts one resident 256 MiB batch (source and slots cached in L2 between steps): upper bound"
+
+    clocks = sampler.stop()
+    stats = capi.aps_stats_t()
+    capi.check(L.aps_stats(h, C.byref(stats)), "stats")
+    assert stats.crc_mismatches == 0
+    capi.check(L.aps_close(h), "close")
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    # ---- CPU baseline on a bounded sample (rank 0, N = 1 only)
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        orc.build()
+        threads = os.cpu_count() or 1
+        gbps_c, _, desc = cpu_reference_run(steps=int(os.environ.get("APS_CPU_STEPS", "40")), warmup=2, threads=threads)
+        cpu = {"value": round(gbps_c, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get("copy_kernel_crc_dram_bytes_per_launch")
+    step_bytes = BATCH * PAGE
+    achieved = 2 * step_bytes / (copy_ms.value / max(1, copy_n.value) * 1e-3) / 1e9
+    value = world * K * step_bytes / (ms_total * 1e-3) / 1e9
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": round(ms_total / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(resident), "page_bytes": PAGE, "resident_pages": resident,
+                   "batch_pages": BATCH, "populate_s": round(t_pop, 2),
+                   "l2": "inputs larger than L2: each step reads 256 MiB drawn from the resident set and writes 256 MiB",
+                   "shards": "one store per GPU, disjoint files, no data-path collective"},
+        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                     "kernel": "aps::copy_kernel<true> (K2+K3 gather + fused CRC32C)",
+                     "algorithmic_bytes_per_launch": 2 * step_bytes,
+                     "avg_launch_ms": round(copy_ms.value / max(1, copy_n.value), 5), "launches_timed": copy_n.value,
+                     "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
+        "e2e": {"value": round(world * e2e_steps * step_bytes / e2e_s / 1e9, 2), "unit": UNIT,
+                "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
+                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound)"},
+        "gpu_launches": int(launches), "clocks": clocks, "aux": aux,
+        "table": {"lookups": int(stats.lookups), "probe_buckets": int(stats.probe_buckets)},
+    }
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

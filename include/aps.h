@@ -1,0 +1,224 @@
+/*
+ * aps.h -- C ABI of the B200 page store ("Alluxio Page Store", libaps.so).
+ *
+ * This is the drop-in boundary for the client-side page-cache data path.  It is what a JNI shim
+ * under a Java `GpuPageStore implements PageStore` binds (INTEGRATION.md shows that shim), and it
+ * is what the JVM-free host mirror in alluxio_b200/host/ and the tests call.  Plain C: opaque
+ * handle, pointers and sizes, integer status codes.  No C++ or torch types cross it.
+ *
+ * "CACHE/" = /root/reference/core/client/fs/src/main/java/alluxio/client/file/cache/.
+ *
+ * Status codes map to the reference's exceptions:
+ *   APS_OK                         success
+ *   APS_ENOTFOUND  -> alluxio.exception.PageNotFoundException
+ *   APS_EINVAL     -> IllegalArgumentException (Preconditions.checkArgument in LocalPageStore.get)
+ *   anything else  -> java.io.IOException(aps_strerror(code))
+ *
+ * Ownership: the caller owns every buffer.  Single-page calls do not touch caller memory after
+ * they return.  Batched calls on a caller stream do not touch it after that stream has completed.
+ *
+ * Threading: every entry point may be called from any host thread.  Calls on one store are
+ * serialised by a mutex inside the library while they enqueue work.  As in the reference
+ * ("does not need to provide thread-safety", CACHE/PageStore.java:34-35), ordering between
+ * operations on the SAME PageId is the caller's job (LocalCacheManager's striped page locks);
+ * operations on different PageIds may be issued concurrently.
+ */
+#ifndef APS_H_
+#define APS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define APS_API __attribute__((visibility("default")))
+#else
+#define APS_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define APS_OK 0
+#define APS_ENOTFOUND 1  /* page not in the store */
+#define APS_EINVAL 2     /* bad offset / length / argument */
+#define APS_ENOSPC 3     /* no free slab slot or table entry */
+#define APS_ECUDA 4      /* a CUDA call failed; aps_last_cuda_error() has the text */
+#define APS_ECORRUPT 5   /* whole-page read whose CRC32C differs from the one recorded at put */
+#define APS_ECLOSED 6    /* store already closed */
+#define APS_ENOMEM 7     /* host or device allocation failed */
+#define APS_EFAULT 8     /* injected fault (APS_FAULT_* below) */
+
+/* PageId on the device: CACHE/PageId.java:23-74 is (String fileId, long pageIndex).  The file id
+ * is carried as 128 bits; the host side maps strings to 128 bits without collisions (decimal,
+ * 32-hex and UUID ids parse exactly, anything else is interned -- see alluxio_b200/host). */
+typedef struct aps_key {
+  uint64_t file_hi;
+  uint64_t file_lo;
+  uint64_t page_index;
+} aps_key;
+
+#define APS_FLAG_CRC 1u        /* compute CRC32C inside every copy, record it at put, verify whole-page gets */
+#define APS_FLAG_TMA_COPY 2u   /* when CRC is off, move pages with bulk-async (TMA) copies instead of LDG/STG */
+
+/* Replaces LocalPageStoreOptions / PageStoreOptions (CACHE/store/PageStoreOptions.java:23-182). */
+typedef struct aps_config {
+  int32_t device;           /* CUDA ordinal */
+  uint32_t page_size;       /* bytes per slab slot = alluxio.user.client.cache.page.size; multiple of 16 */
+  uint64_t cache_bytes;     /* alluxio.user.client.cache.size; what getCacheSize() reports */
+  uint64_t slab_slots;      /* slots in the HBM slab; 0 = ceil(cache_bytes / page_size) + 1/8 slack (min 64) */
+  uint64_t table_capacity;  /* hash-table entries; 0 = next power of two >= 2 * slab_slots (min 1024) */
+  uint32_t max_batch;       /* largest n accepted by one batched call; 0 = 4096 */
+  uint32_t flags;           /* APS_FLAG_* */
+} aps_config;
+
+typedef struct aps_store aps_store; /* opaque; one HBM slab + table on one GPU */
+typedef void* aps_stream;           /* a cudaStream_t, or NULL for the store's own stream */
+
+/* PageStore.open / PageStore.create (CACHE/PageStore.java:49-77).  HBM is volatile, so open and
+ * create are the same thing: the store starts empty (getPages() yields nothing, which
+ * LocalCacheManager.restore accepts, CACHE/LocalCacheManager.java:466-509). */
+APS_API int aps_open(const aps_config* cfg, aps_store** out);
+/* AutoCloseable.close (CACHE/PageStore.java:37).  Idempotent on a live handle; frees it. */
+APS_API int aps_close(aps_store* s);
+
+/* ---- single-page operations: exactly the PageStore contract, host pointers ------------------ */
+
+/* PageStore.put(PageId, byte[]) CACHE/PageStore.java:119 / LocalPageStore.java:68-86.
+ * Stores exactly len bytes (0 <= len <= page_size); replaces the page if the id is present.
+ * On failure no partial page is left behind. */
+APS_API int aps_put(aps_store* s, const aps_key* key, const void* src, uint32_t len);
+
+/* PageStore.get(PageId, pageOffset, bytesToRead, buffer, bufferOffset) CACHE/PageStore.java:147 /
+ * LocalPageStore.java:88-121.  dst = buffer + bufferOffset and dst_cap = buffer.length -
+ * bufferOffset (the shim checks bufferOffset <= buffer.length itself).  Copies
+ * min(pageLen - page_off, dst_cap, bytes_to_read) bytes and reports that count in *out_len.
+ * page_off > pageLen -> APS_EINVAL; unknown id -> APS_ENOTFOUND.  *out_crc (optional) receives the
+ * CRC32C of the bytes returned when the store was opened with APS_FLAG_CRC. */
+APS_API int aps_get(aps_store* s, const aps_key* key, uint32_t page_off, uint32_t bytes_to_read, void* dst, uint32_t dst_cap,
+            uint32_t* out_len, uint32_t* out_crc);
+
+/* PageStore.delete(PageId) CACHE/PageStore.java:157 / LocalPageStore.java:123-137. */
+APS_API int aps_delete(aps_store* s, const aps_key* key);
+
+/* PageStore.getCacheSize() CACHE/PageStore.java:171. */
+APS_API uint64_t aps_cache_size(const aps_store* s);
+
+/* PageStore.getPages() CACHE/PageStore.java:166 / LocalPageStore.java:193-199: calls cb once per
+ * resident page with its id and stored length.  A non-zero return from cb stops the walk. */
+typedef int (*aps_iter_cb)(void* user, const aps_key* key, uint32_t len);
+APS_API int aps_iterate(aps_store* s, aps_iter_cb cb, void* user);
+
+/* ---- batched operations: the benchmarked path (additive; the reference API is one page per
+ *      call, CACHE/CacheManager.java:148-182) ------------------------------------- */
+
+/* One request of a batched get.  dst may be device memory or pinned (page-locked) host memory. */
+typedef struct aps_get_req {
+  aps_key key;
+  uint32_t page_off;
+  uint32_t nbytes; /* min(bytes_to_read, room in dst) */
+  void* dst;
+} aps_get_req;
+
+/* len >= 0: bytes copied.  len < 0: -(status code) for this request (-APS_ENOTFOUND, ...). */
+typedef struct aps_result {
+  int32_t len;
+  uint32_t crc;
+} aps_result;
+
+typedef struct aps_put_req {
+  aps_key key;
+  uint32_t len;
+  uint32_t reserved;
+  const void* src; /* device memory or pinned host memory */
+} aps_put_req;
+
+/* Batched LocalPageStore.get.  reqs and res are HOST arrays; the call stages them, runs the
+ * lookup + gather (+CRC) kernels on `stream`, copies the results back and waits for them.
+ * Keys within one batch need not be distinct for gets. */
+APS_API int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream);
+
+/* Batched LocalPageStore.put.  Keys within one batch must be distinct (else APS_EINVAL). */
+APS_API int aps_put_batch(aps_store* s, uint32_t n, const aps_put_req* reqs, aps_result* res, aps_stream stream);
+
+/* Batched LocalPageStore.delete; res[i].len is 0 or -APS_ENOTFOUND.  Keys must be distinct. */
+APS_API int aps_delete_batch(aps_store* s, uint32_t n, const aps_key* keys, aps_result* res, aps_stream stream);
+
+/* Device-resident forms: d_reqs / d_res / d_keys are DEVICE arrays that are already in HBM.
+ * Fully asynchronous on `stream`: nothing is copied to or from the host and the call does not
+ * wait.  This is what the kernel-only benchmark times. */
+APS_API int aps_get_batch_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream);
+APS_API int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_result* d_res, aps_stream stream);
+APS_API int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, aps_result* d_res, aps_stream stream);
+
+/* Membership only: the device form of DefaultMetaStore.hasPage (CACHE/DefaultMetaStore.java:51-53)
+ * for a batch of ids.  d_len[i] = stored length, or -1 when absent. */
+APS_API int aps_lookup_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, int32_t* d_len, aps_stream stream);
+
+/* ---- checksum path: `alluxio fs checksum` ------------------------------------------------------
+ * ChecksumCommand.calculateChecksum (shell/src/main/java/alluxio/cli/fs/command/
+ * ChecksumCommand.java:83-90) = DigestUtils.md5Hex over the file's bytes.  One digest per file,
+ * files processed in parallel.  d_data[i] points at len[i] bytes in device memory (or pinned host
+ * memory); d_data, d_len and d_out are DEVICE arrays.  Asynchronous on `stream`. */
+APS_API int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
+                      uint8_t (*d_out)[16], aps_stream stream);
+/* Host form: arrays on the host, file payloads wherever they are (device or pinned); waits. */
+APS_API int aps_md5_batch(int32_t device, uint32_t n_files, const void* const* data, const uint64_t* len, uint8_t (*out)[16]);
+
+/* CRC32C (RFC 3720, Castagnoli) of n device-resident byte ranges, without a copy.  Stand-alone
+ * verify pass; the reference has no CRC at all. */
+APS_API int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_data, const uint32_t* d_len, uint32_t* d_crc,
+                         aps_stream stream);
+
+/* ---- synthetic data, stats, diagnostics ---------------------------------------------------------*/
+
+/* Fills device memory with the benchmark payload: 64-bit word k of page (file, index) is the k-th
+ * splitmix64 output for seed ^ (file << 32) ^ index.  Writes n_pages pages of
+ * page_len bytes, page p at d_dst + p * stride, for ids files[p], indices[p] (DEVICE arrays). */
+APS_API int aps_fill_pages_dev(int32_t device, void* d_dst, uint64_t stride, uint32_t page_len, uint32_t n_pages,
+                       const uint64_t* d_files, const uint64_t* d_indices, uint64_t seed, aps_stream stream);
+
+typedef struct aps_stats_t {
+  uint64_t pages;           /* resident pages */
+  uint64_t bytes;           /* sum of their stored lengths */
+  uint64_t slots_free;      /* free slab slots */
+  uint64_t table_capacity;  /* entries */
+  uint64_t tombstones;      /* deleted entries still in probe chains */
+  uint64_t lookups;         /* keys looked up since open */
+  uint64_t probe_buckets;   /* 256-byte buckets read by those lookups */
+  uint64_t bytes_copied;    /* payload bytes moved by get/put kernels */
+  uint64_t crc_mismatches;  /* whole-page gets whose CRC differed from the one recorded at put */
+  uint64_t kernel_launches; /* kernels this store has launched */
+} aps_stats_t;
+APS_API int aps_stats(aps_store* s, aps_stats_t* out);
+
+/* Timing of the copy kernel (K2/K3) alone, for the roofline line of bench.py: between begin and end
+ * every launch of it is bracketed by CUDA events on its own stream.  end() waits for them and
+ * returns the summed device time and the number of launches timed. */
+APS_API int aps_profile_begin(aps_store* s, uint32_t max_launches);
+APS_API int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_launches);
+
+/* Fault injection for the reference's FaultyPageStore tests (CTEST/LocalCacheManagerTest.java:
+ * 660-691): while set, aps_put / aps_delete fail with APS_EFAULT and change nothing. */
+#define APS_FAULT_PUT 1u
+#define APS_FAULT_DELETE 2u
+APS_API int aps_set_faults(aps_store* s, uint32_t fault_mask);
+
+/* Test hook: flips one byte of a resident page in the slab so the CRC check can be shown to fire. */
+APS_API int aps_debug_corrupt(aps_store* s, const aps_key* key, uint32_t byte_offset);
+
+/* Test hook, host arithmetic only (needs no GPU): the GF(2) constants of the fused CRC32C copy --
+ * fold[4][256] (x^(8*512) per byte lane), z4[4][256] (x^32), xpow8[32] (x^(8*2^k)) and
+ * lane_shift[32].  tests/test_crc_algebra.py replays the kernel's arithmetic with them on the CPU. */
+APS_API int aps_debug_crc_constants(uint32_t* fold, uint32_t* z4, uint32_t* xpow8, uint32_t* lane_shift);
+
+APS_API const char* aps_strerror(int code);
+APS_API const char* aps_last_cuda_error(void); /* thread-local text of the last failed CUDA call */
+APS_API const char* aps_version(void);
+/* Total kernels launched by this library in this process (all stores + stateless entry points). */
+APS_API uint64_t aps_total_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APS_H_ */

@@ -1,0 +1,57 @@
+"""The C-ABI library loads and exports every symbol include/aps.h declares (no GPU needed), and the
+data path fails loudly -- never falls back -- when no CUDA device is present."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from alluxio_b200 import capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "aps.h")).read()
+    return sorted(set(re.findall(r"APS_API\s+[\w\s\*]+?\b(aps_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_surface():
+    syms = declared_symbols()
+    for must in ("aps_open", "aps_close", "aps_put", "aps_get", "aps_delete", "aps_iterate", "aps_get_batch",
+                 "aps_put_batch", "aps_md5_batch", "aps_stats", "aps_strerror"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol():
+    L = C.CDLL(capi.LIB_PATH)
+    for name in declared_symbols():
+        assert hasattr(L, name), name
+
+
+def test_binding_covers_every_declared_symbol():
+    assert sorted(capi.SIGNATURES) == declared_symbols()
+
+
+def test_host_only_entry_points():
+    L = capi.lib()
+    assert b"sm_100a" in L.aps_version()
+    assert L.aps_strerror(capi.APS_ENOTFOUND) == b"page not found"
+    assert L.aps_total_kernel_launches() >= 0
+
+
+def test_open_rejects_bad_config_and_fails_loudly_without_gpu():
+    import torch
+    L = capi.lib()
+    h = C.c_void_p()
+    bad = capi.aps_config(device=0, page_size=100, cache_bytes=1 << 20)  # not a multiple of 16
+    assert L.aps_open(C.byref(bad), C.byref(h)) == capi.APS_EINVAL
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present; the no-device branch cannot be shown here")
+    cfg = capi.aps_config(device=0, page_size=4096, cache_bytes=1 << 20)
+    rc = L.aps_open(C.byref(cfg), C.byref(h))
+    assert rc == capi.APS_ECUDA and not h.value
+    assert L.aps_last_cuda_error() != b""
+    from alluxio_b200.page_store import GpuPageStore, IOExceptionJ
+    with pytest.raises(IOExceptionJ):
+        GpuPageStore(page_size=4096, cache_size=1 << 20)

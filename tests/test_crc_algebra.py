@@ -1,0 +1,145 @@
+"""CPU replay of the fused-CRC kernel's arithmetic (alluxio_b200/csrc/aps_kernels.cuh: warp_rows,
+warp_bytes, copy_kernel's chunk combine) using the GF(2) constants libaps computes on the host.
+Runs without a GPU: it proves the tables, the per-lane shift constants and the combine formulas
+before any kernel is launched.  The device result itself is checked in tests/test_gpu_*.py."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from alluxio_b200 import capi
+from oracle import binding as orc
+
+POLY = 0x82F63B78
+CHUNK, ROW = 16384, 512
+
+
+def gf_mul(a, b):
+    r = 0
+    for i in range(32):
+        if (b >> (31 - i)) & 1:
+            r ^= a
+        a = (a >> 1) ^ (POLY if a & 1 else 0)
+    return r
+
+
+@pytest.fixture(scope="module")
+def consts():
+    fold = np.zeros((4, 256), np.uint32)
+    z4 = np.zeros((4, 256), np.uint32)
+    xp = np.zeros(32, np.uint32)
+    ls = np.zeros(32, np.uint32)
+    capi.check(capi.lib().aps_debug_crc_constants(fold.ctypes.data, z4.ctypes.data, xp.ctypes.data, ls.ctypes.data))
+    return fold, z4, xp, ls
+
+
+def xpow8(n, xp):
+    r, k = 0x80000000, 0
+    while n:
+        if n & 1:
+            r = gf_mul(r, int(xp[k]))
+        n >>= 1
+        k += 1
+    return r
+
+
+def apply4(tab, s):
+    """vectorised T0[s&255]^T1[(s>>8)&255]^T2[(s>>16)&255]^T3[s>>24] on uint32 arrays"""
+    return tab[0][s & 0xFF] ^ tab[1][(s >> 8) & 0xFF] ^ tab[2][(s >> 16) & 0xFF] ^ tab[3][s >> 24]
+
+
+def warp_rows(data, consts):
+    fold, z4, xp, ls = consts
+    rows = data.size // ROW
+    w = data[:rows * ROW].view("<u4").reshape(rows, 32, 4)  # [row][lane][k]
+    S = np.zeros((32, 4), np.uint32)
+    for r in range(rows):
+        S = apply4(fold, S) ^ w[r]
+    t = apply4(z4, apply4(z4, apply4(z4, S[:, 0]) ^ S[:, 1]) ^ S[:, 2]) ^ S[:, 3]
+    acc = 0
+    for lane in range(32):
+        acc ^= gf_mul(int(t[lane]), int(ls[lane]))
+    return acc
+
+
+def crc_bitwise_zero_init(b):
+    r = 0
+    for x in b:
+        r ^= int(x)
+        for _ in range(8):
+            r = (r >> 1) ^ (POLY if r & 1 else 0)
+    return r
+
+
+def warp_bytes(data, consts):
+    xp = consts[2]
+    n = data.size
+    per = (n + 31) >> 5
+    acc = 0
+    for lane in range(32):
+        lo = min(n, lane * per)
+        hi = min(n, lo + per)
+        acc ^= gf_mul(crc_bitwise_zero_init(data[lo:hi]), xpow8(n - hi, xp))
+    return acc
+
+
+def kernel_crc(data, consts, aligned=True):
+    """copy_kernel<true> for one job of len(data) bytes."""
+    xp = consts[2]
+    n = data.size
+    nchunks = (n + CHUNK - 1) // CHUNK
+    partials = []
+    for c in range(nchunks):
+        chunk = data[c * CHUNK:min(n, (c + 1) * CHUNK)]
+        rows = chunk.size // ROW if aligned else 0
+        tail = chunk.size - rows * ROW
+        crc = warp_rows(chunk, consts) if rows else 0
+        if tail:
+            ct = warp_bytes(chunk[rows * ROW:], consts)
+            crc = (gf_mul(crc, xpow8(tail, xp)) ^ ct) if rows else ct
+        partials.append(crc)
+    acc = 0
+    for j, p in enumerate(partials):
+        end = min(n, (j + 1) * CHUNK)
+        acc ^= gf_mul(p, xpow8(n - end, xp))
+    return acc ^ gf_mul(0xFFFFFFFF, xpow8(n, xp)) ^ 0xFFFFFFFF
+
+
+def test_constants_match_their_definitions(consts):
+    fold, z4, xp, ls = consts
+    assert int(xp[0]) == 0x00800000  # x^8 in the reflected register
+    # advancing the register by n zero bytes == multiplying by x^(8n): check against the oracle
+    for n in (1, 4, 512, 4096, 12345):
+        for r in (1, 0x80000000, 0xDEADBEEF):
+            raw = r
+            for _ in range(n):
+                raw = (raw >> 8) ^ crc_bitwise_zero_init(bytes([raw & 0xFF]))
+            assert gf_mul(r, xpow8(n, xp)) == raw
+    for j in range(4):
+        for b in (0, 1, 0x80, 0xFF):
+            assert int(fold[j][b]) == gf_mul((b << (8 * j)) & 0xFFFFFFFF, xpow8(512, xp))
+            assert int(z4[j][b]) == gf_mul((b << (8 * j)) & 0xFFFFFFFF, xpow8(4, xp))
+    for lane in (0, 1, 31):
+        assert int(ls[lane]) == xpow8(500 - 16 * lane, xp)
+
+
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 511, 512, 513, 1024, 4096 + 7, CHUNK - 1, CHUNK, CHUNK + 1,
+                               CHUNK + 512, 3 * CHUNK + 100, 65536])
+def test_kernel_arithmetic_matches_oracle(consts, n):
+    rng = np.random.default_rng(n)
+    data = rng.integers(0, 256, n, dtype=np.uint8)
+    assert kernel_crc(data, consts) == orc.crc32c(data)
+
+
+def test_unaligned_path_matches_oracle(consts):
+    rng = np.random.default_rng(5)
+    for n in (33, 700, CHUNK + 9):
+        data = rng.integers(0, 256, n, dtype=np.uint8)
+        assert kernel_crc(data, consts, aligned=False) == orc.crc32c(data)
+
+
+def test_known_answers_through_kernel_arithmetic(consts):
+    assert kernel_crc(np.frombuffer(b"123456789", np.uint8), consts) == 0xE3069283
+    assert kernel_crc(np.zeros(32, np.uint8), consts) == 0x8A9136AA
+    assert kernel_crc(np.full(32, 0xFF, np.uint8), consts) == 0x62A8AB43
+    assert kernel_crc(np.arange(32, dtype=np.uint8), consts) == 0x46DD794E
