@@ -4,6 +4,7 @@
 // when the runtime cannot provide one.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_set>
@@ -59,6 +60,34 @@ struct DeviceConsts {
 std::mutex g_dev_mu;
 DeviceConsts g_dev[64];
 
+// Launch shapes of the copy kernel (threads per CTA x rows per pipelined group).  The default was
+// picked from measurements on B200 (profiles/); APS_COPY_VARIANT=<threads>x<group> overrides it.
+typedef void (*CopyKernelFn)(CopyArgs);
+struct CopyVariant {
+  const char* name;
+  uint32_t threads;
+  CopyKernelFn crc, plain, get_crc, get_plain;
+};
+#define APS_VARIANT(T, G)                                                                                  \
+  {#T "x" #G, T, copy_kernel<true, T, G, false>, copy_kernel<false, T, G, false>, copy_kernel<true, T, G, true>, \
+   copy_kernel<false, T, G, true>}
+const CopyVariant kCopyVariants[] = {
+    APS_VARIANT(512, 4), APS_VARIANT(1024, 4), APS_VARIANT(1024, 2), APS_VARIANT(768, 4),
+    APS_VARIANT(512, 8), APS_VARIANT(512, 2),  APS_VARIANT(640, 4),  APS_VARIANT(384, 8),
+};
+#undef APS_VARIANT
+const CopyVariant& copy_variant() {
+  static const CopyVariant* v = [] {
+    const char* want = getenv("APS_COPY_VARIANT");
+    const CopyVariant* pick = &kCopyVariants[0];
+    if (want)
+      for (const CopyVariant& c : kCopyVariants)
+        if (!strcmp(c.name, want)) pick = &c;
+    return pick;
+  }();
+  return *v;
+}
+
 struct HostCrcConsts {
   CrcTables tables;
   uint32_t xpow8[32];
@@ -93,7 +122,10 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
     CUDA_TRY(cudaMemcpy(d.d_tables, &h.tables, sizeof(CrcTables), cudaMemcpyHostToDevice));
     CUDA_TRY(cudaMemcpyToSymbol(c_xpow8, h.xpow8, sizeof(h.xpow8)));
     CUDA_TRY(cudaMemcpyToSymbol(c_lane_shift, h.lane_shift, sizeof(h.lane_shift)));
-    CUDA_TRY(cudaFuncSetAttribute(copy_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+    for (const CopyVariant& v : kCopyVariants) {
+      CUDA_TRY(cudaFuncSetAttribute(v.crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+      CUDA_TRY(cudaFuncSetAttribute(v.get_crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+    }
     CUDA_TRY(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev));
     d.ready = true;
   }
@@ -116,11 +148,12 @@ struct aps_store {
   cudaStream_t stream = nullptr;
   Table table{};
   uint64_t slots = 0, n_entries = 0;
-  uint32_t chunks_per_page = 0;
+  uint32_t page_rows = 0;  // 512-byte rows in a full page
   DeviceConsts* dc = nullptr;
   // scratch, sized for cfg.max_batch requests
   Job* d_jobs = nullptr;
-  uint32_t* d_partials = nullptr;
+  uint32_t* d_acc = nullptr;
+  uint32_t* d_rowshift = nullptr;  // x^(8*512*k) for k = 0 .. page_rows
   uint32_t* d_done = nullptr;
   int* d_error = nullptr;
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
@@ -142,28 +175,44 @@ inline void count_launch(aps_store* s, uint64_t k = 1) {
   if (s) s->launches += k;
 }
 
-int launch_copy(aps_store* s, uint32_t n, aps_result* d_res, uint32_t* d_crc_out, cudaStream_t st) {
+int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_result* d_res, uint32_t* d_crc_out,
+                cudaStream_t st) {
   const bool crc = (s->cfg.flags & APS_FLAG_CRC) != 0 || d_crc_out != nullptr;
+  const CopyVariant& v = copy_variant();
+  const uint32_t warps_per_block = v.threads / 32;
+  const uint32_t chip_warps = (uint32_t)s->dc->num_sms * warps_per_block;
+  // cut every job into equal warp-tasks so that one round of the persistent grid covers the batch
+  uint32_t tpj = std::max(1u, chip_warps / n);
+  tpj = std::min(tpj, std::min(kMaxTasksPerJob, std::max(1u, s->page_rows / 8)));
+  const uint32_t rpt = (s->page_rows + tpj - 1) / tpj;
+  tpj = (s->page_rows + rpt - 1) / rpt;
   CopyArgs a{};
   a.jobs = s->d_jobs;
+  a.reqs = d_get_reqs;
+  a.table = s->table;
+  a.crc_on = (s->cfg.flags & APS_FLAG_CRC) != 0;
   a.n_jobs = n;
-  a.chunks_per_job = s->chunks_per_page;
+  a.tasks_per_job = tpj;
+  a.rows_per_task = rpt;
   a.res = d_res;
   a.crc_out = d_crc_out;
-  a.partials = s->d_partials;
+  a.acc = s->d_acc;
   a.done = s->d_done;
   a.tables = s->dc->d_tables;
-  a.slot_crc = s->table.slot_crc;
-  a.counters = s->table.counters;
+  a.rowshift = s->d_rowshift;
   a.error_flag = s->d_error;
-  const uint64_t items = (uint64_t)n * s->chunks_per_page;
-  const uint32_t warps_per_block = kCopyThreads / 32;
+  const uint64_t items = (uint64_t)n * tpj;
   uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, (items + warps_per_block - 1) / warps_per_block);
   if (grid == 0) grid = 1;
   const bool timed = s->prof_on && s->prof_used + 2 <= s->prof_events.size();
   if (timed) CUDA_TRY(cudaEventRecord(s->prof_events[s->prof_used], st));
-  if (crc) copy_kernel<true><<<grid, kCopyThreads, kCopyDynSmem, st>>>(a);
-  else copy_kernel<false><<<grid, kCopyThreads, 0, st>>>(a);
+  if (d_get_reqs) {
+    if (crc) v.get_crc<<<grid, v.threads, kCopyDynSmem, st>>>(a);
+    else v.get_plain<<<grid, v.threads, 0, st>>>(a);
+  } else {
+    if (crc) v.crc<<<grid, v.threads, kCopyDynSmem, st>>>(a);
+    else v.plain<<<grid, v.threads, 0, st>>>(a);
+  }
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
   if (timed) {
@@ -218,7 +267,8 @@ void free_store(aps_store* s) {
   cudaFree(s->table.slot_crc);
   cudaFree(s->table.counters);
   cudaFree(s->d_jobs);
-  cudaFree(s->d_partials);
+  cudaFree(s->d_acc);
+  cudaFree(s->d_rowshift);
   cudaFree(s->d_done);
   cudaFree(s->d_error);
   cudaFree(s->d_reqs);
@@ -302,7 +352,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   if (s->cfg.max_batch == 0) s->cfg.max_batch = 4096;
   s->slots = slots;
   s->n_entries = entries;
-  s->chunks_per_page = (cfg->page_size + kChunkBytes - 1) / kChunkBytes;
+  s->page_rows = (cfg->page_size + kRowBytes - 1) / kRowBytes;
   const uint32_t mb = s->cfg.max_batch;
 
 #define OPEN_TRY(expr)                                                                                    \
@@ -325,7 +375,15 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaMalloc(&s->table.slot_crc, slots * sizeof(uint32_t)));
   OPEN_TRY(cudaMalloc(&s->table.counters, kNumCounters * sizeof(unsigned long long)));
   OPEN_TRY(cudaMalloc(&s->d_jobs, (uint64_t)mb * sizeof(Job)));
-  OPEN_TRY(cudaMalloc(&s->d_partials, (uint64_t)mb * s->chunks_per_page * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->d_acc, (uint64_t)mb * sizeof(uint32_t)));
+  {
+    std::vector<uint32_t> rs(s->page_rows + 1);
+    const uint32_t xrow = host_xpow8(kRowBytes);
+    rs[0] = 0x80000000u;
+    for (uint32_t k = 1; k <= s->page_rows; ++k) rs[k] = gf_mul(rs[k - 1], xrow);
+    OPEN_TRY(cudaMalloc(&s->d_rowshift, rs.size() * sizeof(uint32_t)));
+    OPEN_TRY(cudaMemcpy(s->d_rowshift, rs.data(), rs.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+  }
   OPEN_TRY(cudaMalloc(&s->d_done, (uint64_t)mb * sizeof(uint32_t)));
   OPEN_TRY(cudaMalloc(&s->d_error, sizeof(int)));
   OPEN_TRY(cudaMalloc(&s->d_reqs, (uint64_t)mb * sizeof(aps_get_req)));
@@ -339,6 +397,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaMemsetAsync(s->table.slot_crc, 0, slots * sizeof(uint32_t), s->stream));
   OPEN_TRY(cudaMemsetAsync(s->table.counters, 0, kNumCounters * sizeof(unsigned long long), s->stream));
   OPEN_TRY(cudaMemsetAsync(s->d_done, 0, (uint64_t)mb * sizeof(uint32_t), s->stream));
+  OPEN_TRY(cudaMemsetAsync(s->d_acc, 0, (uint64_t)mb * sizeof(uint32_t), s->stream));
   OPEN_TRY(cudaMemsetAsync(s->d_error, 0, sizeof(int), s->stream));
   OPEN_TRY(cudaMemcpyAsync(s->table.free_top, &top, sizeof(top), cudaMemcpyHostToDevice, s->stream));
   init_free_slots_kernel<<<(unsigned)((slots + 255) / 256), 256, 0, s->stream>>>(s->table.free_slots, slots);
@@ -382,10 +441,7 @@ int aps_get_batch_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_r
   if (n > s->cfg.max_batch || !d_reqs || !d_res) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  get_resolve_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
-  count_launch(s);
-  CUDA_TRY(cudaGetLastError());
-  return launch_copy(s, n, d_res, nullptr, st);
+  return launch_copy(s, n, d_reqs, d_res, nullptr, st);  // lookup + gather + CRC in one launch
 }
 
 int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_result* d_res, aps_stream stream) {
@@ -398,7 +454,7 @@ int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_r
   put_resolve_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
-  return launch_copy(s, n, d_res, nullptr, st);
+  return launch_copy(s, n, nullptr, d_res, nullptr, st);
 }
 
 int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, aps_result* d_res, aps_stream stream) {
@@ -439,7 +495,7 @@ int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_data, co
   crc_jobs_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_data, d_len, n, s->cfg.page_size, s->d_jobs, d_crc);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
-  return launch_copy(s, n, nullptr, d_crc, st);
+  return launch_copy(s, n, nullptr, nullptr, d_crc, st);
 }
 
 // ---------------------------------------------------------------- host-array batched forms

@@ -20,9 +20,7 @@ constexpr uint32_t kJobVerify = 1u;  // whole-page get: compare with the CRC rec
 constexpr uint32_t kJobRecord = 2u;  // put: record the CRC for the slot
 constexpr uint32_t kJobOutCrc = 4u;  // write the CRC to crc_out[job] (stand-alone checksum pass)
 
-constexpr uint32_t kChunkBytes = 16384;  // one warp-task: 32 rows of 512 bytes
-constexpr uint32_t kRowBytes = 512;      // one warp-wide 128-bit access
-constexpr uint32_t kCopyThreads = 1024;
+constexpr uint32_t kRowBytes = 512;  // one warp-wide 128-bit access
 
 // Shared-memory map of the CRC copy kernel, as absolute shared-window addresses:
 //   0x0F000 .. 0x0FFFF  Z_4 tables  G[j][b], j = 0..3 (plain, 4 KiB)         -- row-state reduction
@@ -88,38 +86,53 @@ __device__ __forceinline__ uint32_t warp_xor(uint32_t v) {
   return v;
 }
 
-// Aligned fast path: `rows` 512-byte rows, 16 bytes per lane per row, four rows in flight.
+// One 512-byte row per call: fold the four lane words forward by a row and add the new data.
+#define APS_FOLD_ROW(v_)                                                  \
+  do {                                                                    \
+    S0 = fold_word(S0, rb) ^ (v_).x; S1 = fold_word(S1, rb) ^ (v_).y;     \
+    S2 = fold_word(S2, rb) ^ (v_).z; S3 = fold_word(S3, rb) ^ (v_).w;     \
+  } while (0)
+
+// Aligned fast path: `rows` 512-byte rows, 16 bytes per lane per row.  Software pipelined: while the
+// G rows of one group are stored and folded, the loads of the next group are already in flight.
 // Returns the zero-init CRC of the rows (same value in every lane) when kCrc.
-template <bool kCrc>
+template <bool kCrc, int G>
 __device__ __forceinline__ uint32_t warp_rows(const uint8_t* src, uint8_t* dst, uint32_t rows, uint32_t lane) {
   const uint4* s = reinterpret_cast<const uint4*>(src) + lane;
   uint4* d = reinterpret_cast<uint4*>(dst) + lane;
   const bool store = dst != nullptr;
   const uint32_t rb = 0x00010000u | (lane << 2);
   uint32_t S0 = 0, S1 = 0, S2 = 0, S3 = 0;
-  uint32_t r = 0;
-  for (; r + 4 <= rows; r += 4) {
-    uint4 w0 = ldg_stream(s + (r + 0) * 32), w1 = ldg_stream(s + (r + 1) * 32);
-    uint4 w2 = ldg_stream(s + (r + 2) * 32), w3 = ldg_stream(s + (r + 3) * 32);
+  const uint32_t ng = rows / G;
+  uint4 A[G], B[G];
+  auto load = [&](uint4(&buf)[G], uint32_t g) {
+#pragma unroll
+    for (int u = 0; u < G; ++u) buf[u] = ldg_stream(s + (size_t)(g * G + u) * 32);
+  };
+  auto consume = [&](uint4(&buf)[G], uint32_t g) {
     if (store) {
-      stg_stream(d + (r + 0) * 32, w0);
-      stg_stream(d + (r + 1) * 32, w1);
-      stg_stream(d + (r + 2) * 32, w2);
-      stg_stream(d + (r + 3) * 32, w3);
+#pragma unroll
+      for (int u = 0; u < G; ++u) stg_stream(d + (size_t)(g * G + u) * 32, buf[u]);
     }
     if (kCrc) {
-      S0 = fold_word(S0, rb) ^ w0.x; S1 = fold_word(S1, rb) ^ w0.y; S2 = fold_word(S2, rb) ^ w0.z; S3 = fold_word(S3, rb) ^ w0.w;
-      S0 = fold_word(S0, rb) ^ w1.x; S1 = fold_word(S1, rb) ^ w1.y; S2 = fold_word(S2, rb) ^ w1.z; S3 = fold_word(S3, rb) ^ w1.w;
-      S0 = fold_word(S0, rb) ^ w2.x; S1 = fold_word(S1, rb) ^ w2.y; S2 = fold_word(S2, rb) ^ w2.z; S3 = fold_word(S3, rb) ^ w2.w;
-      S0 = fold_word(S0, rb) ^ w3.x; S1 = fold_word(S1, rb) ^ w3.y; S2 = fold_word(S2, rb) ^ w3.z; S3 = fold_word(S3, rb) ^ w3.w;
+#pragma unroll
+      for (int u = 0; u < G; ++u) APS_FOLD_ROW(buf[u]);
     }
+  };
+  uint32_t g = 0;
+  if (ng) load(A, 0);
+  while (g + 2 <= ng) {
+    load(B, g + 1);
+    consume(A, g);
+    if (g + 2 < ng) load(A, g + 2);
+    consume(B, g + 1);
+    g += 2;
   }
-  for (; r < rows; ++r) {
-    uint4 w = ldg_stream(s + r * 32);
-    if (store) stg_stream(d + r * 32, w);
-    if (kCrc) {
-      S0 = fold_word(S0, rb) ^ w.x; S1 = fold_word(S1, rb) ^ w.y; S2 = fold_word(S2, rb) ^ w.z; S3 = fold_word(S3, rb) ^ w.w;
-    }
+  if (g < ng) consume(A, g);
+  for (uint32_t r = ng * G; r < rows; ++r) {
+    uint4 w = ldg_stream(s + (size_t)r * 32);
+    if (store) stg_stream(d + (size_t)r * 32, w);
+    if (kCrc) APS_FOLD_ROW(w);
   }
   if (!kCrc) return 0;
   // lane words -> one register: t = Z4(Z4(Z4(S0)^S1)^S2)^S3, then shift to the end of the row
@@ -143,29 +156,45 @@ __device__ __forceinline__ uint32_t warp_bytes(const uint8_t* src, uint8_t* dst,
   return warp_xor(gf_mul(r, xpow8(n - hi)));
 }
 
+constexpr uint32_t kMaxTasksPerJob = 128;
+
 struct CopyArgs {
-  const Job* jobs;
+  const Job* jobs;           // kGet == false: jobs prepared by a resolve kernel
+  const aps_get_req* reqs;   // kGet == true: requests, resolved in this kernel
+  Table table;
+  int crc_on;
   uint32_t n_jobs;
-  uint32_t chunks_per_job;  // ceil(max job bytes / kChunkBytes)
-  aps_result* res;          // may be null
-  uint32_t* crc_out;        // for kJobOutCrc
-  uint32_t* partials;       // scratch: n_jobs * chunks_per_job zero-init chunk CRCs
-  uint32_t* done;           // scratch: per-job finished-chunk counters; zero on entry, reset by the finisher
+  uint32_t tasks_per_job;  // a job is cut into this many warp-tasks ...
+  uint32_t rows_per_task;  // ... of this many 512-byte rows (the last one takes what is left)
+  aps_result* res;         // may be null
+  uint32_t* crc_out;       // for kJobOutCrc
+  uint32_t* acc;           // scratch: per-job XOR of the shifted task CRCs; zero on entry, reset by the finisher
+  uint32_t* done;          // scratch: per-job finished-task counters; zero on entry, reset by the finisher
   const CrcTables* tables;
-  uint32_t* slot_crc;
-  unsigned long long* counters;
-  int* error_flag;  // set if the shared-memory window is not where the kernel needs it
+  const uint32_t* rowshift;  // rowshift[k] = x^(8 * 512 * k), k = 0 .. rows of a full page
+  int* error_flag;           // set if the shared-memory window is not where the kernel needs it
 };
 
-// K2 + K3.  Persistent: one CTA per SM, every warp takes chunk-tasks round robin.  A task is one
-// 16 KiB chunk of one job: rows of 512 bytes are loaded and stored 128 bits per lane, and (kCrc)
-// folded into four per-lane CRC words; the warp reduces them to the chunk's zero-init CRC; the warp
-// that finishes the last chunk of a job combines the chunk CRCs (GF(2) shift by the bytes that
-// follow each chunk), applies init/xorout, and verifies or records the page CRC.
-template <bool kCrc>
-__global__ void __launch_bounds__(kCopyThreads, 1) copy_kernel(CopyArgs a) {
+// x^(8 * nbytes) from the per-row table plus (ragged lengths only) the sub-row remainder
+__device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t nbytes) {
+  uint32_t sh = __ldg(&rowshift[nbytes >> 9]);
+  if (nbytes & 511u) sh = gf_mul(sh, xpow8(nbytes & 511u));
+  return sh;
+}
+
+// K2 + K3 (+ K1 lookup when kGet).  Persistent grid: one CTA per SM.  A job (one page request) is
+// cut into tasks_per_job warp-tasks of rows_per_task 512-byte rows, sized by the host so that one
+// round of all warps of the chip covers the batch (no wave quantisation).  A task resolves its
+// page (kGet: eight lanes probe the hash table), streams its rows (128-bit loads and stores per
+// lane, next group in flight while the current one is folded), reduces the four per-lane CRC words
+// to the zero-init CRC of the task, shifts it by the bytes that follow it in the page (GF(2)
+// multiply) and XORs it into the job's accumulator.  The warp that finishes a job's last task
+// applies init/xorout and verifies or records the page CRC.
+template <bool kCrc, int kThreads, int G, bool kGet>
+__global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  constexpr uint32_t nwarps = kThreads / 32;
   if (kCrc) {
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     uint32_t dyn;
@@ -174,63 +203,95 @@ __global__ void __launch_bounds__(kCopyThreads, 1) copy_kernel(CopyArgs a) {
       if (threadIdx.x == 0) *a.error_flag = 1;
       return;
     }
-    for (uint32_t idx = warp; idx < 1024; idx += nwarps) {
-      uint32_t j = idx >> 8, b = idx & 255u;
-      sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, a.tables->fold[j][b]);
+    // each thread fetches one table entry (coalesced); the warp then broadcasts entry by entry and
+    // every lane writes its own replica: no dependent global loads in the loop
+    const uint32_t* gfold = &a.tables->fold[0][0];
+    for (uint32_t e0 = warp * 32; e0 < 1024; e0 += nwarps * 32) {
+      const uint32_t mine = gfold[e0 + lane];
+#pragma unroll
+      for (uint32_t k = 0; k < 32; ++k) {
+        const uint32_t idx = e0 + k, j = idx >> 8, b = idx & 255u;
+        sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine, k));
+      }
     }
-    for (uint32_t idx = threadIdx.x; idx < 1024; idx += blockDim.x) sts_u32(kSmemG + idx * 4u, (&a.tables->z4[0][0])[idx]);
+    for (uint32_t idx = threadIdx.x; idx < 1024; idx += kThreads) sts_u32(kSmemG + idx * 4u, (&a.tables->z4[0][0])[idx]);
     __syncthreads();
   }
   const uint32_t total_warps = gridDim.x * nwarps;
-  const uint32_t n_items = a.n_jobs * a.chunks_per_job;
+  const uint32_t n_items = a.n_jobs * a.tasks_per_job;
+  const uint32_t task_bytes = a.rows_per_task * kRowBytes;
   for (uint32_t item = blockIdx.x * nwarps + warp; item < n_items; item += total_warps) {
-    const uint32_t job = item / a.chunks_per_job, c = item - job * a.chunks_per_job;
-    const Job j = a.jobs[job];
-    const uint32_t off = c * kChunkBytes;
-    if (off >= j.n) continue;
-    const uint32_t len = min(kChunkBytes, j.n - off);
+    const uint32_t job = item / a.tasks_per_job, c = item - job * a.tasks_per_job;
+    Job j;
+    if (kGet) {
+      // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
+      const aps_get_req rq = a.reqs[job];
+      Probe pr{0, 0, 0, 0};
+      if (lane < 8) pr = tile_lookup(a.table, rq.key, lane, 0);
+      __syncwarp();
+      const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
+      int32_t status = 0;
+      j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
+      if (!meta) {
+        status = -APS_ENOTFOUND;
+      } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
+        status = -APS_EINVAL;
+      } else {
+        const uint32_t plen = meta_len(meta);
+        j.slot = meta_slot(meta);
+        j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
+        j.src = a.table.slab + (uint64_t)j.slot * a.table.page_size + rq.page_off;
+        j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
+        status = (int32_t)j.n;
+      }
+      if (c == 0 && lane == 0) {
+        atomicAdd(&a.table.counters[kCtrLookups], 1ull);
+        atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
+        if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
+        if (!kCrc || j.n == 0) a.res[job] = aps_result{status, 0};  // otherwise the finisher reports
+      }
+    } else {
+      j = a.jobs[job];
+    }
+    const uint64_t off64 = (uint64_t)c * task_bytes;
+    if (off64 >= j.n) continue;
+    const uint32_t off = (uint32_t)off64;
+    const uint32_t len = min(task_bytes, j.n - off);
     const uint8_t* src = j.src + off;
     uint8_t* dst = j.dst ? j.dst + off : nullptr;
     const bool aligned = (((uintptr_t)src | (uintptr_t)dst) & 15u) == 0;
     const uint32_t rows = aligned ? len / kRowBytes : 0;
     const uint32_t tail = len - rows * kRowBytes;
     uint32_t crc = 0;
-    if (rows) crc = warp_rows<kCrc>(src, dst, rows, lane);
+    if (rows) crc = warp_rows<kCrc, G>(src, dst, rows, lane);
     if (tail) {
       uint32_t ct = warp_bytes<kCrc>(src + rows * kRowBytes, dst ? dst + rows * kRowBytes : nullptr, tail, lane);
       if (kCrc) crc = rows ? (gf_mul(crc, xpow8(tail)) ^ ct) : ct;
     }
     if (!kCrc) continue;
-    const uint32_t nchunks = (j.n + kChunkBytes - 1) / kChunkBytes;
+    // shift the task CRC to the end of the job and fold it into the job's accumulator
+    const uint32_t contrib = gf_mul(crc, shift_for(a.rowshift, j.n - (off + len)));
+    const uint32_t ntasks = (j.n + task_bytes - 1) / task_bytes;
     uint32_t prev = 0;
     if (lane == 0) {
-      a.partials[item] = crc;
+      atomicXor(&a.acc[job], contrib);
       __threadfence();
       prev = atomicAdd(&a.done[job], 1u);
     }
     prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
-    if (prev != nchunks - 1) continue;
-    // last chunk of this job: combine
-    __threadfence();
-    uint32_t acc = 0;
-    for (uint32_t base = 0; base < nchunks; base += 32) {
-      uint32_t jj = base + lane;
-      if (jj < nchunks) {
-        uint32_t p = __ldcg(&a.partials[job * a.chunks_per_job + jj]);
-        uint32_t end = min(j.n, (jj + 1) * kChunkBytes);
-        acc ^= gf_mul(p, xpow8(j.n - end));
-      }
-    }
-    acc = warp_xor(acc);
-    if (lane == 0) {
-      uint32_t full = acc ^ gf_mul(0xFFFFFFFFu, xpow8(j.n)) ^ 0xFFFFFFFFu;
-      if (j.flags & kJobRecord) a.slot_crc[j.slot] = full;
-      if (a.res) a.res[job].crc = full;
+    if (prev != ntasks - 1) continue;
+    if (lane == 0) {  // last task of this job
+      __threadfence();
+      const uint32_t x = atomicExch(&a.acc[job], 0u);
+      const uint32_t full = x ^ gf_mul(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
+      bool corrupt = false;
+      if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
       if (j.flags & kJobOutCrc) a.crc_out[job] = full;
-      if ((j.flags & kJobVerify) && a.slot_crc[j.slot] != full) {
-        if (a.res) a.res[job].len = -APS_ECORRUPT;
-        atomicAdd(&a.counters[kCtrCrcMismatch], 1ull);
+      if ((j.flags & kJobVerify) && a.table.slot_crc[j.slot] != full) {
+        corrupt = true;
+        atomicAdd(&a.table.counters[kCtrCrcMismatch], 1ull);
       }
+      if (a.res) a.res[job] = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
       a.done[job] = 0;
     }
   }
@@ -239,38 +300,6 @@ __global__ void __launch_bounds__(kCopyThreads, 1) copy_kernel(CopyArgs a) {
 // ------------------------------------------------------------------------------------------------
 // K1 kernels: eight lanes per request.
 // ------------------------------------------------------------------------------------------------
-__global__ void get_resolve_kernel(Table t, const aps_get_req* reqs, uint32_t n, Job* jobs, aps_result* res, int crc_on) {
-  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
-  if (i >= n) return;
-  const aps_get_req rq = reqs[i];
-  Probe pr = tile_lookup(t, rq.key, sub, tshift);
-  if (sub) return;
-  atomicAdd(&t.counters[kCtrLookups], 1ull);
-  atomicAdd(&t.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
-  Job jb{nullptr, nullptr, 0, 0, 0, 0};
-  aps_result rs{0, 0};
-  if (!pr.meta) {
-    rs.len = -APS_ENOTFOUND;
-  } else {
-    const uint32_t len = meta_len(pr.meta), slot = meta_slot(pr.meta);
-    if (rq.page_off > len) {  // LocalPageStore.java:99-100
-      rs.len = -APS_EINVAL;
-    } else {
-      const uint32_t nb = min(len - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
-      jb.src = t.slab + (uint64_t)slot * t.page_size + rq.page_off;
-      jb.dst = (uint8_t*)rq.dst;
-      jb.n = nb;
-      jb.slot = slot;
-      jb.flags = (crc_on && rq.page_off == 0 && nb == len && len > 0) ? kJobVerify : 0u;
-      rs.len = (int32_t)nb;
-      atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)nb);
-    }
-  }
-  jobs[i] = jb;
-  res[i] = rs;
-}
-
 __global__ void put_resolve_kernel(Table t, const aps_put_req* reqs, uint32_t n, Job* jobs, aps_result* res, int crc_on) {
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;

@@ -185,11 +185,17 @@ def run_ours(args):
     while resident * PAGE + (6 << 30) > free_b and resident > 1024:
         resident //= 2  # a smaller GPU slice: stated in config.workload
     cfg = capi.aps_config(device=local_rank, page_size=PAGE, cache_bytes=resident * PAGE, slab_slots=resident,
-                          table_capacity=0, max_batch=BATCH, flags=capi.APS_FLAG_CRC)
+                          table_capacity=0, max_batch=BATCH,
+                          flags=0 if os.environ.get("APS_BENCH_NOCRC") == "1" else capi.APS_FLAG_CRC)
+    with_crc = cfg.flags != 0
     h = C.c_void_p()
     capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "aps_open")
-    stream = torch.cuda.current_stream(dev)
+    # one explicit non-default stream for everything: torch copies, our kernels and the timing events
+    # (a NULL aps_stream would mean "the store's own stream", which torch events cannot see)
+    stream = torch.cuda.Stream(dev)
+    torch.cuda.set_stream(stream)
     sp = C.c_void_p(stream.cuda_stream)
+    assert sp.value, "need a real stream handle"
 
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from gpu_util import GET_REQ, PUT_REQ, RESULT
@@ -222,7 +228,8 @@ def run_ours(args):
     from oracle import binding as orc
     for i in (0, 1, 255):
         want = orc.crc32c(orc.fill_page(DATA_SEED, file_base + i // 1024, i % 1024, PAGE))
-        assert int(first_put_res[i]["crc"]) == want and int(first_put_res[i]["len"]) == PAGE, "put CRC differs from oracle"
+        assert (not with_crc or int(first_put_res[i]["crc"]) == want) and int(first_put_res[i]["len"]) == PAGE, \
+            "put CRC differs from oracle"
 
     # ---- request pool: uniform random page ids, seed 2 + rank
     rng = np.random.default_rng(2 + rank)
@@ -249,7 +256,8 @@ def run_ours(args):
     for i in (0, 17, 255):
         p = int(picks[k_last, i])
         page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
-        assert int(res[i]["len"]) == PAGE and int(res[i]["crc"]) == orc.crc32c(page), "get CRC differs from oracle"
+        assert int(res[i]["len"]) == PAGE and (not with_crc or int(res[i]["crc"]) == orc.crc32c(page)), \
+            "get CRC differs from oracle"
         assert np.array_equal(dst[i * PAGE:(i + 1) * PAGE].cpu().numpy(), page), "get bytes differ from oracle"
 
     sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None))
@@ -281,7 +289,8 @@ def run_ours(args):
         ms_total = float(t.item())
 
     # ---- end to end: host request arrays, pinned host destinations, results read back
-    e2e_steps = max(1, min(K, 100))
+    quick = os.environ.get("APS_BENCH_QUICK") == "1"  # kernel sweeps: skip the slow PCIe and CPU legs
+    e2e_steps = 2 if quick else max(1, min(K, 100))
     pinned = torch.empty(BATCH * PAGE, dtype=torch.uint8).pin_memory()
     h_reqs = reqs.copy()
     h_reqs["dst"] = pinned.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
@@ -294,7 +303,8 @@ def run_ours(args):
         step_host(k)
     p = int(picks[2 % pool, 5])
     page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
-    assert np.array_equal(pinned.numpy()[5 * PAGE:6 * PAGE], page) and int(h_res[5]["crc"]) == orc.crc32c(page)
+    assert np.array_equal(pinned.numpy()[5 * PAGE:6 * PAGE], page)
+    assert not with_crc or int(h_res[5]["crc"]) == orc.crc32c(page)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
@@ -345,7 +355,7 @@ def run_ours(args):
 
     # ---- CPU baseline on a bounded sample (rank 0, N = 1 only)
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and not quick:
         orc.build()
         threads = os.cpu_count() or 1
         gbps_c, _, desc = cpu_reference_run(steps=int(os.environ.get("APS_CPU_STEPS", "40")), warmup=2, threads=threads)
@@ -381,6 +391,7 @@ def run_ours(args):
                 "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
                 "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound)"},
         "gpu_launches": int(launches), "clocks": clocks, "aux": aux,
+        "copy_variant": os.environ.get("APS_COPY_VARIANT", "default") + ("" if with_crc else " NOCRC"),
         "table": {"lookups": int(stats.lookups), "probe_buckets": int(stats.probe_buckets)},
     }
     if cpu is not None:

@@ -24,3 +24,20 @@ def increasing(start_or_len, length=None):
 @pytest.fixture
 def inc():
     return increasing
+
+
+@pytest.fixture(autouse=True)
+def _gpu_stream(request):
+    """GPU tests run torch ops and libaps kernels on ONE non-default stream, so they are ordered
+    (libaps treats a NULL stream as "the store's own stream", which torch's default stream does
+    not synchronise with)."""
+    if request.node.get_closest_marker("gpu") is None:
+        yield
+        return
+    import torch
+    s = torch.cuda.Stream()
+    prev = torch.cuda.current_stream()
+    torch.cuda.set_stream(s)
+    yield
+    torch.cuda.synchronize()
+    torch.cuda.set_stream(prev)

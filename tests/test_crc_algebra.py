@@ -11,7 +11,7 @@ from alluxio_b200 import capi
 from oracle import binding as orc
 
 POLY = 0x82F63B78
-CHUNK, ROW = 16384, 512
+CHUNK, ROW = 16384, 512  # CHUNK only sizes the test inputs
 
 
 def gf_mul(a, b):
@@ -83,25 +83,25 @@ def warp_bytes(data, consts):
     return acc
 
 
-def kernel_crc(data, consts, aligned=True):
-    """copy_kernel<true> for one job of len(data) bytes."""
+def kernel_crc(data, consts, aligned=True, rows_per_task=32):
+    """copy_kernel<true> for one job of len(data) bytes cut into tasks of rows_per_task rows: every
+    task CRC is shifted by the bytes that follow it (x^(8*after)) and XORed into the accumulator; the
+    finisher adds init/xorout."""
     xp = consts[2]
     n = data.size
-    nchunks = (n + CHUNK - 1) // CHUNK
-    partials = []
-    for c in range(nchunks):
-        chunk = data[c * CHUNK:min(n, (c + 1) * CHUNK)]
-        rows = chunk.size // ROW if aligned else 0
-        tail = chunk.size - rows * ROW
-        crc = warp_rows(chunk, consts) if rows else 0
-        if tail:
-            ct = warp_bytes(chunk[rows * ROW:], consts)
-            crc = (gf_mul(crc, xpow8(tail, xp)) ^ ct) if rows else ct
-        partials.append(crc)
+    task_bytes = rows_per_task * ROW
+    ntasks = (n + task_bytes - 1) // task_bytes
     acc = 0
-    for j, p in enumerate(partials):
-        end = min(n, (j + 1) * CHUNK)
-        acc ^= gf_mul(p, xpow8(n - end, xp))
+    for c in range(ntasks):
+        task = data[c * task_bytes:min(n, (c + 1) * task_bytes)]
+        rows = task.size // ROW if aligned else 0
+        tail = task.size - rows * ROW
+        crc = warp_rows(task, consts) if rows else 0
+        if tail:
+            ct = warp_bytes(task[rows * ROW:], consts)
+            crc = (gf_mul(crc, xpow8(tail, xp)) ^ ct) if rows else ct
+        after = n - min(n, (c + 1) * task_bytes)
+        acc ^= gf_mul(crc, xpow8(after, xp))
     return acc ^ gf_mul(0xFFFFFFFF, xpow8(n, xp)) ^ 0xFFFFFFFF
 
 
@@ -129,6 +129,14 @@ def test_kernel_arithmetic_matches_oracle(consts, n):
     rng = np.random.default_rng(n)
     data = rng.integers(0, 256, n, dtype=np.uint8)
     assert kernel_crc(data, consts) == orc.crc32c(data)
+
+
+def test_task_partitions_do_not_change_the_result(consts):
+    rng = np.random.default_rng(77)
+    data = rng.integers(0, 256, 100000, dtype=np.uint8)
+    want = orc.crc32c(data)
+    for rpt in (1, 7, 114, 228, 4096):
+        assert kernel_crc(data, consts, rows_per_task=rpt) == want
 
 
 def test_unaligned_path_matches_oracle(consts):

@@ -168,7 +168,9 @@ def test_host_array_batch_forms_with_pinned_memory():
     pinned_src = torch.from_numpy(rng.integers(0, 256, n * ps, dtype=np.uint8)).pin_memory()
     pids = [PageId("abc/def", i) for i in range(n)]
     lens = [ps if i % 4 else ps - 100 - i for i in range(n)]
-    res = store.put_batch([(pids[i], lens[i], pinned_src.data_ptr() + i * ps) for i in range(n)])
+    from gpu_util import cur_stream
+    torch.cuda.synchronize()
+    res = store.put_batch([(pids[i], lens[i], pinned_src.data_ptr() + i * ps) for i in range(n)], cur_stream())
     src_np = pinned_src.numpy()
     assert [r[0] for r in res] == lens
     assert [r[1] for r in res] == [orc.crc32c(src_np[i * ps:i * ps + lens[i]]) for i in range(n)]
@@ -176,7 +178,7 @@ def test_host_array_batch_forms_with_pinned_memory():
     with pytest.raises(capi.ApsError):
         store.put_batch([(pids[0], 1, pinned_src.data_ptr()), (pids[0], 1, pinned_src.data_ptr())])
     pinned_dst = torch.zeros(n * ps, dtype=torch.uint8).pin_memory()
-    res = store.get_batch([(pids[i], 0, ps, pinned_dst.data_ptr() + i * ps) for i in range(n)])
+    res = store.get_batch([(pids[i], 0, ps, pinned_dst.data_ptr() + i * ps) for i in range(n)], cur_stream())
     dst_np = pinned_dst.numpy()
     for i in range(n):
         assert res[i][0] == lens[i]

@@ -23,6 +23,7 @@ def md5_many(blobs, misalign=0):
     for o, b in zip(offs, blobs):
         host[o:o + len(b)] = np.frombuffer(b, np.uint8)
     dev = torch.from_numpy(host).cuda()
+    torch.cuda.synchronize()
     ptrs = (__import__("ctypes").c_void_p * n)(*[dev.data_ptr() + o for o in offs])
     lens = (__import__("ctypes").c_uint64 * n)(*[len(b) for b in blobs])
     out = (__import__("ctypes").c_uint8 * (16 * n))()
@@ -64,7 +65,8 @@ def test_many_files_of_synthetic_pages():
     ptrs = torch.tensor([buf.data_ptr() + i * flen for i in range(n)], dtype=torch.int64, device="cuda:0")
     d_len = torch.tensor(lens, dtype=torch.int64, device="cuda:0")
     d_out = torch.zeros(n * 16, dtype=torch.uint8, device="cuda:0")
-    capi.check(capi.lib().aps_md5_batch_dev(0, n, ptrs.data_ptr(), d_len.data_ptr(), d_out.data_ptr(), None))
+    from gpu_util import cur_stream
+    capi.check(capi.lib().aps_md5_batch_dev(0, n, ptrs.data_ptr(), d_len.data_ptr(), d_out.data_ptr(), cur_stream()))
     torch.cuda.synchronize()
     out = d_out.cpu().numpy().reshape(n, 16)
     host = buf.cpu().numpy()
