@@ -39,7 +39,7 @@ class aps_result(C.Structure):
 
 class aps_stats_t(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("pages", "bytes", "slots_free", "table_capacity", "tombstones", "lookups",
-                                           "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches")]
+                                           "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches", "slow_sms")]
 
 
 ITER_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(aps_key), C.c_uint32)
@@ -70,6 +70,7 @@ SIGNATURES = {
     "aps_profile_begin": (C.c_int, [_vp, _u32]),
     "aps_profile_end": (C.c_int, [_vp, C.POINTER(C.c_double), C.POINTER(_u32)]),
     "aps_debug_corrupt": (C.c_int, [_vp, C.POINTER(aps_key), _u32]),
+    "aps_debug_timeline": (C.c_int, [_vp, C.c_int, _vp, _u32]),
     "aps_debug_crc_constants": (C.c_int, [_vp, _vp, _vp, _vp]),
     "aps_strerror": (C.c_char_p, [C.c_int]),
     "aps_last_cuda_error": (C.c_char_p, []),

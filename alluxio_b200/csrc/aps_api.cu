@@ -2,6 +2,7 @@
 // buffers of one store, stages request arrays, launches the kernels in aps_kernels.cuh.
 // There is NO CPU fallback: every data-path entry point needs a CUDA device and fails with APS_ECUDA
 // when the runtime cannot provide one.
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -56,6 +57,10 @@ struct DeviceConsts {
   bool ready = false;
   CrcTables* d_tables = nullptr;
   int num_sms = 0;
+  // SM speed classes (see calibrate_sms): d_sm_slow[smid] = 1 for SMs that stream measurably slower
+  uint8_t* d_sm_slow = nullptr;
+  int n_slow = 0;
+  bool calibrated = false;
 };
 std::mutex g_dev_mu;
 DeviceConsts g_dev[64];
@@ -72,8 +77,8 @@ struct CopyVariant {
   {#T "x" #G, T, copy_kernel<true, T, G, false>, copy_kernel<false, T, G, false>, copy_kernel<true, T, G, true>, \
    copy_kernel<false, T, G, true>}
 const CopyVariant kCopyVariants[] = {
-    APS_VARIANT(512, 4), APS_VARIANT(1024, 4), APS_VARIANT(1024, 2), APS_VARIANT(768, 4),
-    APS_VARIANT(512, 8), APS_VARIANT(512, 2),  APS_VARIANT(640, 4),  APS_VARIANT(384, 8),
+    APS_VARIANT(512, 4), APS_VARIANT(1024, 4), APS_VARIANT(1024, 2), APS_VARIANT(512, 8),
+    APS_VARIANT(512, 2), APS_VARIANT(256, 8),
 };
 #undef APS_VARIANT
 const CopyVariant& copy_variant() {
@@ -87,6 +92,8 @@ const CopyVariant& copy_variant() {
   }();
   return *v;
 }
+
+constexpr size_t kTimelineWords = 1024 + 256 * 32 + 256;  // 256 CTAs x 4 stamps, 256 x 32 warp end stamps, 256 SM ids
 
 struct HostCrcConsts {
   CrcTables tables;
@@ -127,6 +134,8 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
       CUDA_TRY(cudaFuncSetAttribute(v.get_crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
     }
     CUDA_TRY(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    CUDA_TRY(cudaMalloc(&d.d_sm_slow, 256));
+    CUDA_TRY(cudaMemset(d.d_sm_slow, 0, 256));
     d.ready = true;
   }
   *out = &d;
@@ -154,6 +163,8 @@ struct aps_store {
   Job* d_jobs = nullptr;
   uint32_t* d_acc = nullptr;
   uint32_t* d_rowshift = nullptr;  // x^(8*512*k) for k = 0 .. page_rows
+  unsigned long long* d_timeline = nullptr;  // aps_debug_timeline
+  uint32_t* d_sched = nullptr;               // CTA rank counters of the copy kernel (self-resetting)
   uint32_t* d_done = nullptr;
   int* d_error = nullptr;
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
@@ -161,6 +172,8 @@ struct aps_store {
   uint8_t* h_stage = nullptr;   // pinned: requests, then results
   uint8_t* h_bounce = nullptr;  // pinned: one page, for pageable single-page callers
   uint32_t faults = 0;
+  bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
+  bool use_steal = true;  // APS_NO_STEAL=1 turns intra-CTA work stealing off
   std::atomic<uint64_t> launches{0};
   // optional timing of the copy kernel (aps_profile_*): event pairs recorded around each launch
   bool prof_on = false;
@@ -182,7 +195,9 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   const uint32_t warps_per_block = v.threads / 32;
   const uint32_t chip_warps = (uint32_t)s->dc->num_sms * warps_per_block;
   // cut every job into equal warp-tasks so that one round of the persistent grid covers the batch
-  uint32_t tpj = std::max(1u, chip_warps / n);
+  // ... leaving one warp-slot free per slow SM, so that the CTAs on those SMs get one task less
+  const uint32_t usable = chip_warps > (uint32_t)s->dc->n_slow + n ? chip_warps - (uint32_t)s->dc->n_slow : chip_warps;
+  uint32_t tpj = std::max(1u, usable / n);
   tpj = std::min(tpj, std::min(kMaxTasksPerJob, std::max(1u, s->page_rows / 8)));
   const uint32_t rpt = (s->page_rows + tpj - 1) / tpj;
   tpj = (s->page_rows + rpt - 1) / rpt;
@@ -201,17 +216,31 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.tables = s->dc->d_tables;
   a.rowshift = s->d_rowshift;
   a.error_flag = s->d_error;
+  a.timeline = s->d_timeline;
+  a.steal = s->use_steal ? 1 : 0;
+  a.sched = s->d_sched;
+  a.sm_slow = s->dc->d_sm_slow;
+  if (s->d_timeline) CUDA_TRY(cudaMemsetAsync(s->d_timeline, 0xFF, kTimelineWords * sizeof(unsigned long long), st));
   const uint64_t items = (uint64_t)n * tpj;
-  uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, (items + warps_per_block - 1) / warps_per_block);
+  uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, items);  // every SM takes part
   if (grid == 0) grid = 1;
   const bool timed = s->prof_on && s->prof_used + 2 <= s->prof_events.size();
   if (timed) CUDA_TRY(cudaEventRecord(s->prof_events[s->prof_used], st));
-  if (d_get_reqs) {
-    if (crc) v.get_crc<<<grid, v.threads, kCopyDynSmem, st>>>(a);
-    else v.get_plain<<<grid, v.threads, 0, st>>>(a);
-  } else {
-    if (crc) v.crc<<<grid, v.threads, kCopyDynSmem, st>>>(a);
-    else v.plain<<<grid, v.threads, 0, st>>>(a);
+  {
+    // Programmatic dependent launch: back-to-back copy kernels overlap launch latency; each kernel
+    // still waits (griddepcontrol.wait) for all earlier work before it touches any data.
+    CopyKernelFn fn = d_get_reqs ? (crc ? v.get_crc : v.get_plain) : (crc ? v.crc : v.plain);
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(v.threads);
+    lc.dynamicSmemBytes = crc ? kCopyDynSmem : 0;
+    lc.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = s->use_pdl ? 1 : 0;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&lc, fn, a));
   }
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
@@ -269,6 +298,8 @@ void free_store(aps_store* s) {
   cudaFree(s->d_jobs);
   cudaFree(s->d_acc);
   cudaFree(s->d_rowshift);
+  cudaFree(s->d_timeline);
+  cudaFree(s->d_sched);
   cudaFree(s->d_done);
   cudaFree(s->d_error);
   cudaFree(s->d_reqs);
@@ -278,6 +309,77 @@ void free_store(aps_store* s) {
   if (s->h_stage) cudaFreeHost(s->h_stage);
   if (s->h_bounce) cudaFreeHost(s->h_bounce);
   if (s->stream) cudaStreamDestroy(s->stream);
+}
+
+// SM speed classes.  On a saturated memory system equal streams do not finish together: some SMs
+// (larger GPCs share one path to L2) are consistently a few percent slower.  Measured once per
+// device: copy a dummy batch inside the still empty slab a few times with per-CTA time stamps, and
+// mark the SMs whose CTAs end later than the median by more than 2.5 % of the kernel time.  The copy
+// kernel then deals the surplus tasks to the other SMs (see copy_kernel's rank logic).
+int calibrate_sms(aps_store* s) {
+  DeviceConsts* dc = s->dc;
+  if (dc->calibrated || getenv("APS_NO_SMWEIGHT")) return APS_OK;
+  const uint64_t n64 = std::min<uint64_t>(std::min<uint64_t>(s->cfg.max_batch, 256), s->slots / 2);
+  if (n64 * s->cfg.page_size < (64ull << 20)) return APS_OK;  // too small to say anything; all SMs equal
+  const uint32_t n = (uint32_t)n64;
+  std::vector<Job> jobs(n);
+  for (uint32_t i = 0; i < n; ++i)
+    jobs[i] = Job{s->table.slab + (uint64_t)i * s->cfg.page_size, s->table.slab + (uint64_t)(n + i) * s->cfg.page_size,
+                  s->cfg.page_size, 0, 0, 0};
+  CUDA_TRY(cudaMemcpy(s->d_jobs, jobs.data(), n * sizeof(Job), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMalloc(&s->d_timeline, kTimelineWords * sizeof(unsigned long long)));
+  std::vector<unsigned long long> tl(kTimelineWords);
+  std::vector<double> offset(256, 0.0);
+  std::vector<int> seen(256, 0);
+  double dur_sum = 0;
+  const int kWarm = 2, kRuns = 4;
+  int rc = APS_OK;
+  for (int run = 0; run < kWarm + kRuns && rc == APS_OK; ++run) {
+    rc = launch_copy(s, n, nullptr, nullptr, nullptr, s->stream);
+    if (rc != APS_OK) break;
+    if (cudaStreamSynchronize(s->stream) != cudaSuccess ||
+        cudaMemcpy(tl.data(), s->d_timeline, kTimelineWords * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) {
+      rc = APS_ECUDA;
+      break;
+    }
+    if (run < kWarm) continue;
+    std::vector<std::pair<unsigned, double>> ends;
+    unsigned long long t0 = ~0ull;
+    for (int c = 0; c < 256; ++c)
+      if (tl[c * 4] != ~0ull) t0 = std::min(t0, tl[c * 4]);
+    for (int c = 0; c < 256; ++c)
+      if (tl[c * 4] != ~0ull && tl[c * 4 + 3] != ~0ull)
+        ends.push_back({(unsigned)(tl[1024 + 256 * 32 + c] & 255u), (double)(tl[c * 4 + 3] - t0)});
+    if (ends.size() < 8) continue;
+    std::vector<double> v;
+    for (auto& e : ends) v.push_back(e.second);
+    std::nth_element(v.begin(), v.begin() + v.size() / 2, v.end());
+    const double med = v[v.size() / 2];
+    dur_sum += med;
+    for (auto& e : ends) {
+      offset[e.first] += e.second - med;
+      seen[e.first]++;
+    }
+  }
+  cudaFree(s->d_timeline);
+  s->d_timeline = nullptr;
+  if (rc != APS_OK) return rc;
+  const double dur = dur_sum / kRuns;
+  std::vector<uint8_t> slow(256, 0);
+  int n_slow = 0;
+  for (int i = 0; i < 256; ++i)
+    if (seen[i] == kRuns && offset[i] / kRuns > 0.025 * dur) {
+      slow[i] = 1;
+      ++n_slow;
+    }
+  if (n_slow > dc->num_sms / 2) {  // not a few stragglers but a bimodal chip: leave the plain split
+    std::fill(slow.begin(), slow.end(), 0);
+    n_slow = 0;
+  }
+  CUDA_TRY(cudaMemcpy(dc->d_sm_slow, slow.data(), 256, cudaMemcpyHostToDevice));
+  dc->n_slow = n_slow;
+  dc->calibrated = true;
+  return APS_OK;
 }
 
 __global__ void corrupt_kernel(Table t, aps_key key, uint32_t off, int* found) {
@@ -341,6 +443,8 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   if (!s) return APS_ENOMEM;
   s->cfg = *cfg;
   s->dc = dc;
+  s->use_pdl = getenv("APS_NO_PDL") == nullptr;
+  s->use_steal = getenv("APS_NO_STEAL") == nullptr;
   uint64_t slots = cfg->slab_slots;
   if (slots == 0) {
     uint64_t base = (cfg->cache_bytes + cfg->page_size - 1) / cfg->page_size;
@@ -376,6 +480,8 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaMalloc(&s->table.counters, kNumCounters * sizeof(unsigned long long)));
   OPEN_TRY(cudaMalloc(&s->d_jobs, (uint64_t)mb * sizeof(Job)));
   OPEN_TRY(cudaMalloc(&s->d_acc, (uint64_t)mb * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->d_sched, 4 * sizeof(uint32_t)));
+  OPEN_TRY(cudaMemset(s->d_sched, 0, 4 * sizeof(uint32_t)));
   {
     std::vector<uint32_t> rs(s->page_rows + 1);
     const uint32_t xrow = host_xpow8(kRowBytes);
@@ -405,6 +511,15 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaGetLastError());
   OPEN_TRY(cudaStreamSynchronize(s->stream));
 #undef OPEN_TRY
+  {
+    std::lock_guard<std::mutex> lk(g_dev_mu);
+    int crc_rc = calibrate_sms(s);
+    if (crc_rc != APS_OK) {
+      free_store(s);
+      delete s;
+      return crc_rc;
+    }
+  }
   *out = s;
   return APS_OK;
 }
@@ -681,6 +796,7 @@ int aps_stats(aps_store* s, aps_stats_t* out) {
   out->bytes_copied = c[kCtrBytesCopied];
   out->crc_mismatches = c[kCtrCrcMismatch];
   out->kernel_launches = s->launches.load();
+  out->slow_sms = (uint64_t)s->dc->n_slow;
   return APS_OK;
 }
 
@@ -715,6 +831,25 @@ int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_launches
   if (copy_ms_total) *copy_ms_total = total;
   if (copy_launches) *copy_launches = (uint32_t)(s->prof_used / 2);
   s->prof_used = 0;
+  return APS_OK;
+}
+
+int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_ctas) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  if (enable && !s->d_timeline) CUDA_TRY(cudaMalloc(&s->d_timeline, kTimelineWords * sizeof(unsigned long long)));
+  if (out && s->d_timeline) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpy(out, s->d_timeline, std::min<size_t>(max_ctas, kTimelineWords) * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  }
+  if (!enable && s->d_timeline) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    cudaFree(s->d_timeline);
+  cudaFree(s->d_sched);
+    s->d_timeline = nullptr;
+  }
   return APS_OK;
 }
 

@@ -93,47 +93,80 @@ __device__ __forceinline__ uint32_t warp_xor(uint32_t v) {
     S2 = fold_word(S2, rb) ^ (v_).z; S3 = fold_word(S3, rb) ^ (v_).w;     \
   } while (0)
 
-// Aligned fast path: `rows` 512-byte rows, 16 bytes per lane per row.  Software pipelined: while the
-// G rows of one group are stored and folded, the loads of the next group are already in flight.
-// Returns the zero-init CRC of the rows (same value in every lane) when kCrc.
+// ---- row ranges shared inside a CTA ------------------------------------------------------------
+// Every warp publishes the rows it still has to do in one 64-bit shared-memory word:
+//   bits  0..31  next unclaimed row (relative to the job)
+//   bits 32..59  end row (exclusive)
+//   bits 60..63  generation (bumped whenever the warp installs a new range)
+// The owner claims G rows at a time with an atomic add on the low half; a warp that has run out of
+// work takes the back half of the largest remaining range with a compare-and-swap on the whole word.
+// Both are atomics on the same word, so a row is processed exactly once.
+constexpr uint32_t kStealMinGroups = 2;  // do not split ranges shorter than this many groups
+
+__device__ __forceinline__ unsigned long long range_pack(uint32_t lo, uint32_t hi, uint32_t gen) {
+  return (unsigned long long)lo | ((unsigned long long)(hi & 0x0FFFFFFFu) << 32) | ((unsigned long long)(gen & 15u) << 60);
+}
+__device__ __forceinline__ uint32_t range_lo(unsigned long long w) { return (uint32_t)w; }
+__device__ __forceinline__ uint32_t range_hi(unsigned long long w) { return (uint32_t)(w >> 32) & 0x0FFFFFFFu; }
+__device__ __forceinline__ uint32_t range_gen(unsigned long long w) { return (uint32_t)(w >> 60); }
+
+struct Claim {
+  uint32_t pos, cnt;
+};
+template <int G>
+__device__ __forceinline__ Claim claim_rows(unsigned long long* range, uint32_t lane) {
+  unsigned long long old = 0;
+  if (lane == 0) old = atomicAdd(range, (unsigned long long)G);
+  old = __shfl_sync(0xFFFFFFFFu, old, 0);
+  const uint32_t pos = range_lo(old), hi = range_hi(old);
+  return Claim{pos, pos < hi ? min((uint32_t)G, hi - pos) : 0u};
+}
+
+// Aligned fast path: streams the rows this warp can claim from *range (512-byte rows, 16 bytes per
+// lane per row).  Software pipelined: while the rows of one group are stored and folded, the loads of
+// the next claimed group are already in flight.  Returns the zero-init CRC of the rows it processed
+// (same value in every lane, when kCrc); *row_end receives the first row it did NOT process.
 template <bool kCrc, int G>
-__device__ __forceinline__ uint32_t warp_rows(const uint8_t* src, uint8_t* dst, uint32_t rows, uint32_t lane) {
-  const uint4* s = reinterpret_cast<const uint4*>(src) + lane;
+__device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst, unsigned long long* range, uint32_t row_lo,
+                                                uint32_t lane, uint32_t* row_end) {
+  const uint4* s = reinterpret_cast<const uint4*>(src) + lane;  // src/dst point at row 0 of the job
   uint4* d = reinterpret_cast<uint4*>(dst) + lane;
   const bool store = dst != nullptr;
   const uint32_t rb = 0x00010000u | (lane << 2);
   uint32_t S0 = 0, S1 = 0, S2 = 0, S3 = 0;
-  const uint32_t ng = rows / G;
   uint4 A[G], B[G];
-  auto load = [&](uint4(&buf)[G], uint32_t g) {
+  auto load = [&](uint4(&buf)[G], const Claim& c) {
 #pragma unroll
-    for (int u = 0; u < G; ++u) buf[u] = ldg_stream(s + (size_t)(g * G + u) * 32);
+    for (int u = 0; u < G; ++u)
+      if ((uint32_t)u < c.cnt) buf[u] = ldg_stream(s + (size_t)(c.pos + u) * 32);
   };
-  auto consume = [&](uint4(&buf)[G], uint32_t g) {
+  auto consume = [&](uint4(&buf)[G], const Claim& c) {
     if (store) {
 #pragma unroll
-      for (int u = 0; u < G; ++u) stg_stream(d + (size_t)(g * G + u) * 32, buf[u]);
+      for (int u = 0; u < G; ++u)
+        if ((uint32_t)u < c.cnt) stg_stream(d + (size_t)(c.pos + u) * 32, buf[u]);
     }
     if (kCrc) {
 #pragma unroll
-      for (int u = 0; u < G; ++u) APS_FOLD_ROW(buf[u]);
+      for (int u = 0; u < G; ++u)
+        if ((uint32_t)u < c.cnt) APS_FOLD_ROW(buf[u]);
     }
   };
-  uint32_t g = 0;
-  if (ng) load(A, 0);
-  while (g + 2 <= ng) {
-    load(B, g + 1);
-    consume(A, g);
-    if (g + 2 < ng) load(A, g + 2);
-    consume(B, g + 1);
-    g += 2;
+  uint32_t end = row_lo;
+  Claim ca = claim_rows<G>(range, lane);
+  load(A, ca);
+  while (ca.cnt) {
+    Claim cb = claim_rows<G>(range, lane);
+    load(B, cb);
+    consume(A, ca);
+    end = ca.pos + ca.cnt;
+    if (!cb.cnt) break;
+    ca = claim_rows<G>(range, lane);
+    load(A, ca);
+    consume(B, cb);
+    end = cb.pos + cb.cnt;
   }
-  if (g < ng) consume(A, g);
-  for (uint32_t r = ng * G; r < rows; ++r) {
-    uint4 w = ldg_stream(s + (size_t)r * 32);
-    if (store) stg_stream(d + (size_t)r * 32, w);
-    if (kCrc) APS_FOLD_ROW(w);
-  }
+  *row_end = end;
   if (!kCrc) return 0;
   // lane words -> one register: t = Z4(Z4(Z4(S0)^S1)^S2)^S3, then shift to the end of the row
   uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
@@ -168,12 +201,22 @@ struct CopyArgs {
   uint32_t rows_per_task;  // ... of this many 512-byte rows (the last one takes what is left)
   aps_result* res;         // may be null
   uint32_t* crc_out;       // for kJobOutCrc
-  uint32_t* acc;           // scratch: per-job XOR of the shifted task CRCs; zero on entry, reset by the finisher
-  uint32_t* done;          // scratch: per-job finished-task counters; zero on entry, reset by the finisher
+  uint32_t* acc;           // scratch: per-job XOR of the shifted segment CRCs; zero on entry, reset by the finisher
+  uint32_t* done;          // scratch: per-job count of finished 512-byte rows; zero on entry, reset by the finisher
   const CrcTables* tables;
   const uint32_t* rowshift;  // rowshift[k] = x^(8 * 512 * k), k = 0 .. rows of a full page
   int* error_flag;           // set if the shared-memory window is not where the kernel needs it
+  unsigned long long* timeline;  // optional (aps_debug_timeline)
+  int steal;                 // intra-CTA work stealing on/off
+  uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
+  const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
 // x^(8 * nbytes) from the per-row table plus (ragged lengths only) the sub-row remainder
 __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t nbytes) {
@@ -185,16 +228,45 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
 // K2 + K3 (+ K1 lookup when kGet).  Persistent grid: one CTA per SM.  A job (one page request) is
 // cut into tasks_per_job warp-tasks of rows_per_task 512-byte rows, sized by the host so that one
 // round of all warps of the chip covers the batch (no wave quantisation).  A task resolves its
-// page (kGet: eight lanes probe the hash table), streams its rows (128-bit loads and stores per
-// lane, next group in flight while the current one is folded), reduces the four per-lane CRC words
-// to the zero-init CRC of the task, shifts it by the bytes that follow it in the page (GF(2)
-// multiply) and XORs it into the job's accumulator.  The warp that finishes a job's last task
-// applies init/xorout and verifies or records the page CRC.
+// page (kGet: eight lanes probe the hash table), publishes its row range in shared memory and
+// streams the rows it claims from it (128-bit loads and stores per lane, next group in flight while
+// the current one is folded).  It reduces the four per-lane CRC words to the zero-init CRC of the
+// segment, shifts it by the bytes that follow it in the page (GF(2) multiply) and XORs it into the
+// job's accumulator.  Warps that run out of work take the back half of the longest remaining range
+// in their CTA (finish times of equal streams differ by ~10 % on a saturated memory system).  The
+// warp that completes a job's last row applies init/xorout and verifies or records the page CRC.
 template <bool kCrc, int kThreads, int G, bool kGet>
 __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   extern __shared__ __align__(16) uint8_t smem_raw[];
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
   constexpr uint32_t nwarps = kThreads / 32;
+  __shared__ unsigned long long s_range[nwarps];  // published ranges: open to stealing
+  __shared__ unsigned long long s_priv[nwarps];   // ranges of tasks that are not a warp's last: private
+  __shared__ Job s_job[nwarps];
+  __shared__ uint32_t s_jobidx[nwarps];
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  if (a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 0] = globaltimer_ns();
+  // Programmatic dependent launch: let the next kernel in the stream be scheduled as soon as SMs free
+  // up, and wait here until everything launched before this kernel has completed and is visible.
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const uint32_t n_items = a.n_jobs * a.tasks_per_job;
+  // Rank of this CTA among the CTAs of the launch: CTAs on fast SMs count up from 0, CTAs on slow SMs
+  // count down from the top, so the ranks are unique whatever the placement.  Tasks are dealt out by
+  // rank and the ranks below (n_items % grid) get one task more: the surplus lands on the fast SMs.
+  __shared__ uint32_t s_rank;
+  if (threadIdx.x == 0) {
+    uint32_t smid;
+    asm("mov.u32 %0, %%smid;" : "=r"(smid));
+    const bool slow = a.sm_slow[smid & 255u] != 0;
+    s_rank = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
+    __threadfence();
+    if (atomicAdd(&a.sched[2], 1u) == gridDim.x - 1u) {  // every CTA has its rank: re-arm for the next launch
+      a.sched[0] = 0;
+      a.sched[1] = 0;
+      a.sched[2] = 0;
+    }
+  }
+  if (lane == 0) s_range[warp] = 0;
   if (kCrc) {
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     uint32_t dyn;
@@ -203,84 +275,182 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       if (threadIdx.x == 0) *a.error_flag = 1;
       return;
     }
-    // each thread fetches one table entry (coalesced); the warp then broadcasts entry by entry and
-    // every lane writes its own replica: no dependent global loads in the loop
+    // Each thread fetches its table entries up front (coalesced, independent loads); the warp then
+    // broadcasts entry by entry and every lane writes its own replica.
     const uint32_t* gfold = &a.tables->fold[0][0];
-    for (uint32_t e0 = warp * 32; e0 < 1024; e0 += nwarps * 32) {
-      const uint32_t mine = gfold[e0 + lane];
+    const uint32_t* gz4 = &a.tables->z4[0][0];
+    constexpr uint32_t kPerWarp = 1024 / nwarps;  // fold entries per warp
+    static_assert(1024 % nwarps == 0 && kPerWarp % 32 == 0, "fold table split");
+    uint32_t mine[kPerWarp / 32], zmine[(1024 + kThreads - 1) / kThreads];
+#pragma unroll
+    for (uint32_t q = 0; q < kPerWarp / 32; ++q) mine[q] = __ldg(&gfold[warp * kPerWarp + q * 32 + lane]);
+#pragma unroll
+    for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
+      const uint32_t idx = threadIdx.x + q * kThreads;
+      zmine[q] = idx < 1024 ? __ldg(&gz4[idx]) : 0u;
+    }
+#pragma unroll
+    for (uint32_t q = 0; q < kPerWarp / 32; ++q) {
 #pragma unroll
       for (uint32_t k = 0; k < 32; ++k) {
-        const uint32_t idx = e0 + k, j = idx >> 8, b = idx & 255u;
-        sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine, k));
+        const uint32_t idx = warp * kPerWarp + q * 32 + k, j = idx >> 8, b = idx & 255u;
+        sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine[q], k));
       }
     }
-    for (uint32_t idx = threadIdx.x; idx < 1024; idx += kThreads) sts_u32(kSmemG + idx * 4u, (&a.tables->z4[0][0])[idx]);
-    __syncthreads();
+#pragma unroll
+    for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
+      const uint32_t idx = threadIdx.x + q * kThreads;
+      if (idx < 1024) sts_u32(kSmemG + idx * 4u, zmine[q]);
+    }
   }
-  const uint32_t total_warps = gridDim.x * nwarps;
-  const uint32_t n_items = a.n_jobs * a.tasks_per_job;
-  const uint32_t task_bytes = a.rows_per_task * kRowBytes;
-  for (uint32_t item = blockIdx.x * nwarps + warp; item < n_items; item += total_warps) {
-    const uint32_t job = item / a.tasks_per_job, c = item - job * a.tasks_per_job;
+  __syncthreads();
+  if (a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();
+  const uint32_t rank = s_rank;
+  const uint32_t base_cnt = n_items / gridDim.x, extra = n_items % gridDim.x;
+  const uint32_t my_first = rank * base_cnt + min(rank, extra);
+  const uint32_t my_count = base_cnt + (rank < extra ? 1u : 0u);
+  uint32_t local = warp;  // this warp takes the CTA's tasks local, local + nwarps, ...
+
+  uint32_t gen = 0;
+  for (;;) {
+    // ---- pick the next segment: a static task, or (when those are exhausted) half of a neighbour's rows
     Job j;
-    if (kGet) {
-      // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
-      const aps_get_req rq = a.reqs[job];
-      Probe pr{0, 0, 0, 0};
-      if (lane < 8) pr = tile_lookup(a.table, rq.key, lane, 0);
-      __syncwarp();
-      const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
-      int32_t status = 0;
-      j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
-      if (!meta) {
-        status = -APS_ENOTFOUND;
-      } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
-        status = -APS_EINVAL;
+    uint32_t job, row_lo, row_hi;
+    bool tail_mine = false;  // task 0 of a job also owns the sub-row tail (n % 512 bytes)
+    bool publish = false;
+    if (local < my_count) {
+      const uint32_t item = my_first + local;
+      job = item / a.tasks_per_job;
+      const uint32_t c = item - job * a.tasks_per_job;
+      const bool last_item = local + nwarps >= my_count;
+      local += nwarps;
+      if (kGet) {
+        // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
+        const aps_get_req rq = a.reqs[job];
+        Probe pr{0, 0, 0, 0};
+        if (lane < 8) pr = tile_lookup(a.table, rq.key, lane, 0);
+        __syncwarp();
+        const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
+        int32_t status = 0;
+        j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
+        if (!meta) {
+          status = -APS_ENOTFOUND;
+        } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
+          status = -APS_EINVAL;
+        } else {
+          const uint32_t plen = meta_len(meta);
+          j.slot = meta_slot(meta);
+          j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
+          j.src = a.table.slab + (uint64_t)j.slot * a.table.page_size + rq.page_off;
+          j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
+          status = (int32_t)j.n;
+        }
+        if (c == 0 && lane == 0) {
+          atomicAdd(&a.table.counters[kCtrLookups], 1ull);
+          atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
+          if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
+          if (!kCrc || j.n == 0) a.res[job] = aps_result{status, 0};  // otherwise the finisher reports
+        }
       } else {
-        const uint32_t plen = meta_len(meta);
-        j.slot = meta_slot(meta);
-        j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
-        j.src = a.table.slab + (uint64_t)j.slot * a.table.page_size + rq.page_off;
-        j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
-        status = (int32_t)j.n;
+        j = a.jobs[job];
       }
-      if (c == 0 && lane == 0) {
-        atomicAdd(&a.table.counters[kCtrLookups], 1ull);
-        atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
-        if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
-        if (!kCrc || j.n == 0) a.res[job] = aps_result{status, 0};  // otherwise the finisher reports
-      }
+      const uint32_t rows_full = j.n / kRowBytes;
+      row_lo = min(rows_full, c * a.rows_per_task);
+      row_hi = min(rows_full, row_lo + a.rows_per_task);
+      tail_mine = c == 0 && (j.n % kRowBytes) != 0;
+      if (row_lo >= row_hi && !tail_mine) continue;
+      publish = last_item;  // only a warp's final task is open to stealing (its descriptor stays valid)
     } else {
-      j = a.jobs[job];
+      if (!a.steal) break;
+      // ---- steal: lanes look at one neighbour each, the warp agrees on the longest remaining range
+      bool got = false;
+      for (int attempt = 0; attempt < 8 && !got; ++attempt) {
+        unsigned long long w = 0;
+        if (lane < nwarps) w = *(volatile unsigned long long*)&s_range[lane];
+        uint32_t rem = range_hi(w) > range_lo(w) ? range_hi(w) - range_lo(w) : 0u;
+        uint32_t best = rem, who = lane;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+          const uint32_t ob = __shfl_xor_sync(0xFFFFFFFFu, best, o), ow = __shfl_xor_sync(0xFFFFFFFFu, who, o);
+          if (ob > best || (ob == best && ow < who)) { best = ob; who = ow; }
+        }
+        if (best < kStealMinGroups * G) break;
+        const unsigned long long vw = __shfl_sync(0xFFFFFFFFu, w, who);
+        // the descriptor is read BEFORE the swap: if the swap succeeds the word (and its generation)
+        // did not change in between, so the descriptor read here belongs to that range
+        const Job vj = s_job[who];
+        const uint32_t vjob = s_jobidx[who];
+        __threadfence_block();
+        const uint32_t take = max((uint32_t)G, ((best / 2) / G) * G);
+        const uint32_t new_hi = range_hi(vw) - take;
+        int ok = 0;
+        if (lane == 0)
+          ok = atomicCAS(&s_range[who], vw, range_pack(range_lo(vw), new_hi, range_gen(vw))) == vw;
+        ok = __shfl_sync(0xFFFFFFFFu, ok, 0);
+        if (ok) {
+          j = vj;
+          job = vjob;
+          row_lo = new_hi;
+          row_hi = range_hi(vw);
+          got = true;
+        }
+      }
+      if (!got) break;
+      publish = true;
     }
-    const uint64_t off64 = (uint64_t)c * task_bytes;
-    if (off64 >= j.n) continue;
-    const uint32_t off = (uint32_t)off64;
-    const uint32_t len = min(task_bytes, j.n - off);
-    const uint8_t* src = j.src + off;
-    uint8_t* dst = j.dst ? j.dst + off : nullptr;
-    const bool aligned = (((uintptr_t)src | (uintptr_t)dst) & 15u) == 0;
-    const uint32_t rows = aligned ? len / kRowBytes : 0;
-    const uint32_t tail = len - rows * kRowBytes;
-    uint32_t crc = 0;
-    if (rows) crc = warp_rows<kCrc, G>(src, dst, rows, lane);
-    if (tail) {
-      uint32_t ct = warp_bytes<kCrc>(src + rows * kRowBytes, dst ? dst + rows * kRowBytes : nullptr, tail, lane);
-      if (kCrc) crc = rows ? (gf_mul(crc, xpow8(tail)) ^ ct) : ct;
+
+    // ---- run the segment [row_lo, row_hi) of job `job` (+ its sub-row tail when tail_mine)
+    const bool aligned = (((uintptr_t)j.src | (uintptr_t)j.dst) & 15u) == 0;
+    uint32_t crc = 0, rows_done = 0, end_byte = row_lo * kRowBytes;
+    if (row_lo < row_hi) {
+      if (aligned) {
+        ++gen;
+        unsigned long long* rp = publish ? &s_range[warp] : &s_priv[warp];
+        if (lane == 0) {
+          if (publish) {
+            s_job[warp] = j;
+            s_jobidx[warp] = job;
+            __threadfence_block();
+          }
+          *(volatile unsigned long long*)rp = range_pack(row_lo, row_hi, gen);
+        }
+        __syncwarp();
+        uint32_t row_end = row_lo;
+        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end);
+        rows_done = row_end - row_lo;
+        end_byte = row_end * kRowBytes;
+      } else {
+        const uint32_t nb = (row_hi - row_lo) * kRowBytes;
+        crc = warp_bytes<kCrc>(j.src + (size_t)row_lo * kRowBytes, j.dst ? j.dst + (size_t)row_lo * kRowBytes : nullptr, nb, lane);
+        rows_done = row_hi - row_lo;
+        end_byte = row_hi * kRowBytes;
+      }
     }
-    if (!kCrc) continue;
-    // shift the task CRC to the end of the job and fold it into the job's accumulator
-    const uint32_t contrib = gf_mul(crc, shift_for(a.rowshift, j.n - (off + len)));
-    const uint32_t ntasks = (j.n + task_bytes - 1) / task_bytes;
+    if (!kCrc) {
+      if (tail_mine) {
+        const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
+        warp_bytes<false>(j.src + t0, j.dst ? j.dst + t0 : nullptr, j.n - t0, lane);
+      }
+      continue;
+    }
+    // shift the segment CRC to the end of the job and fold it into the job's accumulator
+    uint32_t contrib = rows_done ? gf_mul(crc, shift_for(a.rowshift, j.n - end_byte)) : 0u;
+    uint32_t units = rows_done;
+    if (tail_mine) {  // the last n % 512 bytes: nothing follows them
+      const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
+      contrib ^= warp_bytes<true>(j.src + t0, j.dst ? j.dst + t0 : nullptr, j.n - t0, lane);
+      units += 1;
+    }
+    const uint32_t target = (j.n + kRowBytes - 1) / kRowBytes;
     uint32_t prev = 0;
     if (lane == 0) {
       atomicXor(&a.acc[job], contrib);
       __threadfence();
-      prev = atomicAdd(&a.done[job], 1u);
+      prev = atomicAdd(&a.done[job], units);
     }
     prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
-    if (prev != ntasks - 1) continue;
-    if (lane == 0) {  // last task of this job
+    if (prev + units != target) continue;
+    if (lane == 0) {  // this segment completed the job
       __threadfence();
       const uint32_t x = atomicExch(&a.acc[job], 0u);
       const uint32_t full = x ^ gf_mul(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
@@ -293,6 +463,17 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       }
       if (a.res) a.res[job] = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
       a.done[job] = 0;
+    }
+  }
+  if (a.timeline) {
+    if (lane == 0) a.timeline[1024 + blockIdx.x * 32 + warp] = globaltimer_ns();
+    if (lane == 0) atomicMin(&a.timeline[blockIdx.x * 4 + 2], globaltimer_ns());
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      a.timeline[blockIdx.x * 4 + 3] = globaltimer_ns();
+      uint32_t smid;
+      asm("mov.u32 %0, %%smid;" : "=r"(smid));
+      a.timeline[1024 + 256 * 32 + blockIdx.x] = smid;
     }
   }
 }

@@ -189,6 +189,7 @@ typedef struct aps_stats_t {
   uint64_t bytes_copied;    /* payload bytes moved by get/put kernels */
   uint64_t crc_mismatches;  /* whole-page gets whose CRC differed from the one recorded at put */
   uint64_t kernel_launches; /* kernels this store has launched */
+  uint64_t slow_sms;        /* SMs the open-time calibration classed as slow (they get one task less per launch) */
 } aps_stats_t;
 APS_API int aps_stats(aps_store* s, aps_stats_t* out);
 
@@ -203,6 +204,13 @@ APS_API int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_
 #define APS_FAULT_PUT 1u
 #define APS_FAULT_DELETE 2u
 APS_API int aps_set_faults(aps_store* s, uint32_t fault_mask);
+
+/* Profiling hook: while enabled, every CTA of the copy kernel records four globaltimer stamps (ns):
+ * start, CRC tables ready, first warp finished, end; every warp also records when it finished.  out
+ * receives max_words values of the last launch: words [4*cta .. 4*cta+3] are the CTA stamps and
+ * words [1024 + 32*cta + warp] the warp end stamps (all-ones = not written).  Costs a memset per
+ * launch; off by default. */
+APS_API int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_words);
 
 /* Test hook: flips one byte of a resident page in the slab so the CRC check can be shown to fire. */
 APS_API int aps_debug_corrupt(aps_store* s, const aps_key* key, uint32_t byte_offset);
