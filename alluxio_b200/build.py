@@ -25,7 +25,8 @@ def build_libaps(force=False, verbose=False):
     sources = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [os.path.join(ROOT, "include", "aps.h")]
     if force or _newer(LIBAPS, sources):
         cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [
-            "-I", os.path.join(ROOT, "include"), "-o", LIBAPS, os.path.join(csrc, "aps_api.cu")]
+            "-I", os.path.join(ROOT, "include"), "-o", LIBAPS] + sorted(
+                os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith(".cu"))
         subprocess.check_call(cmd)
     return LIBAPS
 

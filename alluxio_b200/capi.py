@@ -10,7 +10,9 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libaps.so")
 
-APS_OK, APS_ENOTFOUND, APS_EINVAL, APS_ENOSPC, APS_ECUDA, APS_ECORRUPT, APS_ECLOSED, APS_ENOMEM, APS_EFAULT = range(9)
+(APS_OK, APS_ENOTFOUND, APS_EINVAL, APS_ENOSPC, APS_ECUDA, APS_ECORRUPT, APS_ECLOSED, APS_ENOMEM, APS_EFAULT,
+ APS_ELIMIT) = range(10)
+APS_NOALLOC_MAX_RANGES, APS_NOALLOC_MAX_LEN = 1024, 4 << 20
 APS_FLAG_CRC, APS_FLAG_TMA_COPY = 1, 2
 APS_FAULT_PUT, APS_FAULT_DELETE = 1, 2
 
@@ -64,6 +66,7 @@ SIGNATURES = {
     "aps_md5_batch_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp]),
     "aps_md5_batch": (C.c_int, [_i32, _u32, _vp, _vp, _vp]),
     "aps_crc32c_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
+    "aps_crc32c_noalloc": (C.c_int, [_i32, _u32, _vp, _vp, _u32, _vp, _vp]),
     "aps_fill_pages_dev": (C.c_int, [_i32, _vp, _u64, _u32, _u32, _vp, _vp, _u64, _vp]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),

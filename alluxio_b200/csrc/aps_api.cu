@@ -419,6 +419,7 @@ const char* aps_strerror(int code) {
     case APS_ECLOSED: return "store is closed";
     case APS_ENOMEM: return "out of memory";
     case APS_EFAULT: return "injected fault";
+    case APS_ELIMIT: return "request exceeds the fixed scratch of the no-allocation entry point";
     default: return "unknown error";
   }
 }

@@ -478,6 +478,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   }
 }
 
+#ifndef APS_KERNELS_TEMPLATES_ONLY  // a second translation unit wants the templates above, not these definitions
 // ------------------------------------------------------------------------------------------------
 // K1 kernels: eight lanes per request.
 // ------------------------------------------------------------------------------------------------
@@ -725,5 +726,7 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
   for (int i = 0; i < 4; ++i)
     for (int k = 0; k < 4; ++k) out[file][4 * i + k] = (uint8_t)(h[i] >> (8 * k));
 }
+
+#endif  // APS_KERNELS_TEMPLATES_ONLY
 
 }  // namespace aps

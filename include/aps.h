@@ -48,6 +48,7 @@ extern "C" {
 #define APS_ECLOSED 6    /* store already closed */
 #define APS_ENOMEM 7     /* host or device allocation failed */
 #define APS_EFAULT 8     /* injected fault (APS_FAULT_* below) */
+#define APS_ELIMIT 9     /* request larger than the fixed scratch of aps_crc32c_noalloc */
 
 /* PageId on the device: CACHE/PageId.java:23-74 is (String fileId, long pageIndex).  The file id
  * is carried as 128 bits; the host side maps strings to 128 bits without collisions (decimal,
@@ -169,6 +170,25 @@ APS_API int aps_md5_batch(int32_t device, uint32_t n_files, const void* const* d
  * verify pass; the reference has no CRC at all. */
 APS_API int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_data, const uint32_t* d_len, uint32_t* d_crc,
                          aps_stream stream);
+
+/* CRC32C of n device-resident byte ranges WITHOUT any allocation.  This entry point has no
+ * counterpart in the reference; it exists for callers of this library that cannot ask the driver
+ * for memory when they need a checksum: a scrubber re-checking pages while the slab already fills
+ * HBM (cudaMalloc may fail then), read threads that must not be stalled by the device-wide
+ * synchronisation cudaMalloc/cudaFree imply, or a host process whose device memory all belongs to
+ * another component's pool.  It needs no aps_store.  All working memory beyond the caller's d_data,
+ * d_len and d_crc is a fixed 128 KiB array inside the library (held by every GPU that loads the
+ * library until the process exits), hence the limits: n <= APS_NOALLOC_MAX_RANGES and max_len <=
+ * APS_NOALLOC_MAX_LEN, otherwise APS_ELIMIT is returned and nothing is launched.  max_len is the
+ * caller's bound on every d_len[i]; longer ranges are cut to max_len.  d_data, d_len, d_crc are
+ * DEVICE arrays.  Asynchronous on `stream` (NULL = the default stream).
+ * The first call on a device sets that device's copy of the array up (a few synchronous copies): make
+ * that call before any stream capture begins.  Every call reuses the same array, so calls that can
+ * overlap on the GPU race with each other: issue them on one stream or order them yourself. */
+#define APS_NOALLOC_MAX_RANGES 1024u
+#define APS_NOALLOC_MAX_LEN (4u << 20)
+APS_API int aps_crc32c_noalloc(int32_t device, uint32_t n, const void* const* d_data, const uint32_t* d_len,
+                               uint32_t max_len, uint32_t* d_crc, aps_stream stream);
 
 /* ---- synthetic data, stats, diagnostics ---------------------------------------------------------*/
 
