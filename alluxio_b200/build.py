@@ -31,5 +31,22 @@ def build_libaps(force=False, verbose=False):
     return LIBAPS
 
 
+LIBHOST = os.path.join(HERE, "libaps_host.so")
+
+
+def build_host(force=False):
+    """g++: the host-side cache layer (alluxio_b200/host) on top of libaps.so."""
+    build_libaps()
+    host = os.path.join(HERE, "host")
+    sources = [os.path.join(host, f) for f in os.listdir(host)] + [os.path.join(ROOT, "include", "aps_cache.h"), LIBAPS]
+    if force or _newer(LIBHOST, sources):
+        cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-Wall", "-Wextra", "-pthread",
+               "-I", os.path.join(ROOT, "include"), "-o", LIBHOST, os.path.join(host, "cache.cc"),
+               "-L", HERE, "-laps", "-Wl,-rpath,$ORIGIN"]
+        subprocess.check_call(cmd)
+    return LIBHOST
+
+
 if __name__ == "__main__":
     print(build_libaps(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

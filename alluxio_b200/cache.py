@@ -1,0 +1,251 @@
+"""ctypes view of libaps_host.so: the native mirror of the reference's classes above the PageStore
+boundary (include/aps_cache.h).  Names follow the Java classes (CACHE/LocalCacheManager.java,
+CACHE/DefaultMetaStore.java, CACHE/CacheEvictor.java) so tests read like the reference's."""
+import ctypes as C
+import os
+
+from . import capi
+from .page_store import PageId  # noqa: F401  (re-export)
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libaps_host.so")
+
+_vp, _cp, _i32, _i64, _u64, _dbl = C.c_void_p, C.c_char_p, C.c_int32, C.c_int64, C.c_uint64, C.c_double
+EXTERNAL_READ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32)
+
+SIGNATURES = {
+    "apc_manager_create": (C.c_int, [C.POINTER(capi.aps_config), _cp, _dbl, C.POINTER(_vp)]),
+    "apc_manager_close": (C.c_int, [_vp]),
+    "apc_put": (C.c_int, [_vp, _cp, _i64, _vp, _i32]),
+    "apc_get": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
+    "apc_delete": (C.c_int, [_vp, _cp, _i64]),
+    "apc_state": (C.c_int, [_vp]),
+    "apc_bytes": (_i64, [_vp]),
+    "apc_pages": (_i64, [_vp]),
+    "apc_page_lock_id": (_i32, [_vp, _cp, _i64]),
+    "apc_set_store_faults": (C.c_int, [_vp, C.c_uint32]),
+    "apc_store": (_vp, [_vp]),
+    "apc_positioned_read": (_i32, [_vp, _cp, _i64, _i64, _vp, _i32, EXTERNAL_READ, _vp, C.POINTER(_i64), C.POINTER(_i64)]),
+    "apc_replay": (_i64, [_vp, _i64, _vp, _vp, _vp, _u64, C.c_int, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64),
+                          C.POINTER(_i64), C.POINTER(_i64)]),
+    "apc_evictor_create": (_vp, [_cp, _dbl]),
+    "apc_evictor_destroy": (None, [_vp]),
+    "apc_evictor_update_on_get": (None, [_vp, _cp, _i64]),
+    "apc_evictor_update_on_put": (None, [_vp, _cp, _i64]),
+    "apc_evictor_update_on_delete": (None, [_vp, _cp, _i64]),
+    "apc_evictor_reset": (None, [_vp]),
+    "apc_evictor_evict": (C.c_int, [_vp, _vp, C.c_size_t, C.POINTER(_i64)]),
+    "apc_meta_create": (_vp, [_cp, _dbl]),
+    "apc_meta_destroy": (None, [_vp]),
+    "apc_meta_has_page": (C.c_int, [_vp, _cp, _i64]),
+    "apc_meta_add_page": (None, [_vp, _cp, _i64, _i64]),
+    "apc_meta_get_page_info": (C.c_int, [_vp, _cp, _i64, C.POINTER(_i64)]),
+    "apc_meta_remove_page": (C.c_int, [_vp, _cp, _i64]),
+    "apc_meta_bytes": (_i64, [_vp]),
+    "apc_meta_pages": (_i64, [_vp]),
+    "apc_meta_reset": (None, [_vp]),
+    "apc_meta_evict": (C.c_int, [_vp, _vp, C.c_size_t, C.POINTER(_i64), C.POINTER(_i64)]),
+    "apc_file_key": (None, [_vp, _cp, C.POINTER(_u64), C.POINTER(_u64)]),
+    "apc_java_string_hashcode": (_i32, [_cp]),
+}
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("libaps_host.so is not built: run `python -m alluxio_b200.build`")
+        capi.lib()  # libaps.so first (the host library links against it)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+class PageNotFoundException(Exception):
+    pass
+
+
+def _f(p):
+    return p.file_id.encode("utf-8")
+
+
+class CacheEvictor:
+    """CACHE/CacheEvictor.java:26-69; kind in {"LRU", "LFU", "FIFO"}."""
+
+    def __init__(self, kind, lfu_logbase=2.0):
+        self._h = lib().apc_evictor_create(kind.encode(), lfu_logbase)
+        if not self._h:
+            raise ValueError(kind)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().apc_evictor_destroy(self._h)
+            self._h = None
+
+    def update_on_get(self, p):
+        lib().apc_evictor_update_on_get(self._h, _f(p), p.page_index)
+
+    def update_on_put(self, p):
+        lib().apc_evictor_update_on_put(self._h, _f(p), p.page_index)
+
+    def update_on_delete(self, p):
+        lib().apc_evictor_update_on_delete(self._h, _f(p), p.page_index)
+
+    def reset(self):
+        lib().apc_evictor_reset(self._h)
+
+    def evict(self):
+        name = C.create_string_buffer(512)
+        idx = C.c_int64()
+        if not lib().apc_evictor_evict(self._h, name, 512, C.byref(idx)):
+            return None
+        return PageId(name.value.decode(), idx.value)
+
+
+class MetaStore:
+    """CACHE/DefaultMetaStore.java:33-132."""
+
+    def __init__(self, evictor="LRU", lfu_logbase=2.0):
+        self._h = lib().apc_meta_create(evictor.encode(), lfu_logbase)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().apc_meta_destroy(self._h)
+            self._h = None
+
+    def has_page(self, p):
+        return bool(lib().apc_meta_has_page(self._h, _f(p), p.page_index))
+
+    def add_page(self, p, size):
+        lib().apc_meta_add_page(self._h, _f(p), p.page_index, size)
+
+    def get_page_info(self, p):
+        size = C.c_int64()
+        if not lib().apc_meta_get_page_info(self._h, _f(p), p.page_index, C.byref(size)):
+            raise PageNotFoundException(repr(p))
+        return (p, size.value)
+
+    def remove_page(self, p):
+        if not lib().apc_meta_remove_page(self._h, _f(p), p.page_index):
+            raise PageNotFoundException(repr(p))
+
+    def bytes(self):
+        return lib().apc_meta_bytes(self._h)
+
+    def pages(self):
+        return lib().apc_meta_pages(self._h)
+
+    def reset(self):
+        lib().apc_meta_reset(self._h)
+
+    def evict(self):
+        name = C.create_string_buffer(512)
+        idx, size = C.c_int64(), C.c_int64()
+        if not lib().apc_meta_evict(self._h, name, 512, C.byref(idx), C.byref(size)):
+            return None
+        return (PageId(name.value.decode(), idx.value), size.value)
+
+
+class LocalCacheManager:
+    """CACHE/LocalCacheManager.java:75-627 over a GpuPageStore (sync write, sync restore)."""
+    NOT_IN_USE, READ_ONLY, READ_WRITE = 0, 1, 2
+
+    def __init__(self, page_size, cache_size, evictor="LRU", lfu_logbase=2.0, device=0, slab_slots=0, crc=True,
+                 max_batch=0):
+        cfg = capi.aps_config(device=device, page_size=page_size, cache_bytes=cache_size, slab_slots=slab_slots,
+                              table_capacity=0, max_batch=max_batch, flags=capi.APS_FLAG_CRC if crc else 0)
+        h = C.c_void_p()
+        capi.check(lib().apc_manager_create(C.byref(cfg), evictor.encode(), lfu_logbase, C.byref(h)), "apc_manager_create")
+        self._h = h
+        self.page_size = page_size
+
+    def close(self):
+        if self._h is not None:
+            lib().apc_manager_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def put(self, p, page):
+        data = bytes(page)
+        buf = (C.c_uint8 * max(1, len(data))).from_buffer_copy(data or b"\0")
+        return bool(lib().apc_put(self._h, _f(p), p.page_index, buf, len(data)))
+
+    def get(self, p, bytes_to_read, buffer, offset_in_buffer=0, page_offset=0):
+        cbuf = (C.c_uint8 * max(1, len(buffer))).from_buffer(buffer) if len(buffer) else (C.c_uint8 * 1)()
+        r = lib().apc_get(self._h, _f(p), p.page_index, page_offset, bytes_to_read, C.addressof(cbuf), len(buffer),
+                          offset_in_buffer)
+        del cbuf
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        return r
+
+    def delete(self, p):
+        return bool(lib().apc_delete(self._h, _f(p), p.page_index))
+
+    def state(self):
+        return lib().apc_state(self._h)
+
+    def bytes(self):
+        return lib().apc_bytes(self._h)
+
+    def pages(self):
+        return lib().apc_pages(self._h)
+
+    def page_lock_id(self, p):
+        return lib().apc_page_lock_id(self._h, _f(p), p.page_index)
+
+    def set_store_faulty(self, put=False, delete=False):
+        mask = (capi.APS_FAULT_PUT if put else 0) | (capi.APS_FAULT_DELETE if delete else 0)
+        capi.check(lib().apc_set_store_faults(self._h, mask))
+
+    def store_stats(self):
+        st = capi.aps_stats_t()
+        capi.check(capi.lib().aps_stats(lib().apc_store(self._h), C.byref(st)))
+        return {n: getattr(st, n) for n, _ in capi.aps_stats_t._fields_}
+
+    def positioned_read(self, file_id, file_len, pos, length, external):
+        """LocalCacheFileInStream.positionedRead: `external(pos, n) -> bytes` stands for the
+        external FileInStream.  Returns (data or None at EOF, bytes_from_cache, bytes_from_external)."""
+        import numpy as np
+        out = np.zeros(max(1, length), np.uint8)
+        fc, fe = C.c_int64(0), C.c_int64(0)
+
+        def ext(user, file_pos, dst, n):
+            data = external(file_pos, n)
+            C.memmove(dst, data, len(data))
+            return len(data)
+
+        cb = EXTERNAL_READ(ext)
+        r = lib().apc_positioned_read(self._h, str(file_id).encode(), file_len, pos, out.ctypes.data, length, cb, None,
+                                      C.byref(fc), C.byref(fe))
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        return (None if r < 0 else out[:r].tobytes()), fc.value, fe.value
+
+    def replay(self, files, pages, page_lens, seed, verify=True, victims_cap=None):
+        """Reference read flow (get; on a miss put the synthetic page) over a trace."""
+        import numpy as np
+        files = np.ascontiguousarray(files, dtype=np.int64)
+        pages = np.ascontiguousarray(pages, dtype=np.int64)
+        page_lens = np.ascontiguousarray(page_lens, dtype=np.int32)
+        n = files.size
+        cap = n if victims_cap is None else victims_cap
+        hit, put_ok = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        vf, vp = np.zeros(cap, np.int64), np.zeros(cap, np.int64)
+        fp, fb, bad = C.c_int64(), C.c_int64(), C.c_int64()
+        nv = lib().apc_replay(self._h, n, files.ctypes.data, pages.ctypes.data, page_lens.ctypes.data, seed, int(verify),
+                              hit.ctypes.data, put_ok.ctypes.data, vf.ctypes.data, vp.ctypes.data, cap, C.byref(fp),
+                              C.byref(fb), C.byref(bad))
+        k = min(nv, cap)
+        return dict(hit=hit, put_ok=put_ok, victims=np.stack([vf[:k], vp[:k]], axis=1), n_victims=nv,
+                    final_pages=fp.value, final_bytes=fb.value, verify_failures=bad.value)

@@ -1,0 +1,720 @@
+// Host-side cache layer (see cache.h).  Product code: links libaps.so, never the oracle.
+#include "cache.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "../../include/aps_cache.h"
+
+namespace alluxio_b200 {
+
+// ================================================================================ Java-isms, keys
+
+int32_t JavaStringHashCode(const std::string& s) {
+  // 31-polynomial over UTF-16 code units with int32 wrap-around; the input is UTF-8.
+  uint32_t h = 0;
+  for (size_t i = 0; i < s.size();) {
+    const uint8_t c = (uint8_t)s[i];
+    uint32_t cp;
+    int more;
+    if (c < 0x80) { cp = c; more = 0; }
+    else if (c < 0xE0) { cp = c & 0x1Fu; more = 1; }
+    else if (c < 0xF0) { cp = c & 0x0Fu; more = 2; }
+    else { cp = c & 0x07u; more = 3; }
+    ++i;
+    while (more-- > 0 && i < s.size()) cp = (cp << 6) | ((uint8_t)s[i++] & 0x3Fu);
+    if (cp > 0xFFFF) {
+      const uint32_t v = cp - 0x10000;
+      h = h * 31u + (0xD800u | (v >> 10));
+      h = h * 31u + (0xDC00u | (v & 0x3FFu));
+    } else {
+      h = h * 31u + cp;
+    }
+  }
+  return (int32_t)h;
+}
+
+static int32_t FloorMod(int32_t x, int32_t y) {
+  const int32_t r = x % y;
+  return (r != 0 && ((r < 0) != (y < 0))) ? r + y : r;
+}
+
+static bool IsCanonicalDecimalLong(const std::string& s, int64_t* out) {
+  if (s.empty() || s.size() > 20) return false;
+  size_t i = 0;
+  const bool neg = s[0] == '-';
+  if (neg) i = 1;
+  if (i >= s.size()) return false;
+  if (s[i] == '0') {
+    if (neg || s.size() != 1) return false;
+    *out = 0;
+    return true;
+  }
+  unsigned long long v = 0;
+  const unsigned long long limit = neg ? (1ull << 63) : (1ull << 63) - 1;
+  for (; i < s.size(); ++i) {
+    if (s[i] < '0' || s[i] > '9') return false;
+    const unsigned d = (unsigned)(s[i] - '0');
+    if (v > (limit - d) / 10) return false;
+    v = v * 10 + d;
+  }
+  *out = neg ? (int64_t)(0ull - v) : (int64_t)v;
+  return true;
+}
+
+static bool ParseHex32(const std::string& s, uint64_t* hi, uint64_t* lo) {
+  if (s.size() != 32) return false;
+  uint64_t w[2] = {0, 0};
+  for (int i = 0; i < 32; ++i) {
+    const char c = s[(size_t)i];
+    unsigned d;
+    if (c >= '0' && c <= '9') d = (unsigned)(c - '0');
+    else if (c >= 'a' && c <= 'f') d = (unsigned)(c - 'a' + 10);
+    else return false;
+    w[i / 16] = (w[i / 16] << 4) | d;
+  }
+  *hi = w[0];
+  *lo = w[1];
+  return true;
+}
+
+void FileKeyCodec::Encode(const std::string& fileId, uint64_t* hi, uint64_t* lo) {
+  int64_t v;
+  if (IsCanonicalDecimalLong(fileId, &v)) {
+    *hi = 0;
+    *lo = (uint64_t)v;
+    return;
+  }
+  uint64_t h, l;
+  if (ParseHex32(fileId, &h, &l) && h != 0 && h != ~0ull) {
+    *hi = h;
+    *lo = l;
+    return;
+  }
+  std::lock_guard<std::mutex> g(mMu);
+  auto it = mIds.find(fileId);
+  if (it == mIds.end()) {
+    it = mIds.emplace(fileId, (uint64_t)mNames.size()).first;
+    mNames.push_back(fileId);
+  }
+  *hi = ~0ull;
+  *lo = it->second;
+}
+
+std::string FileKeyCodec::Decode(uint64_t hi, uint64_t lo) {
+  if (hi == 0) return std::to_string((int64_t)lo);
+  if (hi == ~0ull) {
+    std::lock_guard<std::mutex> g(mMu);
+    return lo < mNames.size() ? mNames[(size_t)lo] : std::string();
+  }
+  char buf[33];
+  snprintf(buf, sizeof(buf), "%016llx%016llx", (unsigned long long)hi, (unsigned long long)lo);
+  return buf;
+}
+
+// ================================================================================ node pool
+
+int32_t NodePool::Alloc(const Key& k) {
+  int32_t n;
+  if (!mFree.empty()) {
+    n = mFree.back();
+    mFree.pop_back();
+  } else {
+    n = (int32_t)mNodes.size();
+    mNodes.push_back(ListNode());
+  }
+  mNodes[(size_t)n] = ListNode{k, -1, -1};
+  return n;
+}
+void NodePool::Free(int32_t n) { mFree.push_back(n); }
+
+void ListPushBack(NodePool& p, ListHead& l, int32_t n) {
+  p[n].prev = l.tail;
+  p[n].next = -1;
+  if (l.tail >= 0) p[l.tail].next = n; else l.head = n;
+  l.tail = n;
+}
+void ListUnlink(NodePool& p, ListHead& l, int32_t n) {
+  const int32_t a = p[n].prev, b = p[n].next;
+  if (a >= 0) p[a].next = b; else l.head = b;
+  if (b >= 0) p[b].prev = a; else l.tail = a;
+  p[n].prev = p[n].next = -1;
+}
+
+// ================================================================================ evictors
+
+namespace {
+
+// CACHE/evictor/LRUCacheEvictor.java:29-75: an access-ordered LinkedHashMap; put and get both move the
+// id to the tail, evict() names the head without removing it.  `refreshOnPut` = false gives the FIFO
+// double of the reference's tests (CTEST/LocalCacheManagerTest.java:731-761).
+class RecencyEvictor : public CacheEvictor {
+ public:
+  RecencyEvictor(bool refreshOnGet, bool refreshOnPut) : mOnGet(refreshOnGet), mOnPut(refreshOnPut) {}
+  void UpdateOnGet(const Key& k) override {
+    if (mOnGet) Touch(k, false);
+  }
+  void UpdateOnPut(const Key& k) override { Touch(k, /*keepPlaceIfPresent=*/!mOnPut); }
+  void UpdateOnDelete(const Key& k) override {
+    std::lock_guard<std::mutex> g(mMu);
+    auto it = mWhere.find(k);
+    if (it == mWhere.end()) return;
+    ListUnlink(mPool, mList, it->second);
+    mPool.Free(it->second);
+    mWhere.erase(it);
+  }
+  bool Evict(Key* victim) override {
+    std::lock_guard<std::mutex> g(mMu);
+    if (mList.Empty()) return false;
+    *victim = mPool[mList.head].key;
+    return true;
+  }
+  void Reset() override {
+    std::lock_guard<std::mutex> g(mMu);
+    mWhere.clear();
+    mPool = NodePool();
+    mList = ListHead();
+  }
+ private:
+  void Touch(const Key& k, bool keepPlaceIfPresent) {
+    std::lock_guard<std::mutex> g(mMu);
+    auto it = mWhere.find(k);
+    int32_t n;
+    if (it != mWhere.end()) {
+      if (keepPlaceIfPresent) return;
+      n = it->second;
+      ListUnlink(mPool, mList, n);
+    } else {
+      n = mPool.Alloc(k);
+      mWhere.emplace(k, n);
+    }
+    ListPushBack(mPool, mList, n);
+  }
+  const bool mOnGet, mOnPut;
+  std::mutex mMu;
+  NodePool mPool;
+  ListHead mList;
+  std::unordered_map<Key, int32_t, KeyHash> mWhere;
+};
+
+// CACHE/evictor/LFUCacheEvictor.java:35-161: ids grouped by bucket = (int)(ln(count)/ln(base)), LRU
+// inside a bucket, the victim is the head of the lowest occupied bucket as tracked by mMinBucket.
+class LFUEvictor : public CacheEvictor {
+ public:
+  explicit LFUEvictor(double logBase) : mDivisor(std::log(logBase)) {}
+  void UpdateOnGet(const Key& k) override {
+    std::lock_guard<std::mutex> g(mMu);
+    Entry& e = mEntries[k];  // count starts at 0
+    const int newCount = ++e.count;
+    const int newBucket = Bucket(newCount);
+    if (newCount > 1) {
+      const int oldBucket = Bucket(newCount - 1);
+      if (newBucket != oldBucket) {                          // :103-109
+        const bool left = Detach(e.node, oldBucket);
+        if (!left && oldBucket == mMinBucket) mMinBucket = newBucket;
+        Attach(e.node, newBucket);
+      } else {                                               // :110-112 touch = move to the bucket's tail
+        auto it = mBuckets.find(newBucket);
+        if (it != mBuckets.end()) {
+          ListUnlink(mPool, it->second, e.node);
+          ListPushBack(mPool, it->second, e.node);
+        }
+      }
+    } else {                                                 // :113-116
+      e.node = mPool.Alloc(k);
+      mMinBucket = newBucket;
+      Attach(e.node, newBucket);
+    }
+  }
+  void UpdateOnPut(const Key& k) override { UpdateOnGet(k); }
+  void UpdateOnDelete(const Key& k) override {
+    std::lock_guard<std::mutex> g(mMu);
+    auto it = mEntries.find(k);
+    if (it == mEntries.end()) return;
+    const int bucket = Bucket(it->second.count);
+    const int32_t node = it->second.node;
+    mEntries.erase(it);
+    const bool left = Detach(node, bucket);
+    mPool.Free(node);
+    if (!left && bucket == mMinBucket && !mBuckets.empty())
+      while (!mBuckets.count(mMinBucket)) ++mMinBucket;      // :133-137
+  }
+  bool Evict(Key* victim) override {
+    std::lock_guard<std::mutex> g(mMu);
+    auto it = mBuckets.find(mMinBucket);
+    if (it == mBuckets.end()) return false;
+    *victim = mPool[it->second.head].key;
+    return true;
+  }
+  void Reset() override {
+    std::lock_guard<std::mutex> g(mMu);
+    mEntries.clear();
+    mBuckets.clear();
+    mPool = NodePool();
+    mMinBucket = -1;
+  }
+ private:
+  struct Entry { int count = 0; int32_t node = -1; };
+  int Bucket(int count) const { return (int)(std::log((double)count) / mDivisor); }
+  void Attach(int32_t node, int bucket) { ListPushBack(mPool, mBuckets[bucket], node); }
+  // true if the bucket still exists afterwards (computeIfPresent semantics, :76-85)
+  bool Detach(int32_t node, int bucket) {
+    auto it = mBuckets.find(bucket);
+    if (it == mBuckets.end()) return false;
+    ListUnlink(mPool, it->second, node);
+    if (it->second.Empty()) {
+      mBuckets.erase(it);
+      return false;
+    }
+    return true;
+  }
+  std::mutex mMu;
+  const double mDivisor;
+  NodePool mPool;
+  std::unordered_map<Key, Entry, KeyHash> mEntries;
+  std::map<int, ListHead> mBuckets;
+  int mMinBucket = -1;
+};
+
+}  // namespace
+
+std::unique_ptr<CacheEvictor> CacheEvictor::Create(const std::string& kind, double lfuLogBase) {
+  if (kind == "LRU") return std::unique_ptr<CacheEvictor>(new RecencyEvictor(true, true));
+  if (kind == "FIFO") return std::unique_ptr<CacheEvictor>(new RecencyEvictor(false, false));
+  if (kind == "LFU") return std::unique_ptr<CacheEvictor>(new LFUEvictor(lfuLogBase));
+  return nullptr;
+}
+
+// ================================================================================ meta store
+
+void MetaStore::AddPage(const Key& k, const PageMeta& m) {  // DefaultMetaStore.java:56-63
+  mPages[k] = m;
+  mBytes += m.size;
+  mCount += 1;
+  mEvictor->UpdateOnPut(k);
+}
+bool MetaStore::GetPageInfo(const Key& k, PageMeta* out) {  // :66-72
+  auto it = mPages.find(k);
+  if (it == mPages.end()) return false;
+  mEvictor->UpdateOnGet(k);
+  *out = it->second;
+  return true;
+}
+bool MetaStore::RemovePage(const Key& k) {  // :75-85
+  auto it = mPages.find(k);
+  if (it == mPages.end()) return false;
+  mBytes -= it->second.size;
+  mCount -= 1;
+  mPages.erase(it);
+  mEvictor->UpdateOnDelete(k);
+  return true;
+}
+void MetaStore::Reset() {  // :98-105
+  mPages.clear();
+  mBytes = 0;
+  mCount = 0;
+  mEvictor->Reset();
+}
+bool MetaStore::Evict(Key* victim, PageMeta* meta) {  // :108-122
+  if (!mEvictor->Evict(victim)) return false;
+  auto it = mPages.find(*victim);
+  if (it == mPages.end()) {
+    mEvictor->UpdateOnDelete(*victim);  // heal an evictor that named an unknown page
+    return false;
+  }
+  *meta = it->second;
+  return true;
+}
+
+// ================================================================================ GpuPageStore
+
+int GpuPageStore::Open(const aps_config& cfg, std::unique_ptr<GpuPageStore>* out) {
+  aps_store* s = nullptr;
+  const int rc = aps_open(&cfg, &s);
+  if (rc != APS_OK) return rc;
+  std::unique_ptr<GpuPageStore> g(new GpuPageStore());
+  g->mStore = s;
+  g->mCacheBytes = cfg.cache_bytes;
+  *out = std::move(g);
+  return APS_OK;
+}
+GpuPageStore::~GpuPageStore() {
+  if (mStore) aps_close(mStore);
+}
+static aps_key ToAps(const Key& k) { return aps_key{k.hi, k.lo, k.idx}; }
+int GpuPageStore::Put(const Key& k, const void* page, int32_t len) {
+  const aps_key a = ToAps(k);
+  return aps_put(mStore, &a, page, (uint32_t)len);
+}
+int GpuPageStore::Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) {
+  *bytesRead = 0;
+  if (pageOffset < 0) return APS_EINVAL;  // LocalPageStore.java:91
+  if (room < 0) return APS_EINVAL;        // :92-93 (bufferOffset beyond the buffer)
+  const aps_key a = ToAps(k);
+  uint32_t got = 0;
+  const int rc = aps_get(mStore, &a, (uint32_t)pageOffset, (uint32_t)std::max(bytesToRead, 0), dst, (uint32_t)room, &got, nullptr);
+  *bytesRead = (int32_t)got;
+  return rc;
+}
+int GpuPageStore::Delete(const Key& k) {
+  const aps_key a = ToAps(k);
+  return aps_delete(mStore, &a);
+}
+int GpuPageStore::GetPages(std::vector<std::pair<Key, int64_t>>* out) {
+  out->clear();
+  return aps_iterate(
+      mStore,
+      [](void* user, const aps_key* key, uint32_t len) {
+        static_cast<std::vector<std::pair<Key, int64_t>>*>(user)->push_back({Key{key->file_hi, key->file_lo, key->page_index}, (int64_t)len});
+        return 0;
+      },
+      out);
+}
+
+// ================================================================================ LocalCacheManager
+
+LocalCacheManager::LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store)
+    : mPageSize(pageSize), mCacheSize(store->GetCacheSize()), mMetaStore(std::move(meta)), mPageStore(std::move(store)),
+      mState(READ_ONLY) {  // LocalCacheManager.java:145-166
+  RestoreOrInit();          // :134
+}
+
+Key LocalCacheManager::MakeKey(const std::string& fileId, int64_t pageIndex) {
+  Key k;
+  mCodec.Encode(fileId, &k.hi, &k.lo);
+  k.idx = (uint64_t)pageIndex;
+  return k;
+}
+
+int32_t LocalCacheManager::GetPageLockId(const std::string& fileId, int64_t pageIndex) const {  // :172-174
+  const uint64_t sum = (uint64_t)(int64_t)JavaStringHashCode(fileId) + (uint64_t)pageIndex;  // long add, wraps
+  return FloorMod((int32_t)(uint32_t)sum, kLockSize);                                        // (int) narrowing
+}
+
+bool LocalCacheManager::Put(const std::string& fileId, int64_t pageIndex, const void* page, int32_t len) {  // :206-246
+  if (mState.load() != READ_WRITE) return false;
+  return PutInternal(MakeKey(fileId, pageIndex), GetPageLockId(fileId, pageIndex), page, len);
+}
+
+bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* page, int32_t len) {  // :249-347
+  Key victim{};
+  PageMeta victimMeta{};
+  bool enoughSpace;
+  {
+    std::unique_lock<std::shared_mutex> pageLock(mPageLocks[lockId]);
+    {
+      std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+      if (mMetaStore->HasPage(k)) return true;  // :256-260 an existing page is NOT overwritten
+      enoughSpace = mMetaStore->Bytes() + len <= mCacheSize;
+      if (enoughSpace) {
+        mMetaStore->AddPage(k, PageMeta{len, lockId});
+      } else if (!mMetaStore->Evict(&victim, &victimMeta)) {
+        return false;  // :265-271
+      }
+    }
+    if (enoughSpace) {  // :274-285
+      if (mPageStore->Put(k, page, len) == APS_OK) return true;
+      UndoAddPage(k);
+      return false;
+    }
+  }
+  // two page locks in id order (:197-203), then the two-phase commit (:288-346)
+  const int32_t a = std::min(lockId, victimMeta.lockId), b = std::max(lockId, victimMeta.lockId);
+  std::unique_lock<std::shared_mutex> first(mPageLocks[a]);
+  std::unique_lock<std::shared_mutex> second;
+  if (b != a) second = std::unique_lock<std::shared_mutex>(mPageLocks[b]);
+  {
+    std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+    if (mMetaStore->HasPage(k)) return true;  // :296-300 a racing thread inserted it
+    if (!mMetaStore->RemovePage(victim)) {     // :301-309 benign race: victim already gone
+      mMetaStore->RemovePage(k);
+      return false;
+    }
+    enoughSpace = mMetaStore->Bytes() + len <= mCacheSize;                // :310
+    if (enoughSpace) mMetaStore->AddPage(k, PageMeta{len, lockId});      // :311-313
+  }
+  if (mPageStore->Delete(victim) != APS_OK) {  // :318-330 the victim is deleted whatever enoughSpace says
+    if (enoughSpace) UndoAddPage(k);
+    return false;
+  }
+  if (logEvictions) evicted.push_back(victim);
+  if (!enoughSpace) return false;  // :331-334 one victim per put
+  if (mPageStore->Put(k, page, len) == APS_OK) return true;
+  UndoAddPage(k);  // :339-344
+  return false;
+}
+
+void LocalCacheManager::UndoAddPage(const Key& k) {  // :349-357
+  std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+  mMetaStore->RemovePage(k);
+}
+
+int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int32_t pageOffset, int32_t bytesToRead,
+                               void* buffer, int32_t bufLen, int32_t offsetInBuffer) {  // :360-399
+  if (!(pageOffset <= mPageSize)) return kGetIllegalArgument;
+  if (!(bytesToRead <= bufLen - offsetInBuffer)) return kGetIllegalArgument;
+  if (mState.load() == NOT_IN_USE) return -1;
+  const Key k = MakeKey(fileId, pageIndex);
+  std::shared_lock<std::shared_mutex> pageLock(mPageLocks[GetPageLockId(fileId, pageIndex)]);
+  bool hasPage;
+  {
+    std::shared_lock<std::shared_mutex> metaLock(mMetaLock);
+    hasPage = mMetaStore->HasPage(k);  // hasPage does not touch the evictor
+  }
+  if (!hasPage) return 0;
+  int32_t got = 0;
+  const int rc = mPageStore->Get(k, pageOffset, bytesToRead, (uint8_t*)buffer + offsetInBuffer, bufLen - offsetInBuffer, &got);
+  if (rc == APS_EINVAL) return kGetIllegalArgument;  // IllegalArgumentException is not caught by getPage (:550)
+  if (rc != APS_OK || got != bytesToRead) {           // :544-549, :384-395
+    std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+    mMetaStore->RemovePage(k);
+    return -1;
+  }
+  return bytesToRead;
+}
+
+bool LocalCacheManager::Delete(const std::string& fileId, int64_t pageIndex) {  // :402-429
+  if (mState.load() != READ_WRITE) return false;
+  const Key k = MakeKey(fileId, pageIndex);
+  std::unique_lock<std::shared_mutex> pageLock(mPageLocks[GetPageLockId(fileId, pageIndex)]);
+  {
+    std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+    if (!mMetaStore->RemovePage(k)) return false;
+  }
+  return mPageStore->Delete(k) == APS_OK;
+}
+
+void LocalCacheManager::RestoreOrInit() {  // :441-464
+  if (!Restore()) {
+    mMetaStore->Reset();
+    mState = NOT_IN_USE;  // a GPU store cannot be "re-created in place"; the caller falls back (FileSystem.java:156-158)
+    return;
+  }
+  mState = READ_WRITE;
+}
+
+bool LocalCacheManager::Restore() {  // :466-509
+  std::vector<std::pair<Key, int64_t>> pages;
+  if (mPageStore->GetPages(&pages) != APS_OK) return false;
+  for (auto& p : pages) {
+    const bool enoughSpace = mMetaStore->Bytes() + p.second <= mPageStore->GetCacheSize();
+    const std::string fileId = mCodec.Decode(p.first.hi, p.first.lo);
+    if (enoughSpace) mMetaStore->AddPage(p.first, PageMeta{p.second, GetPageLockId(fileId, (int64_t)p.first.idx)});
+    else if (mPageStore->Delete(p.first) != APS_OK) return false;
+  }
+  return true;
+}
+
+void FillSyntheticPage(uint64_t seed, uint64_t file, uint64_t index, uint8_t* out, int64_t len) {
+  const uint64_t s = seed ^ (file << 32) ^ index;
+  for (int64_t k = 0; k * 8 < len; ++k) {
+    uint64_t z = s + (uint64_t)(k + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    memcpy(out + 8 * k, &z, (size_t)std::min<int64_t>(8, len - 8 * k));
+  }
+}
+
+}  // namespace alluxio_b200
+
+// ==================================================================================== C view
+
+using namespace alluxio_b200;
+
+struct apc_manager {
+  std::unique_ptr<LocalCacheManager> mgr;
+  GpuPageStore* gpu = nullptr;  // owned by mgr
+};
+struct apc_evictor {
+  std::unique_ptr<CacheEvictor> ev;
+  FileKeyCodec codec;
+};
+struct apc_meta {
+  std::unique_ptr<MetaStore> meta;
+  FileKeyCodec codec;
+};
+
+static Key KeyOf(FileKeyCodec& c, const char* f, int64_t i) {
+  Key k;
+  c.Encode(f, &k.hi, &k.lo);
+  k.idx = (uint64_t)i;
+  return k;
+}
+static void CopyName(const std::string& s, char* out, size_t cap) {
+  if (!cap) return;
+  strncpy(out, s.c_str(), cap - 1);
+  out[cap - 1] = 0;
+}
+
+extern "C" {
+
+int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_logbase, apc_manager** out) {
+  if (!cfg || !evictor || !out) return APS_EINVAL;
+  *out = nullptr;
+  auto ev = CacheEvictor::Create(evictor, lfu_logbase);
+  if (!ev) return APS_EINVAL;
+  std::unique_ptr<GpuPageStore> store;
+  const int rc = GpuPageStore::Open(*cfg, &store);
+  if (rc != APS_OK) return rc;
+  apc_manager* m = new apc_manager();
+  m->gpu = store.get();
+  m->mgr.reset(new LocalCacheManager(cfg->page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(store)));
+  *out = m;
+  return APS_OK;
+}
+int apc_manager_close(apc_manager* m) {
+  delete m;
+  return APS_OK;
+}
+int apc_put(apc_manager* m, const char* f, int64_t i, const void* page, int32_t len) { return m->mgr->Put(f, i, page, len); }
+int32_t apc_get(apc_manager* m, const char* f, int64_t i, int32_t page_offset, int32_t bytes_to_read, void* buffer,
+                int32_t buffer_len, int32_t offset_in_buffer) {
+  return m->mgr->Get(f, i, page_offset, bytes_to_read, buffer, buffer_len, offset_in_buffer);
+}
+int apc_delete(apc_manager* m, const char* f, int64_t i) { return m->mgr->Delete(f, i); }
+int apc_state(apc_manager* m) { return m->mgr->state(); }
+int64_t apc_bytes(apc_manager* m) { return m->mgr->meta()->Bytes(); }
+int64_t apc_pages(apc_manager* m) { return m->mgr->meta()->Pages(); }
+int32_t apc_page_lock_id(apc_manager* m, const char* f, int64_t i) { return m->mgr->GetPageLockId(f, i); }
+int apc_set_store_faults(apc_manager* m, uint32_t mask) { return aps_set_faults(m->gpu->handle(), mask); }
+aps_store* apc_store(apc_manager* m) { return m->gpu->handle(); }
+void apc_file_key(apc_manager* m, const char* f, uint64_t* hi, uint64_t* lo) { m->mgr->codec()->Encode(f, hi, lo); }
+int32_t apc_java_string_hashcode(const char* utf8) { return JavaStringHashCode(utf8); }
+
+// CACHE/LocalCacheFileInStream.java:175-223 + readExternalPage :291-310
+int32_t apc_positioned_read(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst, int32_t len,
+                            apc_external_read external, void* user, int64_t* from_cache, int64_t* from_external) {
+  if (len < 0 || pos < 0) return APC_GET_ILLEGAL_ARGUMENT;
+  if (len == 0) return 0;
+  if (pos >= file_len) return -1;
+  LocalCacheManager* mgr = m->mgr.get();
+  const int64_t ps = mgr->pageSize();
+  int32_t total = 0;
+  int64_t cur = pos;
+  const int64_t toRead = std::min<int64_t>(len, file_len - pos);
+  std::vector<uint8_t> page;
+  while (total < toRead) {
+    const int64_t pageIdx = cur / ps;
+    const int32_t pageOff = (int32_t)(cur % ps);
+    const int32_t inPage = (int32_t)std::min<int64_t>(ps - pageOff, toRead - total);
+    const int32_t got = mgr->Get(file_id, pageIdx, pageOff, inPage, dst, len, total);
+    if (got > 0) {
+      total += got;
+      cur += got;
+      if (from_cache) *from_cache += got;
+    } else {
+      const int64_t pageStart = cur - (cur % ps);
+      const int32_t plen = (int32_t)std::min<int64_t>(ps, file_len - pageStart);
+      page.resize((size_t)plen);
+      int32_t have = 0;
+      while (have < plen) {
+        const int r = external(user, pageStart + have, page.data() + have, plen - have);
+        if (r <= 0) break;
+        have += r;
+      }
+      if (have != plen) return -1;  // "Failed to read complete page from external storage"
+      memcpy((uint8_t*)dst + total, page.data() + pageOff, (size_t)inPage);
+      total += inPage;
+      cur += inPage;
+      if (from_external) *from_external += inPage;
+      mgr->Put(file_id, pageIdx, page.data(), plen);
+    }
+  }
+  return total;
+}
+
+int64_t apc_replay(apc_manager* m, int64_t n, const int64_t* file, const int64_t* page, const int32_t* page_len,
+                   uint64_t seed, int verify, uint8_t* hit, uint8_t* put_ok, int64_t* victim_file, int64_t* victim_page,
+                   int64_t victims_cap, int64_t* final_pages, int64_t* final_bytes, int64_t* verify_failures) {
+  LocalCacheManager* mgr = m->mgr.get();
+  mgr->logEvictions = true;
+  mgr->evicted.clear();
+  int64_t nv = 0, bad = 0;
+  std::vector<uint8_t> buf, want;
+  for (int64_t k = 0; k < n; ++k) {
+    const std::string f = std::to_string(file[k]);
+    const int32_t len = page_len[k];
+    buf.resize((size_t)std::max(len, 1));
+    const int32_t got = mgr->Get(f, page[k], 0, len, buf.data(), len, 0);
+    hit[k] = got > 0;
+    put_ok[k] = 255;
+    if (got > 0) {
+      if (verify) {
+        want.resize((size_t)len);
+        FillSyntheticPage(seed, (uint64_t)file[k], (uint64_t)page[k], want.data(), len);
+        if (memcmp(want.data(), buf.data(), (size_t)len) != 0) ++bad;
+      }
+    } else {
+      FillSyntheticPage(seed, (uint64_t)file[k], (uint64_t)page[k], buf.data(), len);
+      put_ok[k] = mgr->Put(f, page[k], buf.data(), len) ? 1 : 0;
+    }
+    for (const Key& v : mgr->evicted) {
+      if (nv < victims_cap) {
+        victim_file[nv] = (int64_t)v.lo;  // decimal ids encode as (0, value)
+        victim_page[nv] = (int64_t)v.idx;
+      }
+      ++nv;
+    }
+    mgr->evicted.clear();
+  }
+  mgr->logEvictions = false;
+  if (final_pages) *final_pages = mgr->meta()->Pages();
+  if (final_bytes) *final_bytes = mgr->meta()->Bytes();
+  if (verify_failures) *verify_failures = bad;
+  return nv;
+}
+
+// ---- policy objects on their own
+apc_evictor* apc_evictor_create(const char* kind, double lfu_logbase) {
+  auto ev = CacheEvictor::Create(kind, lfu_logbase);
+  if (!ev) return nullptr;
+  apc_evictor* e = new apc_evictor();
+  e->ev = std::move(ev);
+  return e;
+}
+void apc_evictor_destroy(apc_evictor* e) { delete e; }
+void apc_evictor_update_on_get(apc_evictor* e, const char* f, int64_t i) { e->ev->UpdateOnGet(KeyOf(e->codec, f, i)); }
+void apc_evictor_update_on_put(apc_evictor* e, const char* f, int64_t i) { e->ev->UpdateOnPut(KeyOf(e->codec, f, i)); }
+void apc_evictor_update_on_delete(apc_evictor* e, const char* f, int64_t i) { e->ev->UpdateOnDelete(KeyOf(e->codec, f, i)); }
+void apc_evictor_reset(apc_evictor* e) { e->ev->Reset(); }
+int apc_evictor_evict(apc_evictor* e, char* file_out, size_t cap, int64_t* index_out) {
+  Key v;
+  if (!e->ev->Evict(&v)) return 0;
+  CopyName(e->codec.Decode(v.hi, v.lo), file_out, cap);
+  *index_out = (int64_t)v.idx;
+  return 1;
+}
+
+apc_meta* apc_meta_create(const char* evictor, double lfu_logbase) {
+  auto ev = CacheEvictor::Create(evictor, lfu_logbase);
+  if (!ev) return nullptr;
+  apc_meta* m = new apc_meta();
+  m->meta.reset(new MetaStore(std::move(ev)));
+  return m;
+}
+void apc_meta_destroy(apc_meta* m) { delete m; }
+int apc_meta_has_page(apc_meta* m, const char* f, int64_t i) { return m->meta->HasPage(KeyOf(m->codec, f, i)); }
+void apc_meta_add_page(apc_meta* m, const char* f, int64_t i, int64_t size) { m->meta->AddPage(KeyOf(m->codec, f, i), PageMeta{size, 0}); }
+int apc_meta_get_page_info(apc_meta* m, const char* f, int64_t i, int64_t* size) {
+  PageMeta pm;
+  if (!m->meta->GetPageInfo(KeyOf(m->codec, f, i), &pm)) return 0;
+  *size = pm.size;
+  return 1;
+}
+int apc_meta_remove_page(apc_meta* m, const char* f, int64_t i) { return m->meta->RemovePage(KeyOf(m->codec, f, i)); }
+int64_t apc_meta_bytes(apc_meta* m) { return m->meta->Bytes(); }
+int64_t apc_meta_pages(apc_meta* m) { return m->meta->Pages(); }
+void apc_meta_reset(apc_meta* m) { m->meta->Reset(); }
+int apc_meta_evict(apc_meta* m, char* file_out, size_t cap, int64_t* index_out, int64_t* size_out) {
+  Key v;
+  PageMeta pm;
+  if (!m->meta->Evict(&v, &pm)) return 0;
+  CopyName(m->codec.Decode(v.hi, v.lo), file_out, cap);
+  *index_out = (int64_t)v.idx;
+  *size_out = pm.size;
+  return 1;
+}
+
+}  // extern "C"

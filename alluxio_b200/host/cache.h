@@ -1,0 +1,177 @@
+// Host-side cache layer: a native mirror of the reference's Java classes that sit above the
+// PageStore boundary, for embedders without a JVM.  Same names, argument meaning and results as
+//   CACHE/PageId.java, CACHE/CacheEvictor.java, CACHE/evictor/LRUCacheEvictor.java,
+//   CACHE/evictor/LFUCacheEvictor.java, CACHE/DefaultMetaStore.java, CACHE/LocalCacheManager.java,
+//   CACHE/LocalCacheFileInStream.java (page arithmetic)
+// (CACHE/ = /root/reference/core/client/fs/src/main/java/alluxio/client/file/cache/), but its own
+// design: ids are turned into fixed 24-byte keys once at the API edge, policy state lives in index-
+// linked node pools, and the manager is thread-safe with the reference's lock hierarchy.
+// This is product code: it never touches oracle/.
+#pragma once
+#include <atomic>
+#include <cstdint>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <shared_mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/aps.h"
+
+namespace alluxio_b200 {
+
+// ---- keys -----------------------------------------------------------------------------------------
+struct Key {
+  uint64_t hi, lo, idx;
+  bool operator==(const Key& o) const { return hi == o.hi && lo == o.lo && idx == o.idx; }
+};
+struct KeyHash {
+  size_t operator()(const Key& k) const {
+    uint64_t z = k.idx + 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z ^= k.lo;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= k.hi;
+    return (size_t)(z ^ (z >> 31));
+  }
+};
+
+int32_t JavaStringHashCode(const std::string& utf8);  // String.hashCode over UTF-16 units
+
+// String file id -> 128 bits, collision free: decimal longs -> (0, v); 32 lower-case hex
+// chars -> (hi, lo) unless hi is 0 or all ones; anything else interned -> (all ones, n).
+class FileKeyCodec {
+ public:
+  void Encode(const std::string& fileId, uint64_t* hi, uint64_t* lo);
+  std::string Decode(uint64_t hi, uint64_t lo);
+ private:
+  std::mutex mMu;
+  std::unordered_map<std::string, uint64_t> mIds;
+  std::vector<std::string> mNames;
+};
+
+// ---- index-linked list pool (shared by the evictors) ---------------------------------------------------
+struct ListNode {
+  Key key;
+  int32_t prev, next;
+};
+class NodePool {
+ public:
+  int32_t Alloc(const Key& k);
+  void Free(int32_t n);
+  ListNode& operator[](int32_t n) { return mNodes[(size_t)n]; }
+ private:
+  std::vector<ListNode> mNodes;
+  std::vector<int32_t> mFree;
+};
+struct ListHead {
+  int32_t head = -1, tail = -1;
+  bool Empty() const { return head < 0; }
+};
+void ListPushBack(NodePool& p, ListHead& l, int32_t n);
+void ListUnlink(NodePool& p, ListHead& l, int32_t n);
+
+// ---- CACHE/CacheEvictor.java:26-69 ---------------------------------------------------------------------
+class CacheEvictor {
+ public:
+  virtual ~CacheEvictor() {}
+  virtual void UpdateOnGet(const Key& k) = 0;
+  virtual void UpdateOnPut(const Key& k) = 0;
+  virtual void UpdateOnDelete(const Key& k) = 0;
+  virtual bool Evict(Key* victim) = 0;  // false == null; the victim is NOT removed
+  virtual void Reset() = 0;
+  static std::unique_ptr<CacheEvictor> Create(const std::string& kind, double lfuLogBase);
+};
+
+// ---- CACHE/DefaultMetaStore.java:33-132 ----------------------------------------------------------------
+struct PageMeta {
+  int64_t size;
+  int32_t lockId;  // LocalCacheManager.getPageLockId of this page, kept so a victim's lock is known
+};
+class MetaStore {
+ public:
+  explicit MetaStore(std::unique_ptr<CacheEvictor> e) : mEvictor(std::move(e)) {}
+  bool HasPage(const Key& k) const { return mPages.find(k) != mPages.end(); }
+  void AddPage(const Key& k, const PageMeta& m);
+  bool GetPageInfo(const Key& k, PageMeta* out);  // false == PageNotFoundException; refreshes the evictor
+  bool RemovePage(const Key& k);                  // false == PageNotFoundException
+  int64_t Bytes() const { return mBytes.load(); }
+  int64_t Pages() const { return mCount.load(); }
+  void Reset();
+  bool Evict(Key* victim, PageMeta* meta);  // false == null
+ private:
+  std::unordered_map<Key, PageMeta, KeyHash> mPages;
+  std::atomic<int64_t> mBytes{0}, mCount{0};
+  std::unique_ptr<CacheEvictor> mEvictor;
+};
+
+// ---- the boundary, CACHE/PageStore.java:37-181 -----------------------------------------------------------
+class PageStore {
+ public:
+  virtual ~PageStore() {}
+  virtual int Put(const Key& k, const void* page, int32_t len) = 0;  // aps status
+  virtual int Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) = 0;
+  virtual int Delete(const Key& k) = 0;
+  virtual int GetPages(std::vector<std::pair<Key, int64_t>>* out) = 0;
+  virtual int64_t GetCacheSize() const = 0;
+};
+
+// PageStoreType.GPU: the HBM slab + table behind include/aps.h.
+class GpuPageStore : public PageStore {
+ public:
+  static int Open(const aps_config& cfg, std::unique_ptr<GpuPageStore>* out);
+  ~GpuPageStore() override;
+  int Put(const Key& k, const void* page, int32_t len) override;
+  int Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) override;
+  int Delete(const Key& k) override;
+  int GetPages(std::vector<std::pair<Key, int64_t>>* out) override;
+  int64_t GetCacheSize() const override { return (int64_t)mCacheBytes; }
+  aps_store* handle() { return mStore; }
+ private:
+  aps_store* mStore = nullptr;
+  uint64_t mCacheBytes = 0;
+};
+
+// ---- CACHE/LocalCacheManager.java:75-627 (sync write, sync restore) -------------------------------------
+enum State { NOT_IN_USE = 0, READ_ONLY = 1, READ_WRITE = 2 };
+constexpr int32_t kGetIllegalArgument = -2;
+
+class LocalCacheManager {
+ public:
+  LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store);
+  bool Put(const std::string& fileId, int64_t pageIndex, const void* page, int32_t len);
+  int32_t Get(const std::string& fileId, int64_t pageIndex, int32_t pageOffset, int32_t bytesToRead, void* buffer,
+              int32_t bufLen, int32_t offsetInBuffer);
+  bool Delete(const std::string& fileId, int64_t pageIndex);
+  State state() const { return mState.load(); }
+  int64_t pageSize() const { return mPageSize; }
+  int32_t GetPageLockId(const std::string& fileId, int64_t pageIndex) const;
+  MetaStore* meta() { return mMetaStore.get(); }
+  PageStore* store() { return mPageStore.get(); }
+  FileKeyCodec* codec() { return &mCodec; }
+  // eviction log for replays (cleared by the caller)
+  std::vector<Key> evicted;
+  bool logEvictions = false;
+ private:
+  static constexpr int kLockSize = 1024;
+  Key MakeKey(const std::string& fileId, int64_t pageIndex);
+  bool PutInternal(const Key& k, int32_t lockId, const void* page, int32_t len);
+  void UndoAddPage(const Key& k);
+  void RestoreOrInit();
+  bool Restore();
+  int64_t mPageSize, mCacheSize;
+  std::unique_ptr<MetaStore> mMetaStore;
+  std::unique_ptr<PageStore> mPageStore;
+  FileKeyCodec mCodec;
+  std::shared_mutex mPageLocks[kLockSize];
+  std::shared_mutex mMetaLock;
+  std::atomic<State> mState;
+};
+
+// Page payload of the benchmarks and replays: 64-bit word k of page (file, index) is the k-th
+// splitmix64 output for seed ^ (file << 32) ^ index.
+void FillSyntheticPage(uint64_t seed, uint64_t file, uint64_t index, uint8_t* out, int64_t len);
+
+}  // namespace alluxio_b200

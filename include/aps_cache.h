@@ -1,0 +1,102 @@
+/*
+ * aps_cache.h -- flat C view of the host-side cache layer (libaps_host.so).
+ *
+ * In an Alluxio deployment this layer IS the reference's Java code, unchanged: LocalCacheManager,
+ * DefaultMetaStore and the evictors keep running in the JVM and drive the GPU store through the
+ * PageStore interface.  Where there is no JVM (this repository's tests, bench, and
+ * C/C++ embedders) the same logic is provided natively by alluxio_b200/host/: a C++ mirror with the
+ * reference's names, argument meaning and results.  This header exposes it to C and ctypes.
+ *
+ * CACHE/ = /root/reference/core/client/fs/src/main/java/alluxio/client/file/cache/.
+ */
+#ifndef APS_CACHE_H_
+#define APS_CACHE_H_
+
+#include "aps.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct apc_manager apc_manager; /* LocalCacheManager over a GpuPageStore */
+typedef struct apc_evictor apc_evictor; /* CacheEvictor */
+typedef struct apc_meta apc_meta;       /* DefaultMetaStore */
+
+/* CacheManager.State, CACHE/CacheManager.java:39-65 */
+#define APC_NOT_IN_USE 0
+#define APC_READ_ONLY 1
+#define APC_READ_WRITE 2
+/* get() result standing for the IllegalArgumentException of Preconditions.checkArgument,
+ * CACHE/LocalCacheManager.java:362-366 */
+#define APC_GET_ILLEGAL_ARGUMENT (-2)
+
+/* LocalCacheManager.create(conf) with sync write + sync restore (CACHE/LocalCacheManager.java:102-138):
+ * opens a GpuPageStore from cfg (cfg->cache_bytes = alluxio.user.client.cache.size, cfg->page_size =
+ * ...page.size), restores (an HBM store starts empty) and goes READ_WRITE.
+ * evictor: "LRU" (evictor/LRUCacheEvictor.java), "LFU" (evictor/LFUCacheEvictor.java) or "FIFO" (the
+ * test double of CTEST/LocalCacheManagerTest.java:731-761). */
+APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_logbase, apc_manager** out);
+APS_API int apc_manager_close(apc_manager* m);
+/* CacheManager.put(PageId, byte[]) -> boolean, CACHE/LocalCacheManager.java:206-347 */
+APS_API int apc_put(apc_manager* m, const char* file_id, int64_t page_index, const void* page, int32_t len);
+/* CacheManager.get(PageId, pageOffset, bytesToRead, buffer, offsetInBuffer) -> bytes read, 0 on a
+ * miss, -1 on error, CACHE/LocalCacheManager.java:360-399 */
+APS_API int32_t apc_get(apc_manager* m, const char* file_id, int64_t page_index, int32_t page_offset,
+                        int32_t bytes_to_read, void* buffer, int32_t buffer_len, int32_t offset_in_buffer);
+/* CacheManager.delete(PageId) -> boolean, CACHE/LocalCacheManager.java:402-429 */
+APS_API int apc_delete(apc_manager* m, const char* file_id, int64_t page_index);
+APS_API int apc_state(apc_manager* m);
+APS_API int64_t apc_bytes(apc_manager* m); /* MetaStore.bytes() */
+APS_API int64_t apc_pages(apc_manager* m); /* MetaStore.pages() */
+APS_API int32_t apc_page_lock_id(apc_manager* m, const char* file_id, int64_t page_index); /* :172-174 */
+APS_API int apc_set_store_faults(apc_manager* m, uint32_t fault_mask);                     /* APS_FAULT_* */
+APS_API aps_store* apc_store(apc_manager* m);
+
+/* LocalCacheFileInStream.positionedRead (CACHE/LocalCacheFileInStream.java:175-223): reads
+ * [pos, pos+len) of a file of file_len bytes through the cache; pages that miss are fetched whole from
+ * `external` (readExternalPage, :291-310) and put into the cache.  Returns bytes read or -1 at EOF /
+ * on an external read failure.  Counters (optional): bytes served from the cache / from outside. */
+typedef int (*apc_external_read)(void* user, int64_t file_pos, void* dst, int32_t len); /* returns bytes read */
+APS_API int32_t apc_positioned_read(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst,
+                                    int32_t len, apc_external_read external, void* user, int64_t* bytes_from_cache,
+                                    int64_t* bytes_from_external);
+
+/* Trace replay, BASELINE config 3: for every access run the reference read flow -- get; on a miss the
+ * page (page_len[k] bytes of the synthetic payload for (file, page), seed) is put.  file ids are the
+ * decimal strings of file[k].  Outputs as in the oracle's replay so they can be compared element by
+ * element: hit[k], put_ok[k] (255 = no put), victims in eviction order, final page/byte counts.
+ * verify != 0 additionally checks every hit's bytes against the generator. Returns victims, or -1. */
+APS_API int64_t apc_replay(apc_manager* m, int64_t n, const int64_t* file, const int64_t* page, const int32_t* page_len,
+                           uint64_t seed, int verify, uint8_t* hit, uint8_t* put_ok, int64_t* victim_file,
+                           int64_t* victim_page, int64_t victims_cap, int64_t* final_pages, int64_t* final_bytes,
+                           int64_t* verify_failures);
+
+/* ---- policy objects on their own (no GPU needed) ------------------------------------------------ */
+APS_API apc_evictor* apc_evictor_create(const char* kind, double lfu_logbase);
+APS_API void apc_evictor_destroy(apc_evictor* e);
+APS_API void apc_evictor_update_on_get(apc_evictor* e, const char* file_id, int64_t page_index);
+APS_API void apc_evictor_update_on_put(apc_evictor* e, const char* file_id, int64_t page_index);
+APS_API void apc_evictor_update_on_delete(apc_evictor* e, const char* file_id, int64_t page_index);
+APS_API void apc_evictor_reset(apc_evictor* e);
+/* 1 and the victim, or 0 for Java null */
+APS_API int apc_evictor_evict(apc_evictor* e, char* file_out, size_t cap, int64_t* index_out);
+
+APS_API apc_meta* apc_meta_create(const char* evictor, double lfu_logbase);
+APS_API void apc_meta_destroy(apc_meta* m);
+APS_API int apc_meta_has_page(apc_meta* m, const char* file_id, int64_t page_index);
+APS_API void apc_meta_add_page(apc_meta* m, const char* file_id, int64_t page_index, int64_t size);
+APS_API int apc_meta_get_page_info(apc_meta* m, const char* file_id, int64_t page_index, int64_t* size); /* 0 = not found */
+APS_API int apc_meta_remove_page(apc_meta* m, const char* file_id, int64_t page_index);                   /* 0 = not found */
+APS_API int64_t apc_meta_bytes(apc_meta* m);
+APS_API int64_t apc_meta_pages(apc_meta* m);
+APS_API void apc_meta_reset(apc_meta* m);
+APS_API int apc_meta_evict(apc_meta* m, char* file_out, size_t cap, int64_t* index_out, int64_t* size_out);
+
+/* String file id -> 128-bit key, and Java's String.hashCode for the lock striping. */
+APS_API void apc_file_key(apc_manager* m, const char* file_id, uint64_t* hi, uint64_t* lo);
+APS_API int32_t apc_java_string_hashcode(const char* utf8);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APS_CACHE_H_ */

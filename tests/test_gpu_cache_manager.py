@@ -1,0 +1,199 @@
+"""-m gpu: the native LocalCacheManager driving the GPU page store -- the reference's
+LocalCacheManagerTest cases (CTEST/LocalCacheManagerTest.java), LocalCacheFileInStreamTest-style
+reads, and whole-trace replays compared element by element with the oracle (hit/miss vector, put
+results, victim sequence, final residency)."""
+import numpy as np
+import pytest
+
+from conftest import increasing
+from oracle import binding as orc
+
+pytestmark = pytest.mark.gpu
+
+PAGE_SIZE = 1024
+CACHE_SIZE = 512 * 1024
+PAGE1, PAGE2 = increasing(PAGE_SIZE), increasing(255, PAGE_SIZE)
+
+
+def PID(f, i):
+    from alluxio_b200.page_store import PageId
+    return PageId(f, i)
+
+
+def manager(cache_size=CACHE_SIZE, evictor="FIFO", page_size=PAGE_SIZE, slab_slots=0, **kw):
+    from alluxio_b200.cache import LocalCacheManager
+    return LocalCacheManager(page_size, cache_size, evictor=evictor, slab_slots=slab_slots, **kw)
+
+
+PAGE_ID1, PAGE_ID2 = ("0L", 0), ("1L", 1)
+
+
+def test_put_new_put_exist_get_delete():
+    m = manager()
+    p1, p2 = PID(*PAGE_ID1), PID(*PAGE_ID2)
+    buf = bytearray(PAGE_SIZE)
+    assert m.state() == m.READ_WRITE
+    assert m.get(p1, PAGE_SIZE, buf) == 0                       # getNotExist
+    assert not m.delete(p1)                                     # deleteNotExist
+    assert m.put(p1, PAGE1)
+    assert m.put(p1, PAGE2)                                     # putExist: old bytes stay
+    assert m.get(p1, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1
+    for off in (0, 1, PAGE_SIZE // 2, PAGE_SIZE - 1):           # getOffset
+        assert m.get(p1, PAGE_SIZE - off, buf, page_offset=off) == PAGE_SIZE - off
+        assert bytes(buf[:PAGE_SIZE - off]) == PAGE1[off:]
+    with pytest.raises(ValueError):                             # getNotEnoughSpaceException
+        m.get(p1, PAGE_SIZE, bytearray(PAGE_SIZE - 1))
+    with pytest.raises(ValueError):
+        m.get(p1, 1, buf, page_offset=PAGE_SIZE + 1)
+    assert m.delete(p1)
+    assert m.get(p1, PAGE_SIZE, buf) == 0
+    assert (m.bytes(), m.pages()) == (0, 0)
+    m.close()
+
+
+def test_put_evict_and_more_than_capacity():
+    m = manager(cache_size=PAGE_SIZE)
+    p1, p2 = PID(*PAGE_ID1), PID(*PAGE_ID2)
+    buf = bytearray(PAGE_SIZE)
+    assert m.put(p1, PAGE1) and m.put(p2, PAGE2)
+    assert m.get(p1, PAGE_SIZE, buf) == 0
+    assert m.get(p2, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE2
+    m.close()
+    m = manager()
+    cache_pages = CACHE_SIZE // PAGE_SIZE
+    for i in range(2 * cache_pages):                            # putMoreThanCacheCapacity (FIFO order)
+        m.put(PID("3", i), increasing(i, PAGE_SIZE))
+        if i >= cache_pages:
+            assert m.get(PID("3", i - cache_pages), PAGE_SIZE, buf) == 0
+            assert m.get(PID("3", i - cache_pages + 1), PAGE_SIZE, buf) == PAGE_SIZE
+            assert bytes(buf) == increasing(i - cache_pages + 1, PAGE_SIZE)
+    m.close()
+
+
+def test_byte_based_capacity_one_victim_per_put():
+    small, n = 8, PAGE_SIZE // 8
+    m = manager(cache_size=PAGE_SIZE, slab_slots=n + 8)         # short pages need their own slots
+    for i in range(n):                                          # putSmallPages
+        assert m.put(PID(i, 0), increasing(i, small))
+    for i in range(n):
+        b = bytearray(small)
+        assert m.get(PID(i, 0), small, b) == small and bytes(b) == increasing(i, small)
+    assert m.put(PID(n, 0), increasing(-1 & 0xFF, small))       # evictSmallPageByPutSmallPage
+    assert m.get(PID(0, 0), small, bytearray(small)) == 0
+    big, big_id = increasing(0, PAGE_SIZE), PID(-1, 0)
+    for _ in range(n - 1):                                      # evictSmallPagesByPutPigPage
+        assert not m.put(big_id, big)
+    assert m.put(big_id, big)
+    b = bytearray(PAGE_SIZE)
+    assert m.get(big_id, PAGE_SIZE, b) == PAGE_SIZE and bytes(b) == big
+    for i in range(n):                                          # evictBigPagesByPutSmallPage
+        assert m.put(PID(1000 + i, 0), increasing(small))
+    m.close()
+
+
+def test_partial_pages_large_ids_and_short_read_drops_page():
+    m = manager()
+    for size in (1, PAGE_SIZE // 2, PAGE_SIZE - 1):             # putGetPartialPage
+        pid, data = PID("3", size), increasing(0, size)
+        assert m.put(pid, data)
+        b = bytearray(size)
+        assert m.get(pid, size, b) == size and bytes(b) == data
+    for idx in (2**63 - 2, 2**63 - 1):                          # putLargeId
+        pid = PID("0", idx)
+        m.put(pid, PAGE1)
+        b = bytearray(PAGE_SIZE)
+        assert m.get(pid, PAGE_SIZE, b) == PAGE_SIZE and bytes(b) == PAGE1
+    pid = PID("4", 0)
+    m.put(pid, increasing(0, 100))
+    assert m.get(pid, 200, bytearray(200)) == -1                # ret != bytesToRead -> -1, page dropped
+    assert m.get(pid, 100, bytearray(100)) == 0
+    m.close()
+
+
+def test_store_faults_leave_no_state():
+    m = manager()
+    p1, p2 = PID(*PAGE_ID1), PID(*PAGE_ID2)
+    buf = bytearray(PAGE_SIZE)
+    m.set_store_faulty(put=True)                                # recoverCacheFromFailedPut
+    assert not m.put(p1, PAGE1)
+    assert m.get(p1, PAGE_SIZE, buf) == 0
+    assert not m.put(p1, PAGE1)
+    m.set_store_faulty()
+    assert m.put(p1, PAGE1)
+    assert m.get(p1, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1
+    m.close()
+    m = manager(cache_size=PAGE_SIZE)                           # failedPageStoreDeleteOnEviction
+    m.set_store_faulty(delete=True)
+    assert m.put(p1, PAGE1)
+    assert not m.put(p2, PAGE2)
+    m.set_store_faulty()
+    assert m.put(p1, PAGE1)
+    assert m.get(p1, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1
+    m.close()
+
+
+def test_lock_ids_match_oracle():
+    m = manager()
+    store = orc.PageStore.open_mem(PAGE_SIZE, CACHE_SIZE)
+    om = orc.LocalCacheManager(store, PAGE_SIZE)
+    for f, i in [("0", 0), ("0", 2**63 - 1), ("polygenelubricants", 5), ("d41d8cd98f00b204e9800998ecf8427e", 77),
+                 ("/some/path/é", 12345678901234)]:
+        assert m.page_lock_id(PID(f, i)) == om.page_lock_id(orc.PageId(f, i))
+    m.close()
+
+
+def test_positioned_read_through_the_cache():
+    """CTEST/LocalCacheFileInStreamTest.java: reads across page boundaries; a miss fetches the whole
+    page from outside and caches it; the last page is short."""
+    ps = 4096
+    m = manager(cache_size=64 * ps, evictor="LRU", page_size=ps)
+    file_len = 5 * ps + 123
+    data = np.random.default_rng(5).integers(0, 256, file_len, dtype=np.uint8).tobytes()
+    calls = []
+
+    def external(pos, n):
+        calls.append((pos, n))
+        return data[pos:pos + n]
+
+    got, fc, fe = m.positioned_read("77", file_len, 100, 3 * ps, external)
+    assert got == data[100:100 + 3 * ps] and fc == 0 and fe == 3 * ps
+    assert [c[0] for c in calls] == [0, ps, 2 * ps, 3 * ps] and all(c[1] == ps for c in calls)
+    calls.clear()
+    got, fc, fe = m.positioned_read("77", file_len, 0, 4 * ps, external)     # all four pages now hit
+    assert got == data[:4 * ps] and (fc, fe) == (4 * ps, 0) and not calls
+    got, fc, fe = m.positioned_read("77", file_len, 5 * ps - 10, 1000, external)   # crosses into the short last page
+    assert got == data[5 * ps - 10:] and len(got) == 133
+    assert calls == [(4 * ps, ps), (5 * ps, 123)]
+    got, _, _ = m.positioned_read("77", file_len, file_len, 10, external)
+    assert got is None                                                        # EOF
+    assert m.pages() == 6 and m.bytes() == file_len
+    m.close()
+
+
+@pytest.mark.parametrize("evictor", ["LRU", "LFU", "FIFO"])
+def test_replay_matches_oracle_element_by_element(evictor):
+    """BASELINE config 3 in miniature: 64 KiB pages, Zipf(0.99) accesses, capacity << universe; the
+    evictor on the host drives GPU table inserts and erases.  Everything observable must equal the
+    oracle's replay of the same trace; returned bytes are checked against the generator."""
+    ps = 65536
+    n_ids, cap_pages, n_acc = 6000, 400, 12000
+    rng = np.random.default_rng(3)
+    ranks = np.arange(1, n_ids + 1, dtype=np.float64)
+    pz = ranks ** -0.99
+    pz /= pz.sum()
+    ids = rng.permutation(n_ids)[rng.choice(n_ids, size=n_acc, p=pz)]
+    files, pages = ids // 100, ids % 100
+    lens = np.where(pages == 99, 1000 + files, ps).astype(np.int32)   # last page of every file is short
+    cache_bytes = cap_pages * ps
+    want = orc.replay(evictor, ps, cache_bytes, files, pages, lens)
+    m = manager(cache_size=cache_bytes, evictor=evictor, page_size=ps, slab_slots=cap_pages + 128)
+    got = m.replay(files, pages, lens, seed=0xA11C10, verify=True)
+    assert got["verify_failures"] == 0
+    assert np.array_equal(got["hit"], want["hit"])
+    assert np.array_equal(got["put_ok"], want["put_ok"])
+    assert got["n_victims"] == want["n_victims"] > 0
+    assert np.array_equal(got["victims"], want["victims"])
+    assert (got["final_pages"], got["final_bytes"]) == (want["final_pages"], want["final_bytes"])
+    st = m.store_stats()
+    assert st["pages"] == got["final_pages"] and st["bytes"] == got["final_bytes"] and st["crc_mismatches"] == 0
+    m.close()

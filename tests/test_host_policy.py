@@ -1,0 +1,110 @@
+"""The product's native evictors and meta store (alluxio_b200/host, no GPU needed) against the
+reference's scripted sequences (CTEST/LRUCacheEvictorTest.java, CTEST/LFUCacheEvictorTest.java,
+CTEST/DefaultMetaStoreTest.java) and, on long random op sequences, against the oracle."""
+import numpy as np
+import pytest
+
+from alluxio_b200 import cache as apc
+from alluxio_b200.page_store import FileKeyCodec, PageId
+from oracle import binding as orc
+
+F, S, T = PageId("1L", 2), PageId("3L", 4), PageId("5L", 6)
+ONE, TWO, THREE, FOUR = PageId("1L", 1), PageId("2L", 2), PageId("3L", 3), PageId("4L", 4)
+
+
+def test_lru_scripted_sequences():
+    e = apc.CacheEvictor("LRU")
+    for p in (F, S, T, F):
+        e.update_on_get(p)
+    assert e.evict() == S; e.update_on_delete(S)
+    assert e.evict() == T; e.update_on_delete(T)
+    assert e.evict() == F and e.evict() == F  # evict() only peeks
+    e.reset()
+    assert e.evict() is None
+    for p in (F, S, T):
+        e.update_on_put(p)
+    e.update_on_delete(S)
+    assert e.evict() == F; e.update_on_delete(F)
+    assert e.evict() == T; e.update_on_delete(T)
+    assert e.evict() is None
+
+
+def test_lfu_scripted_sequences():
+    e = apc.CacheEvictor("LFU", 2.0)
+    for p in (ONE, ONE, TWO, TWO, THREE, THREE, TWO, THREE, ONE):   # evictUpdatedGetRecentOrder
+        e.update_on_get(p)
+    assert e.evict() == TWO; e.update_on_delete(TWO)
+    assert e.evict() == THREE; e.update_on_delete(THREE)
+    assert e.evict() == ONE
+    e.reset()
+    for p in (ONE, FOUR, FOUR, FOUR, FOUR):                          # evictDeleteSkippedBucket
+        e.update_on_get(p)
+    assert e.evict() == ONE; e.update_on_delete(ONE)
+    assert e.evict() == FOUR; e.update_on_delete(FOUR)
+    assert e.evict() is None
+    for p in (FOUR, TWO, FOUR, TWO, FOUR, ONE, FOUR):                # evictGetMixedOrder
+        e.update_on_get(p)
+    assert e.evict() == ONE; e.update_on_delete(ONE)
+    assert e.evict() == TWO; e.update_on_delete(TWO)
+    assert e.evict() == FOUR
+
+
+@pytest.mark.parametrize("kind", ["LRU", "LFU", "FIFO"])
+def test_evictors_match_oracle_on_random_sequences(kind):
+    rng = np.random.default_rng(hash(kind) % 1000)
+    ids = [PageId(str(f), i) for f in range(6) for i in range(10)] + [PageId("some/path", 3), PageId("x" * 40, 1)]
+    a, b = apc.CacheEvictor(kind, 2.0), orc.Evictor(kind, 2.0)
+    live = set()
+    for step in range(6000):
+        p = ids[rng.integers(len(ids))]
+        o = orc.PageId(p.file_id, p.page_index)
+        op = rng.integers(10)
+        if op < 4:
+            if kind == "FIFO" and p in live:
+                continue  # the FIFO double is only ever fed new ids by the manager
+            a.update_on_put(p); b.update_on_put(o); live.add(p)
+        elif op < 7:
+            if p in live or kind != "LFU":
+                a.update_on_get(p); b.update_on_get(o)
+                if kind != "FIFO":
+                    live.add(p)
+        elif op < 9:
+            a.update_on_delete(p); b.update_on_delete(o); live.discard(p)
+        va, vb = a.evict(), b.evict()
+        assert (va is None) == (vb is None), step
+        if va is not None:
+            assert (va.file_id, va.page_index) == (vb.file_id, vb.page_index), (kind, step)
+
+
+def test_meta_store_matches_reference_cases_and_oracle():
+    m = apc.MetaStore("LRU")
+    page = PageId("9L", 9)
+    assert not m.has_page(page)
+    with pytest.raises(apc.PageNotFoundException):
+        m.remove_page(page)
+    with pytest.raises(apc.PageNotFoundException):
+        m.get_page_info(page)
+    m.add_page(page, 1024)
+    assert m.has_page(page) and m.get_page_info(page) == (page, 1024)
+    m.add_page(F, 10); m.add_page(S, 20)
+    assert (m.bytes(), m.pages()) == (1054, 3)
+    m.has_page(page)
+    assert m.evict() == (page, 1024)          # hasPage does not refresh recency ...
+    m.get_page_info(page)
+    assert m.evict() == (F, 10)               # ... getPageInfo does
+    m.remove_page(F)
+    assert (m.bytes(), m.pages()) == (1044, 2)
+    m.reset()
+    assert (m.bytes(), m.pages()) == (0, 0) and m.evict() is None
+
+
+def test_java_string_hashcode_and_file_keys_agree_with_the_python_codec():
+    L = apc.lib()
+    for s in ("", "0", "hello", "polygenelubricants", "/a/b", "é中", "\U0001F600"):
+        assert L.apc_java_string_hashcode(s.encode("utf-8")) == orc.java_string_hashcode(s)
+    py = FileKeyCodec()
+    assert py.encode("123") == (0, 123)
+    assert py.encode("-1") == (0, 2**64 - 1)
+    assert py.encode("0123")[0] == 2**64 - 1          # not canonical -> interned
+    assert py.encode("d41d8cd98f00b204e9800998ecf8427e") == (0xd41d8cd98f00b204, 0xe9800998ecf8427e)
+    assert py.encode("0000000000000000ffffffffffffffff")[0] == 2**64 - 1  # reserved high word -> interned
