@@ -39,6 +39,10 @@ class aps_result(C.Structure):
     _fields_ = [("len", C.c_int32), ("crc", C.c_uint32)]
 
 
+class aps_shard_handle(C.Structure):
+    _fields_ = [("opaque", C.c_ubyte * 256)]
+
+
 class aps_stats_t(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("pages", "bytes", "slots_free", "table_capacity", "tombstones", "lookups",
                                            "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches", "slow_sms")]
@@ -63,6 +67,12 @@ SIGNATURES = {
     "aps_put_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_delete_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_lookup_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
+    "aps_shard_of": (_u32, [C.POINTER(aps_key), _u32]),
+    "aps_shard_export": (C.c_int, [_vp, C.POINTER(aps_shard_handle)]),
+    "aps_shard_attach": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "aps_shard_attach_local": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "aps_get_batch_sharded_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
+    "aps_get_batch_sharded": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_md5_batch_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp]),
     "aps_md5_batch": (C.c_int, [_i32, _u32, _vp, _vp, _vp]),
     "aps_crc32c_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),

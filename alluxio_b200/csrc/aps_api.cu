@@ -165,6 +165,10 @@ struct aps_store {
   uint32_t* d_rowshift = nullptr;  // x^(8*512*k) for k = 0 .. page_rows
   unsigned long long* d_timeline = nullptr;  // aps_debug_timeline
   uint32_t* d_sched = nullptr;               // CTA rank counters of the copy kernel (self-resetting)
+  // sharded cache: tables of all shards (own + peers mapped over NVLink), see aps_shard_attach
+  Table* d_shards = nullptr;
+  uint32_t n_shards = 0, my_shard = 0;
+  std::vector<void*> ipc_ptrs;  // peer allocations opened through CUDA IPC (closed in aps_close)
   uint32_t* d_done = nullptr;
   int* d_error = nullptr;
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
@@ -189,7 +193,7 @@ inline void count_launch(aps_store* s, uint64_t k = 1) {
 }
 
 int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_result* d_res, uint32_t* d_crc_out,
-                cudaStream_t st) {
+                cudaStream_t st, bool sharded = false) {
   const bool crc = (s->cfg.flags & APS_FLAG_CRC) != 0 || d_crc_out != nullptr;
   const CopyVariant& v = copy_variant();
   const uint32_t warps_per_block = v.threads / 32;
@@ -220,6 +224,8 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.steal = s->use_steal ? 1 : 0;
   a.sched = s->d_sched;
   a.sm_slow = s->dc->d_sm_slow;
+  a.shards = sharded ? s->d_shards : nullptr;
+  a.n_shards = sharded ? s->n_shards : 0;
   if (s->d_timeline) CUDA_TRY(cudaMemsetAsync(s->d_timeline, 0xFF, kTimelineWords * sizeof(unsigned long long), st));
   const uint64_t items = (uint64_t)n * tpj;
   uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, items);  // every SM takes part
@@ -300,6 +306,9 @@ void free_store(aps_store* s) {
   cudaFree(s->d_rowshift);
   cudaFree(s->d_timeline);
   cudaFree(s->d_sched);
+  cudaFree(s->d_shards);
+  for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
+  s->ipc_ptrs.clear();
   cudaFree(s->d_done);
   cudaFree(s->d_error);
   cudaFree(s->d_reqs);
@@ -616,7 +625,17 @@ int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_data, co
 
 // ---------------------------------------------------------------- host-array batched forms
 
+static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream, bool sharded);
+
 int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream) {
+  return get_batch_host(s, n, reqs, res, stream, false);
+}
+int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream) {
+  if (s && s->n_shards == 0) return APS_EINVAL;
+  return get_batch_host(s, n, reqs, res, stream, true);
+}
+
+static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream, bool sharded) {
   int rc = check_open(s);
   if (rc) return rc;
   if (n == 0) return APS_OK;
@@ -628,7 +647,8 @@ int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result*
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_get_req));
   CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
-  rc = aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
+  rc = sharded ? aps_get_batch_sharded_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st)
+               : aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
   if (rc) return rc;
   CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
   rc = check_device_error(s, st);  // also waits for the stream
@@ -835,6 +855,113 @@ int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_launches
   return APS_OK;
 }
 
+// ---------------------------------------------------------------- sharded cache (several GPUs)
+
+namespace {
+struct ShardHandleBlob {
+  cudaIpcMemHandle_t slab, entries, slot_crc;
+  uint64_t bucket_mask;
+  uint32_t page_size;
+  int32_t device;
+  uint32_t magic;
+};
+static_assert(sizeof(ShardHandleBlob) <= sizeof(aps_shard_handle), "handle blob must fit the opaque handle");
+constexpr uint32_t kShardMagic = 0x41505348u;  // "APSH"
+
+int install_shards(aps_store* s, const std::vector<Table>& tables, uint32_t my_shard) {
+  cudaFree(s->d_shards);
+  s->d_shards = nullptr;
+  CUDA_TRY(cudaMalloc(&s->d_shards, tables.size() * sizeof(Table)));
+  CUDA_TRY(cudaMemcpy(s->d_shards, tables.data(), tables.size() * sizeof(Table), cudaMemcpyHostToDevice));
+  s->n_shards = (uint32_t)tables.size();
+  s->my_shard = my_shard;
+  return APS_OK;
+}
+}  // namespace
+
+uint32_t aps_shard_of(const aps_key* key, uint32_t n_shards) { return (key && n_shards) ? shard_of(*key, n_shards) : 0; }
+
+int aps_shard_export(aps_store* s, aps_shard_handle* out) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!out) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  ShardHandleBlob b{};
+  CUDA_TRY(cudaIpcGetMemHandle(&b.slab, s->table.slab));
+  CUDA_TRY(cudaIpcGetMemHandle(&b.entries, s->table.entries));
+  CUDA_TRY(cudaIpcGetMemHandle(&b.slot_crc, s->table.slot_crc));
+  b.bucket_mask = s->table.bucket_mask;
+  b.page_size = s->table.page_size;
+  b.device = s->cfg.device;
+  b.magic = kShardMagic;
+  memset(out, 0, sizeof(*out));
+  memcpy(out, &b, sizeof(b));
+  return APS_OK;
+}
+
+int aps_shard_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const aps_shard_handle* handles) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!handles || n_shards == 0 || my_shard >= n_shards) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  std::vector<Table> tables(n_shards);
+  for (uint32_t i = 0; i < n_shards; ++i) {
+    if (i == my_shard) {
+      tables[i] = s->table;
+      continue;
+    }
+    ShardHandleBlob b;
+    memcpy(&b, &handles[i], sizeof(b));
+    if (b.magic != kShardMagic || b.page_size != s->table.page_size) return APS_EINVAL;
+    void *slab = nullptr, *entries = nullptr, *crc = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&slab, b.slab, cudaIpcMemLazyEnablePeerAccess));
+    s->ipc_ptrs.push_back(slab);
+    CUDA_TRY(cudaIpcOpenMemHandle(&entries, b.entries, cudaIpcMemLazyEnablePeerAccess));
+    s->ipc_ptrs.push_back(entries);
+    CUDA_TRY(cudaIpcOpenMemHandle(&crc, b.slot_crc, cudaIpcMemLazyEnablePeerAccess));
+    s->ipc_ptrs.push_back(crc);
+    tables[i] = Table{(Entry*)entries, b.bucket_mask, nullptr, nullptr, (uint32_t*)crc, nullptr, (uint8_t*)slab, b.page_size};
+  }
+  return install_shards(s, tables, my_shard);
+}
+
+int aps_shard_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, aps_store* const* stores) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!stores || n_shards == 0 || my_shard >= n_shards) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  std::vector<Table> tables(n_shards);
+  for (uint32_t i = 0; i < n_shards; ++i) {
+    aps_store* p = i == my_shard ? s : stores[i];
+    if (!p || p->closed || p->table.page_size != s->table.page_size) return APS_EINVAL;
+    if (p->cfg.device != s->cfg.device) {
+      cudaError_t e = cudaDeviceEnablePeerAccess(p->cfg.device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        snprintf(tl_cuda_error, sizeof(tl_cuda_error), "cudaDeviceEnablePeerAccess(%d): %s", p->cfg.device, cudaGetErrorString(e));
+        return APS_ECUDA;
+      }
+      cudaGetLastError();
+    }
+    tables[i] = p->table;
+    tables[i].free_slots = nullptr;
+    tables[i].free_top = nullptr;
+    if (i != my_shard) tables[i].counters = nullptr;
+  }
+  return install_shards(s, tables, my_shard);
+}
+
+int aps_get_batch_sharded_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n == 0) return APS_OK;
+  if (n > s->cfg.max_batch || !d_reqs || !d_res || s->n_shards == 0) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  return launch_copy(s, n, d_reqs, d_res, nullptr, st, /*sharded=*/true);
+}
+
 int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_ctas) {
   int rc = check_open(s);
   if (rc) return rc;
@@ -849,6 +976,9 @@ int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_cta
     CUDA_TRY(cudaDeviceSynchronize());
     cudaFree(s->d_timeline);
   cudaFree(s->d_sched);
+  cudaFree(s->d_shards);
+  for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
+  s->ipc_ptrs.clear();
     s->d_timeline = nullptr;
   }
   return APS_OK;

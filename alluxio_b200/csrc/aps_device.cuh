@@ -38,6 +38,12 @@ __host__ __device__ __forceinline__ uint64_t hash_key(const aps_key& k) {
   return mix64(k.file_hi ^ mix64(k.file_lo ^ mix64(k.page_index + 0x9E3779B97F4A7C15ull)));
 }
 
+// Owner shard of a page in a cache sharded over several GPUs.  Uses the high half of the key hash:
+// the low bits pick the bucket inside the owner's table and must stay uniform there.
+__host__ __device__ __forceinline__ uint32_t shard_of(const aps_key& k, uint32_t n_shards) {
+  return (uint32_t)((hash_key(k) >> 32) % n_shards);
+}
+
 enum Counter { kCtrPages = 0, kCtrBytes, kCtrTombs, kCtrLookups, kCtrProbes, kCtrBytesCopied, kCtrCrcMismatch, kNumCounters };
 
 struct Table {

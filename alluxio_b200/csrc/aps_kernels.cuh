@@ -208,6 +208,8 @@ struct CopyArgs {
   int* error_flag;           // set if the shared-memory window is not where the kernel needs it
   unsigned long long* timeline;  // optional (aps_debug_timeline)
   int steal;                 // intra-CTA work stealing on/off
+  const Table* shards;       // kGet with n_shards > 1: table + slab of every shard (peer memory mapped over NVLink)
+  uint32_t n_shards;         // 0 or 1: only this GPU's table
   uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
   const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
 };
@@ -327,8 +329,11 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       if (kGet) {
         // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
         const aps_get_req rq = a.reqs[job];
+        // sharded cache: the page lives on GPU shard_of(key); its table and slab are read in place over
+        // NVLink (P2P), so lookup, gather and CRC stay one kernel on the requesting GPU
+        const Table tb = a.n_shards > 1 ? a.shards[shard_of(rq.key, a.n_shards)] : a.table;
         Probe pr{0, 0, 0, 0};
-        if (lane < 8) pr = tile_lookup(a.table, rq.key, lane, 0);
+        if (lane < 8) pr = tile_lookup(tb, rq.key, lane, 0);
         __syncwarp();
         const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
         int32_t status = 0;
@@ -341,7 +346,8 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           const uint32_t plen = meta_len(meta);
           j.slot = meta_slot(meta);
           j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
-          j.src = a.table.slab + (uint64_t)j.slot * a.table.page_size + rq.page_off;
+          j.src = tb.slab + (uint64_t)j.slot * tb.page_size + rq.page_off;
+          j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;  // which shard's slot_crc to check
           j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
           status = (int32_t)j.n;
         }
@@ -457,7 +463,8 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       bool corrupt = false;
       if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
       if (j.flags & kJobOutCrc) a.crc_out[job] = full;
-      if ((j.flags & kJobVerify) && a.table.slot_crc[j.slot] != full) {
+      const uint32_t* recorded = (kGet && j.pad) ? a.shards[j.pad - 1u].slot_crc : a.table.slot_crc;
+      if ((j.flags & kJobVerify) && __ldcg(&recorded[j.slot]) != full) {
         corrupt = true;
         atomicAdd(&a.table.counters[kCtrCrcMismatch], 1ull);
       }

@@ -180,11 +180,26 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     K, W = args.steps, max(3, args.warmup)
 
-    resident = int(os.environ.get("APS_BENCH_PAGES", "65536"))
+    resident = int(os.environ.get("APS_BENCH_PAGES", "65536"))  # pages per GPU
     free_b, _ = torch.cuda.mem_get_info(dev)
-    while resident * PAGE + (6 << 30) > free_b and resident > 1024:
+    while resident * PAGE + (8 << 30) > free_b and resident > 1024:
         resident //= 2  # a smaller GPU slice: stated in config.workload
-    cfg = capi.aps_config(device=local_rank, page_size=PAGE, cache_bytes=resident * PAGE, slab_slots=resident,
+    if world > 1:
+        t = torch.tensor([resident], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        resident = int(t.item())
+    # Global id space: world * resident pages; page g is (file g // 1024, index g % 1024).  With several
+    # GPUs the cache is sharded: GPU aps_shard_of(key) owns the page (hash routing).
+    from alluxio_b200 import sharding
+    total_pages = world * resident
+    gids = np.arange(total_pages, dtype=np.uint64)
+    if world > 1:
+        mine = sharding.owned_by(rank, world, gids // np.uint64(1024), gids % np.uint64(1024))
+        owned = gids[mine]
+    else:
+        owned = gids
+    slots = int(len(owned)) + 64
+    cfg = capi.aps_config(device=local_rank, page_size=PAGE, cache_bytes=slots * PAGE, slab_slots=slots,
                           table_capacity=0, max_batch=BATCH,
                           flags=0 if os.environ.get("APS_BENCH_NOCRC") == "1" else capi.APS_FLAG_CRC)
     with_crc = cfg.flags != 0
@@ -200,24 +215,24 @@ def run_ours(args):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from gpu_util import GET_REQ, PUT_REQ, RESULT
 
-    # ---- populate: generate pages on the device, put them 256 at a time (file = page // 1024)
+    # ---- populate the pages this GPU owns: generate on the device, put 256 at a time
     stage = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
     d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
-    file_base = rank << 20  # shards hold disjoint files
     t_pop = time.time()
     first_put_res = None
-    for b0 in range(0, resident, BATCH):
-        ids = np.arange(b0, b0 + BATCH, dtype=np.uint64)
-        files, idx = ids // 1024 + file_base, ids % 1024
+    for b0 in range(0, len(owned), BATCH):
+        ids = owned[b0:b0 + BATCH]
+        nb = len(ids)
+        files, idx = ids // np.uint64(1024), ids % np.uint64(1024)
         d_files = torch.from_numpy(files.view(np.int64)).to(dev)
         d_idx = torch.from_numpy(idx.view(np.int64)).to(dev)
-        capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, BATCH, d_files.data_ptr(),
+        capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, nb, d_files.data_ptr(),
                                         d_idx.data_ptr(), DATA_SEED, sp), "fill")
-        reqs = np.zeros(BATCH, PUT_REQ)
+        reqs = np.zeros(nb, PUT_REQ)
         reqs["file_lo"], reqs["page_index"], reqs["len"] = files, idx, PAGE
-        reqs["src"] = stage.data_ptr() + np.arange(BATCH, dtype=np.uint64) * PAGE
+        reqs["src"] = stage.data_ptr() + np.arange(nb, dtype=np.uint64) * PAGE
         d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
-        capi.check(L.aps_put_batch_dev(h, BATCH, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
+        capi.check(L.aps_put_batch_dev(h, nb, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
         if b0 == 0:
             torch.cuda.synchronize(dev)
             first_put_res = d_res.cpu().numpy().view(RESULT).copy()
@@ -227,25 +242,46 @@ def run_ours(args):
     # ---- parity spot check against the oracle (the checker; never the thing measured)
     from oracle import binding as orc
     for i in (0, 1, 255):
-        want = orc.crc32c(orc.fill_page(DATA_SEED, file_base + i // 1024, i % 1024, PAGE))
+        g = int(owned[i])
+        want = orc.crc32c(orc.fill_page(DATA_SEED, g // 1024, g % 1024, PAGE))
         assert (not with_crc or int(first_put_res[i]["crc"]) == want) and int(first_put_res[i]["len"]) == PAGE, \
             "put CRC differs from oracle"
 
-    # ---- request pool: uniform random page ids, seed 2 + rank
+    # ---- several GPUs: map every peer's table and slab (CUDA IPC handles travel over torch.distributed)
+    if world > 1:
+        hnd = capi.aps_shard_handle()
+        capi.check(L.aps_shard_export(h, C.byref(hnd)), "shard_export")
+        blobs = [None] * world
+        dist.all_gather_object(blobs, bytes(hnd.opaque))
+        arr = (capi.aps_shard_handle * world)()
+        for i, bl in enumerate(blobs):
+            C.memmove(C.addressof(arr[i]), bl, 256)
+        capi.check(L.aps_shard_attach(h, world, rank, arr), "shard_attach")
+        dist.barrier()
+
+    # ---- request pool: uniform random page ids over the whole (global) id space, seed 2 + rank
     rng = np.random.default_rng(2 + rank)
     pool = min(K + W, 512)
     dst = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
-    picks = rng.integers(0, resident, size=(pool, BATCH)).astype(np.uint64)
+    picks = rng.integers(0, total_pages, size=(pool, BATCH)).astype(np.uint64)
     reqs = np.zeros((pool, BATCH), GET_REQ)
-    reqs["file_lo"], reqs["page_index"] = picks // 1024 + file_base, picks % 1024
+    reqs["file_lo"], reqs["page_index"] = picks // np.uint64(1024), picks % np.uint64(1024)
     reqs["page_off"], reqs["nbytes"] = 0, PAGE
     reqs["dst"] = dst.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
     d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
     d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
     req_bytes = BATCH * GET_REQ.itemsize
+    if world > 1:
+        pick_owner = sharding.shard_of_keys(np.zeros(picks.size, np.uint64), (picks // np.uint64(1024)).reshape(-1),
+                                            (picks % np.uint64(1024)).reshape(-1), world)
+        remote_frac = float((pick_owner != rank).mean())
+    else:
+        remote_frac = 0.0
+    get_dev = L.aps_get_batch_sharded_dev if world > 1 else L.aps_get_batch_dev
+    get_host = L.aps_get_batch_sharded if world > 1 else L.aps_get_batch
 
     def step_dev(k):
-        capi.check(L.aps_get_batch_dev(h, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+        capi.check(get_dev(h, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
 
     for k in range(W):
         step_dev(k)
@@ -255,7 +291,7 @@ def run_ours(args):
     k_last = (W - 1) % pool
     for i in (0, 17, 255):
         p = int(picks[k_last, i])
-        page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
+        page = orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE)
         assert int(res[i]["len"]) == PAGE and (not with_crc or int(res[i]["crc"]) == orc.crc32c(page)), \
             "get CRC differs from oracle"
         assert np.array_equal(dst[i * PAGE:(i + 1) * PAGE].cpu().numpy(), page), "get bytes differ from oracle"
@@ -334,12 +370,12 @@ def run_ours(args):
     h_res = np.zeros(BATCH, RESULT)
 
     def step_host(k):
-        capi.check(L.aps_get_batch(h, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+        capi.check(get_host(h, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
 
     for k in range(3):
         step_host(k)
     p = int(picks[2 % pool, 5])
-    page = orc.fill_page(DATA_SEED, file_base + p // 1024, p % 1024, PAGE)
+    page = orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE)
     assert np.array_equal(pinned.numpy()[5 * PAGE:6 * PAGE], page)
     assert not with_crc or int(h_res[5]["crc"]) == orc.crc32c(page)
     if world > 1:
@@ -360,11 +396,11 @@ def run_ours(args):
     aux = {}
     aux_steps = max(1, min(K, 50))
     put_reqs = np.zeros(BATCH, PUT_REQ)
-    ids = np.arange(BATCH, dtype=np.uint64)
-    put_reqs["file_lo"], put_reqs["page_index"], put_reqs["len"] = ids // 1024 + file_base, ids % 1024, PAGE
-    put_reqs["src"] = stage.data_ptr() + ids * PAGE  # stage still holds the last populated batch: rewrite ids 0..255
-    files0 = torch.from_numpy((ids // 1024 + file_base).view(np.int64)).to(dev)
-    idx0 = torch.from_numpy((ids % 1024).view(np.int64)).to(dev)
+    ids = owned[:BATCH]
+    put_reqs["file_lo"], put_reqs["page_index"], put_reqs["len"] = ids // np.uint64(1024), ids % np.uint64(1024), PAGE
+    put_reqs["src"] = stage.data_ptr() + np.arange(BATCH, dtype=np.uint64) * PAGE  # re-put this GPU's first 256 pages
+    files0 = torch.from_numpy((ids // np.uint64(1024)).view(np.int64)).to(dev)
+    idx0 = torch.from_numpy((ids % np.uint64(1024)).view(np.int64)).to(dev)
     capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, BATCH, files0.data_ptr(), idx0.data_ptr(),
                                     DATA_SEED, sp), "fill")
     d_put = torch.from_numpy(put_reqs.view(np.uint8).reshape(-1)).to(dev)
@@ -379,10 +415,65 @@ def run_ours(args):
     aux["put_fused_crc32c_GBps"] = round(aux_steps * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
     aux["put_note"] = "re-puts one resident 256 MiB batch (source and slots cached in L2 between steps): upper bound"
 
+    # ---- several GPUs: the same multi-get through NCCL (all-to-all of keys, owner-side gather into a send
+    # buffer, all-to-all of pages): the plain-collective baseline that the fused P2P kernel is compared with
+    if world > 1 and not quick:
+        nccl_steps = max(1, min(K, 50))
+        sendbuf = torch.empty(2 * BATCH * PAGE, dtype=torch.uint8, device=dev)   # pages this GPU serves per step
+        recvbuf = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
+        srv_res = torch.zeros(2 * BATCH * 8, dtype=torch.uint8, device=dev)
+
+        def step_nccl(k):
+            pk = picks[k % pool]
+            own = sharding.shard_of_keys(np.zeros(BATCH, np.uint64), pk // np.uint64(1024), pk % np.uint64(1024), world)
+            order = np.argsort(own, kind="stable")
+            counts = np.bincount(own, minlength=world)
+            keys = torch.from_numpy(np.stack([pk[order] // np.uint64(1024), pk[order] % np.uint64(1024)], 1).astype(np.int64)).to(dev)
+            cnt_out = torch.from_numpy(counts.astype(np.int64)).to(dev)
+            cnt_in = torch.empty_like(cnt_out)
+            dist.all_to_all_single(cnt_in, cnt_out)
+            n_in = cnt_in.cpu().tolist()
+            n_srv = int(sum(n_in))
+            assert n_srv <= 2 * BATCH, "request skew beyond the serve buffer"
+            keys_in = torch.empty((n_srv, 2), dtype=torch.int64, device=dev)
+            dist.all_to_all_single(keys_in, keys, output_split_sizes=n_in, input_split_sizes=counts.tolist())
+            # owner side: one local batched get straight into the send buffer
+            rq = torch.zeros((n_srv, 5), dtype=torch.int64, device=dev)
+            rq[:, 1], rq[:, 2] = keys_in[:, 0], keys_in[:, 1]
+            rq[:, 3] = PAGE << 32                                   # page_off = 0, nbytes = PAGE
+            rq[:, 4] = sendbuf.data_ptr() + torch.arange(n_srv, device=dev, dtype=torch.int64) * PAGE
+            for lo in range(0, n_srv, BATCH):
+                m = min(BATCH, n_srv - lo)
+                capi.check(L.aps_get_batch_dev(h, m, rq.data_ptr() + lo * 40, srv_res.data_ptr() + lo * 8, sp), "serve")
+            dist.all_to_all_single(recvbuf[:BATCH * PAGE], sendbuf[:n_srv * PAGE],
+                                   output_split_sizes=[int(c) * PAGE for c in counts], input_split_sizes=[c * PAGE for c in n_in])
+            return order
+
+        order = step_nccl(0)
+        torch.cuda.synchronize(dev)
+        p0 = int(picks[0, order[3]])
+        assert np.array_equal(recvbuf[3 * PAGE:4 * PAGE].cpu().numpy(), orc.fill_page(DATA_SEED, p0 // 1024, p0 % 1024, PAGE))
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for k in range(nccl_steps):
+            step_nccl(1 + k)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        aux["nccl_all_to_all_GBps"] = round(world * nccl_steps * BATCH * PAGE / float(t.item()) / 1e9, 1)
+        aux["nccl_note"] = "same multi-get via torch.distributed all_to_all_single (keys, then pages served by aps_get_batch_dev)"
+
     clocks = sampler.stop()
     stats = capi.aps_stats_t()
     capi.check(L.aps_stats(h, C.byref(stats)), "stats")
     assert stats.crc_mismatches == 0
+    if world > 1:
+        t = torch.tensor([remote_frac], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        remote_frac = float(t.item()) / world
+        dist.barrier()  # peers may still be reading this GPU's slab
     capi.check(L.aps_close(h), "close")
 
     if rank != 0:
@@ -412,15 +503,34 @@ def run_ours(args):
     # region is ms_total / K (CUDA events on the launching stream; launch gaps included: conservative).
     achieved = 2 * step_bytes / (ms_total / K * 1e-3) / 1e9
     value = world * K * step_bytes / (ms_total * 1e-3) / 1e9
+    if world > 1:
+        # cross-shard multi-get: the bytes that cross NVLink per GPU per step bound the step
+        nv_peak = 770.0  # measured peer-copy bandwidth per direction per GPU on this pool (B200_PROFILING.md); 900 nominal
+        nv_achieved = remote_frac * step_bytes / (ms_total / K * 1e-3) / 1e9
+        roofline = {"bound": "nvlink", "achieved": round(nv_achieved, 1), "peak": nv_peak, "unit": "GB/s",
+                    "frac": round(nv_achieved / nv_peak, 4), "traffic": None,
+                    "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
+                    "kernel": "aps::copy_kernel<crc,512,4,get> reading peer slabs over NVLink (lookup + gather + CRC, one launch per step)",
+                    "algorithmic_bytes_per_launch": int(remote_frac * step_bytes),
+                    "remote_fraction": round(remote_frac, 4), "avg_launch_ms": round(ms_total / K, 5),
+                    "launches_timed": int(launches), "frac_of_nominal_900": round(nv_achieved / 900.0, 4),
+                    "hbm_traffic_GBps_per_gpu": round(achieved, 1)}
+    else:
+        roofline = None
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms_total / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(resident), "page_bytes": PAGE, "resident_pages": resident,
+        "config": {"workload": workload_name(resident) if world == 1 else
+                   ("hash-sharded cache over %d B200: 1 MiB pages, %d GiB per GPU (%d GiB aggregate), every GPU issues batched "
+                    "gets of %d uniform ids over the whole id space, served from the owning GPU over NVLink P2P with fused "
+                    "CRC32C (BASELINE configs[4])" % (world, resident * PAGE >> 30, world * resident * PAGE >> 30, BATCH)),
+                   "page_bytes": PAGE, "resident_pages": resident,
                    "batch_pages": BATCH, "populate_s": round(t_pop, 2),
                    "l2": "inputs larger than L2: each step reads 256 MiB drawn from the resident set and writes 256 MiB",
-                   "shards": "one store per GPU, disjoint files, no data-path collective"},
-        "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                   "shards": "one store per GPU; owner = hash(PageId) mod n; gets read the owner's table and slab in place "
+                             "(P2P), no data-path collective" if world > 1 else "single store"},
+        "roofline": roofline if roofline is not None else {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                      "kernel": "aps::copy_kernel<crc, threads, group, get> (K1 lookup + K2 gather + K3 fused CRC32C, one launch per step)",
                      "algorithmic_bytes_per_launch": 2 * step_bytes,

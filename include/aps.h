@@ -156,6 +156,26 @@ APS_API int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys
  * for a batch of ids.  d_len[i] = stored length, or -1 when absent. */
 APS_API int aps_lookup_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, int32_t* d_len, aps_stream stream);
 
+/* ---- sharded cache over the GPUs of one box (additive; the reference cache is process-local) ------
+ * Pages are owned by GPU aps_shard_of(key, n): puts and deletes go to the owner's store.  A batched
+ * get may ask for any page: the requesting GPU probes the owner's table and reads the owner's slab in
+ * place over NVLink (P2P), with lookup, gather and CRC check still one kernel -- no staging buffer and no
+ * collective.  One process per GPU exchanges aps_shard_handle blobs (CUDA IPC) by any means it likes
+ * (bench.py uses torch.distributed); one process that owns several stores passes them directly. */
+typedef struct aps_shard_handle {
+  unsigned char opaque[256];
+} aps_shard_handle;
+APS_API uint32_t aps_shard_of(const aps_key* key, uint32_t n_shards);
+APS_API int aps_shard_export(aps_store* s, aps_shard_handle* out);
+/* handles[i] = export of shard i (handles[my_shard] is ignored).  All shards must share page_size. */
+APS_API int aps_shard_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const aps_shard_handle* handles);
+APS_API int aps_shard_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, aps_store* const* stores);
+/* As aps_get_batch_dev, but every request is served from the shard that owns its key. */
+APS_API int aps_get_batch_sharded_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res,
+                                      aps_stream stream);
+/* As aps_get_batch (host arrays, waits), served from the owning shards. */
+APS_API int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream);
+
 /* ---- checksum path: `alluxio fs checksum` ------------------------------------------------------
  * ChecksumCommand.calculateChecksum (shell/src/main/java/alluxio/cli/fs/command/
  * ChecksumCommand.java:83-90) = DigestUtils.md5Hex over the file's bytes.  One digest per file,
