@@ -75,6 +75,7 @@ SIGNATURES = {
     "aps_get_batch_sharded": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_md5_batch_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp]),
     "aps_md5_batch": (C.c_int, [_i32, _u32, _vp, _vp, _vp]),
+    "aps_md5_stream_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp]),
     "aps_crc32c_batch_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp, _vp]),
     "aps_crc32c_noalloc": (C.c_int, [_i32, _u32, _vp, _vp, _u32, _vp, _vp]),
     "aps_fill_pages_dev": (C.c_int, [_i32, _vp, _u64, _u32, _u32, _vp, _vp, _u64, _vp]),

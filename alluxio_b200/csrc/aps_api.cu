@@ -1022,7 +1022,21 @@ int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_dat
   if (!d_data || !d_len || !d_out) return APS_EINVAL;
   DeviceGuard g(device);
   if (!g.ok) return APS_ECUDA;
-  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out);
+  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, nullptr, nullptr, 1);
+  count_launch(nullptr);
+  CUDA_TRY(cudaGetLastError());
+  return APS_OK;
+}
+
+int aps_md5_stream_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
+                       uint32_t (*d_state)[4], const uint64_t* d_prefix_len, int finalize, uint8_t (*d_out)[16],
+                       aps_stream stream) {
+  if (n_files == 0) return APS_OK;
+  if (!d_data || !d_len || !d_state || (finalize && !d_out)) return APS_EINVAL;
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, d_state, d_prefix_len,
+                                                                    finalize);
   count_launch(nullptr);
   CUDA_TRY(cudaGetLastError());
   return APS_OK;

@@ -588,8 +588,14 @@ constexpr uint32_t kMd5RowWords = kMd5Seg / 4 + 4;  // 528-byte rows: 16-byte al
 
 __device__ __forceinline__ uint32_t rotl32(uint32_t x, int s) { return __funnelshift_l(x, x, s); }
 
-#define APS_MD5_STEP(f, a, b, c, d, m, k, s) \
-  a = b + rotl32(a + f(b, c, d) + (m) + (k), s)
+// The chain through a step is b -> F(b,c,d) -> (+) -> rotate -> (+b).  a + m + k does not depend on the
+// previous step's result, so it is formed first and kept off that chain (3 dependent ops per step).
+#define APS_MD5_STEP(f, a, b, c, d, m, k, s)          \
+  do {                                                \
+    uint32_t pre_;                                    \
+    asm("add.u32 %0, %1, %2;" : "=r"(pre_) : "r"(a), "r"((m) + (k))); /* opaque: keeps the compiler from re-chaining it */ \
+    a = b + rotl32(f(b, c, d) + pre_, s);             \
+  } while (0)
 #define APS_F1(b, c, d) ((d) ^ ((b) & ((c) ^ (d))))
 #define APS_F2(b, c, d) ((c) ^ ((d) & ((b) ^ (c))))
 #define APS_F3(b, c, d) ((b) ^ (c) ^ (d))
@@ -640,8 +646,12 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // One warp per block; lane f digests file blockIdx.x*32 + f.
+// `state` (optional) carries the four chaining words between calls so that files larger than HBM can be
+// digested in waves: with finalize == 0 the call consumes len (a multiple of 64) bytes and stores the
+// words back; with finalize != 0 it also pads for prefix[file] + len total bytes and writes the digest.
 __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* const* data, const uint64_t* len,
-                                                 uint8_t (*out)[16]) {
+                                                 uint8_t (*out)[16], uint32_t (*state)[4], const uint64_t* prefix,
+                                                 int finalize) {
   __shared__ __align__(16) uint32_t tile[2][32 * kMd5RowWords];
   const uint32_t lane = threadIdx.x;
   const uint32_t file = blockIdx.x * 32 + lane;
@@ -656,6 +666,10 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
   const uint64_t nseg = max_len / kMd5Seg;  // segments that are full for at least one file
 
   uint32_t h[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+  if (state && have) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = state[file][i];
+  }
 
   auto stage = [&](uint64_t seg, int buf) {
     // for each file of the warp: 32 lanes fetch its 512-byte segment, 16 bytes each
@@ -715,13 +729,18 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
     md5_block(h, m);
     pos += 64;
   }
+  if (!finalize) {  // intermediate wave: hand the chaining words to the next call
+#pragma unroll
+    for (int i = 0; i < 4; ++i) state[file][i] = h[i];
+    return;
+  }
   uint8_t last[128];
   uint32_t rem = (uint32_t)(my_len - pos);
   for (uint32_t i = 0; i < rem; ++i) last[i] = my[pos + i];
   last[rem] = 0x80;
   const uint32_t total = rem < 56 ? 64 : 128;
   for (uint32_t i = rem + 1; i < total - 8; ++i) last[i] = 0;
-  const uint64_t bits = my_len * 8;
+  const uint64_t bits = (my_len + (prefix ? prefix[file] : 0ull)) * 8;
   for (int i = 0; i < 8; ++i) last[total - 8 + i] = (uint8_t)(bits >> (8 * i));
   for (uint32_t o = 0; o < total; o += 64) {
     uint32_t m[16];

@@ -183,6 +183,14 @@ APS_API int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* r
  * memory); d_data, d_len and d_out are DEVICE arrays.  Asynchronous on `stream`. */
 APS_API int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
                       uint8_t (*d_out)[16], aps_stream stream);
+/* Streaming form for file sets larger than HBM (4,096 x 64 MiB does not fit one GPU): the files are fed
+ * in waves.  d_state[i] holds file i's four chaining words: initialise it to the MD5 IV (0x67452301,
+ * 0xefcdab89, 0x98badcfe, 0x10325476) before the first wave.  With finalize == 0 a wave consumes d_len[i]
+ * bytes (a multiple of 64) and updates d_state; with finalize != 0 it also pads for
+ * d_prefix_len[i] + d_len[i] total bytes and writes the digests. */
+APS_API int aps_md5_stream_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
+                               uint32_t (*d_state)[4], const uint64_t* d_prefix_len, int finalize, uint8_t (*d_out)[16],
+                               aps_stream stream);
 /* Host form: arrays on the host, file payloads wherever they are (device or pinned); waits. */
 APS_API int aps_md5_batch(int32_t device, uint32_t n_files, const void* const* data, const uint64_t* len, uint8_t (*out)[16]);
 
