@@ -81,6 +81,21 @@ const CopyVariant kCopyVariants[] = {
     APS_VARIANT(512, 2), APS_VARIANT(256, 8),
 };
 #undef APS_VARIANT
+// The bulk-async (TMA) form of the copy kernel, selected with APS_COPY_VARIANT=tma.
+bool use_tma_variant() {
+  static const bool v = [] {
+    const char* want = getenv("APS_COPY_VARIANT");
+    return want && !strcmp(want, "tma");
+  }();
+  return v;
+}
+struct TmaKernels {
+  CopyKernelFn crc, plain, get_crc, get_plain;
+  int dyn_crc = 0, dyn_plain = 0;
+};
+TmaKernels g_tma = {tma_copy_kernel<true, false>, tma_copy_kernel<false, false>, tma_copy_kernel<true, true>,
+                    tma_copy_kernel<false, true>};
+
 const CopyVariant& copy_variant() {
   static const CopyVariant* v = [] {
     const char* want = getenv("APS_COPY_VARIANT");
@@ -132,6 +147,17 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
     for (const CopyVariant& v : kCopyVariants) {
       CUDA_TRY(cudaFuncSetAttribute(v.crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
       CUDA_TRY(cudaFuncSetAttribute(v.get_crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+    }
+    {
+      int optin = 0;
+      CUDA_TRY(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+      for (CopyKernelFn fn : {g_tma.crc, g_tma.plain, g_tma.get_crc, g_tma.get_plain}) {
+        cudaFuncAttributes fa{};
+        CUDA_TRY(cudaFuncGetAttributes(&fa, fn));
+        const int dyn = optin - (int)fa.sharedSizeBytes;
+        CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn));
+        g_tma.dyn_crc = g_tma.dyn_plain = dyn;
+      }
     }
     CUDA_TRY(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev));
     CUDA_TRY(cudaMalloc(&d.d_sm_slow, 256));
@@ -226,6 +252,31 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.sm_slow = s->dc->d_sm_slow;
   a.shards = sharded ? s->d_shards : nullptr;
   a.n_shards = sharded ? s->n_shards : 0;
+  a.n_slow = (uint32_t)s->dc->n_slow;
+  if (use_tma_variant()) {
+    // bulk-async form: chunks of 16 rows, a contiguous weighted slice of the chunk space per CTA
+    const uint32_t cpj = (s->page_rows + kStageRows - 1) / kStageRows;
+    a.tasks_per_job = cpj;
+    a.rows_per_task = kStageRows;
+    const uint64_t chunks = (uint64_t)n * cpj;
+    uint32_t tgrid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, chunks);
+    if (tgrid == 0) tgrid = 1;
+    if ((uint64_t)n / tgrid + 2 > kJobCache) return APS_EINVAL;
+    CopyKernelFn fn = d_get_reqs ? (crc ? g_tma.get_crc : g_tma.get_plain) : (crc ? g_tma.crc : g_tma.plain);
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(tgrid);
+    lc.blockDim = dim3(kTmaThreads);
+    lc.dynamicSmemBytes = (size_t)g_tma.dyn_crc;
+    lc.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = s->use_pdl ? 1 : 0;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&lc, fn, a));
+    count_launch(s);
+    return APS_OK;
+  }
   if (s->d_timeline) CUDA_TRY(cudaMemsetAsync(s->d_timeline, 0xFF, kTimelineWords * sizeof(unsigned long long), st));
   const uint64_t items = (uint64_t)n * tpj;
   uint32_t grid = (uint32_t)std::min<uint64_t>((uint64_t)s->dc->num_sms, items);  // every SM takes part

@@ -212,6 +212,7 @@ struct CopyArgs {
   uint32_t n_shards;         // 0 or 1: only this GPU's table
   uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
   const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
+  uint32_t n_slow;           // how many SMs that is
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -483,6 +484,319 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       a.timeline[1024 + 256 * 32 + blockIdx.x] = smid;
     }
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 + K3, bulk-async (TMA) form.  Same job and CRC algebra as copy_kernel, different data movement:
+// one producer thread per CTA walks the CTA's contiguous slice of the batch and issues
+// cp.async.bulk global -> shared copies of 16-row (8 KiB) chunks into a ring of shared-memory stages,
+// each guarded by a full/empty mbarrier pair; consumer warps take the stages round robin, start the
+// cp.async.bulk shared -> global store of the chunk at once, fold its rows into the CRC straight from
+// shared memory (conflict-free 128-bit reads), publish the chunk's shifted CRC, and hand the stage back
+// when the store has finished reading it.  No data passes through registers on its way to the
+// destination, and an SM keeps ~88 KiB of loads in flight whatever its warps are doing.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kStageRows = 16;
+constexpr uint32_t kStageBytes = kStageRows * kRowBytes;
+constexpr uint32_t kMaxStages = 27;
+constexpr uint32_t kTmaThreads = 512;
+constexpr uint32_t kTmaConsumers = 12;    // warps 1..12 consume; warp 0 produces
+constexpr uint32_t kJobCache = 128;       // jobs a CTA's slice may span
+constexpr uint32_t kDescTma = 1u, kDescTail = 2u, kDescEnd = 8u;
+
+struct StageDesc {
+  uint32_t job_local, row_lo, rows, flags;
+};
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+               "l"(gsrc), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+  return r;
+}
+
+template <bool kCrc, bool kGet>
+__global__ void __launch_bounds__(kTmaThreads, 1) tma_copy_kernel(CopyArgs a) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  constexpr uint32_t nwarps = kTmaThreads / 32;
+  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+
+  // ---- shared-memory map (absolute shared-window addresses)
+  //   [base, +4 KiB)   job cache      [.., +NS*16) stage descriptors   [.., +NS*16) full/empty barriers
+  //   stages of 8 KiB fill the rest below 0x0F000 (kCrc: the CRC tables sit at 0x0F000..0x30000) and
+  //   everything above 0x30000; without CRC the whole window is stages.
+  const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+  uint32_t dyn;
+  asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
+  const uint32_t win_end = base + dyn;
+  const uint32_t jobs_at = base, desc_at = jobs_at + kJobCache * sizeof(Job), bar_at = desc_at + kMaxStages * 16u;
+  const uint32_t addr_at = bar_at + kMaxStages * 16u, stages_lo = (addr_at + kMaxStages * 4u + 127u) & ~127u;
+  __shared__ uint32_t s_rank, s_ns;
+  if (kCrc && (base > 0x2000u || win_end < kSmemEnd)) {
+    if (threadIdx.x == 0) *a.error_flag = 1;
+    return;
+  }
+  Job* s_jobs = reinterpret_cast<Job*>(smem_raw);
+  StageDesc* s_desc = reinterpret_cast<StageDesc*>(smem_raw + (desc_at - base));
+  uint32_t* s_stage_addr = reinterpret_cast<uint32_t*>(smem_raw + (addr_at - base));
+
+  if (threadIdx.x == 0) {
+    uint32_t smid;
+    asm("mov.u32 %0, %%smid;" : "=r"(smid));
+    const bool slow = a.sm_slow[smid & 255u] != 0;
+    s_rank = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
+    __threadfence();
+    if (atomicAdd(&a.sched[2], 1u) == gridDim.x - 1u) {
+      a.sched[0] = 0;
+      a.sched[1] = 0;
+      a.sched[2] = 0;
+    }
+    // lay the stages out
+    uint32_t ns = 0;
+    const uint32_t lo_end = kCrc ? kSmemG : win_end;
+    for (uint32_t p = stages_lo; p + kStageBytes <= lo_end && ns < kMaxStages; p += kStageBytes) s_stage_addr[ns++] = p;
+    if (kCrc)
+      for (uint32_t p = kSmemEnd; p + kStageBytes <= win_end && ns < kMaxStages; p += kStageBytes) s_stage_addr[ns++] = p;
+    // A stage must always come back to the SAME consumer warp (a warp that ran ahead to the stage's next
+    // lap could otherwise pass a full-barrier whose current lap has not completed yet): keep the number of
+    // stages a multiple of the number of consumers.
+    {
+      const uint32_t c = min(kTmaConsumers, ns);
+      ns = c ? (ns / c) * c : 0;
+    }
+    s_ns = ns;
+    for (uint32_t i = 0; i < ns; ++i) {
+      mbar_init(bar_at + i * 16u, 1);       // full:  the producer's arrive (+ the bytes of the bulk load)
+      mbar_init(bar_at + i * 16u + 8u, 1);  // empty: the consumer that drained the stage
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (kCrc) {
+    const uint32_t* gfold = &a.tables->fold[0][0];
+    const uint32_t* gz4 = &a.tables->z4[0][0];
+    constexpr uint32_t kPerWarp = 1024 / nwarps;
+    uint32_t mine[kPerWarp / 32], zmine[1024 / kTmaThreads];
+#pragma unroll
+    for (uint32_t q = 0; q < kPerWarp / 32; ++q) mine[q] = __ldg(&gfold[warp * kPerWarp + q * 32 + lane]);
+#pragma unroll
+    for (uint32_t q = 0; q < 1024 / kTmaThreads; ++q) zmine[q] = __ldg(&gz4[threadIdx.x + q * kTmaThreads]);
+#pragma unroll
+    for (uint32_t q = 0; q < kPerWarp / 32; ++q) {
+#pragma unroll
+      for (uint32_t k = 0; k < 32; ++k) {
+        const uint32_t idx = warp * kPerWarp + q * 32 + k, j = idx >> 8, b = idx & 255u;
+        sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine[q], k));
+      }
+    }
+#pragma unroll
+    for (uint32_t q = 0; q < 1024 / kTmaThreads; ++q) sts_u32(kSmemG + (threadIdx.x + q * kTmaThreads) * 4u, zmine[q]);
+  }
+  __syncthreads();
+
+  // ---- this CTA's contiguous slice of the chunk space, weighted by SM speed class
+  const uint32_t cpj = a.tasks_per_job;  // chunks per job
+  const uint64_t total = (uint64_t)a.n_jobs * cpj;
+  const uint32_t rank = s_rank, ns = s_ns, grid = gridDim.x;
+  const uint32_t n_slow = min(a.n_slow, grid), n_fast = grid - n_slow;
+  const uint64_t units = 16ull * n_fast + 15ull * n_slow;
+  auto cum = [&](uint32_t r) -> uint64_t {  // weight of the ranks below r: fast ranks first
+    return r <= n_fast ? 16ull * r : 16ull * n_fast + 15ull * (r - n_fast);
+  };
+  const uint64_t lo = total * cum(rank) / units, hi = total * cum(rank + 1) / units;
+  if (lo >= hi) return;
+  const uint32_t jlo = (uint32_t)(lo / cpj), jhi = (uint32_t)((hi - 1) / cpj);
+  if (jhi - jlo + 1 > kJobCache) {  // the host sizes batches so that this cannot happen
+    if (threadIdx.x == 0) *a.error_flag = 2;
+    return;
+  }
+
+  // ---- resolve the jobs of the slice (all warps, four jobs per warp at a time)
+  for (uint32_t k = warp * 4 + (lane >> 3); jlo + (k & ~3u) <= jhi; k += nwarps * 4) {
+    const uint32_t job = jlo + k;
+    const uint32_t sub = lane & 7u, tshift = lane & 24u;
+    if (job <= jhi) {  // tile-uniform
+      Job j;
+      if (kGet) {
+        const aps_get_req rq = a.reqs[job];
+        const Table tb = a.n_shards > 1 ? a.shards[shard_of(rq.key, a.n_shards)] : a.table;
+        Probe pr = tile_lookup(tb, rq.key, sub, tshift);
+        int32_t status = 0;
+        j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
+        if (!pr.meta) {
+          status = -APS_ENOTFOUND;
+        } else if (rq.page_off > meta_len(pr.meta)) {
+          status = -APS_EINVAL;
+        } else {
+          const uint32_t plen = meta_len(pr.meta);
+          j.slot = meta_slot(pr.meta);
+          j.n = min(plen - rq.page_off, rq.nbytes);
+          j.src = tb.slab + (uint64_t)j.slot * tb.page_size + rq.page_off;
+          j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
+          j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;
+          status = (int32_t)j.n;
+        }
+        // the CTA whose slice holds the job's first chunk reports
+        if (sub == 0 && (uint64_t)job * cpj >= lo) {
+          atomicAdd(&a.table.counters[kCtrLookups], 1ull);
+          atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
+          if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
+          if (!kCrc || j.n == 0) a.res[job] = aps_result{status, 0};
+        }
+      } else {
+        j = a.jobs[job];
+      }
+      if (sub == 0) s_jobs[k] = j;
+    }
+  }
+  __syncthreads();
+
+  const uint32_t nc = min(kTmaConsumers, ns);
+  if (warp == 0) {
+    // ================================ producer: one thread
+    if (lane == 0) {
+      uint32_t q = 0;
+      auto post = [&](const StageDesc& d, const Job* J) {
+        const uint32_t st = q % ns, par = (q / ns) & 1u;
+        mbar_wait(bar_at + st * 16u + 8u, par ^ 1u);  // stage drained (passes at once on the first lap)
+        s_desc[st] = d;
+        if (d.flags & kDescTma) {
+          mbar_arrive_expect_tx(bar_at + st * 16u, d.rows * kRowBytes);
+          bulk_load(s_stage_addr[st], J->src + (size_t)d.row_lo * kRowBytes, d.rows * kRowBytes, bar_at + st * 16u);
+        } else {
+          __threadfence_block();
+          mbar_arrive(bar_at + st * 16u);
+        }
+        ++q;
+      };
+      for (uint64_t g = lo; g < hi; ++g) {
+        const uint32_t job = (uint32_t)(g / cpj), c = (uint32_t)(g - (uint64_t)job * cpj);
+        const Job* J = &s_jobs[job - jlo];
+        const uint32_t rows_full = J->n / kRowBytes, tail = J->n % kRowBytes;
+        const uint32_t job_rows = rows_full + (tail ? 1u : 0u);
+        const uint32_t row_lo = c * kStageRows;
+        if (row_lo >= job_rows) continue;
+        const uint32_t rows = rows_full > row_lo ? min(kStageRows, rows_full - row_lo) : 0u;
+        const bool aligned = (((uintptr_t)J->src | (uintptr_t)J->dst) & 15u) == 0;
+        StageDesc d{job - jlo, row_lo, rows, 0u};
+        if (aligned && rows) d.flags |= kDescTma;
+        if (tail && row_lo + kStageRows >= job_rows) d.flags |= kDescTail;
+        post(d, J);
+      }
+      for (uint32_t e = 0; e < nc; ++e) post(StageDesc{0, 0, 0, kDescEnd}, nullptr);
+    }
+    return;
+  }
+  if (warp > nc) return;
+
+  // ================================ consumers: stage q goes to consumer q % nc
+  const uint32_t rb = 0x00010000u | (lane << 2);
+  for (uint32_t q = warp - 1;; q += nc) {
+    const uint32_t st = q % ns, par = (q / ns) & 1u;
+    mbar_wait(bar_at + st * 16u, par);
+    const StageDesc d = s_desc[st];
+    if (d.flags & kDescEnd) {
+      if (lane == 0) mbar_arrive(bar_at + st * 16u + 8u);
+      break;
+    }
+    const Job j = s_jobs[d.job_local];
+    const uint32_t job = jlo + d.job_local;
+    const uint32_t sbase = s_stage_addr[st];
+    const size_t byte_lo = (size_t)d.row_lo * kRowBytes;
+    uint32_t crc = 0;
+    if (d.flags & kDescTma) {
+      if (lane == 0 && j.dst) bulk_store(j.dst + byte_lo, sbase, d.rows * kRowBytes);  // starts at once; reads shared only
+      if (kCrc) {
+        uint32_t S0 = 0, S1 = 0, S2 = 0, S3 = 0;
+        const uint32_t p = sbase + lane * 16u;
+        uint32_t r = 0;
+        for (; r + 4 <= d.rows; r += 4) {
+          const uint4 w0 = lds_v4(p + (r + 0) * kRowBytes), w1 = lds_v4(p + (r + 1) * kRowBytes);
+          const uint4 w2 = lds_v4(p + (r + 2) * kRowBytes), w3 = lds_v4(p + (r + 3) * kRowBytes);
+          APS_FOLD_ROW(w0);
+          APS_FOLD_ROW(w1);
+          APS_FOLD_ROW(w2);
+          APS_FOLD_ROW(w3);
+        }
+        for (; r < d.rows; ++r) {
+          const uint4 w = lds_v4(p + r * kRowBytes);
+          APS_FOLD_ROW(w);
+        }
+        const uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
+        crc = warp_xor(gf_mul(t, c_lane_shift[lane]));
+      }
+    } else if (d.rows) {  // unaligned job: bytes straight from global memory
+      crc = warp_bytes<kCrc>(j.src + byte_lo, j.dst ? j.dst + byte_lo : nullptr, d.rows * kRowBytes, lane);
+    }
+    // the rows have been read (and the store has finished reading them): give the stage back before the
+    // per-chunk arithmetic, so that its refill overlaps it
+    if (lane == 0) {
+      if (d.flags & kDescTma) bulk_store_wait_read();
+      mbar_arrive(bar_at + st * 16u + 8u);
+    }
+    uint32_t contrib = 0, units = d.rows;
+    if (kCrc && d.rows) contrib = gf_mul(crc, shift_for(a.rowshift, j.n - (uint32_t)(byte_lo + (size_t)d.rows * kRowBytes)));
+    if (d.flags & kDescTail) {
+      const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
+      const uint32_t ct = warp_bytes<kCrc>(j.src + t0, j.dst ? j.dst + t0 : nullptr, j.n - t0, lane);
+      if (kCrc) contrib ^= ct;
+      units += 1;
+    }
+    if (!kCrc) continue;
+    const uint32_t target = (j.n + kRowBytes - 1) / kRowBytes;
+    if (lane == 0) {
+      atomicXor(&a.acc[job], contrib);
+      __threadfence();
+      const uint32_t prev = atomicAdd(&a.done[job], units);
+      if (prev + units == target) {
+        __threadfence();
+        const uint32_t x = atomicExch(&a.acc[job], 0u);
+        const uint32_t full = x ^ gf_mul(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
+        bool corrupt = false;
+        if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
+        if (j.flags & kJobOutCrc) a.crc_out[job] = full;
+        const uint32_t* recorded = (kGet && j.pad) ? a.shards[j.pad - 1u].slot_crc : a.table.slot_crc;
+        if ((j.flags & kJobVerify) && __ldcg(&recorded[j.slot]) != full) {
+          corrupt = true;
+          atomicAdd(&a.table.counters[kCtrCrcMismatch], 1ull);
+        }
+        if (a.res) a.res[job] = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
+        a.done[job] = 0;
+      }
+    }
+  }
+  if (lane == 0) bulk_store_wait_all();  // the stores must have landed before the kernel is reported complete
 }
 
 #ifndef APS_KERNELS_TEMPLATES_ONLY  // a second translation unit wants the templates above, not these definitions
