@@ -28,6 +28,8 @@ SIGNATURES = {
     "apc_positioned_read": (_i32, [_vp, _cp, _i64, _i64, _vp, _i32, EXTERNAL_READ, _vp, C.POINTER(_i64), C.POINTER(_i64)]),
     "apc_replay": (_i64, [_vp, _i64, _vp, _vp, _vp, _u64, C.c_int, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64),
                           C.POINTER(_i64), C.POINTER(_i64)]),
+    "apc_replay_batched": (_i64, [_vp, _i64, _vp, _vp, _vp, _u64, C.c_uint32, _vp, _vp, _vp, _vp, _i64, C.POINTER(_i64),
+                                  C.POINTER(_i64), _vp, C.POINTER(_dbl), C.POINTER(_dbl)]),
     "apc_evictor_create": (_vp, [_cp, _dbl]),
     "apc_evictor_destroy": (None, [_vp]),
     "apc_evictor_update_on_get": (None, [_vp, _cp, _i64]),
@@ -249,3 +251,30 @@ class LocalCacheManager:
         k = min(nv, cap)
         return dict(hit=hit, put_ok=put_ok, victims=np.stack([vf[:k], vp[:k]], axis=1), n_victims=nv,
                     final_pages=fp.value, final_bytes=fb.value, verify_failures=bad.value)
+
+
+def _replay_batched(self, files, pages, page_lens, seed, window=4096, victims_cap=None):
+    """apc_replay_batched: same decisions as replay(), store operations issued in batches."""
+    import numpy as np
+    files = np.ascontiguousarray(files, dtype=np.int64)
+    pages = np.ascontiguousarray(pages, dtype=np.int64)
+    page_lens = np.ascontiguousarray(page_lens, dtype=np.int32)
+    n = files.size
+    cap = n if victims_cap is None else victims_cap
+    hit, put_ok = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+    vf, vp = np.zeros(max(cap, 1), np.int64), np.zeros(max(cap, 1), np.int64)
+    fp, fb = C.c_int64(), C.c_int64()
+    ops = np.zeros(5, np.int64)
+    th, ts = C.c_double(), C.c_double()
+    nv = lib().apc_replay_batched(self._h, n, files.ctypes.data, pages.ctypes.data, page_lens.ctypes.data, seed, window,
+                                  hit.ctypes.data, put_ok.ctypes.data, vf.ctypes.data, vp.ctypes.data, cap, C.byref(fp),
+                                  C.byref(fb), ops.ctypes.data, C.byref(th), C.byref(ts))
+    if nv < 0:
+        raise RuntimeError("apc_replay_batched failed")
+    k = min(nv, cap)
+    return dict(hit=hit, put_ok=put_ok, victims=np.stack([vf[:k], vp[:k]], axis=1), n_victims=nv,
+                final_pages=fp.value, final_bytes=fb.value, deletes=int(ops[0]), puts=int(ops[1]), gets=int(ops[2]),
+                flushes=int(ops[3]), bad_gets=int(ops[4]), seconds_host=th.value, seconds_store=ts.value)
+
+
+LocalCacheManager.replay_batched = _replay_batched

@@ -1067,6 +1067,45 @@ int aps_fill_pages_dev(int32_t device, void* d_dst, uint64_t stride, uint32_t pa
   return APS_OK;
 }
 
+int aps_fill_pages(aps_store* s, void* d_dst, uint64_t stride, uint32_t page_len, uint32_t n_pages, const uint64_t* files,
+                   const uint64_t* indices, uint64_t seed, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (n_pages == 0) return APS_OK;
+  if (!d_dst || !files || !indices || n_pages > s->cfg.max_batch) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  uint64_t* h = reinterpret_cast<uint64_t*>(s->h_stage);  // 16 bytes per page <= sizeof(aps_get_req)
+  memcpy(h, files, (size_t)n_pages * 8);
+  memcpy(h + n_pages, indices, (size_t)n_pages * 8);
+  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h, (size_t)n_pages * 16, cudaMemcpyHostToDevice, st));
+  const uint64_t* d = reinterpret_cast<const uint64_t*>(s->d_reqs);
+  rc = aps_fill_pages_dev(s->cfg.device, d_dst, stride, page_len, n_pages, d, d + n_pages, seed, st);
+  if (rc) return rc;
+  CUDA_TRY(cudaStreamSynchronize(st));  // the staging area is reused by the next call
+  return APS_OK;
+}
+
+int aps_device_alloc(int32_t device, uint64_t bytes, void** out) {
+  if (!out) return APS_EINVAL;
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "cudaMalloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? APS_ENOMEM : APS_ECUDA;
+  }
+  return APS_OK;
+}
+int aps_device_free(int32_t device, void* p) {
+  DeviceGuard g(device);
+  if (!g.ok) return APS_ECUDA;
+  CUDA_TRY(cudaFree(p));
+  return APS_OK;
+}
+
 int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_data, const uint64_t* d_len,
                       uint8_t (*d_out)[16], aps_stream stream) {
   if (n_files == 0) return APS_OK;

@@ -240,7 +240,7 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
 // warp that completes a job's last row applies init/xorout and verifies or records the page CRC.
 template <bool kCrc, int kThreads, int G, bool kGet>
 __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr uint32_t nwarps = kThreads / 32;
   __shared__ unsigned long long s_range[nwarps];  // published ranges: open to stealing
   __shared__ unsigned long long s_priv[nwarps];   // ranges of tasks that are not a warp's last: private

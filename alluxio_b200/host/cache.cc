@@ -526,6 +526,7 @@ using namespace alluxio_b200;
 struct apc_manager {
   std::unique_ptr<LocalCacheManager> mgr;
   GpuPageStore* gpu = nullptr;  // owned by mgr
+  int32_t device = 0;
 };
 struct apc_evictor {
   std::unique_ptr<CacheEvictor> ev;
@@ -560,6 +561,7 @@ int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_lo
   if (rc != APS_OK) return rc;
   apc_manager* m = new apc_manager();
   m->gpu = store.get();
+  m->device = cfg->device;
   m->mgr.reset(new LocalCacheManager(cfg->page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(store)));
   *out = m;
   return APS_OK;
@@ -718,3 +720,128 @@ int apc_meta_evict(apc_meta* m, char* file_out, size_t cap, int64_t* index_out, 
 }
 
 }  // extern "C"
+
+// ==================================================================================== batched replay
+#include <chrono>
+#include <unordered_set>
+
+namespace {
+using Clock = std::chrono::steady_clock;
+inline double Secs(Clock::time_point a, Clock::time_point b) { return std::chrono::duration<double>(b - a).count(); }
+}  // namespace
+
+extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* file, const int64_t* page,
+                                      const int32_t* page_len, uint64_t seed, uint32_t window, uint8_t* hit, uint8_t* put_ok,
+                                      int64_t* victim_file, int64_t* victim_page, int64_t victims_cap, int64_t* final_pages,
+                                      int64_t* final_bytes, int64_t* store_ops, double* seconds_host, double* seconds_store) {
+  LocalCacheManager* mgr = m->mgr.get();
+  MetaStore* meta = mgr->meta();
+  aps_store* store = m->gpu->handle();
+  const int64_t cacheSize = mgr->store()->GetCacheSize();
+  const uint32_t ps = (uint32_t)mgr->pageSize();
+  if (window == 0) window = 1024;
+  // device staging: put payloads and a sink for gets (aps_config.device is not visible here: the store knows)
+  aps_stats_t st0{};
+  if (aps_stats(store, &st0) != APS_OK) return -1;
+  void *d_put = nullptr, *d_sink = nullptr;
+  const int32_t dev = m->device;
+  if (aps_device_alloc(dev, (uint64_t)window * ps, &d_put) != APS_OK) return -1;
+  if (aps_device_alloc(dev, (uint64_t)window * ps, &d_sink) != APS_OK) {
+    aps_device_free(dev, d_put);
+    return -1;
+  }
+  std::vector<aps_key> dels;
+  std::vector<aps_put_req> puts;
+  std::vector<aps_get_req> gets;
+  std::vector<uint64_t> put_files, put_pages;
+  std::vector<aps_result> res;
+  std::unordered_set<Key, KeyHash> pendingPuts, pendingGets;
+  int64_t ops[5] = {0, 0, 0, 0, 0};
+  double tStore = 0;
+  bool failed = false;
+  auto flush = [&]() {
+    if (dels.empty() && puts.empty() && gets.empty()) return;
+    const auto t0 = Clock::now();
+    ops[3]++;
+    if (!dels.empty()) {
+      res.resize(dels.size());
+      if (aps_delete_batch(store, (uint32_t)dels.size(), dels.data(), res.data(), nullptr) != APS_OK) failed = true;
+      for (auto& r : res) if (r.len != 0) failed = true;
+      ops[0] += (int64_t)dels.size();
+    }
+    if (!puts.empty()) {
+      // payload: all pages of this flush generated at full page stride, then put with their real lengths
+      if (aps_fill_pages(store, d_put, ps, ps, (uint32_t)puts.size(), put_files.data(), put_pages.data(), seed, nullptr) != APS_OK)
+        failed = true;
+      res.resize(puts.size());
+      if (aps_put_batch(store, (uint32_t)puts.size(), puts.data(), res.data(), nullptr) != APS_OK) failed = true;
+      for (size_t i = 0; i < puts.size(); ++i) if (res[i].len != (int32_t)puts[i].len) failed = true;
+      ops[1] += (int64_t)puts.size();
+    }
+    if (!gets.empty()) {
+      res.resize(gets.size());
+      if (aps_get_batch(store, (uint32_t)gets.size(), gets.data(), res.data(), nullptr) != APS_OK) failed = true;
+      for (size_t i = 0; i < gets.size(); ++i) if (res[i].len != (int32_t)gets[i].nbytes) ops[4]++;
+      ops[2] += (int64_t)gets.size();
+    }
+    dels.clear(); puts.clear(); gets.clear(); put_files.clear(); put_pages.clear();
+    pendingPuts.clear(); pendingGets.clear();
+    tStore += Secs(t0, Clock::now());
+  };
+  const auto tBegin = Clock::now();
+  int64_t nv = 0;
+  for (int64_t k = 0; k < n && !failed; ++k) {
+    const Key key{0, (uint64_t)file[k], (uint64_t)page[k]};  // decimal file ids encode as (0, value)
+    const int32_t len = page_len[k];
+    put_ok[k] = 255;
+    if (meta->HasPage(key)) {  // LocalCacheManager.get: hit
+      hit[k] = 1;
+      gets.push_back(aps_get_req{aps_key{key.hi, key.lo, key.idx}, 0, (uint32_t)len, (uint8_t*)d_sink + (size_t)gets.size() * ps});
+      pendingGets.insert(key);
+    } else {  // miss -> put (LocalCacheManager.putInternal, single-threaded reading)
+      hit[k] = 0;
+      bool enough = meta->Bytes() + len <= cacheSize, doPut = false;
+      if (enough) {
+        meta->AddPage(key, PageMeta{len, 0});
+        doPut = true;
+      } else {
+        Key victim;
+        PageMeta vm;
+        if (!meta->Evict(&victim, &vm)) {
+          put_ok[k] = 0;
+        } else {
+          meta->RemovePage(victim);
+          enough = meta->Bytes() + len <= cacheSize;
+          if (enough) meta->AddPage(key, PageMeta{len, 0});
+          if (pendingPuts.count(victim) || pendingGets.count(victim)) flush();  // keep per-id order
+          dels.push_back(aps_key{victim.hi, victim.lo, victim.idx});
+          if (nv < victims_cap) {
+            victim_file[nv] = (int64_t)victim.lo;
+            victim_page[nv] = (int64_t)victim.idx;
+          }
+          ++nv;
+          doPut = enough;
+          if (!enough) put_ok[k] = 0;
+        }
+      }
+      if (doPut) {
+        put_ok[k] = 1;
+        puts.push_back(aps_put_req{aps_key{key.hi, key.lo, key.idx}, (uint32_t)len, 0, (uint8_t*)d_put + (size_t)puts.size() * ps});
+        put_files.push_back((uint64_t)file[k]);
+        put_pages.push_back((uint64_t)page[k]);
+        pendingPuts.insert(key);
+      }
+    }
+    if (dels.size() >= window || puts.size() >= window || gets.size() >= window) flush();
+  }
+  flush();
+  const double tAll = Secs(tBegin, Clock::now());
+  aps_device_free(dev, d_put);
+  aps_device_free(dev, d_sink);
+  if (final_pages) *final_pages = meta->Pages();
+  if (final_bytes) *final_bytes = meta->Bytes();
+  if (store_ops) memcpy(store_ops, ops, sizeof(ops));
+  if (seconds_store) *seconds_store = tStore;
+  if (seconds_host) *seconds_host = tAll - tStore;
+  return failed ? -1 : nv;
+}

@@ -226,6 +226,14 @@ APS_API int aps_crc32c_noalloc(int32_t device, uint32_t n, const void* const* d_
 APS_API int aps_fill_pages_dev(int32_t device, void* d_dst, uint64_t stride, uint32_t page_len, uint32_t n_pages,
                        const uint64_t* d_files, const uint64_t* d_indices, uint64_t seed, aps_stream stream);
 
+/* Host-array form of aps_fill_pages_dev (files / indices on the host, n_pages <= max_batch). */
+APS_API int aps_fill_pages(aps_store* s, void* d_dst, uint64_t stride, uint32_t page_len, uint32_t n_pages,
+                           const uint64_t* files, const uint64_t* indices, uint64_t seed, aps_stream stream);
+/* Plain device buffers for embedders that have no CUDA runtime of their own (staging areas for batched
+ * puts and gets).  Thin wrappers over cudaMalloc / cudaFree on `device`. */
+APS_API int aps_device_alloc(int32_t device, uint64_t bytes, void** out);
+APS_API int aps_device_free(int32_t device, void* p);
+
 typedef struct aps_stats_t {
   uint64_t pages;           /* resident pages */
   uint64_t bytes;           /* sum of their stored lengths */

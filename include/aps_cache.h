@@ -71,6 +71,19 @@ APS_API int64_t apc_replay(apc_manager* m, int64_t n, const int64_t* file, const
                            int64_t* victim_page, int64_t victims_cap, int64_t* final_pages, int64_t* final_bytes,
                            int64_t* verify_failures);
 
+/* The same replay with the store operations BATCHED: admission and eviction are decided on the host
+ * access by access exactly as above (so hit/miss and victim sequences are identical), but the store
+ * operations they imply are collected -- deletes of victims, puts of missed pages (payload generated on
+ * the device), gets of hits -- and issued as aps_delete_batch / aps_put_batch / aps_get_batch in that order
+ * every `window` accesses, or earlier when an operation would be reordered against a pending one on the
+ * same id.  This is how the host-side evictor drives GPU hash-table inserts and erases at speed.
+ * store_ops[0..2] receive the numbers of deletes, puts and gets issued, store_ops[3] the number of flushes,
+ * store_ops[4] the gets whose length or status was not the expected one (must be 0). */
+APS_API int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* file, const int64_t* page,
+                                   const int32_t* page_len, uint64_t seed, uint32_t window, uint8_t* hit, uint8_t* put_ok,
+                                   int64_t* victim_file, int64_t* victim_page, int64_t victims_cap, int64_t* final_pages,
+                                   int64_t* final_bytes, int64_t* store_ops, double* seconds_host, double* seconds_store);
+
 /* ---- policy objects on their own (no GPU needed) ------------------------------------------------ */
 APS_API apc_evictor* apc_evictor_create(const char* kind, double lfu_logbase);
 APS_API void apc_evictor_destroy(apc_evictor* e);

@@ -197,3 +197,43 @@ def test_replay_matches_oracle_element_by_element(evictor):
     st = m.store_stats()
     assert st["pages"] == got["final_pages"] and st["bytes"] == got["final_bytes"] and st["crc_mismatches"] == 0
     m.close()
+
+
+@pytest.mark.parametrize("evictor", ["LRU", "LFU"])
+def test_batched_replay_equals_oracle_and_single_page_replay(evictor):
+    """The batched driver (victim deletes, miss puts and hit gets issued as GPU batches) takes the same
+    decisions as the reference flow: identical hit vector, put results and victim order as the oracle."""
+    ps = 65536
+    n_ids, cap_pages, n_acc = 20000, 1500, 60000
+    rng = np.random.default_rng(11)
+    pz = np.arange(1, n_ids + 1, dtype=np.float64) ** -0.99
+    pz /= pz.sum()
+    ids = rng.permutation(n_ids)[rng.choice(n_ids, size=n_acc, p=pz)]
+    files, pages = ids // 100, ids % 100
+    lens = np.where(pages == 99, 2000 + files, ps).astype(np.int32)
+    cache_bytes = cap_pages * ps
+    want = orc.replay(evictor, ps, cache_bytes, files, pages, lens)
+    m = manager(cache_size=cache_bytes, evictor=evictor, page_size=ps, slab_slots=cap_pages + 256, max_batch=1024)
+    got = m.replay_batched(files, pages, lens, seed=0xA11C10, window=1024)
+    assert got["bad_gets"] == 0
+    assert np.array_equal(got["hit"], want["hit"])
+    assert np.array_equal(got["put_ok"], want["put_ok"])
+    assert got["n_victims"] == want["n_victims"] > 0
+    assert np.array_equal(got["victims"], want["victims"])
+    assert (got["final_pages"], got["final_bytes"]) == (want["final_pages"], want["final_bytes"])
+    assert got["gets"] == int(want["hit"].sum()) and got["deletes"] == want["n_victims"]
+    st = m.store_stats()
+    assert st["pages"] == got["final_pages"] and st["bytes"] == got["final_bytes"] and st["crc_mismatches"] == 0
+    # residency on the device equals the host's view: every id the oracle says is resident reads back
+    buf = bytearray(ps)
+    last_seen = {}
+    for k in range(n_acc):
+        last_seen[(int(files[k]), int(pages[k]))] = int(lens[k])
+    resident = 0
+    for (f, p), ln in list(last_seen.items())[:400]:
+        r = m.get(PID(f, p), ln, buf)
+        if r > 0:
+            resident += 1
+            assert bytes(buf[:ln]) == orc.fill_page(0xA11C10, f, p, ln).tobytes()
+    assert resident > 0
+    m.close()
