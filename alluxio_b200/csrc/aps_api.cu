@@ -56,6 +56,7 @@ uint32_t host_xpow8(uint64_t nbytes) {  // x^(8*nbytes) mod P by square and mult
 struct DeviceConsts {
   bool ready = false;
   CrcTables* d_tables = nullptr;
+  uint8_t* d_table_image = nullptr;  // shared-memory image of the tables (bytes kSmemG..kSmemEnd of the window)
   int num_sms = 0;
   // SM speed classes (see calibrate_sms): d_sm_slow[smid] = 1 for SMs that stream measurably slower
   uint8_t* d_sm_slow = nullptr;
@@ -142,6 +143,20 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
     const HostCrcConsts& h = host_crc_consts();
     CUDA_TRY(cudaMalloc(&d.d_tables, sizeof(CrcTables)));
     CUDA_TRY(cudaMemcpy(d.d_tables, &h.tables, sizeof(CrcTables), cudaMemcpyHostToDevice));
+    {
+      // the image the copy kernel pulls into shared memory with bulk-async copies: plain x^32 tables, then
+      // the four x^(8*512) tables with every entry replicated for the 32 lanes (see kSmemF's layout)
+      std::vector<uint8_t> img(kSmemEnd - kSmemG, 0);
+      memcpy(img.data(), h.tables.z4, sizeof(h.tables.z4));
+      for (uint32_t j = 0; j < 4; ++j)
+        for (uint32_t b = 0; b < 256; ++b)
+          for (uint32_t l = 0; l < 32; ++l) {
+            const uint32_t at = (kSmemF - kSmemG) + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + l * 4u;
+            memcpy(img.data() + at, &h.tables.fold[j][b], 4);
+          }
+      CUDA_TRY(cudaMalloc(&d.d_table_image, img.size()));
+      CUDA_TRY(cudaMemcpy(d.d_table_image, img.data(), img.size(), cudaMemcpyHostToDevice));
+    }
     CUDA_TRY(cudaMemcpyToSymbol(c_xpow8, h.xpow8, sizeof(h.xpow8)));
     CUDA_TRY(cudaMemcpyToSymbol(c_lane_shift, h.lane_shift, sizeof(h.lane_shift)));
     for (const CopyVariant& v : kCopyVariants) {
@@ -244,6 +259,7 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.acc = s->d_acc;
   a.done = s->d_done;
   a.tables = s->dc->d_tables;
+  a.table_image = getenv("APS_NO_TABLE_IMAGE") ? nullptr : s->dc->d_table_image;
   a.rowshift = s->d_rowshift;
   a.error_flag = s->d_error;
   a.timeline = s->d_timeline;

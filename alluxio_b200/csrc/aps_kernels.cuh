@@ -93,6 +93,38 @@ __device__ __forceinline__ uint32_t warp_xor(uint32_t v) {
     S2 = fold_word(S2, rb) ^ (v_).z; S3 = fold_word(S3, rb) ^ (v_).w;     \
   } while (0)
 
+// ---- mbarrier / bulk-async (TMA) primitives
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+               "l"(gsrc), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // ---- row ranges shared inside a CTA ------------------------------------------------------------
 // Every warp publishes the rows it still has to do in one 64-bit shared-memory word:
 //   bits  0..31  next unclaimed row (relative to the job)
@@ -128,7 +160,7 @@ __device__ __forceinline__ Claim claim_rows(unsigned long long* range, uint32_t 
 // (same value in every lane, when kCrc); *row_end receives the first row it did NOT process.
 template <bool kCrc, int G>
 __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst, unsigned long long* range, uint32_t row_lo,
-                                                uint32_t lane, uint32_t* row_end) {
+                                                uint32_t lane, uint32_t* row_end, uint32_t tables_bar) {
   const uint4* s = reinterpret_cast<const uint4*>(src) + lane;  // src/dst point at row 0 of the job
   uint4* d = reinterpret_cast<uint4*>(dst) + lane;
   const bool store = dst != nullptr;
@@ -155,6 +187,8 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   uint32_t end = row_lo;
   Claim ca = claim_rows<G>(range, lane);
   load(A, ca);
+  // the first loads are in flight; only now make sure the CRC tables have landed in shared memory
+  if (kCrc && tables_bar) mbar_wait(tables_bar, 0);
   while (ca.cnt) {
     Claim cb = claim_rows<G>(range, lane);
     load(B, cb);
@@ -204,6 +238,8 @@ struct CopyArgs {
   uint32_t* acc;           // scratch: per-job XOR of the shifted segment CRCs; zero on entry, reset by the finisher
   uint32_t* done;          // scratch: per-job count of finished 512-byte rows; zero on entry, reset by the finisher
   const CrcTables* tables;
+  const uint8_t* table_image;  // optional: the shared-memory image of the CRC tables (bytes 0x0F000..0x30000 of the window),
+                               // fetched with four bulk-async copies while the first pages are being looked up
   const uint32_t* rowshift;  // rowshift[k] = x^(8 * 512 * k), k = 0 .. rows of a full page
   int* error_flag;           // set if the shared-memory window is not where the kernel needs it
   unsigned long long* timeline;  // optional (aps_debug_timeline)
@@ -253,23 +289,23 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   asm volatile("griddepcontrol.launch_dependents;");
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t n_items = a.n_jobs * a.tasks_per_job;
-  // Rank of this CTA among the CTAs of the launch: CTAs on fast SMs count up from 0, CTAs on slow SMs
-  // count down from the top, so the ranks are unique whatever the placement.  Tasks are dealt out by
-  // rank and the ranks below (n_items % grid) get one task more: the surplus lands on the fast SMs.
-  __shared__ uint32_t s_rank;
-  if (threadIdx.x == 0) {
+  // Task assignment.  n_items / grid tasks per CTA are fixed by blockIdx, so warps can start at once.  The
+  // n_items % grid surplus tasks go to the CTAs with the lowest RANK: CTAs on fast SMs count up from 0,
+  // CTAs on slow SMs count down from the top (unique whatever the placement), so the surplus lands on the
+  // fast SMs.  Only the warp that would take the surplus needs the rank; it asks for it now and looks at
+  // the answer when it gets there.
+  const uint32_t base_cnt = n_items / gridDim.x, extra = n_items % gridDim.x;
+  const uint32_t surplus_warp = base_cnt % nwarps;
+  uint32_t rank_reg = 0xFFFFFFFFu;
+  if (warp == surplus_warp && lane == 0) {
     uint32_t smid;
     asm("mov.u32 %0, %%smid;" : "=r"(smid));
     const bool slow = a.sm_slow[smid & 255u] != 0;
-    s_rank = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
-    __threadfence();
-    if (atomicAdd(&a.sched[2], 1u) == gridDim.x - 1u) {  // every CTA has its rank: re-arm for the next launch
-      a.sched[0] = 0;
-      a.sched[1] = 0;
-      a.sched[2] = 0;
-    }
+    rank_reg = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
   }
   if (lane == 0) s_range[warp] = 0;
+  __shared__ __align__(8) unsigned long long s_tables_bar;
+  uint32_t tables_bar = 0;
   if (kCrc) {
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     uint32_t dyn;
@@ -278,41 +314,56 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       if (threadIdx.x == 0) *a.error_flag = 1;
       return;
     }
-    // Each thread fetches its table entries up front (coalesced, independent loads); the warp then
-    // broadcasts entry by entry and every lane writes its own replica.
-    const uint32_t* gfold = &a.tables->fold[0][0];
-    const uint32_t* gz4 = &a.tables->z4[0][0];
-    constexpr uint32_t kPerWarp = 1024 / nwarps;  // fold entries per warp
-    static_assert(1024 % nwarps == 0 && kPerWarp % 32 == 0, "fold table split");
-    uint32_t mine[kPerWarp / 32], zmine[(1024 + kThreads - 1) / kThreads];
-#pragma unroll
-    for (uint32_t q = 0; q < kPerWarp / 32; ++q) mine[q] = __ldg(&gfold[warp * kPerWarp + q * 32 + lane]);
-#pragma unroll
-    for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
-      const uint32_t idx = threadIdx.x + q * kThreads;
-      zmine[q] = idx < 1024 ? __ldg(&gz4[idx]) : 0u;
-    }
-#pragma unroll
-    for (uint32_t q = 0; q < kPerWarp / 32; ++q) {
-#pragma unroll
-      for (uint32_t k = 0; k < 32; ++k) {
-        const uint32_t idx = warp * kPerWarp + q * 32 + k, j = idx >> 8, b = idx & 255u;
-        sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine[q], k));
+    if (a.table_image) {
+      // bulk-async copies of the ready-made table image; nobody waits here
+      tables_bar = (uint32_t)__cvta_generic_to_shared(&s_tables_bar);
+      if (threadIdx.x == 0) {
+        mbar_init(tables_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       }
-    }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        constexpr uint32_t kImage = kSmemEnd - kSmemG, kPiece = kImage / 4;
+        mbar_arrive_expect_tx(tables_bar, kImage);
 #pragma unroll
-    for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
-      const uint32_t idx = threadIdx.x + q * kThreads;
-      if (idx < 1024) sts_u32(kSmemG + idx * 4u, zmine[q]);
+        for (uint32_t q = 0; q < 4; ++q) bulk_load(kSmemG + q * kPiece, a.table_image + q * kPiece, kPiece, tables_bar);
+      }
+    } else {
+      // Each thread fetches its table entries up front (coalesced, independent loads); the warp then
+      // broadcasts entry by entry and every lane writes its own replica.
+      const uint32_t* gfold = &a.tables->fold[0][0];
+      const uint32_t* gz4 = &a.tables->z4[0][0];
+      constexpr uint32_t kPerWarp = 1024 / nwarps;  // fold entries per warp
+      static_assert(1024 % nwarps == 0 && kPerWarp % 32 == 0, "fold table split");
+      uint32_t mine[kPerWarp / 32], zmine[(1024 + kThreads - 1) / kThreads];
+#pragma unroll
+      for (uint32_t q = 0; q < kPerWarp / 32; ++q) mine[q] = __ldg(&gfold[warp * kPerWarp + q * 32 + lane]);
+#pragma unroll
+      for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
+        const uint32_t idx = threadIdx.x + q * kThreads;
+        zmine[q] = idx < 1024 ? __ldg(&gz4[idx]) : 0u;
+      }
+#pragma unroll
+      for (uint32_t q = 0; q < kPerWarp / 32; ++q) {
+#pragma unroll
+        for (uint32_t k = 0; k < 32; ++k) {
+          const uint32_t idx = warp * kPerWarp + q * 32 + k, j = idx >> 8, b = idx & 255u;
+          sts_u32(kSmemF + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + lane * 4u, __shfl_sync(0xFFFFFFFFu, mine[q], k));
+        }
+      }
+#pragma unroll
+      for (uint32_t q = 0; q < (1024 + kThreads - 1) / kThreads; ++q) {
+        const uint32_t idx = threadIdx.x + q * kThreads;
+        if (idx < 1024) sts_u32(kSmemG + idx * 4u, zmine[q]);
+      }
+      __syncthreads();
     }
+  } else {
+    __syncthreads();
   }
-  __syncthreads();
   if (a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();
-  const uint32_t rank = s_rank;
-  const uint32_t base_cnt = n_items / gridDim.x, extra = n_items % gridDim.x;
-  const uint32_t my_first = rank * base_cnt + min(rank, extra);
-  const uint32_t my_count = base_cnt + (rank < extra ? 1u : 0u);
-  uint32_t local = warp;  // this warp takes the CTA's tasks local, local + nwarps, ...
+  uint32_t local = warp;  // this warp takes the CTA's fixed tasks local, local + nwarps, ...
+  bool surplus_pending = warp == surplus_warp && extra > 0;
 
   uint32_t gen = 0;
   for (;;) {
@@ -321,12 +372,23 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     uint32_t job, row_lo, row_hi;
     bool tail_mine = false;  // task 0 of a job also owns the sub-row tail (n % 512 bytes)
     bool publish = false;
-    if (local < my_count) {
-      const uint32_t item = my_first + local;
+    uint32_t item = 0xFFFFFFFFu;
+    bool last_item = false;
+    if (local < base_cnt) {
+      item = blockIdx.x * base_cnt + local;
+      local += nwarps;
+      last_item = local >= base_cnt && !surplus_pending;
+    } else if (surplus_pending) {
+      surplus_pending = false;
+      const uint32_t rank = __shfl_sync(0xFFFFFFFFu, rank_reg, 0);
+      if (rank < extra) {
+        item = base_cnt * gridDim.x + rank;
+        last_item = true;
+      }
+    }
+    if (item != 0xFFFFFFFFu) {
       job = item / a.tasks_per_job;
       const uint32_t c = item - job * a.tasks_per_job;
-      const bool last_item = local + nwarps >= my_count;
-      local += nwarps;
       if (kGet) {
         // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
         const aps_get_req rq = a.reqs[job];
@@ -423,7 +485,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         }
         __syncwarp();
         uint32_t row_end = row_lo;
-        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end);
+        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end, tables_bar);
         rows_done = row_end - row_lo;
         end_byte = row_end * kRowBytes;
       } else {
@@ -473,6 +535,16 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       a.done[job] = 0;
     }
   }
+  if (warp == surplus_warp && lane == 0) {
+    // this CTA holds its rank (the answer was consumed above or is awaited here); the last CTA to say so
+    // re-arms the counters for the next launch
+    if (rank_reg != 0xFFFFFFFFu) __threadfence();
+    if (atomicAdd(&a.sched[2], 1u) == gridDim.x - 1u) {
+      a.sched[0] = 0;
+      a.sched[1] = 0;
+      a.sched[2] = 0;
+    }
+  }
   if (a.timeline) {
     if (lane == 0) a.timeline[1024 + blockIdx.x * 32 + warp] = globaltimer_ns();
     if (lane == 0) atomicMin(&a.timeline[blockIdx.x * 4 + 2], globaltimer_ns());
@@ -508,37 +580,6 @@ struct StageDesc {
   uint32_t job_local, row_lo, rows, flags;
 };
 
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void bulk_load(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
-               "l"(gsrc), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void bulk_store(void* gdst, uint32_t smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_src), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-__device__ __forceinline__ void bulk_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ uint4 lds_v4(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
