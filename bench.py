@@ -299,12 +299,12 @@ def run_ours(args):
     if os.environ.get("APS_BENCH_TIMELINE") == "1":  # diagnostic: per-CTA / per-warp timestamps of single launches
         none = np.uint64(0xFFFFFFFFFFFFFFFF)
         per_sm = []
+        capi.check(L.aps_debug_timeline(h, 1, None, 0))
         for rep in range(4):
-            capi.check(L.aps_debug_timeline(h, 1, None, 0))
             for k in range(3):
                 step_dev(rep * 3 + k)
             raw = np.zeros(1024 + 256 * 32 + 256, np.uint64)
-            capi.check(L.aps_debug_timeline(h, 0, raw.ctypes.data, raw.size))
+            capi.check(L.aps_debug_timeline(h, 1, raw.ctypes.data, raw.size))
             tl = raw[:1024].reshape(256, 4)
             live = tl[:, 0] != none
             tl = tl[live].astype(np.int64)
@@ -331,6 +331,9 @@ def run_ours(args):
         cc = np.corrcoef(m)
         print("timeline per-SM end offset: correlation between launches %s; SMs seen %d (ids %d..%d)" %
               (np.round(cc[0, 1:], 2).tolist(), len(common), common[0], common[-1]), file=sys.stderr)
+        off = np.sort(m.mean(axis=0))
+        print("timeline per-SM mean end offset us, sorted (every 6th): " + " ".join("%.1f" % x for x in off[::6]), file=sys.stderr)
+        capi.check(L.aps_debug_timeline(h, 0, None, 0))
         slow = np.argsort(-m.mean(axis=0))[:8]
         print("timeline slowest SMs (id: mean offset us over 4 launches): " +
               ", ".join("%d: %+.1f" % (common[i], m[:, i].mean()) for i in slow), file=sys.stderr)
