@@ -15,7 +15,12 @@ EXTERNAL_READ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int3
 
 SIGNATURES = {
     "apc_manager_create": (C.c_int, [C.POINTER(capi.aps_config), _cp, _dbl, C.POINTER(_vp)]),
+    "apc_manager_create_over": (C.c_int, [_vp, C.c_uint32, _cp, _dbl, C.POINTER(_vp)]),
     "apc_manager_close": (C.c_int, [_vp]),
+    "apc_get_noexcept": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
+    "apc_metrics_read": (None, [_vp, _vp]),
+    "apc_positioned_read_batched": (_i32, [_vp, _cp, _i64, _i64, _vp, _i32, EXTERNAL_READ, _vp, C.POINTER(_i64),
+                                           C.POINTER(_i64)]),
     "apc_put": (C.c_int, [_vp, _cp, _i64, _vp, _i32]),
     "apc_get": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
     "apc_delete": (C.c_int, [_vp, _cp, _i64]),
@@ -166,6 +171,33 @@ class LocalCacheManager:
         self._h = h
         self.page_size = page_size
 
+    @classmethod
+    def over_store(cls, store, page_size, evictor="LRU", lfu_logbase=2.0):
+        """LocalCacheManager.create(conf, metaStore, pageStore) over a store that already holds pages
+        (a GpuPageStore from alluxio_b200.page_store): runs the reference's restore."""
+        self = cls.__new__(cls)
+        h = C.c_void_p()
+        capi.check(lib().apc_manager_create_over(store.handle, page_size, evictor.encode(), lfu_logbase, C.byref(h)))
+        self._h, self.page_size, self._keep = h, page_size, store
+        return self
+
+    METRIC_NAMES = ("BytesReadCache", "BytesRequestedExternal", "BytesReadExternal", "BytesWrittenCache", "BytesEvicted",
+                    "PagesEvicted", "GetErrors", "PutErrors", "DeleteErrors", "PutEvictionErrors", "PutStoreWriteErrors",
+                    "PutStoreDeleteErrors", "GetStoreReadErrors", "DeleteNonExistingPageErrors")
+
+    def metrics(self):
+        import numpy as np
+        v = np.zeros(14, np.int64)
+        lib().apc_metrics_read(self._h, v.ctypes.data)
+        return dict(zip(self.METRIC_NAMES, v.tolist()))
+
+    def get_noexcept(self, p, bytes_to_read, buffer, offset_in_buffer=0, page_offset=0):
+        cbuf = (C.c_uint8 * max(1, len(buffer))).from_buffer(buffer) if len(buffer) else (C.c_uint8 * 1)()
+        r = lib().apc_get_noexcept(self._h, _f(p), p.page_index, page_offset, bytes_to_read, C.addressof(cbuf), len(buffer),
+                                   offset_in_buffer)
+        del cbuf
+        return r
+
     def close(self):
         if self._h is not None:
             lib().apc_manager_close(self._h)
@@ -215,7 +247,7 @@ class LocalCacheManager:
         capi.check(capi.lib().aps_stats(lib().apc_store(self._h), C.byref(st)))
         return {n: getattr(st, n) for n, _ in capi.aps_stats_t._fields_}
 
-    def positioned_read(self, file_id, file_len, pos, length, external):
+    def positioned_read(self, file_id, file_len, pos, length, external, batched=False):
         """LocalCacheFileInStream.positionedRead: `external(pos, n) -> bytes` stands for the
         external FileInStream.  Returns (data or None at EOF, bytes_from_cache, bytes_from_external)."""
         import numpy as np
@@ -228,8 +260,8 @@ class LocalCacheManager:
             return len(data)
 
         cb = EXTERNAL_READ(ext)
-        r = lib().apc_positioned_read(self._h, str(file_id).encode(), file_len, pos, out.ctypes.data, length, cb, None,
-                                      C.byref(fc), C.byref(fe))
+        fn = lib().apc_positioned_read_batched if batched else lib().apc_positioned_read
+        r = fn(self._h, str(file_id).encode(), file_len, pos, out.ctypes.data, length, cb, None, C.byref(fc), C.byref(fe))
         if r == -2:
             raise ValueError("IllegalArgumentException")
         return (None if r < 0 else out[:r].tobytes()), fc.value, fe.value

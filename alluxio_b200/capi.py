@@ -82,6 +82,8 @@ SIGNATURES = {
     "aps_fill_pages": (C.c_int, [_vp, _vp, _u64, _u32, _u32, _vp, _vp, _u64, _vp]),
     "aps_device_alloc": (C.c_int, [_i32, _u64, C.POINTER(_vp)]),
     "aps_device_free": (C.c_int, [_i32, _vp]),
+    "aps_host_alloc_pinned": (C.c_int, [_u64, C.POINTER(_vp)]),
+    "aps_host_free_pinned": (C.c_int, [_vp]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),
     "aps_profile_begin": (C.c_int, [_vp, _u32]),

@@ -1117,6 +1117,20 @@ int aps_device_alloc(int32_t device, uint64_t bytes, void** out) {
   }
   return APS_OK;
 }
+int aps_host_alloc_pinned(uint64_t bytes, void** out) {
+  if (!out) return APS_EINVAL;
+  cudaError_t e = cudaHostAlloc(out, bytes, cudaHostAllocDefault);
+  if (e != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "cudaHostAlloc(%llu): %s", (unsigned long long)bytes, cudaGetErrorString(e));
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? APS_ENOMEM : APS_ECUDA;
+  }
+  return APS_OK;
+}
+int aps_host_free_pinned(void* p) {
+  CUDA_TRY(cudaFreeHost(p));
+  return APS_OK;
+}
 int aps_device_free(int32_t device, void* p) {
   DeviceGuard g(device);
   if (!g.ok) return APS_ECUDA;

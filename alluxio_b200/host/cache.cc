@@ -339,8 +339,15 @@ int GpuPageStore::Open(const aps_config& cfg, std::unique_ptr<GpuPageStore>* out
   *out = std::move(g);
   return APS_OK;
 }
+std::unique_ptr<GpuPageStore> GpuPageStore::Adopt(aps_store* s) {
+  std::unique_ptr<GpuPageStore> g(new GpuPageStore());
+  g->mStore = s;
+  g->mCacheBytes = aps_cache_size(s);
+  g->mOwned = false;
+  return g;
+}
 GpuPageStore::~GpuPageStore() {
-  if (mStore) aps_close(mStore);
+  if (mStore && mOwned) aps_close(mStore);
 }
 static aps_key ToAps(const Key& k) { return aps_key{k.hi, k.lo, k.idx}; }
 int GpuPageStore::Put(const Key& k, const void* page, int32_t len) {
@@ -393,8 +400,13 @@ int32_t LocalCacheManager::GetPageLockId(const std::string& fileId, int64_t page
 }
 
 bool LocalCacheManager::Put(const std::string& fileId, int64_t pageIndex, const void* page, int32_t len) {  // :206-246
-  if (mState.load() != READ_WRITE) return false;
-  return PutInternal(MakeKey(fileId, pageIndex), GetPageLockId(fileId, pageIndex), page, len);
+  if (mState.load() != READ_WRITE) {
+    metrics.putErrors++;
+    return false;
+  }
+  const bool ok = PutInternal(MakeKey(fileId, pageIndex), GetPageLockId(fileId, pageIndex), page, len);
+  if (ok) metrics.bytesWrittenCache += len; else metrics.putErrors++;
+  return ok;
 }
 
 bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* page, int32_t len) {  // :249-347
@@ -439,7 +451,12 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
     return false;
   }
   if (logEvictions) evicted.push_back(victim);
-  if (!enoughSpace) return false;  // :331-334 one victim per put
+  metrics.bytesEvicted += victimMeta.size;
+  metrics.pagesEvicted++;
+  if (!enoughSpace) {  // :331-334 one victim per put
+    metrics.putEvictionErrors++;
+    return false;
+  }
   if (mPageStore->Put(k, page, len) == APS_OK) return true;
   UndoAddPage(k);  // :339-344
   return false;
@@ -469,20 +486,75 @@ int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int
   if (rc != APS_OK || got != bytesToRead) {           // :544-549, :384-395
     std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
     mMetaStore->RemovePage(k);
+    metrics.getErrors++;
+    metrics.getStoreReadErrors++;
     return -1;
   }
   return bytesToRead;
 }
 
+void LocalCacheManager::GetMany(const std::string& fileId, int64_t firstPage, int32_t n, const int32_t* offset,
+                                const int32_t* len, void* const* dst, int32_t* got) {
+  for (int32_t i = 0; i < n; ++i) got[i] = 0;
+  auto* gpu = dynamic_cast<GpuPageStore*>(mPageStore.get());
+  if (!gpu || mState.load() == NOT_IN_USE || n <= 0) return;
+  // page read locks of all pages involved, in lock-id order (the reference's deadlock rule, :197-203)
+  std::vector<int32_t> lockIds((size_t)n);
+  for (int32_t i = 0; i < n; ++i) lockIds[(size_t)i] = GetPageLockId(fileId, firstPage + i);
+  std::vector<int32_t> order(lockIds);
+  std::sort(order.begin(), order.end());
+  order.erase(std::unique(order.begin(), order.end()), order.end());
+  std::vector<std::shared_lock<std::shared_mutex>> held;
+  held.reserve(order.size());
+  for (int32_t id : order) held.emplace_back(mPageLocks[id]);
+  std::vector<aps_get_req> reqs;
+  std::vector<int32_t> which;
+  std::vector<Key> keys;
+  {
+    std::shared_lock<std::shared_mutex> metaLock(mMetaLock);
+    for (int32_t i = 0; i < n; ++i) {
+      const Key k = MakeKey(fileId, firstPage + i);
+      if (!mMetaStore->HasPage(k)) continue;
+      reqs.push_back(aps_get_req{aps_key{k.hi, k.lo, k.idx}, (uint32_t)offset[i], (uint32_t)len[i], dst[i]});
+      which.push_back(i);
+      keys.push_back(k);
+    }
+  }
+  if (reqs.empty()) return;
+  std::vector<aps_result> res(reqs.size());
+  const int rc = aps_get_batch(gpu->handle(), (uint32_t)reqs.size(), reqs.data(), res.data(), nullptr);
+  for (size_t r = 0; r < reqs.size(); ++r) {
+    const int32_t i = which[r];
+    if (rc == APS_OK && res[r].len == len[i]) {
+      got[i] = len[i];
+    } else {  // inconsistent with the meta store: drop the page, as get() does
+      std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+      mMetaStore->RemovePage(keys[r]);
+      metrics.getErrors++;
+      metrics.getStoreReadErrors++;
+      got[i] = -1;
+    }
+  }
+}
+
 bool LocalCacheManager::Delete(const std::string& fileId, int64_t pageIndex) {  // :402-429
-  if (mState.load() != READ_WRITE) return false;
+  if (mState.load() != READ_WRITE) {
+    metrics.deleteErrors++;
+    return false;
+  }
   const Key k = MakeKey(fileId, pageIndex);
   std::unique_lock<std::shared_mutex> pageLock(mPageLocks[GetPageLockId(fileId, pageIndex)]);
   {
     std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
-    if (!mMetaStore->RemovePage(k)) return false;
+    if (!mMetaStore->RemovePage(k)) {
+      metrics.deleteNonExistingPageErrors++;
+      metrics.deleteErrors++;
+      return false;
+    }
   }
-  return mPageStore->Delete(k) == APS_OK;
+  const bool ok = mPageStore->Delete(k) == APS_OK;
+  if (!ok) metrics.deleteErrors++;
+  return ok;
 }
 
 void LocalCacheManager::RestoreOrInit() {  // :441-464
@@ -566,6 +638,100 @@ int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_lo
   *out = m;
   return APS_OK;
 }
+int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase, apc_manager** out) {
+  if (!store || !evictor || !out) return APS_EINVAL;
+  *out = nullptr;
+  auto ev = CacheEvictor::Create(evictor, lfu_logbase);
+  if (!ev) return APS_EINVAL;
+  std::unique_ptr<GpuPageStore> gs = GpuPageStore::Adopt(store);
+  apc_manager* m = new apc_manager();
+  m->gpu = gs.get();
+  m->mgr.reset(new LocalCacheManager(page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(gs)));
+  *out = m;
+  return APS_OK;
+}
+
+// NoExceptionCacheManager (CACHE/NoExceptionCacheManager.java:37-79): nothing escapes; errors are counted.
+int32_t apc_get_noexcept(apc_manager* m, const char* f, int64_t i, int32_t page_offset, int32_t bytes_to_read, void* buffer,
+                         int32_t buffer_len, int32_t offset_in_buffer) {
+  const int32_t r = m->mgr->Get(f, i, page_offset, bytes_to_read, buffer, buffer_len, offset_in_buffer);
+  if (r == kGetIllegalArgument) {
+    m->mgr->metrics.getErrors++;
+    return -1;
+  }
+  return r;
+}
+
+void apc_metrics_read(apc_manager* m, int64_t* out14) {
+  const CacheMetrics& c = m->mgr->metrics;
+  const int64_t v[14] = {c.bytesReadCache, c.bytesRequestedExternal, c.bytesReadExternal, c.bytesWrittenCache, c.bytesEvicted,
+                         c.pagesEvicted, c.getErrors, c.putErrors, c.deleteErrors, c.putEvictionErrors, c.putStoreWriteErrors,
+                         c.putStoreDeleteErrors, c.getStoreReadErrors, c.deleteNonExistingPageErrors};
+  memcpy(out14, v, sizeof(v));
+}
+
+// Multi-page read in one store call: LocalCacheFileInStream.positionedRead with the per-page
+// CacheManager.get loop (CACHE/LocalCacheFileInStream.java:192-214) replaced by ONE batched get for all resident
+// pages; pages that miss are fetched whole from `external` and put, as in the reference.  dst may be any host
+// memory: a pageable dst is served through a pinned staging buffer.
+int32_t apc_positioned_read_batched(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst, int32_t len,
+                                    apc_external_read external, void* user, int64_t* from_cache, int64_t* from_external) {
+  if (len < 0 || pos < 0) return APC_GET_ILLEGAL_ARGUMENT;
+  if (len == 0) return 0;
+  if (pos >= file_len) return -1;
+  LocalCacheManager* mgr = m->mgr.get();
+  const int64_t ps = mgr->pageSize();
+  const int64_t toRead = std::min<int64_t>(len, file_len - pos);
+  const int64_t firstPage = pos / ps, lastPage = (pos + toRead - 1) / ps;
+  const int32_t n = (int32_t)(lastPage - firstPage + 1);
+  void* stage = nullptr;
+  if (aps_host_alloc_pinned((uint64_t)toRead, &stage) != APS_OK) return -1;
+  std::vector<int32_t> off((size_t)n), ln((size_t)n), got((size_t)n);
+  std::vector<void*> dsts((size_t)n);
+  int64_t cur = pos, done = 0;
+  for (int32_t i = 0; i < n; ++i) {
+    off[(size_t)i] = (int32_t)(cur % ps);
+    ln[(size_t)i] = (int32_t)std::min<int64_t>(ps - off[(size_t)i], toRead - done);
+    dsts[(size_t)i] = (uint8_t*)stage + done;
+    cur += ln[(size_t)i];
+    done += ln[(size_t)i];
+  }
+  mgr->GetMany(file_id, firstPage, n, off.data(), ln.data(), dsts.data(), got.data());
+  std::vector<uint8_t> page;
+  int32_t result = (int32_t)toRead;
+  done = 0;
+  for (int32_t i = 0; i < n && result >= 0; ++i) {
+    uint8_t* out = (uint8_t*)dst + done;
+    if (got[(size_t)i] > 0) {
+      memcpy(out, dsts[(size_t)i], (size_t)ln[(size_t)i]);
+      mgr->metrics.bytesReadCache += ln[(size_t)i];
+      if (from_cache) *from_cache += ln[(size_t)i];
+    } else {
+      const int64_t pageStart = (firstPage + i) * ps;
+      const int32_t plen = (int32_t)std::min<int64_t>(ps, file_len - pageStart);
+      page.resize((size_t)plen);
+      int32_t have = 0;
+      while (have < plen) {
+        const int r = external(user, pageStart + have, page.data() + have, plen - have);
+        if (r <= 0) break;
+        have += r;
+      }
+      mgr->metrics.bytesReadExternal += have;
+      if (have != plen) {
+        result = -1;
+        break;
+      }
+      memcpy(out, page.data() + off[(size_t)i], (size_t)ln[(size_t)i]);
+      mgr->metrics.bytesRequestedExternal += ln[(size_t)i];
+      if (from_external) *from_external += ln[(size_t)i];
+      mgr->Put(file_id, firstPage + i, page.data(), plen);
+    }
+    done += ln[(size_t)i];
+  }
+  aps_host_free_pinned(stage);
+  return result;
+}
+
 int apc_manager_close(apc_manager* m) {
   delete m;
   return APS_OK;

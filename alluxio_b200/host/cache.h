@@ -122,6 +122,8 @@ class PageStore {
 class GpuPageStore : public PageStore {
  public:
   static int Open(const aps_config& cfg, std::unique_ptr<GpuPageStore>* out);
+  // Wraps a store somebody else opened (and will close): PageStore.open over existing contents.
+  static std::unique_ptr<GpuPageStore> Adopt(aps_store* s);
   ~GpuPageStore() override;
   int Put(const Key& k, const void* page, int32_t len) override;
   int Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) override;
@@ -132,6 +134,15 @@ class GpuPageStore : public PageStore {
  private:
   aps_store* mStore = nullptr;
   uint64_t mCacheBytes = 0;
+  bool mOwned = true;
+};
+
+// Counters of the reference's Client.Cache* metrics that live in this layer
+// (core/common/src/main/java/alluxio/metrics/MetricKey.java:778-995; LocalCacheManager.java:557-627).
+struct CacheMetrics {
+  std::atomic<int64_t> bytesReadCache{0}, bytesRequestedExternal{0}, bytesReadExternal{0}, bytesWrittenCache{0},
+      bytesEvicted{0}, pagesEvicted{0}, getErrors{0}, putErrors{0}, deleteErrors{0}, putEvictionErrors{0},
+      putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0};
 };
 
 // ---- CACHE/LocalCacheManager.java:75-627 (sync write, sync restore) -------------------------------------
@@ -154,6 +165,12 @@ class LocalCacheManager {
   // eviction log for replays (cleared by the caller)
   std::vector<Key> evicted;
   bool logEvictions = false;
+  CacheMetrics metrics;
+  // Several pages of one file in one store call: for pages [firstPage, firstPage + n) asks
+  // the store for (offset[i], len[i]) of each page that is resident, into dst[i]; got[i] = bytes read, 0 for a
+  // miss, -1 for an error (the page is then dropped, as in get()).  dst must be device or pinned memory.
+  void GetMany(const std::string& fileId, int64_t firstPage, int32_t n, const int32_t* offset, const int32_t* len,
+               void* const* dst, int32_t* got);
  private:
   static constexpr int kLockSize = 1024;
   Key MakeKey(const std::string& fileId, int64_t pageIndex);

@@ -232,6 +232,9 @@ APS_API int aps_fill_pages(aps_store* s, void* d_dst, uint64_t stride, uint32_t 
 /* Plain device buffers for embedders that have no CUDA runtime of their own (staging areas for batched
  * puts and gets).  Thin wrappers over cudaMalloc / cudaFree on `device`. */
 APS_API int aps_device_alloc(int32_t device, uint64_t bytes, void** out);
+/* Page-locked host memory (cudaHostAlloc / cudaFreeHost): kernels read and write it in place over PCIe. */
+APS_API int aps_host_alloc_pinned(uint64_t bytes, void** out);
+APS_API int aps_host_free_pinned(void* p);
 APS_API int aps_device_free(int32_t device, void* p);
 
 typedef struct aps_stats_t {

@@ -36,6 +36,11 @@ typedef struct apc_meta apc_meta;       /* DefaultMetaStore */
  * evictor: "LRU" (evictor/LRUCacheEvictor.java), "LFU" (evictor/LFUCacheEvictor.java) or "FIFO" (the
  * test double of CTEST/LocalCacheManagerTest.java:731-761). */
 APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_logbase, apc_manager** out);
+/* LocalCacheManager.create(conf, metaStore, pageStore) over a store that already holds pages: the restore
+ * path (CACHE/LocalCacheManager.java:466-509) adopts them in getPages() order while they fit the cache size
+ * and deletes the rest from the store.  The store stays the caller's (apc_manager_close does not close it). */
+APS_API int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
+                                    apc_manager** out);
 APS_API int apc_manager_close(apc_manager* m);
 /* CacheManager.put(PageId, byte[]) -> boolean, CACHE/LocalCacheManager.java:206-347 */
 APS_API int apc_put(apc_manager* m, const char* file_id, int64_t page_index, const void* page, int32_t len);
@@ -43,6 +48,15 @@ APS_API int apc_put(apc_manager* m, const char* file_id, int64_t page_index, con
  * miss, -1 on error, CACHE/LocalCacheManager.java:360-399 */
 APS_API int32_t apc_get(apc_manager* m, const char* file_id, int64_t page_index, int32_t page_offset,
                         int32_t bytes_to_read, void* buffer, int32_t buffer_len, int32_t offset_in_buffer);
+/* The same through NoExceptionCacheManager (CACHE/NoExceptionCacheManager.java:59-68): an illegal argument
+ * becomes -1 and is counted as a get error. */
+APS_API int32_t apc_get_noexcept(apc_manager* m, const char* file_id, int64_t page_index, int32_t page_offset,
+                                 int32_t bytes_to_read, void* buffer, int32_t buffer_len, int32_t offset_in_buffer);
+/* Client.Cache* counters kept by this layer, in this order: BytesReadCache, BytesRequestedExternal,
+ * BytesReadExternal, BytesWrittenCache, BytesEvicted, PagesEvicted, GetErrors, PutErrors, DeleteErrors,
+ * PutEvictionErrors, PutStoreWriteErrors, PutStoreDeleteErrors, GetStoreReadErrors, DeleteNonExistingPageErrors
+ * (core/common/src/main/java/alluxio/metrics/MetricKey.java:778-995). */
+APS_API void apc_metrics_read(apc_manager* m, int64_t* out14);
 /* CacheManager.delete(PageId) -> boolean, CACHE/LocalCacheManager.java:402-429 */
 APS_API int apc_delete(apc_manager* m, const char* file_id, int64_t page_index);
 APS_API int apc_state(apc_manager* m);
@@ -60,6 +74,11 @@ typedef int (*apc_external_read)(void* user, int64_t file_pos, void* dst, int32_
 APS_API int32_t apc_positioned_read(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst,
                                     int32_t len, apc_external_read external, void* user, int64_t* bytes_from_cache,
                                     int64_t* bytes_from_external);
+
+/* The same read with ONE batched store call for all resident pages it touches. */
+APS_API int32_t apc_positioned_read_batched(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst,
+                                            int32_t len, apc_external_read external, void* user,
+                                            int64_t* bytes_from_cache, int64_t* bytes_from_external);
 
 /* Trace replay, BASELINE config 3: for every access run the reference read flow -- get; on a miss the
  * page (page_len[k] bytes of the synthetic payload for (file, page), seed) is put.  file ids are the

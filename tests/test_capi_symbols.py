@@ -55,3 +55,19 @@ def test_open_rejects_bad_config_and_fails_loudly_without_gpu():
     from alluxio_b200.page_store import GpuPageStore, IOExceptionJ
     with pytest.raises(IOExceptionJ):
         GpuPageStore(page_size=4096, cache_size=1 << 20)
+
+
+def declared_cache_symbols():
+    text = open(os.path.join(ROOT, "include", "aps_cache.h")).read()
+    return sorted(set(re.findall(r"APS_API\s+[\w\s\*]+?\b(apc_\w+)\s*\(", text)))
+
+
+def test_host_library_exports_and_binds_every_symbol_of_aps_cache_h():
+    from alluxio_b200 import cache
+    syms = declared_cache_symbols()
+    assert "apc_manager_create" in syms and "apc_replay_batched" in syms and "apc_evictor_evict" in syms
+    capi.lib()  # libaps.so first: the host library links against it
+    L = C.CDLL(cache.LIB_PATH)
+    for name in syms:
+        assert hasattr(L, name), name
+    assert sorted(cache.SIGNATURES) == syms

@@ -237,3 +237,73 @@ def test_batched_replay_equals_oracle_and_single_page_replay(evictor):
             assert bytes(buf[:ln]) == orc.fill_page(0xA11C10, f, p, ln).tobytes()
     assert resident > 0
     m.close()
+
+
+def test_restore_over_a_populated_store():
+    """CTEST/LocalCacheManagerTest.java:357-369 (syncRestore) and :494-511 (more pages than capacity): a manager
+    created over a store that already holds pages adopts what fits and deletes the rest from the store."""
+    import uuid
+    from alluxio_b200.cache import LocalCacheManager
+    from alluxio_b200.page_store import GpuPageStore
+    store = GpuPageStore(page_size=PAGE_SIZE, cache_size=CACHE_SIZE)
+    uid = PID(str(uuid.uuid4()), 0)
+    store.put(PID(*PAGE_ID1), PAGE1)
+    store.put(uid, PAGE2)
+    m = LocalCacheManager.over_store(store, PAGE_SIZE, "FIFO")
+    buf = bytearray(PAGE_SIZE)
+    assert m.state() == m.READ_WRITE
+    assert m.get(PID(*PAGE_ID1), PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1
+    assert m.get(uid, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE2
+    assert (m.pages(), m.bytes()) == (2, 2 * PAGE_SIZE)
+    m.close()
+    store.close()
+    # capacity for two pages, three in the store: one is discarded from the store during restore
+    store = GpuPageStore(page_size=PAGE_SIZE, cache_size=2 * PAGE_SIZE, slab_slots=16)
+    for i in range(3):
+        store.put(PID("5", i), increasing(i, PAGE_SIZE))
+    m = LocalCacheManager.over_store(store, PAGE_SIZE, "LRU")
+    assert (m.pages(), m.bytes()) == (2, 2 * PAGE_SIZE)
+    assert len(store.get_pages()) == 2
+    hits = sum(m.get(PID("5", i), PAGE_SIZE, buf) == PAGE_SIZE for i in range(3))
+    assert hits == 2
+    m.close()
+    store.close()
+
+
+def test_no_exception_manager_and_metrics():
+    m = manager(cache_size=2 * PAGE_SIZE)
+    p1, p2, p3 = PID("a", 0), PID("a", 1), PID("a", 2)
+    buf = bytearray(PAGE_SIZE)
+    assert m.get_noexcept(p1, PAGE_SIZE, bytearray(PAGE_SIZE - 1)) == -1      # IllegalArgument swallowed
+    assert m.put(p1, PAGE1) and m.put(p2, PAGE2) and m.put(p3, PAGE1)          # third put evicts one page
+    assert not m.delete(PID("a", 99))
+    assert m.get_noexcept(p3, PAGE_SIZE, buf) == PAGE_SIZE
+    mt = m.metrics()
+    assert mt["GetErrors"] == 1 and mt["BytesWrittenCache"] == 3 * PAGE_SIZE
+    assert mt["PagesEvicted"] == 1 and mt["BytesEvicted"] == PAGE_SIZE
+    assert mt["DeleteErrors"] == 1 and mt["DeleteNonExistingPageErrors"] == 1
+    m.close()
+
+
+def test_batched_positioned_read_equals_per_page_reads():
+    """a multi-page read becomes one batched store call; same bytes, same cache effects."""
+    ps = 4096
+    file_len = 9 * ps + 777
+    data = np.random.default_rng(8).integers(0, 256, file_len, dtype=np.uint8).tobytes()
+    a = manager(cache_size=64 * ps, evictor="LRU", page_size=ps)
+    b = manager(cache_size=64 * ps, evictor="LRU", page_size=ps)
+    ext = lambda pos, n: data[pos:pos + n]  # noqa: E731
+    rng = np.random.default_rng(9)
+    for _ in range(40):
+        pos = int(rng.integers(0, file_len))
+        n = int(rng.integers(1, 4 * ps))
+        ra = a.positioned_read("12", file_len, pos, n, ext)
+        rb = b.positioned_read("12", file_len, pos, n, ext, batched=True)
+        assert ra == rb and ra[0] == data[pos:pos + n]
+    assert (a.pages(), a.bytes()) == (b.pages(), b.bytes())
+    got, fc, fe = b.positioned_read("12", file_len, 0, file_len, ext, batched=True)
+    got, fc, fe = b.positioned_read("12", file_len, 0, file_len, ext, batched=True)
+    assert got == data and fc == file_len and fe == 0            # second full read: every page from the cache
+    assert b.metrics()["BytesReadCache"] >= file_len
+    a.close()
+    b.close()
