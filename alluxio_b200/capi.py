@@ -84,6 +84,7 @@ SIGNATURES = {
     "aps_device_free": (C.c_int, [_i32, _vp]),
     "aps_host_alloc_pinned": (C.c_int, [_u64, C.POINTER(_vp)]),
     "aps_host_free_pinned": (C.c_int, [_vp]),
+    "aps_compact": (C.c_int, [_vp]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),
     "aps_profile_begin": (C.c_int, [_vp, _u32]),

@@ -708,7 +708,14 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   int rc = check_open(s);
   if (rc) return rc;
   if (n == 0) return APS_OK;
-  if (n > s->cfg.max_batch || !reqs || !res) return APS_EINVAL;
+  if (!reqs || !res) return APS_EINVAL;
+  if (n > s->cfg.max_batch) {  // larger than the staging area: serve it in pieces
+    for (uint32_t lo = 0; lo < n; lo += s->cfg.max_batch) {
+      rc = get_batch_host(s, std::min(s->cfg.max_batch, n - lo), reqs + lo, res + lo, stream, sharded);
+      if (rc) return rc;
+    }
+    return APS_OK;
+  }
   DeviceGuard g(s->cfg.device);
   std::lock_guard<std::mutex> lk(s->mu);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
@@ -862,6 +869,35 @@ int aps_iterate(aps_store* s, aps_iter_cb cb, void* user) {
     aps_key k{e.k0, e.k1, e.k2};
     if (cb(user, &k, meta_len(e.meta))) break;
   }
+  return APS_OK;
+}
+
+int aps_compact(aps_store* s) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (s->n_shards > 1) return APS_EINVAL;  // peers hold pointers into the current table
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  Entry* fresh = nullptr;
+  CUDA_TRY(cudaMalloc(&fresh, s->n_entries * sizeof(Entry)));
+  cudaError_t e = cudaMemsetAsync(fresh, 0, s->n_entries * sizeof(Entry), s->stream);
+  if (e == cudaSuccess) {
+    Table nt = s->table;
+    nt.entries = fresh;
+    const uint64_t threads = s->n_entries * 8;
+    rehash_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, s->stream>>>(nt, s->table.entries, s->n_entries);
+    count_launch(s);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemsetAsync(&s->table.counters[kCtrTombs], 0, sizeof(unsigned long long), s->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+  }
+  if (e != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "aps_compact: %s", cudaGetErrorString(e));
+    cudaFree(fresh);
+    return APS_ECUDA;
+  }
+  cudaFree(s->table.entries);
+  s->table.entries = fresh;
   return APS_OK;
 }
 

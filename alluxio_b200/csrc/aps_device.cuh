@@ -106,7 +106,7 @@ __device__ __forceinline__ int tile_insert(const Table& t, const aps_key& key, u
                                            uint32_t* slot_out) {
   const uint32_t tmask = 0xFFu << tshift;
   const uint64_t home = hash_key(key) & t.bucket_mask;
-  for (int attempt = 0; attempt < 64; ++attempt) {
+  for (int attempt = 0; attempt < (1 << 16); ++attempt) {  // a lost race means another key took one entry: bounded by the batch size
     uint64_t b = home;
     uint64_t cand = ~0ull, cand_seen = 0;
     bool ended = false;

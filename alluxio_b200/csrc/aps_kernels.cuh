@@ -905,6 +905,43 @@ __global__ void crc_jobs_kernel(const void* const* data, const uint32_t* len, ui
   if (l == 0) crc_out[i] = 0;
 }
 
+// Rebuild of the table without tombstones: every VALID entry of `old` is re-inserted (same slot, same
+// length) into the zeroed table `t`.  One tile of eight lanes per old entry.
+__global__ void rehash_kernel(Table t, const Entry* old, uint64_t n_old) {
+  const uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t i = gid >> 3;
+  const uint32_t sub = (uint32_t)gid & 7u, tshift = threadIdx.x & 24u, tmask = 0xFFu << tshift;
+  if (i >= n_old) return;
+  uint64_t k0, k1, k2, meta;
+  load_entry(old + i, k0, k1, k2, meta);
+  if (!(meta >> 63)) return;  // tile-uniform: all eight lanes read the same entry
+  const aps_key key{k0, k1, k2};
+  uint64_t b = hash_key(key) & t.bucket_mask;
+  for (uint64_t visited = 0; visited <= t.bucket_mask;) {  // a lost race re-reads the same bucket and is not a visit
+    uint64_t e0, e1, e2, em;
+    load_entry(t.entries + b * kBucketEntries + sub, e0, e1, e2, em);
+    uint32_t be = (__ballot_sync(tmask, em == kMetaEmpty) >> tshift) & 0xFFu;
+    int ok = 0;
+    if (be) {
+      const uint64_t cand = b * kBucketEntries + (__ffs(be) - 1);
+      if (sub == 0) ok = atomicCAS((unsigned long long*)&t.entries[cand].meta, 0ull, (unsigned long long)kMetaLocked) == 0ull;
+      ok = __shfl_sync(tmask, ok, tshift);
+      if (ok) {
+        if (sub == 0) {
+          Entry* e = t.entries + cand;
+          e->k0 = k0; e->k1 = k1; e->k2 = k2;
+          __threadfence();
+          e->meta = meta;
+        }
+        return;
+      }
+      continue;  // lost the entry to another key: look at the same bucket again
+    }
+    b = (b + 1) & t.bucket_mask;
+    ++visited;
+  }
+}
+
 __global__ void init_free_slots_kernel(uint32_t* free_slots, uint64_t n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) free_slots[i] = (uint32_t)(n - 1 - i);  // slot 0 is handed out first

@@ -136,7 +136,7 @@ typedef struct aps_put_req {
 
 /* Batched LocalPageStore.get.  reqs and res are HOST arrays; the call stages them, runs the
  * lookup + gather (+CRC) kernels on `stream`, copies the results back and waits for them.
- * Keys within one batch need not be distinct for gets. */
+ * Keys within one batch need not be distinct for gets.  n may exceed max_batch (served in pieces). */
 APS_API int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream);
 
 /* Batched LocalPageStore.put.  Keys within one batch must be distinct (else APS_EINVAL). */
@@ -257,6 +257,11 @@ APS_API int aps_stats(aps_store* s, aps_stats_t* out);
  * returns the summed device time and the number of launches timed. */
 APS_API int aps_profile_begin(aps_store* s, uint32_t max_launches);
 APS_API int aps_profile_end(aps_store* s, double* copy_ms_total, uint32_t* copy_launches);
+
+/* Rebuilds the hash table without tombstones (they only arise when pages are deleted from buckets that were
+ * completely full; aps_stats reports how many there are).  Waits; no other call may run
+ * on the store meanwhile; not available once peers are attached (aps_shard_attach). */
+APS_API int aps_compact(aps_store* s);
 
 /* Fault injection for the reference's FaultyPageStore tests (CTEST/LocalCacheManagerTest.java:
  * 660-691): while set, aps_put / aps_delete fail with APS_EFAULT and change nothing. */

@@ -92,3 +92,42 @@ def test_table_full_reports_no_space():
         b = bytearray(1)
         assert store.get(PageId("3", i), b) == 1
     store.close()
+
+
+def test_compact_removes_tombstones_and_keeps_every_page():
+    import ctypes as C
+    from alluxio_b200 import capi
+    from alluxio_b200.page_store import GpuPageStore, PageId
+    # a table of 4 buckets for 32 slots: buckets fill up completely, so deletes leave tombstones
+    store = GpuPageStore(page_size=16, cache_size=1 << 20, slab_slots=32, table_capacity=32, crc=True)
+    for i in range(32):
+        store.put(PageId("8", i), bytes([i]) * 16)
+    for i in range(0, 32, 2):
+        store.delete(PageId("8", i))
+    st = store.stats()
+    assert st["pages"] == 16 and st["tombstones"] > 0
+    capi.check(capi.lib().aps_compact(store.handle))
+    st = store.stats()
+    assert st["pages"] == 16 and st["tombstones"] == 0
+    for i in range(32):
+        buf = bytearray(16)
+        if i % 2:
+            assert store.get(PageId("8", i), buf) == 16 and bytes(buf) == bytes([i]) * 16
+        else:
+            with pytest.raises(Exception):
+                store.get(PageId("8", i), buf)
+    for i in range(0, 32, 2):           # the freed slots and entries are usable again
+        store.put(PageId("9", i), bytes([i + 100]) * 16)
+    assert store.stats()["pages"] == 32
+    # host-array batches larger than max_batch are served in pieces
+    import torch
+    from gpu_util import GET_REQ, RESULT
+    s2 = GpuPageStore(page_size=16, cache_size=1 << 20, slab_slots=64, max_batch=8, crc=True)
+    for i in range(40):
+        s2.put(PageId("1", i), bytes([i]) * 16)
+    pinned = torch.zeros(40 * 16, dtype=torch.uint8).pin_memory()
+    res = s2.get_batch([(PageId("1", i), 0, 16, pinned.data_ptr() + i * 16) for i in range(40)])
+    assert [r[0] for r in res] == [16] * 40
+    assert pinned.numpy().reshape(40, 16)[:, 0].tolist() == list(range(40))
+    s2.close()
+    store.close()

@@ -53,6 +53,11 @@ int main() {
     if (width == 16) copy_k<16><<<148 * 2, 512, 0, st[d]>>>(s, dst[d], bytes);
     else copy_k<32><<<148 * 2, 512, 0, st[d]>>>(s, dst[d], bytes);
   };
+  auto push = [&](int d, int width) {  // read local, write into the peer
+    cudaSetDevice(d);
+    if (width == 16) copy_k<16><<<148 * 2, 512, 0, st[d]>>>(src[d], dst[1 - d], bytes);
+    else copy_k<32><<<148 * 2, 512, 0, st[d]>>>(src[d], dst[1 - d], bytes);
+  };
   for (int width : {16, 32}) {
     // local copy, for reference
     run(0, src[0], width);
@@ -76,6 +81,19 @@ int main() {
     for (int d = 0; d < 2; ++d) { cudaSetDevice(d); cudaEventRecord(e1[d], st[d]); }
     for (int d = 0; d < 2; ++d) { cudaSetDevice(d); cudaEventSynchronize(e1[d]); cudaEventElapsedTime(&ms, e0[d], e1[d]); worst = ms > worst ? ms : worst; }
     printf("width %2d  peer read, both ways: %.1f GB/s per GPU\n", width, 5.0 * bytes / worst / 1e6);
+    // peer writes: one way, then both ways
+    push(0, width);
+    cudaSetDevice(0); cudaEventRecord(e0[0], st[0]);
+    for (int i = 0; i < 5; ++i) push(0, width);
+    cudaEventRecord(e1[0], st[0]); cudaEventSynchronize(e1[0]);
+    cudaEventElapsedTime(&ms, e0[0], e1[0]);
+    printf("width %2d  peer write, one way : %.1f GB/s\n", width, 5.0 * bytes / ms / 1e6);
+    for (int d = 0; d < 2; ++d) { cudaSetDevice(d); cudaEventRecord(e0[d], st[d]); }
+    for (int i = 0; i < 5; ++i) for (int d = 0; d < 2; ++d) push(d, width);
+    worst = 0;
+    for (int d = 0; d < 2; ++d) { cudaSetDevice(d); cudaEventRecord(e1[d], st[d]); }
+    for (int d = 0; d < 2; ++d) { cudaSetDevice(d); cudaEventSynchronize(e1[d]); cudaEventElapsedTime(&ms, e0[d], e1[d]); worst = ms > worst ? ms : worst; }
+    printf("width %2d  peer write, both ways: %.1f GB/s per GPU\n", width, 5.0 * bytes / worst / 1e6);
   }
   return 0;
 }
