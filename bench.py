@@ -394,6 +394,20 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     assert (h_res["len"] == PAGE).all()
+    # what the link allows: a plain copy-engine transfer of the same 256 MiB from HBM to the pinned buffer
+    pcie_gbps = None
+    if not quick:
+        dsrc = dst[:BATCH * PAGE]
+        for _ in range(2):
+            pinned.copy_(dsrc, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record(stream)
+        for _ in range(5):
+            pinned.copy_(dsrc, non_blocking=True)
+        c1.record(stream)
+        torch.cuda.synchronize(dev)
+        pcie_gbps = 5 * BATCH * PAGE / (c0.elapsed_time(c1) * 1e-3) / 1e9
 
     # ---- auxiliary numbers (not the headline): put with CRC
     aux = {}
@@ -541,7 +555,9 @@ def run_ours(args):
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
         "e2e": {"value": round(world * e2e_steps * step_bytes / e2e_s / 1e9, 2), "unit": UNIT,
                 "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
-                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound)"},
+                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound)",
+                "pcie_memcpy_d2h_GBps": None if pcie_gbps is None else round(pcie_gbps, 2),
+                "frac_of_pcie_memcpy": None if pcie_gbps is None else round(e2e_steps * step_bytes / e2e_s / 1e9 / pcie_gbps, 4)},
         "gpu_launches": int(launches), "clocks": clocks, "aux": aux,
         "copy_variant": os.environ.get("APS_COPY_VARIANT", "default") + ("" if with_crc else " NOCRC"),
         "table": {"lookups": int(stats.lookups), "probe_buckets": int(stats.probe_buckets)},
