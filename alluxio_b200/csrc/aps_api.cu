@@ -645,7 +645,7 @@ int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_r
   if (n > s->cfg.max_batch || !d_reqs || !d_res) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  put_resolve_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
+  put_resolve_kernel<<<tile_grid(n), kK1Threads, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
   return launch_copy(s, n, nullptr, d_res, nullptr, st);
@@ -658,7 +658,7 @@ int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, aps_re
   if (!d_keys || !d_res) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  delete_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_keys, n, d_res);
+  delete_kernel<<<tile_grid(n), kK1Threads, 0, st>>>(s->table, d_keys, n, d_res);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
   return APS_OK;
@@ -671,7 +671,7 @@ int aps_lookup_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, int32_
   if (!d_keys || !d_len) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  lookup_kernel<<<tile_grid(n), 256, 0, st>>>(s->table, d_keys, n, d_len);
+  lookup_kernel<<<tile_grid(n), kK1Threads, 0, st>>>(s->table, d_keys, n, d_len);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
   return APS_OK;

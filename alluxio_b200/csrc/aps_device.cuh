@@ -100,10 +100,44 @@ __device__ __forceinline__ Probe tile_lookup(const Table& t, const aps_key& key,
   return r;
 }
 
-// Tile-cooperative insert-or-replace.  Returns APS_OK and the slot; *replaced_len >= 0 when the id was
-// already present (its slot is kept, PageStore.put overwrites).  Keys in one launch must be distinct.
-__device__ __forceinline__ int tile_insert(const Table& t, const aps_key& key, uint32_t len, uint32_t sub, uint32_t tshift,
-                                           uint32_t* slot_out) {
+// Block-scope accounting.  A batch kernel touches the store's counters and its free-slot stack once per
+// request; done as global atomics these all land on a handful of addresses and serialise in L2 at about
+// one per clock, which is what bounded the K1 kernels (1.1 G lookups/s against a random-read rate of 27 G
+// buckets/s).  Instead each block adds into shared memory and issues one global atomic per counter, and
+// takes or returns its free slots with one atomic for the whole block.
+struct BlockAcct {
+  uint32_t lo[kNumCounters], hi[kNumCounters];  // 64-bit sums kept as halves: shared memory adds natively in 32 bits only
+  int need;   // tiles of this block that take (put) or return (delete) a slot
+  int base;   // stack position the block's range starts at
+  int avail;  // how many of `need` were granted
+};
+__device__ __forceinline__ void acct_init(BlockAcct& a) {
+  if (threadIdx.x < kNumCounters) a.lo[threadIdx.x] = a.hi[threadIdx.x] = 0;
+  if (threadIdx.x == 0) a.need = 0;
+  __syncthreads();
+}
+__device__ __forceinline__ void acct_add(BlockAcct& a, Counter c, unsigned long long v) {  // v may be a two's complement negative
+  const uint32_t vlo = (uint32_t)v, old = atomicAdd(&a.lo[c], vlo);
+  const uint32_t vhi = (uint32_t)(v >> 32) + ((uint32_t)(old + vlo) < old ? 1u : 0u);  // carry out of the low half
+  if (vhi) atomicAdd(&a.hi[c], vhi);
+}
+__device__ __forceinline__ void acct_flush(BlockAcct& a, const Table& t) {  // call with the whole block
+  __syncthreads();
+  if (threadIdx.x < kNumCounters) {
+    const unsigned long long v = ((unsigned long long)a.hi[threadIdx.x] << 32) | a.lo[threadIdx.x];
+    if (v) atomicAdd(&t.counters[threadIdx.x], v);
+  }
+}
+
+// Tile-cooperative first half of insert-or-replace: finds the id or claims an entry for it (the entry is
+// left LOCKED, which probes of other ids step over).  Keys in one launch must be distinct.
+enum ClaimKind { kClaimFull = 0, kClaimReplace = 1, kClaimNew = 2 };
+struct EntryClaim {
+  int kind;
+  uint64_t entry_idx;  // the id's entry (replace) or the claimed one (new)
+  uint64_t was;        // replace: the old meta; new: what the claimed entry held (EMPTY or TOMB)
+};
+__device__ __forceinline__ EntryClaim tile_claim(const Table& t, const aps_key& key, uint32_t sub, uint32_t tshift) {
   const uint32_t tmask = 0xFFu << tshift;
   const uint64_t home = hash_key(key) & t.bucket_mask;
   for (int attempt = 0; attempt < (1 << 16); ++attempt) {  // a lost race means another key took one entry: bounded by the batch size
@@ -117,16 +151,9 @@ __device__ __forceinline__ int tile_insert(const Table& t, const aps_key& key, u
       uint32_t bm = (__ballot_sync(tmask, match) >> tshift) & 0xFFu;
       uint32_t be = (__ballot_sync(tmask, meta == kMetaEmpty) >> tshift) & 0xFFu;
       uint32_t bt = (__ballot_sync(tmask, meta == kMetaTomb) >> tshift) & 0xFFu;
-      if (bm) {  // replace in place: same slot, new length
+      if (bm) {  // present: PageStore.put overwrites, the slot is kept
         uint32_t src = __ffs(bm) - 1;
-        uint64_t old = __shfl_sync(tmask, meta, tshift + src);
-        uint32_t slot = meta_slot(old);
-        if (sub == src) {
-          t.entries[b * kBucketEntries + src].meta = meta_make(slot, len);
-          atomicAdd(&t.counters[kCtrBytes], (unsigned long long)len - (unsigned long long)meta_len(old));
-        }
-        *slot_out = slot;
-        return APS_OK;
+        return EntryClaim{kClaimReplace, b * kBucketEntries + src, __shfl_sync(tmask, meta, tshift + src)};
       }
       if (cand == ~0ull && (bt | be)) {  // keep EMPTY entries for chain termination: prefer a tombstone
         uint32_t pick = bt ? (__ffs(bt) - 1) : (__ffs(be) - 1);
@@ -136,54 +163,36 @@ __device__ __forceinline__ int tile_insert(const Table& t, const aps_key& key, u
       if (be) ended = true;
       b = (b + 1) & t.bucket_mask;
     }
-    if (cand == ~0ull) return APS_ENOSPC;  // every bucket full
+    if (cand == ~0ull) return EntryClaim{kClaimFull, 0, 0};  // every bucket full
     int ok = 0;
     if (sub == 0)
       ok = atomicCAS((unsigned long long*)&t.entries[cand].meta, (unsigned long long)cand_seen,
                      (unsigned long long)kMetaLocked) == cand_seen;
     ok = __shfl_sync(tmask, ok, tshift);
-    if (!ok) continue;  // another key took the entry first: rescan
-    uint32_t slot = kNoSlot;
-    if (sub == 0) {
-      int idx = atomicSub(t.free_top, 1) - 1;
-      if (idx < 0) atomicAdd(t.free_top, 1);
-      else slot = t.free_slots[idx];
-    }
-    slot = __shfl_sync(tmask, slot, tshift);
-    if (slot == kNoSlot) {
-      if (sub == 0) t.entries[cand].meta = cand_seen;  // give the entry back
-      return APS_ENOSPC;
-    }
-    if (sub == 0) {
-      Entry* e = t.entries + cand;
-      e->k0 = key.file_hi; e->k1 = key.file_lo; e->k2 = key.page_index;
-      __threadfence();
-      e->meta = meta_make(slot, len);
-      atomicAdd(&t.counters[kCtrPages], 1ull);
-      atomicAdd(&t.counters[kCtrBytes], (unsigned long long)len);
-      if (cand_seen == kMetaTomb) atomicAdd(&t.counters[kCtrTombs], ~0ull);
-    }
-    *slot_out = slot;
-    return APS_OK;
+    if (ok) return EntryClaim{kClaimNew, cand, cand_seen};
+    // another key took the entry first: rescan
   }
-  return APS_ENOSPC;
+  return EntryClaim{kClaimFull, 0, 0};
 }
 
-// Tile-cooperative erase.  An entry in a bucket that still has an EMPTY entry goes straight back to
-// EMPTY (no probe chain runs through such a bucket); otherwise it becomes a tombstone.
-__device__ __forceinline__ int tile_erase(const Table& t, const aps_key& key, uint32_t sub, uint32_t tshift) {
-  Probe pr = tile_lookup(t, key, sub, tshift);
-  if (!pr.meta) return APS_ENOTFOUND;
-  if (sub == 0) {
-    bool to_empty = pr.empties != 0;
-    t.entries[pr.entry_idx].meta = to_empty ? kMetaEmpty : kMetaTomb;
-    int idx = atomicAdd(t.free_top, 1);
-    t.free_slots[idx] = meta_slot(pr.meta);
-    atomicAdd(&t.counters[kCtrPages], ~0ull);
-    atomicAdd(&t.counters[kCtrBytes], 0ull - (unsigned long long)meta_len(pr.meta));
-    if (!to_empty) atomicAdd(&t.counters[kCtrTombs], 1ull);
+// Block-wide pop of `a.need` slots from the free stack with one atomic; fewer may be granted.
+// Call with the whole block, after every tile that needs a slot has taken its rank from a.need.
+__device__ __forceinline__ void block_take_slots(BlockAcct& a, const Table& t) {
+  __syncthreads();
+  if (threadIdx.x == 0 && a.need) {
+    const int old = atomicSub(t.free_top, a.need);
+    const int got = max(0, min(a.need, old));
+    if (got < a.need) atomicAdd(t.free_top, a.need - got);
+    a.base = old;
+    a.avail = got;
   }
-  return APS_OK;
+  __syncthreads();
+}
+// Block-wide push: reserves a.need positions; tile `rank` then writes its slot at a.base + rank.
+__device__ __forceinline__ void block_return_slots(BlockAcct& a, const Table& t) {
+  __syncthreads();
+  if (threadIdx.x == 0 && a.need) a.base = atomicAdd(t.free_top, a.need);
+  __syncthreads();
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -844,55 +844,114 @@ __global__ void __launch_bounds__(kTmaThreads, 1) tma_copy_kernel(CopyArgs a) {
 // ------------------------------------------------------------------------------------------------
 // K1 kernels: eight lanes per request.
 // ------------------------------------------------------------------------------------------------
-__global__ void put_resolve_kernel(Table t, const aps_put_req* reqs, uint32_t n, Job* jobs, aps_result* res, int crc_on) {
+constexpr int kK1Threads = 256;  // 32 tiles per block
+
+__global__ void __launch_bounds__(kK1Threads) put_resolve_kernel(Table t, const aps_put_req* reqs, uint32_t n, Job* jobs,
+                                                                 aps_result* res, int crc_on) {
+  __shared__ BlockAcct acct;
+  acct_init(acct);
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
-  if (i >= n) return;
-  const aps_put_req rq = reqs[i];
-  Job jb{nullptr, nullptr, 0, 0, 0, 0};
-  aps_result rs{0, 0};
-  if (rq.len > t.page_size) {
-    rs.len = -APS_EINVAL;
-  } else {
-    uint32_t slot = kNoSlot;
-    int st = tile_insert(t, rq.key, rq.len, sub, tshift, &slot);
-    if (st != APS_OK) {
-      rs.len = -st;
-    } else {
-      jb.src = (const uint8_t*)rq.src;
-      jb.dst = t.slab + (uint64_t)slot * t.page_size;
-      jb.n = rq.len;
-      jb.slot = slot;
-      jb.flags = crc_on ? kJobRecord : 0u;
-      rs.len = (int32_t)rq.len;
-      if (sub == 0) {
-        if (rq.len == 0) t.slot_crc[slot] = 0;  // CRC32C of the empty string
-        atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)rq.len);
-      }
+  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u, tmask = 0xFFu << tshift;
+  const bool live = i < n;  // tile-uniform
+  aps_put_req rq{};
+  EntryClaim c{kClaimFull, 0, 0};
+  int err = 0, rank = -1;
+  if (live) {
+    rq = reqs[i];
+    if (rq.len > t.page_size) err = APS_EINVAL;
+    else {
+      c = tile_claim(t, rq.key, sub, tshift);
+      if (c.kind == kClaimFull) err = APS_ENOSPC;
+      if (c.kind == kClaimNew && sub == 0) rank = atomicAdd(&acct.need, 1);
     }
   }
-  if (sub) return;
-  jobs[i] = jb;
-  res[i] = rs;
+  block_take_slots(acct, t);
+  if (live) {
+    Job jb{nullptr, nullptr, 0, 0, 0, 0};
+    uint32_t slot = kNoSlot;
+    if (!err && c.kind == kClaimReplace) {
+      slot = meta_slot(c.was);
+      if (sub == 0) {
+        t.entries[c.entry_idx].meta = meta_make(slot, rq.len);
+        acct_add(acct, kCtrBytes, (unsigned long long)rq.len - (unsigned long long)meta_len(c.was));
+      }
+    } else if (!err) {
+      if (sub == 0) {
+        Entry* e = t.entries + c.entry_idx;
+        if (rank < acct.avail) {
+          slot = t.free_slots[acct.base - 1 - rank];
+          e->k0 = rq.key.file_hi; e->k1 = rq.key.file_lo; e->k2 = rq.key.page_index;
+          __threadfence();
+          e->meta = meta_make(slot, rq.len);
+          acct_add(acct, kCtrPages, 1ull);
+          acct_add(acct, kCtrBytes, (unsigned long long)rq.len);
+          if (c.was == kMetaTomb) acct_add(acct, kCtrTombs, ~0ull);
+        } else {
+          e->meta = c.was;  // no slab slot left: give the entry back
+        }
+      }
+      slot = __shfl_sync(tmask, slot, tshift);
+      if (slot == kNoSlot) err = APS_ENOSPC;
+    }
+    if (sub == 0) {
+      aps_result rs{err ? -err : (int32_t)rq.len, 0};
+      if (!err) {
+        jb = Job{(const uint8_t*)rq.src, t.slab + (uint64_t)slot * t.page_size, rq.len, slot, crc_on ? kJobRecord : 0u, 0};
+        if (rq.len == 0) t.slot_crc[slot] = 0;  // CRC32C of the empty string
+        else acct_add(acct, kCtrBytesCopied, (unsigned long long)rq.len);
+      }
+      jobs[i] = jb;
+      res[i] = rs;
+    }
+  }
+  acct_flush(acct, t);
 }
 
-__global__ void delete_kernel(Table t, const aps_key* keys, uint32_t n, aps_result* res) {
+// An erased entry in a bucket that still has an EMPTY entry goes straight back to EMPTY (no probe chain
+// runs through such a bucket); otherwise it becomes a tombstone.
+__global__ void __launch_bounds__(kK1Threads) delete_kernel(Table t, const aps_key* keys, uint32_t n, aps_result* res) {
+  __shared__ BlockAcct acct;
+  acct_init(acct);
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
-  if (i >= n) return;
-  int st = tile_erase(t, keys[i], sub, tshift);
-  if (sub == 0) res[i] = aps_result{-st, 0};
+  const bool live = i < n;
+  Probe pr{0, 0, 0, 0};
+  int rank = -1;
+  if (live) {
+    const aps_key key = keys[i];  // a copy: a reference into global memory is re-read on every probe
+    pr = tile_lookup(t, key, sub, tshift);
+    if (pr.meta && sub == 0) {
+      const bool to_empty = pr.empties != 0;
+      t.entries[pr.entry_idx].meta = to_empty ? kMetaEmpty : kMetaTomb;
+      rank = atomicAdd(&acct.need, 1);
+      acct_add(acct, kCtrPages, ~0ull);
+      acct_add(acct, kCtrBytes, 0ull - (unsigned long long)meta_len(pr.meta));
+      if (!to_empty) acct_add(acct, kCtrTombs, 1ull);
+    }
+  }
+  block_return_slots(acct, t);
+  if (live && sub == 0) {
+    if (rank >= 0) t.free_slots[acct.base + rank] = meta_slot(pr.meta);
+    res[i] = aps_result{pr.meta ? 0 : -APS_ENOTFOUND, 0};
+  }
+  acct_flush(acct, t);
 }
 
-__global__ void lookup_kernel(Table t, const aps_key* keys, uint32_t n, int32_t* len_out) {
+__global__ void __launch_bounds__(kK1Threads) lookup_kernel(Table t, const aps_key* keys, uint32_t n, int32_t* len_out) {
+  __shared__ BlockAcct acct;
+  acct_init(acct);
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
-  if (i >= n) return;
-  Probe pr = tile_lookup(t, keys[i], sub, tshift);
-  if (sub) return;
-  atomicAdd(&t.counters[kCtrLookups], 1ull);
-  atomicAdd(&t.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
-  len_out[i] = pr.meta ? (int32_t)meta_len(pr.meta) : -1;
+  if (i < n) {
+    const aps_key key = keys[i];
+    Probe pr = tile_lookup(t, key, sub, tshift);
+    if (sub == 0) {
+      acct_add(acct, kCtrLookups, 1ull);
+      acct_add(acct, kCtrProbes, (unsigned long long)pr.nbuckets);
+      len_out[i] = pr.meta ? (int32_t)meta_len(pr.meta) : -1;
+    }
+  }
+  acct_flush(acct, t);
 }
 
 // jobs for the stand-alone checksum pass
