@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libaps.so")
 
 (APS_OK, APS_ENOTFOUND, APS_EINVAL, APS_ENOSPC, APS_ECUDA, APS_ECORRUPT, APS_ECLOSED, APS_ENOMEM, APS_EFAULT,
- APS_ELIMIT) = range(10)
+ APS_ELIMIT, APS_EIO) = range(11)
 APS_NOALLOC_MAX_RANGES, APS_NOALLOC_MAX_LEN = 1024, 4 << 20
 APS_FLAG_CRC, APS_FLAG_TMA_COPY = 1, 2
 APS_FAULT_PUT, APS_FAULT_DELETE = 1, 2
@@ -85,6 +85,8 @@ SIGNATURES = {
     "aps_host_alloc_pinned": (C.c_int, [_u64, C.POINTER(_vp)]),
     "aps_host_free_pinned": (C.c_int, [_vp]),
     "aps_compact": (C.c_int, [_vp]),
+    "aps_snapshot_save": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64)]),
+    "aps_snapshot_load": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64), C.POINTER(_u64)]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),
     "aps_profile_begin": (C.c_int, [_vp, _u32]),

@@ -11,6 +11,7 @@
 #include <unordered_set>
 #include <vector>
 
+#include "aps_internal.h"
 #include "aps_kernels.cuh"
 
 using namespace aps;
@@ -471,6 +472,15 @@ __global__ void corrupt_kernel(Table t, aps_key key, uint32_t off, int* found) {
 
 }  // namespace
 
+namespace aps {
+int store_config(aps_store* s, aps_config* out) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  *out = s->cfg;
+  return APS_OK;
+}
+}  // namespace aps
+
 extern "C" {
 
 const char* aps_version(void) { return "libaps 0.1 (sm_100a)"; }
@@ -498,6 +508,7 @@ const char* aps_strerror(int code) {
     case APS_ENOMEM: return "out of memory";
     case APS_EFAULT: return "injected fault";
     case APS_ELIMIT: return "request exceeds the fixed scratch of the no-allocation entry point";
+    case APS_EIO: return "snapshot file could not be read or written";
     default: return "unknown error";
   }
 }

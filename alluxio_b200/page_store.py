@@ -7,6 +7,7 @@ PageStoreTest.  It is a thin veneer: every call goes through include/aps.h via c
 (CACHE/ = /root/reference/core/client/fs/src/main/java/alluxio/client/file/cache/.)
 """
 import ctypes as C
+import os
 import re
 import threading
 
@@ -205,6 +206,20 @@ class GpuPageStore:
         st = aps_stats_t()
         capi.check(capi.lib().aps_stats(self.handle, C.byref(st)), "aps_stats")
         return {n: getattr(st, n) for n, _ in aps_stats_t._fields_}
+
+    def save_snapshot(self, path):
+        """Warm restart, SURVEY.md 8f-4: writes every resident page to `path`; returns the number written."""
+        n = C.c_uint64()
+        self._raise(capi.lib().aps_snapshot_save(self.handle, os.fsencode(path), C.byref(n)), "snapshot save %s" % path)
+        return n.value
+
+    def load_snapshot(self, path):
+        """Puts the pages of a snapshot into this store; returns (loaded, rejected).  getPages() lists them
+        afterwards, which is what LocalCacheManager.restore walks (LocalCacheManager.java:466-509)."""
+        n, r = C.c_uint64(), C.c_uint64()
+        self._raise(capi.lib().aps_snapshot_load(self.handle, os.fsencode(path), C.byref(n), C.byref(r)),
+                    "snapshot load %s" % path)
+        return n.value, r.value
 
     def debug_corrupt(self, page_id, byte_offset):
         k = self.key(page_id)

@@ -218,25 +218,29 @@ def run_ours(args):
     # ---- populate the pages this GPU owns: generate on the device, put 256 at a time
     stage = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
     d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
+    def populate(store):
+        first = None
+        for b0 in range(0, len(owned), BATCH):
+            ids = owned[b0:b0 + BATCH]
+            nb = len(ids)
+            files, idx = ids // np.uint64(1024), ids % np.uint64(1024)
+            d_files = torch.from_numpy(files.view(np.int64)).to(dev)
+            d_idx = torch.from_numpy(idx.view(np.int64)).to(dev)
+            capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, nb, d_files.data_ptr(),
+                                            d_idx.data_ptr(), DATA_SEED, sp), "fill")
+            reqs = np.zeros(nb, PUT_REQ)
+            reqs["file_lo"], reqs["page_index"], reqs["len"] = files, idx, PAGE
+            reqs["src"] = stage.data_ptr() + np.arange(nb, dtype=np.uint64) * PAGE
+            d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
+            capi.check(L.aps_put_batch_dev(store, nb, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
+            if b0 == 0:
+                torch.cuda.synchronize(dev)
+                first = d_res.cpu().numpy().view(RESULT).copy()
+        torch.cuda.synchronize(dev)
+        return first
+
     t_pop = time.time()
-    first_put_res = None
-    for b0 in range(0, len(owned), BATCH):
-        ids = owned[b0:b0 + BATCH]
-        nb = len(ids)
-        files, idx = ids // np.uint64(1024), ids % np.uint64(1024)
-        d_files = torch.from_numpy(files.view(np.int64)).to(dev)
-        d_idx = torch.from_numpy(idx.view(np.int64)).to(dev)
-        capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, nb, d_files.data_ptr(),
-                                        d_idx.data_ptr(), DATA_SEED, sp), "fill")
-        reqs = np.zeros(nb, PUT_REQ)
-        reqs["file_lo"], reqs["page_index"], reqs["len"] = files, idx, PAGE
-        reqs["src"] = stage.data_ptr() + np.arange(nb, dtype=np.uint64) * PAGE
-        d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
-        capi.check(L.aps_put_batch_dev(h, nb, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
-        if b0 == 0:
-            torch.cuda.synchronize(dev)
-            first_put_res = d_res.cpu().numpy().view(RESULT).copy()
-    torch.cuda.synchronize(dev)
+    first_put_res = populate(h)
     t_pop = time.time() - t_pop
 
     # ---- parity spot check against the oracle (the checker; never the thing measured)
@@ -492,6 +496,45 @@ def run_ours(args):
         remote_frac = float(t.item()) / world
         dist.barrier()  # peers may still be reading this GPU's slab
     capi.check(L.aps_close(h), "close")
+
+    # ---- the same three paths with the checksum off (BASELINE configs[1]: "each with CRC off/on"): a second
+    # store opened without APS_FLAG_CRC over the same resident set, after the first one released its HBM
+    if world == 1 and with_crc and not quick:
+        cfg.flags = 0
+        h2 = C.c_void_p()
+        capi.check(L.aps_open(C.byref(cfg), C.byref(h2)), "aps_open (no CRC)")
+        populate(h2)
+        n2 = max(1, min(K, 200))
+        for k in range(5):
+            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+        torch.cuda.synchronize(dev)
+        ev0.record(stream)
+        for k in range(n2):
+            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs.data_ptr() + ((5 + k) % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+        ev1.record(stream)
+        torch.cuda.synchronize(dev)
+        aux["get_nocrc_GBps"] = round(n2 * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
+        p = int(picks[(5 + n2 - 1) % pool, 9])
+        assert np.array_equal(dst[9 * PAGE:10 * PAGE].cpu().numpy(), orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE))
+        for _ in range(3):
+            capi.check(L.aps_put_batch_dev(h2, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
+        torch.cuda.synchronize(dev)
+        ev0.record(stream)
+        for _ in range(aux_steps):
+            capi.check(L.aps_put_batch_dev(h2, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
+        ev1.record(stream)
+        torch.cuda.synchronize(dev)
+        aux["put_nocrc_GBps"] = round(aux_steps * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
+        n3 = max(1, min(K, 30))
+        for k in range(2):
+            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+        for k in range(n3):
+            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[(2 + k) % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+        torch.cuda.synchronize(dev)
+        aux["e2e_get_nocrc_GBps"] = round(n3 * BATCH * PAGE / (time.perf_counter() - t0) / 1e9, 2)
+        capi.check(L.aps_close(h2), "close")
 
     if rank != 0:
         if world > 1:

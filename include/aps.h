@@ -49,6 +49,7 @@ extern "C" {
 #define APS_ENOMEM 7     /* host or device allocation failed */
 #define APS_EFAULT 8     /* injected fault (APS_FAULT_* below) */
 #define APS_ELIMIT 9     /* request larger than the fixed scratch of aps_crc32c_noalloc */
+#define APS_EIO 10       /* a snapshot file could not be read or written */
 
 /* PageId on the device: CACHE/PageId.java:23-74 is (String fileId, long pageIndex).  The file id
  * is carried as 128 bits; the host side maps strings to 128 bits without collisions (decimal,
@@ -217,6 +218,19 @@ APS_API int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_
 #define APS_NOALLOC_MAX_LEN (4u << 20)
 APS_API int aps_crc32c_noalloc(int32_t device, uint32_t n, const void* const* d_data, const uint32_t* d_len,
                                uint32_t max_len, uint32_t* d_crc, aps_stream stream);
+
+/* ---- warm restart --------------------------------------------------------------
+ * LocalPageStore's pages are files, so they survive a restart and LocalCacheManager.restore finds them
+ * through getPages() (CACHE/LocalCacheManager.java:466-509; CACHE/store/LocalPageStore.java:193-199).
+ * HBM does not survive; these two calls give a GPU store the same behaviour through a file on local NVMe.
+ * aps_snapshot_save writes every resident page (id, length, CRC32C, bytes) to `path` (written as path.tmp,
+ * then renamed); pages deleted while it runs are simply left out.  aps_snapshot_load puts the pages of a
+ * snapshot into a freshly opened store of the same page size; a page that no longer fits (APS_ENOSPC) or
+ * whose bytes no longer match the recorded CRC32C is counted in *rejected and not kept.  Afterwards
+ * aps_iterate lists the loaded pages and the manager's restore adopts them.  Errors: APS_EIO (file),
+ * APS_ECORRUPT (not a snapshot, truncated), APS_EINVAL (page size differs). */
+APS_API int aps_snapshot_save(aps_store* s, const char* path, uint64_t* pages_out);
+APS_API int aps_snapshot_load(aps_store* s, const char* path, uint64_t* pages_out, uint64_t* rejected_out);
 
 /* ---- synthetic data, stats, diagnostics ---------------------------------------------------------*/
 
