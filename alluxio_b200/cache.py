@@ -15,6 +15,10 @@ EXTERNAL_READ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int3
 
 SIGNATURES = {
     "apc_manager_create": (C.c_int, [C.POINTER(capi.aps_config), _cp, _dbl, C.POINTER(_vp)]),
+    "apc_manager_create_sharded": (C.c_int, [C.POINTER(capi.aps_config), C.c_uint32, C.POINTER(_i32), _cp, _dbl, C.POINTER(_vp)]),
+    "apc_shard_count": (C.c_uint32, [_vp]),
+    "apc_shard_store": (_vp, [_vp, C.c_uint32]),
+    "apc_shard_of": (C.c_uint32, [_vp, _cp, _i64]),
     "apc_manager_create_over": (C.c_int, [_vp, C.c_uint32, _cp, _dbl, C.POINTER(_vp)]),
     "apc_manager_close": (C.c_int, [_vp]),
     "apc_get_noexcept": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
@@ -163,13 +167,31 @@ class LocalCacheManager:
     NOT_IN_USE, READ_ONLY, READ_WRITE = 0, 1, 2
 
     def __init__(self, page_size, cache_size, evictor="LRU", lfu_logbase=2.0, device=0, slab_slots=0, crc=True,
-                 max_batch=0):
+                 max_batch=0, shard_devices=None):
+        """shard_devices: CUDA ordinals, one per shard, for ONE cache spread over several GPUs: the
+        manager, its meta store and its byte budget stay single and global, pages live on GPU hash(PageId) mod n."""
         cfg = capi.aps_config(device=device, page_size=page_size, cache_bytes=cache_size, slab_slots=slab_slots,
                               table_capacity=0, max_batch=max_batch, flags=capi.APS_FLAG_CRC if crc else 0)
         h = C.c_void_p()
-        capi.check(lib().apc_manager_create(C.byref(cfg), evictor.encode(), lfu_logbase, C.byref(h)), "apc_manager_create")
+        if shard_devices:
+            devs = (C.c_int32 * len(shard_devices))(*shard_devices)
+            capi.check(lib().apc_manager_create_sharded(C.byref(cfg), len(shard_devices), devs, evictor.encode(), lfu_logbase,
+                                                        C.byref(h)), "apc_manager_create_sharded")
+        else:
+            capi.check(lib().apc_manager_create(C.byref(cfg), evictor.encode(), lfu_logbase, C.byref(h)), "apc_manager_create")
         self._h = h
         self.page_size = page_size
+
+    def shard_count(self):
+        return lib().apc_shard_count(self._h)
+
+    def shard_of(self, p):
+        return lib().apc_shard_of(self._h, _f(p), p.page_index)
+
+    def shard_stats(self, i):
+        st = capi.aps_stats_t()
+        capi.check(capi.lib().aps_stats(C.c_void_p(lib().apc_shard_store(self._h, i)), C.byref(st)), "aps_stats")
+        return {n: getattr(st, n) for n, _ in capi.aps_stats_t._fields_}
 
     @classmethod
     def over_store(cls, store, page_size, evictor="LRU", lfu_logbase=2.0):

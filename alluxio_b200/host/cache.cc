@@ -336,6 +336,7 @@ int GpuPageStore::Open(const aps_config& cfg, std::unique_ptr<GpuPageStore>* out
   std::unique_ptr<GpuPageStore> g(new GpuPageStore());
   g->mStore = s;
   g->mCacheBytes = cfg.cache_bytes;
+  g->mDevice = cfg.device;
   *out = std::move(g);
   return APS_OK;
 }
@@ -377,6 +378,101 @@ int GpuPageStore::GetPages(std::vector<std::pair<Key, int64_t>>* out) {
         return 0;
       },
       out);
+}
+
+// ================================================================================ ShardedGpuPageStore
+
+int ShardedGpuPageStore::Open(const aps_config& cfg, uint32_t nShards, const int32_t* devices,
+                              std::unique_ptr<ShardedGpuPageStore>* out) {
+  if (nShards == 0 || nShards > 64 || !devices || cfg.page_size == 0) return APS_EINVAL;
+  std::unique_ptr<ShardedGpuPageStore> g(new ShardedGpuPageStore());
+  g->mCacheBytes = cfg.cache_bytes;
+  const uint64_t pages = (cfg.cache_bytes + cfg.page_size - 1) / cfg.page_size;
+  const uint64_t share = (pages + nShards - 1) / nShards;
+  for (uint32_t i = 0; i < nShards; ++i) {
+    aps_config c = cfg;
+    c.device = devices[i];
+    c.slab_slots = cfg.slab_slots ? cfg.slab_slots : share + share / 4 + 64;
+    c.cache_bytes = c.slab_slots * (uint64_t)cfg.page_size;
+    std::unique_ptr<GpuPageStore> s;
+    const int rc = GpuPageStore::Open(c, &s);
+    if (rc != APS_OK) return rc;  // shards opened so far close with g
+    g->mShards.push_back(std::move(s));
+  }
+  std::vector<aps_store*> handles;
+  for (auto& s : g->mShards) handles.push_back(s->handle());
+  for (uint32_t i = 0; i < nShards; ++i) {  // every shard can serve a sharded get; shard 0 is the one used
+    const int rc = aps_shard_attach_local(handles[i], nShards, i, handles.data());
+    if (rc != APS_OK) return rc;
+  }
+  *out = std::move(g);
+  return APS_OK;
+}
+ShardedGpuPageStore::~ShardedGpuPageStore() {}
+uint32_t ShardedGpuPageStore::OwnerOf(const Key& k) const {
+  const aps_key a = ToAps(k);
+  return aps_shard_of(&a, (uint32_t)mShards.size());
+}
+int ShardedGpuPageStore::Put(const Key& k, const void* page, int32_t len) { return mShards[OwnerOf(k)]->Put(k, page, len); }
+int ShardedGpuPageStore::Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) {
+  return mShards[OwnerOf(k)]->Get(k, pageOffset, bytesToRead, dst, room, bytesRead);
+}
+int ShardedGpuPageStore::Delete(const Key& k) { return mShards[OwnerOf(k)]->Delete(k); }
+int ShardedGpuPageStore::GetPages(std::vector<std::pair<Key, int64_t>>* out) {
+  out->clear();
+  std::vector<std::pair<Key, int64_t>> part;
+  for (auto& s : mShards) {
+    const int rc = s->GetPages(&part);
+    if (rc != APS_OK) return rc;
+    out->insert(out->end(), part.begin(), part.end());
+  }
+  return APS_OK;
+}
+int ShardedGpuPageStore::GetBatch(uint32_t n, const aps_get_req* reqs, aps_result* res) {
+  return aps_get_batch_sharded(mShards[0]->handle(), n, reqs, res, nullptr);
+}
+namespace {
+// Splits a batch by owner, runs `call(shard, count, sub-requests, sub-results)` per shard, scatters the results back.
+template <typename Req, typename KeyOfReq, typename Call>
+int ByOwner(uint32_t nShards, uint32_t n, const Req* reqs, aps_result* res, KeyOfReq keyOf, Call call) {
+  std::vector<std::vector<Req>> sub(nShards);
+  std::vector<std::vector<uint32_t>> where(nShards);
+  for (uint32_t i = 0; i < n; ++i) {
+    const uint32_t o = aps_shard_of(&keyOf(reqs[i]), nShards);
+    sub[o].push_back(reqs[i]);
+    where[o].push_back(i);
+  }
+  std::vector<aps_result> part;
+  for (uint32_t o = 0; o < nShards; ++o) {
+    if (sub[o].empty()) continue;
+    part.resize(sub[o].size());
+    const int rc = call(o, (uint32_t)sub[o].size(), sub[o].data(), part.data());
+    if (rc != APS_OK) return rc;
+    for (size_t j = 0; j < part.size(); ++j) res[where[o][j]] = part[j];
+  }
+  return APS_OK;
+}
+}  // namespace
+int ShardedGpuPageStore::PutBatch(uint32_t n, const aps_put_req* reqs, aps_result* res) {
+  return ByOwner(
+      shards(), n, reqs, res, [](const aps_put_req& r) -> const aps_key& { return r.key; },
+      [this](uint32_t o, uint32_t m, const aps_put_req* r, aps_result* out) { return mShards[o]->PutBatch(m, r, out); });
+}
+int ShardedGpuPageStore::DeleteBatch(uint32_t n, const aps_key* keys, aps_result* res) {
+  return ByOwner(
+      shards(), n, keys, res, [](const aps_key& k) -> const aps_key& { return k; },
+      [this](uint32_t o, uint32_t m, const aps_key* k, aps_result* out) { return mShards[o]->DeleteBatch(m, k, out); });
+}
+int ShardedGpuPageStore::FillPages(void* d, uint64_t stride, uint32_t len, uint32_t n, const uint64_t* f, const uint64_t* i,
+                                   uint64_t seed) {
+  return mShards[0]->FillPages(d, stride, len, n, f, i, seed);
+}
+int ShardedGpuPageStore::SetFaults(uint32_t mask) {
+  for (auto& s : mShards) {
+    const int rc = s->SetFaults(mask);
+    if (rc != APS_OK) return rc;
+  }
+  return APS_OK;
 }
 
 // ================================================================================ LocalCacheManager
@@ -496,8 +592,7 @@ int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int
 void LocalCacheManager::GetMany(const std::string& fileId, int64_t firstPage, int32_t n, const int32_t* offset,
                                 const int32_t* len, void* const* dst, int32_t* got) {
   for (int32_t i = 0; i < n; ++i) got[i] = 0;
-  auto* gpu = dynamic_cast<GpuPageStore*>(mPageStore.get());
-  if (!gpu || mState.load() == NOT_IN_USE || n <= 0) return;
+  if (mState.load() == NOT_IN_USE || n <= 0) return;
   // page read locks of all pages involved, in lock-id order (the reference's deadlock rule, :197-203)
   std::vector<int32_t> lockIds((size_t)n);
   for (int32_t i = 0; i < n; ++i) lockIds[(size_t)i] = GetPageLockId(fileId, firstPage + i);
@@ -522,7 +617,7 @@ void LocalCacheManager::GetMany(const std::string& fileId, int64_t firstPage, in
   }
   if (reqs.empty()) return;
   std::vector<aps_result> res(reqs.size());
-  const int rc = aps_get_batch(gpu->handle(), (uint32_t)reqs.size(), reqs.data(), res.data(), nullptr);
+  const int rc = mPageStore->GetBatch((uint32_t)reqs.size(), reqs.data(), res.data());
   for (size_t r = 0; r < reqs.size(); ++r) {
     const int32_t i = which[r];
     if (rc == APS_OK && res[r].len == len[i]) {
@@ -597,8 +692,8 @@ using namespace alluxio_b200;
 
 struct apc_manager {
   std::unique_ptr<LocalCacheManager> mgr;
-  GpuPageStore* gpu = nullptr;  // owned by mgr
-  int32_t device = 0;
+  GpuPageStore* gpu = nullptr;             // single store, owned by mgr
+  ShardedGpuPageStore* sharded = nullptr;  // or several, owned by mgr
 };
 struct apc_evictor {
   std::unique_ptr<CacheEvictor> ev;
@@ -633,10 +728,33 @@ int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_lo
   if (rc != APS_OK) return rc;
   apc_manager* m = new apc_manager();
   m->gpu = store.get();
-  m->device = cfg->device;
   m->mgr.reset(new LocalCacheManager(cfg->page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(store)));
   *out = m;
   return APS_OK;
+}
+int apc_manager_create_sharded(const aps_config* cfg, uint32_t n_shards, const int32_t* devices, const char* evictor,
+                               double lfu_logbase, apc_manager** out) {
+  if (!cfg || !evictor || !out) return APS_EINVAL;
+  *out = nullptr;
+  auto ev = CacheEvictor::Create(evictor, lfu_logbase);
+  if (!ev) return APS_EINVAL;
+  std::unique_ptr<ShardedGpuPageStore> store;
+  const int rc = ShardedGpuPageStore::Open(*cfg, n_shards, devices, &store);
+  if (rc != APS_OK) return rc;
+  apc_manager* m = new apc_manager();
+  m->sharded = store.get();
+  m->mgr.reset(new LocalCacheManager(cfg->page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(store)));
+  *out = m;
+  return APS_OK;
+}
+uint32_t apc_shard_count(apc_manager* m) { return m->sharded ? m->sharded->shards() : 1; }
+aps_store* apc_shard_store(apc_manager* m, uint32_t i) {
+  if (m->sharded) return i < m->sharded->shards() ? m->sharded->shard(i)->handle() : nullptr;
+  return i == 0 ? m->gpu->handle() : nullptr;
+}
+uint32_t apc_shard_of(apc_manager* m, const char* f, int64_t i) {
+  if (!m->sharded) return 0;
+  return m->sharded->OwnerOf(KeyOf(*m->mgr->codec(), f, i));
 }
 int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase, apc_manager** out) {
   if (!store || !evictor || !out) return APS_EINVAL;
@@ -746,8 +864,8 @@ int apc_state(apc_manager* m) { return m->mgr->state(); }
 int64_t apc_bytes(apc_manager* m) { return m->mgr->meta()->Bytes(); }
 int64_t apc_pages(apc_manager* m) { return m->mgr->meta()->Pages(); }
 int32_t apc_page_lock_id(apc_manager* m, const char* f, int64_t i) { return m->mgr->GetPageLockId(f, i); }
-int apc_set_store_faults(apc_manager* m, uint32_t mask) { return aps_set_faults(m->gpu->handle(), mask); }
-aps_store* apc_store(apc_manager* m) { return m->gpu->handle(); }
+int apc_set_store_faults(apc_manager* m, uint32_t mask) { return m->mgr->store()->SetFaults(mask); }
+aps_store* apc_store(apc_manager* m) { return apc_shard_store(m, 0); }
 void apc_file_key(apc_manager* m, const char* f, uint64_t* hi, uint64_t* lo) { m->mgr->codec()->Encode(f, hi, lo); }
 int32_t apc_java_string_hashcode(const char* utf8) { return JavaStringHashCode(utf8); }
 
@@ -902,15 +1020,13 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
                                       int64_t* final_bytes, int64_t* store_ops, double* seconds_host, double* seconds_store) {
   LocalCacheManager* mgr = m->mgr.get();
   MetaStore* meta = mgr->meta();
-  aps_store* store = m->gpu->handle();
-  const int64_t cacheSize = mgr->store()->GetCacheSize();
+  PageStore* store = mgr->store();
+  const int64_t cacheSize = store->GetCacheSize();
   const uint32_t ps = (uint32_t)mgr->pageSize();
   if (window == 0) window = 1024;
-  // device staging: put payloads and a sink for gets (aps_config.device is not visible here: the store knows)
-  aps_stats_t st0{};
-  if (aps_stats(store, &st0) != APS_OK) return -1;
+  // device staging: put payloads and a sink for gets, on the store's (first) GPU
   void *d_put = nullptr, *d_sink = nullptr;
-  const int32_t dev = m->device;
+  const int32_t dev = store->StagingDevice();
   if (aps_device_alloc(dev, (uint64_t)window * ps, &d_put) != APS_OK) return -1;
   if (aps_device_alloc(dev, (uint64_t)window * ps, &d_sink) != APS_OK) {
     aps_device_free(dev, d_put);
@@ -931,22 +1047,21 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
     ops[3]++;
     if (!dels.empty()) {
       res.resize(dels.size());
-      if (aps_delete_batch(store, (uint32_t)dels.size(), dels.data(), res.data(), nullptr) != APS_OK) failed = true;
+      if (store->DeleteBatch((uint32_t)dels.size(), dels.data(), res.data()) != APS_OK) failed = true;
       for (auto& r : res) if (r.len != 0) failed = true;
       ops[0] += (int64_t)dels.size();
     }
     if (!puts.empty()) {
       // payload: all pages of this flush generated at full page stride, then put with their real lengths
-      if (aps_fill_pages(store, d_put, ps, ps, (uint32_t)puts.size(), put_files.data(), put_pages.data(), seed, nullptr) != APS_OK)
-        failed = true;
+      if (store->FillPages(d_put, ps, ps, (uint32_t)puts.size(), put_files.data(), put_pages.data(), seed) != APS_OK) failed = true;
       res.resize(puts.size());
-      if (aps_put_batch(store, (uint32_t)puts.size(), puts.data(), res.data(), nullptr) != APS_OK) failed = true;
+      if (store->PutBatch((uint32_t)puts.size(), puts.data(), res.data()) != APS_OK) failed = true;
       for (size_t i = 0; i < puts.size(); ++i) if (res[i].len != (int32_t)puts[i].len) failed = true;
       ops[1] += (int64_t)puts.size();
     }
     if (!gets.empty()) {
       res.resize(gets.size());
-      if (aps_get_batch(store, (uint32_t)gets.size(), gets.data(), res.data(), nullptr) != APS_OK) failed = true;
+      if (store->GetBatch((uint32_t)gets.size(), gets.data(), res.data()) != APS_OK) failed = true;
       for (size_t i = 0; i < gets.size(); ++i) if (res[i].len != (int32_t)gets[i].nbytes) ops[4]++;
       ops[2] += (int64_t)gets.size();
     }

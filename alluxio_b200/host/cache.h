@@ -116,6 +116,15 @@ class PageStore {
   virtual int Delete(const Key& k) = 0;
   virtual int GetPages(std::vector<std::pair<Key, int64_t>>* out) = 0;
   virtual int64_t GetCacheSize() const = 0;
+  // Additive batched forms, aps_*_batch semantics: host request arrays, device or pinned
+  // payload pointers, one result per request.  A store without a batched path answers APS_EINVAL.
+  virtual int GetBatch(uint32_t, const aps_get_req*, aps_result*) { return APS_EINVAL; }
+  virtual int PutBatch(uint32_t, const aps_put_req*, aps_result*) { return APS_EINVAL; }
+  virtual int DeleteBatch(uint32_t, const aps_key*, aps_result*) { return APS_EINVAL; }
+  // Synthetic payload generated on the store's device (replays): aps_fill_pages semantics.
+  virtual int FillPages(void*, uint64_t, uint32_t, uint32_t, const uint64_t*, const uint64_t*, uint64_t) { return APS_EINVAL; }
+  virtual int SetFaults(uint32_t) { return APS_EINVAL; }
+  virtual int32_t StagingDevice() const { return 0; }
 };
 
 // PageStoreType.GPU: the HBM slab + table behind include/aps.h.
@@ -130,11 +139,50 @@ class GpuPageStore : public PageStore {
   int Delete(const Key& k) override;
   int GetPages(std::vector<std::pair<Key, int64_t>>* out) override;
   int64_t GetCacheSize() const override { return (int64_t)mCacheBytes; }
+  int GetBatch(uint32_t n, const aps_get_req* reqs, aps_result* res) override { return aps_get_batch(mStore, n, reqs, res, nullptr); }
+  int PutBatch(uint32_t n, const aps_put_req* reqs, aps_result* res) override { return aps_put_batch(mStore, n, reqs, res, nullptr); }
+  int DeleteBatch(uint32_t n, const aps_key* keys, aps_result* res) override { return aps_delete_batch(mStore, n, keys, res, nullptr); }
+  int FillPages(void* d, uint64_t stride, uint32_t len, uint32_t n, const uint64_t* f, const uint64_t* i, uint64_t seed) override {
+    return aps_fill_pages(mStore, d, stride, len, n, f, i, seed, nullptr);
+  }
+  int SetFaults(uint32_t mask) override { return aps_set_faults(mStore, mask); }
+  int32_t StagingDevice() const override { return mDevice; }
   aps_store* handle() { return mStore; }
  private:
   aps_store* mStore = nullptr;
   uint64_t mCacheBytes = 0;
+  int32_t mDevice = 0;
   bool mOwned = true;
+};
+
+// One cache over several GPUs: a page lives in the store of GPU aps_shard_of(key, n).  Policy
+// stays where the reference has it -- ONE LocalCacheManager, one meta store, one global byte budget
+// (CACHE/LocalCacheManager.java:261) -- and this class is the PageStore it drives: put and delete go to the
+// owner, a batched get is one kernel on shard 0 that reads every owner's table and slab in place.
+class ShardedGpuPageStore : public PageStore {
+ public:
+  // cfg describes the WHOLE cache (cache_bytes = global budget); devices[i] = CUDA ordinal of shard i (several
+  // shards may share a device).  cfg.slab_slots, when given, is per shard; otherwise each shard gets its share
+  // of the budget plus a quarter (hash routing is only balanced on average) plus 64.
+  static int Open(const aps_config& cfg, uint32_t nShards, const int32_t* devices, std::unique_ptr<ShardedGpuPageStore>* out);
+  ~ShardedGpuPageStore() override;
+  int Put(const Key& k, const void* page, int32_t len) override;
+  int Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) override;
+  int Delete(const Key& k) override;
+  int GetPages(std::vector<std::pair<Key, int64_t>>* out) override;
+  int64_t GetCacheSize() const override { return (int64_t)mCacheBytes; }
+  int GetBatch(uint32_t n, const aps_get_req* reqs, aps_result* res) override;
+  int PutBatch(uint32_t n, const aps_put_req* reqs, aps_result* res) override;
+  int DeleteBatch(uint32_t n, const aps_key* keys, aps_result* res) override;
+  int FillPages(void* d, uint64_t stride, uint32_t len, uint32_t n, const uint64_t* f, const uint64_t* i, uint64_t seed) override;
+  int SetFaults(uint32_t mask) override;
+  int32_t StagingDevice() const override { return mShards.empty() ? 0 : mShards[0]->StagingDevice(); }
+  uint32_t shards() const { return (uint32_t)mShards.size(); }
+  GpuPageStore* shard(uint32_t i) { return mShards[i].get(); }
+  uint32_t OwnerOf(const Key& k) const;
+ private:
+  std::vector<std::unique_ptr<GpuPageStore>> mShards;
+  uint64_t mCacheBytes = 0;
 };
 
 // Counters of the reference's Client.Cache* metrics that live in this layer

@@ -41,6 +41,19 @@ APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, doubl
  * and deletes the rest from the store.  The store stays the caller's (apc_manager_close does not close it). */
 APS_API int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
                                     apc_manager** out);
+/* ONE cache over several GPUs: the manager, its meta store, its evictor and its byte budget
+ * (cfg->cache_bytes) stay single and global, as in the reference (CACHE/LocalCacheManager.java:261); the pages
+ * live in n_shards GPU stores, page -> shard aps_shard_of(key, n_shards) on device devices[shard].  put and
+ * delete go to the owner; batched gets are one kernel that reads the owners in place.  cfg->slab_slots, when
+ * non-zero, is per shard; by default every shard gets its share of the budget plus a quarter plus 64 slots,
+ * because hash routing balances only on average (a put that finds its shard full fails like any store write
+ * failure: the reference's undoAddPage path).  Victim order, hit/miss sequence and residency are those of the
+ * single-store manager. */
+APS_API int apc_manager_create_sharded(const aps_config* cfg, uint32_t n_shards, const int32_t* devices,
+                                       const char* evictor, double lfu_logbase, apc_manager** out);
+APS_API uint32_t apc_shard_count(apc_manager* m);
+APS_API aps_store* apc_shard_store(apc_manager* m, uint32_t shard);
+APS_API uint32_t apc_shard_of(apc_manager* m, const char* file_id, int64_t page_index);
 APS_API int apc_manager_close(apc_manager* m);
 /* CacheManager.put(PageId, byte[]) -> boolean, CACHE/LocalCacheManager.java:206-347 */
 APS_API int apc_put(apc_manager* m, const char* file_id, int64_t page_index, const void* page, int32_t len);
@@ -64,7 +77,7 @@ APS_API int64_t apc_bytes(apc_manager* m); /* MetaStore.bytes() */
 APS_API int64_t apc_pages(apc_manager* m); /* MetaStore.pages() */
 APS_API int32_t apc_page_lock_id(apc_manager* m, const char* file_id, int64_t page_index); /* :172-174 */
 APS_API int apc_set_store_faults(apc_manager* m, uint32_t fault_mask);                     /* APS_FAULT_* */
-APS_API aps_store* apc_store(apc_manager* m);
+APS_API aps_store* apc_store(apc_manager* m); /* the store, or shard 0 of a sharded manager */
 
 /* LocalCacheFileInStream.positionedRead (CACHE/LocalCacheFileInStream.java:175-223): reads
  * [pos, pos+len) of a file of file_len bytes through the cache; pages that miss are fetched whole from
