@@ -13,7 +13,31 @@ LIB_PATH = os.path.join(HERE, "libaps_host.so")
 _vp, _cp, _i32, _i64, _u64, _dbl = C.c_void_p, C.c_char_p, C.c_int32, C.c_int64, C.c_uint64, C.c_double
 EXTERNAL_READ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32)
 
+class apc_options(C.Structure):
+    _fields_ = [("store", capi.aps_config), ("evictor", C.c_char_p), ("lfu_logbase", C.c_double), ("n_shards", C.c_uint32),
+                ("shard_devices", C.POINTER(C.c_int32)), ("over", C.c_void_p), ("async_write_threads", C.c_int32),
+                ("async_restore", C.c_int32)]
+
+
 SIGNATURES = {
+    "apc_manager_create_ex": (C.c_int, [C.POINTER(apc_options), C.POINTER(_vp)]),
+    "apc_wait_async": (None, [_vp]),
+    "apc_put_async_rejections": (_i64, [_vp]),
+    "apc_put_not_ready_errors": (_i64, [_vp]),
+    "apc_factory_get": (C.c_int, [C.POINTER(apc_options), C.POINTER(_vp)]),
+    "apc_factory_clear": (None, []),
+    "apc_factory_create_errors": (_i64, []),
+    "apc_file_open": (_vp, [_vp, _cp, _i64, EXTERNAL_READ, _vp]),
+    "apc_stream_read": (_i32, [_vp, _vp, _i32, _i32, _i32]),
+    "apc_stream_positioned_read": (_i32, [_vp, _i64, _vp, _i32, _i32, _i32]),
+    "apc_stream_skip": (_i64, [_vp, _i64]),
+    "apc_stream_seek": (C.c_int, [_vp, _i64]),
+    "apc_stream_remaining": (_i64, [_vp]),
+    "apc_stream_get_pos": (_i64, [_vp]),
+    "apc_stream_bypass": (C.c_int, [_vp]),
+    "apc_stream_counters": (None, [_vp, _vp]),
+    "apc_stream_close": (None, [_vp]),
+    "apc_stream_destroy": (None, [_vp]),
     "apc_manager_create": (C.c_int, [C.POINTER(capi.aps_config), _cp, _dbl, C.POINTER(_vp)]),
     "apc_manager_create_sharded": (C.c_int, [C.POINTER(capi.aps_config), C.c_uint32, C.POINTER(_i32), _cp, _dbl, C.POINTER(_vp)]),
     "apc_shard_count": (C.c_uint32, [_vp]),
@@ -182,6 +206,47 @@ class LocalCacheManager:
         self._h = h
         self.page_size = page_size
 
+    @staticmethod
+    def _options(page_size, cache_size, evictor="LRU", lfu_logbase=2.0, device=0, slab_slots=0, crc=True, max_batch=0,
+                 shard_devices=None, over=None, async_write_threads=0, async_restore=False):
+        o = apc_options()
+        o.store = capi.aps_config(device=device, page_size=page_size, cache_bytes=cache_size, slab_slots=slab_slots,
+                                  table_capacity=0, max_batch=max_batch, flags=capi.APS_FLAG_CRC if crc else 0)
+        o.evictor, o.lfu_logbase = evictor.encode(), lfu_logbase
+        keep = None
+        if shard_devices:
+            keep = (C.c_int32 * len(shard_devices))(*shard_devices)
+            o.n_shards, o.shard_devices = len(shard_devices), keep
+        if over is not None:
+            o.over = over.handle
+        o.async_write_threads, o.async_restore = async_write_threads, int(async_restore)
+        return o, keep
+
+    @classmethod
+    def create(cls, page_size, cache_size, **kw):
+        """LocalCacheManager.create(conf): every configuration knob of the reference's factory method, including
+        async_write_threads (alluxio.user.client.cache.async.write.*) and async_restore (...async.restore.enabled)."""
+        self = cls.__new__(cls)
+        o, keep = cls._options(page_size, cache_size, **kw)
+        h = C.c_void_p()
+        capi.check(lib().apc_manager_create_ex(C.byref(o), C.byref(h)), "apc_manager_create_ex")
+        self._h, self.page_size, self._keep = h, page_size, kw.get("over")
+        return self
+
+    def wait_async(self):
+        lib().apc_wait_async(self._h)
+
+    def put_async_rejections(self):
+        return lib().apc_put_async_rejections(self._h)
+
+    def put_not_ready_errors(self):
+        return lib().apc_put_not_ready_errors(self._h)
+
+    def open_file(self, file_id, file_len, external):
+        """LocalCacheFileSystem.openFile(status): a LocalCacheFileInStream, or the external stream when the cache
+        is NOT_IN_USE."""
+        return LocalCacheFileInStream(self, file_id, file_len, external)
+
     def shard_count(self):
         return lib().apc_shard_count(self._h)
 
@@ -222,7 +287,8 @@ class LocalCacheManager:
 
     def close(self):
         if self._h is not None:
-            lib().apc_manager_close(self._h)
+            if not getattr(self, "_factory_owned", False):  # the factory's manager goes away with Factory.clear()
+                lib().apc_manager_close(self._h)
             self._h = None
 
     def __del__(self):
@@ -332,3 +398,105 @@ def _replay_batched(self, files, pages, page_lens, seed, window=4096, victims_ca
 
 
 LocalCacheManager.replay_batched = _replay_batched
+
+
+class CacheManagerFactory:
+    """CacheManager.Factory (CACHE/CacheManager.java:69-127): the process-wide manager."""
+
+    @staticmethod
+    def get(page_size, cache_size, **kw):
+        o, keep = LocalCacheManager._options(page_size, cache_size, **kw)
+        h = C.c_void_p()
+        capi.check(lib().apc_factory_get(C.byref(o), C.byref(h)), "Failed to create CacheManager")
+        if not h.value:
+            return None  # another thread is still creating it
+        m = LocalCacheManager.__new__(LocalCacheManager)
+        m._h, m.page_size, m._factory_owned = h, page_size, True
+        return m
+
+    @staticmethod
+    def clear():
+        lib().apc_factory_clear()
+
+    @staticmethod
+    def create_errors():
+        return lib().apc_factory_create_errors()
+
+
+class LocalCacheFileInStream:
+    """CACHE/LocalCacheFileInStream.java:43-330 (+ the bypass of LocalCacheFileSystem.openFile, :51-70).
+    `external(pos, n) -> bytes` stands for the delegated file system's stream."""
+
+    def __init__(self, manager, file_id, file_len, external):
+        def ext(user, file_pos, dst, n):
+            data = external(file_pos, n)
+            C.memmove(dst, data, len(data))
+            return len(data)
+
+        self._cb = EXTERNAL_READ(ext)
+        self._h = C.c_void_p(lib().apc_file_open(manager._h if manager is not None else None, str(file_id).encode(),
+                                                 file_len, self._cb, None))
+        if not self._h.value:
+            raise ValueError("apc_file_open")
+
+    @staticmethod
+    def _result(r, buf, off):
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        if r == -3:
+            raise IOError("Failed to read complete page from external storage")
+        return r
+
+    def read(self, b, off=0, length=None):
+        """int read(byte[] b, int off, int len): fills the bytearray in place; -1 at end of file."""
+        length = len(b) - off if length is None else length
+        cbuf = (C.c_uint8 * max(1, len(b))).from_buffer(b) if len(b) else (C.c_uint8 * 1)()
+        r = lib().apc_stream_read(self._h, C.addressof(cbuf), len(b), off, length)
+        del cbuf
+        return self._result(r, b, off)
+
+    def positioned_read(self, pos, b, off=0, length=None):
+        length = len(b) - off if length is None else length
+        cbuf = (C.c_uint8 * max(1, len(b))).from_buffer(b) if len(b) else (C.c_uint8 * 1)()
+        r = lib().apc_stream_positioned_read(self._h, pos, C.addressof(cbuf), len(b), off, length)
+        del cbuf
+        return self._result(r, b, off)
+
+    def skip(self, n):
+        r = lib().apc_stream_skip(self._h, n)
+        if r == -4:
+            raise RuntimeError("Cannot operate on a closed stream")
+        return r
+
+    def seek(self, pos):
+        r = lib().apc_stream_seek(self._h, pos)
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        if r == -4:
+            raise RuntimeError("Cannot operate on a closed stream")
+
+    def remaining(self):
+        return lib().apc_stream_remaining(self._h)
+
+    def get_pos(self):
+        return lib().apc_stream_get_pos(self._h)
+
+    def bypass(self):
+        return bool(lib().apc_stream_bypass(self._h))
+
+    def counters(self):
+        import numpy as np
+        v = np.zeros(3, np.int64)
+        lib().apc_stream_counters(self._h, v.ctypes.data)
+        return dict(zip(("BytesReadCache", "BytesRequestedExternal", "BytesReadExternal"), v.tolist()))
+
+    def close(self):
+        lib().apc_stream_close(self._h)
+
+    def __del__(self):
+        try:
+            if self._h and self._h.value:
+                lib().apc_stream_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass

@@ -477,10 +477,64 @@ int ShardedGpuPageStore::SetFaults(uint32_t mask) {
 
 // ================================================================================ LocalCacheManager
 
-LocalCacheManager::LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store)
-    : mPageSize(pageSize), mCacheSize(store->GetCacheSize()), mMetaStore(std::move(meta)), mPageStore(std::move(store)),
-      mState(READ_ONLY) {  // LocalCacheManager.java:145-166
-  RestoreOrInit();          // :134
+HandOffPool::HandOffPool(int threads) {
+  for (int i = 0; i < threads; ++i) mWorkers.emplace_back([this] { Work(); });
+}
+HandOffPool::~HandOffPool() {
+  {
+    std::lock_guard<std::mutex> lk(mMu);
+    mStop = true;
+  }
+  mWake.notify_all();
+  for (auto& t : mWorkers) t.join();
+}
+bool HandOffPool::TrySubmit(std::function<void()> task) {
+  {
+    std::lock_guard<std::mutex> lk(mMu);
+    // every thread is running a task or already has one waiting for it: RejectedExecutionException
+    if (mStop || mQueue.size() + (size_t)mRunning >= mWorkers.size()) return false;
+    mQueue.push_back(std::move(task));
+  }
+  mWake.notify_one();
+  return true;
+}
+void HandOffPool::WaitIdle() {
+  std::unique_lock<std::mutex> lk(mMu);
+  mQuiet.wait(lk, [this] { return mQueue.empty() && mRunning == 0; });
+}
+void HandOffPool::Work() {
+  std::unique_lock<std::mutex> lk(mMu);
+  for (;;) {
+    mWake.wait(lk, [this] { return mStop || !mQueue.empty(); });
+    if (mQueue.empty()) return;  // stopping
+    std::function<void()> task = std::move(mQueue.front());
+    mQueue.pop_front();
+    ++mRunning;
+    lk.unlock();
+    task();
+    lk.lock();
+    --mRunning;
+    if (mQueue.empty() && mRunning == 0) mQuiet.notify_all();
+  }
+}
+
+LocalCacheManager::LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store,
+                                     ManagerOptions options)
+    : mOptions(options), mPageSize(pageSize), mCacheSize(store->GetCacheSize()), mMetaStore(std::move(meta)),
+      mPageStore(std::move(store)), mState(READ_ONLY) {  // LocalCacheManager.java:145-166
+  if (mOptions.asyncWriteThreads > 0) mAsyncCacheExecutor.reset(new HandOffPool(mOptions.asyncWriteThreads));
+  if (mOptions.asyncRestore) mInitService = std::thread([this] { RestoreOrInit(); });  // :126-133, READ_ONLY meanwhile
+  else RestoreOrInit();                                                                // :134
+}
+
+LocalCacheManager::~LocalCacheManager() {
+  if (mInitService.joinable()) mInitService.join();
+  mAsyncCacheExecutor.reset();
+}
+
+void LocalCacheManager::WaitAsync() {
+  if (mInitService.joinable()) mInitService.join();
+  if (mAsyncCacheExecutor) mAsyncCacheExecutor->WaitIdle();
 }
 
 Key LocalCacheManager::MakeKey(const std::string& fileId, int64_t pageIndex) {
@@ -497,12 +551,39 @@ int32_t LocalCacheManager::GetPageLockId(const std::string& fileId, int64_t page
 
 bool LocalCacheManager::Put(const std::string& fileId, int64_t pageIndex, const void* page, int32_t len) {  // :206-246
   if (mState.load() != READ_WRITE) {
+    putNotReadyErrors++;
     metrics.putErrors++;
     return false;
   }
-  const bool ok = PutInternal(MakeKey(fileId, pageIndex), GetPageLockId(fileId, pageIndex), page, len);
-  if (ok) metrics.bytesWrittenCache += len; else metrics.putErrors++;
-  return ok;
+  const Key k = MakeKey(fileId, pageIndex);
+  const int32_t lockId = GetPageLockId(fileId, pageIndex);
+  if (!mAsyncCacheExecutor) {
+    const bool ok = PutInternal(k, lockId, page, len);
+    if (ok) metrics.bytesWrittenCache += len; else metrics.putErrors++;
+    return ok;
+  }
+  {
+    std::lock_guard<std::mutex> lk(mPendingMu);
+    if (!mPendingRequests.insert(k).second) return false;  // already queued (:221-223)
+  }
+  // the Java caller hands over its array; a C caller keeps its buffer, so the bytes are copied for the worker
+  auto bytes = std::make_shared<std::vector<uint8_t>>((const uint8_t*)page, (const uint8_t*)page + len);
+  const bool accepted = mAsyncCacheExecutor->TrySubmit([this, k, lockId, bytes] {
+    const bool ok = PutInternal(k, lockId, bytes->data(), (int32_t)bytes->size());
+    if (ok) metrics.bytesWrittenCache += (int64_t)bytes->size(); else metrics.putErrors++;
+    std::lock_guard<std::mutex> lk(mPendingMu);
+    mPendingRequests.erase(k);
+  });
+  if (!accepted) {  // every worker busy (:235-243)
+    {
+      std::lock_guard<std::mutex> lk(mPendingMu);
+      mPendingRequests.erase(k);
+    }
+    putAsyncRejectionErrors++;
+    metrics.putErrors++;
+    return false;
+  }
+  return true;
 }
 
 bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* page, int32_t len) {  // :249-347
@@ -673,6 +754,94 @@ bool LocalCacheManager::Restore() {  // :466-509
   return true;
 }
 
+// ================================================================================ LocalCacheFileInStream
+
+LocalCacheFileInStream::LocalCacheFileInStream(LocalCacheManager* manager, const std::string& fileId, int64_t fileLength,
+                                               ExternalRead external, void* user)
+    : mManager(manager), mFileId(fileId), mLength(fileLength), mPageSize(manager ? manager->pageSize() : 1),
+      mExternal(external), mUser(user), mBypass(!manager || manager->state() == NOT_IN_USE) {}
+
+bool LocalCacheFileInStream::ReadExternalPage(int64_t pos, std::vector<uint8_t>* page) {  // :291-310
+  std::lock_guard<std::mutex> lk(mExternalMu);
+  const int64_t pageStart = pos - (pos % mPageSize);
+  const int32_t pageSize = (int32_t)std::min<int64_t>(mPageSize, mLength - pageStart);
+  page->resize((size_t)pageSize);
+  int32_t total = 0;
+  while (total < pageSize) {
+    const int r = mExternal(mUser, pageStart + total, page->data() + total, pageSize - total);
+    if (r <= 0) break;
+    total += r;
+  }
+  bytesReadExternal += total;
+  if (mManager) mManager->metrics.bytesReadExternal += total;
+  return total == pageSize;  // else "Failed to read complete page from external storage"
+}
+
+int32_t LocalCacheFileInStream::ReadAt(int64_t* position, void* b, int32_t bLen, int32_t off, int32_t len) {
+  if (len < 0 || off < 0 || *position < 0) return kGetIllegalArgument;
+  if (len == 0) return 0;
+  if (*position >= mLength) return -1;
+  if (off > bLen || len > bLen - off) return kGetIllegalArgument;  // Java: ArrayIndexOutOfBounds from the copy
+  if (mBypass) {  // the delegated file system's own stream
+    const int64_t want = std::min<int64_t>(len, mLength - *position);
+    int64_t total = 0;
+    while (total < want) {
+      const int r = mExternal(mUser, *position + total, (uint8_t*)b + off + total, (int32_t)(want - total));
+      if (r <= 0) return -3;
+      total += r;
+    }
+    *position += total;
+    return (int32_t)total;
+  }
+  int32_t total = 0;
+  const int64_t toRead = std::min<int64_t>(len, mLength - *position);
+  std::vector<uint8_t> page;
+  while (total < toRead) {
+    const int64_t pageIdx = *position / mPageSize;
+    const int32_t pageOff = (int32_t)(*position % mPageSize);
+    const int32_t inPage = (int32_t)std::min<int64_t>(mPageSize - pageOff, toRead - total);
+    const int32_t got = mManager->Get(mFileId, pageIdx, pageOff, inPage, b, bLen, off + total);
+    if (got > 0) {
+      total += got;
+      *position += got;
+      bytesReadCache += got;
+      mManager->metrics.bytesReadCache += got;
+    } else {  // miss (0) or error (-1): the whole page comes from outside and is offered to the cache
+      if (!ReadExternalPage(*position, &page)) return -3;
+      if (!page.empty()) {
+        memcpy((uint8_t*)b + off + total, page.data() + pageOff, (size_t)inPage);
+        total += inPage;
+        *position += inPage;
+        bytesRequestedExternal += inPage;
+        mManager->metrics.bytesRequestedExternal += inPage;
+        mManager->Put(mFileId, pageIdx, page.data(), (int32_t)page.size());
+      }
+    }
+  }
+  return total;
+}
+
+int32_t LocalCacheFileInStream::Read(void* b, int32_t bLen, int32_t off, int32_t len) {  // :108-152
+  return ReadAt(&mPosition, b, bLen, off, len);
+}
+int32_t LocalCacheFileInStream::PositionedRead(int64_t pos, void* b, int32_t bLen, int32_t off, int32_t len) {  // :175-223
+  int64_t p = pos;
+  return ReadAt(&p, b, bLen, off, len);
+}
+int64_t LocalCacheFileInStream::Skip(int64_t n) {  // :154-162
+  if (mClosed) return -4;
+  if (n <= 0) return 0;
+  const int64_t toSkip = std::min(Remaining(), n);
+  mPosition += toSkip;
+  return toSkip;
+}
+int LocalCacheFileInStream::Seek(int64_t pos) {  // :230-243
+  if (mClosed) return -4;
+  if (pos < 0 || pos > mLength) return kGetIllegalArgument;
+  mPosition = pos;
+  return 0;
+}
+
 void FillSyntheticPage(uint64_t seed, uint64_t file, uint64_t index, uint8_t* out, int64_t len) {
   const uint64_t s = seed ^ (file << 32) ^ index;
   for (int64_t k = 0; k * 8 < len; ++k) {
@@ -747,6 +916,101 @@ int apc_manager_create_sharded(const aps_config* cfg, uint32_t n_shards, const i
   *out = m;
   return APS_OK;
 }
+int apc_manager_create_ex(const apc_options* o, apc_manager** out) {
+  if (!o || !o->evictor || !out) return APS_EINVAL;
+  *out = nullptr;
+  auto ev = CacheEvictor::Create(o->evictor, o->lfu_logbase);
+  if (!ev) return APS_EINVAL;
+  ManagerOptions mo;
+  mo.asyncWriteThreads = o->async_write_threads;
+  mo.asyncRestore = o->async_restore != 0;
+  std::unique_ptr<apc_manager> m(new apc_manager());
+  std::unique_ptr<PageStore> store;
+  if (o->over) {
+    std::unique_ptr<GpuPageStore> gs = GpuPageStore::Adopt(o->over);
+    m->gpu = gs.get();
+    store = std::move(gs);
+  } else if (o->n_shards > 0) {
+    std::unique_ptr<ShardedGpuPageStore> ss;
+    const int rc = ShardedGpuPageStore::Open(o->store, o->n_shards, o->shard_devices, &ss);
+    if (rc != APS_OK) return rc;
+    m->sharded = ss.get();
+    store = std::move(ss);
+  } else {
+    std::unique_ptr<GpuPageStore> gs;
+    const int rc = GpuPageStore::Open(o->store, &gs);
+    if (rc != APS_OK) return rc;
+    m->gpu = gs.get();
+    store = std::move(gs);
+  }
+  m->mgr.reset(new LocalCacheManager(o->store.page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))),
+                                     std::move(store), mo));
+  *out = m.release();
+  return APS_OK;
+}
+void apc_wait_async(apc_manager* m) { m->mgr->WaitAsync(); }
+int64_t apc_put_async_rejections(apc_manager* m) { return m->mgr->putAsyncRejectionErrors.load(); }
+int64_t apc_put_not_ready_errors(apc_manager* m) { return m->mgr->putNotReadyErrors.load(); }
+
+// CacheManager.Factory (CACHE/CacheManager.java:69-127): one manager per process; a caller that arrives while
+// another thread is still creating it gets null instead of waiting.
+namespace {
+std::mutex gFactoryLock;
+std::atomic<apc_manager*> gFactoryManager{nullptr};
+std::atomic<int64_t> gFactoryCreateErrors{0};
+}  // namespace
+int apc_factory_get(const apc_options* o, apc_manager** out) {
+  if (!out) return APS_EINVAL;
+  *out = nullptr;
+  if (gFactoryManager.load() == nullptr) {
+    std::unique_lock<std::mutex> lk(gFactoryLock, std::try_to_lock);
+    if (lk.owns_lock() && gFactoryManager.load() == nullptr) {
+      apc_manager* m = nullptr;
+      const int rc = apc_manager_create_ex(o, &m);
+      if (rc != APS_OK) {
+        gFactoryCreateErrors++;
+        return rc;  // IOException("Failed to create CacheManager")
+      }
+      gFactoryManager.store(m);
+    }
+  }
+  *out = gFactoryManager.load();
+  return APS_OK;
+}
+void apc_factory_clear(void) {
+  std::lock_guard<std::mutex> lk(gFactoryLock);
+  apc_manager* m = gFactoryManager.exchange(nullptr);
+  if (m) apc_manager_close(m);
+}
+int64_t apc_factory_create_errors(void) { return gFactoryCreateErrors.load(); }
+
+// LocalCacheFileSystem.openFile + LocalCacheFileInStream
+struct apc_stream {
+  std::unique_ptr<LocalCacheFileInStream> in;
+};
+apc_stream* apc_file_open(apc_manager* m, const char* file_id, int64_t file_len, apc_external_read external, void* user) {
+  if (!file_id || !external || file_len < 0) return nullptr;
+  apc_stream* s = new apc_stream();
+  s->in.reset(new LocalCacheFileInStream(m ? m->mgr.get() : nullptr, file_id, file_len, external, user));
+  return s;
+}
+int32_t apc_stream_read(apc_stream* s, void* b, int32_t b_len, int32_t off, int32_t len) { return s->in->Read(b, b_len, off, len); }
+int32_t apc_stream_positioned_read(apc_stream* s, int64_t pos, void* b, int32_t b_len, int32_t off, int32_t len) {
+  return s->in->PositionedRead(pos, b, b_len, off, len);
+}
+int64_t apc_stream_skip(apc_stream* s, int64_t n) { return s->in->Skip(n); }
+int apc_stream_seek(apc_stream* s, int64_t pos) { return s->in->Seek(pos); }
+int64_t apc_stream_remaining(apc_stream* s) { return s->in->Remaining(); }
+int64_t apc_stream_get_pos(apc_stream* s) { return s->in->GetPos(); }
+int apc_stream_bypass(apc_stream* s) { return s->in->bypass() ? 1 : 0; }
+void apc_stream_counters(apc_stream* s, int64_t* out3) {
+  out3[0] = s->in->bytesReadCache;
+  out3[1] = s->in->bytesRequestedExternal;
+  out3[2] = s->in->bytesReadExternal;
+}
+void apc_stream_close(apc_stream* s) { s->in->Close(); }
+void apc_stream_destroy(apc_stream* s) { delete s; }
+
 uint32_t apc_shard_count(apc_manager* m) { return m->sharded ? m->sharded->shards() : 1; }
 aps_store* apc_shard_store(apc_manager* m, uint32_t i) {
   if (m->sharded) return i < m->sharded->shards() ? m->sharded->shard(i)->handle() : nullptr;

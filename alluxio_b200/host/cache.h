@@ -9,13 +9,18 @@
 // This is product code: it never touches oracle/.
 #pragma once
 #include <atomic>
+#include <condition_variable>
 #include <cstdint>
+#include <deque>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
 #include <shared_mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
+#include <unordered_set>
 #include <vector>
 
 #include "../../include/aps.h"
@@ -193,13 +198,41 @@ struct CacheMetrics {
       putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0};
 };
 
-// ---- CACHE/LocalCacheManager.java:75-627 (sync write, sync restore) -------------------------------------
+// new ThreadPoolExecutor(n, n, 60 s, new SynchronousQueue<>()) of CACHE/LocalCacheManager.java:156-161: a task
+// is accepted only while a worker is free to take it, otherwise the submit is rejected at once.
+class HandOffPool {
+ public:
+  explicit HandOffPool(int threads);
+  ~HandOffPool();  // runs what was accepted, then joins
+  bool TrySubmit(std::function<void()> task);
+  void WaitIdle();
+ private:
+  void Work();
+  std::mutex mMu;
+  std::condition_variable mWake, mQuiet;
+  std::deque<std::function<void()>> mQueue;
+  std::vector<std::thread> mWorkers;
+  int mRunning = 0;
+  bool mStop = false;
+};
+
+// ---- CACHE/LocalCacheManager.java:75-627 -----------------------------------------------------------------
 enum State { NOT_IN_USE = 0, READ_ONLY = 1, READ_WRITE = 2 };
 constexpr int32_t kGetIllegalArgument = -2;
 
+struct ManagerOptions {
+  int asyncWriteThreads = 0;  // alluxio.user.client.cache.async.write.enabled / .threads (0 = synchronous puts)
+  bool asyncRestore = false;  // alluxio.user.client.cache.async.restore.enabled
+};
+
 class LocalCacheManager {
  public:
-  LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store);
+  LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store,
+                    ManagerOptions options = ManagerOptions());
+  ~LocalCacheManager();  // close(): :511-521
+  // Blocks until the restore thread has finished and no asynchronous put is queued or running (tests, shutdown).
+  void WaitAsync();
+  std::atomic<int64_t> putAsyncRejectionErrors{0}, putNotReadyErrors{0};
   bool Put(const std::string& fileId, int64_t pageIndex, const void* page, int32_t len);
   int32_t Get(const std::string& fileId, int64_t pageIndex, int32_t pageOffset, int32_t bytesToRead, void* buffer,
               int32_t bufLen, int32_t offsetInBuffer);
@@ -226,6 +259,11 @@ class LocalCacheManager {
   void UndoAddPage(const Key& k);
   void RestoreOrInit();
   bool Restore();
+  ManagerOptions mOptions;
+  std::unique_ptr<HandOffPool> mAsyncCacheExecutor;
+  std::thread mInitService;
+  std::mutex mPendingMu;
+  std::unordered_set<Key, KeyHash> mPendingRequests;
   int64_t mPageSize, mCacheSize;
   std::unique_ptr<MetaStore> mMetaStore;
   std::unique_ptr<PageStore> mPageStore;
@@ -233,6 +271,37 @@ class LocalCacheManager {
   std::shared_mutex mPageLocks[kLockSize];
   std::shared_mutex mMetaLock;
   std::atomic<State> mState;
+};
+
+// ---- CACHE/LocalCacheFileInStream.java:43-330 behind CACHE/LocalCacheFileSystem.java:32-71 ---------------
+// `external(user, filePos, dst, len) -> bytes read` stands for the FileInStream of the delegated file system.
+typedef int (*ExternalRead)(void* user, int64_t filePos, void* dst, int32_t len);
+class LocalCacheFileInStream {
+ public:
+  // LocalCacheFileSystem.openFile: with no manager, or one whose state is NOT_IN_USE, the stream is the
+  // external one (bypass: the cache is neither read nor filled).
+  LocalCacheFileInStream(LocalCacheManager* manager, const std::string& fileId, int64_t fileLength, ExternalRead external,
+                         void* user);
+  // read(byte[] b, int off, int len): bytes read, -1 at EOF, kGetIllegalArgument, or -3 for the IOException paths
+  int32_t Read(void* b, int32_t bLen, int32_t off, int32_t len);
+  int32_t PositionedRead(int64_t pos, void* b, int32_t bLen, int32_t off, int32_t len);
+  int64_t Skip(int64_t n);       // -4 on a closed stream (IllegalStateException)
+  int Seek(int64_t pos);         // 0, kGetIllegalArgument, or -4 on a closed stream
+  int64_t Remaining() const { return mLength - mPosition; }
+  int64_t GetPos() const { return mPosition; }
+  void Close() { mClosed = true; }
+  bool bypass() const { return mBypass; }
+  int64_t bytesReadCache = 0, bytesRequestedExternal = 0, bytesReadExternal = 0;
+ private:
+  int32_t ReadAt(int64_t* position, void* b, int32_t bLen, int32_t off, int32_t len);
+  bool ReadExternalPage(int64_t pos, std::vector<uint8_t>* page);
+  LocalCacheManager* mManager;
+  std::string mFileId;
+  int64_t mLength, mPageSize, mPosition = 0;
+  ExternalRead mExternal;
+  void* mUser;
+  bool mClosed = false, mBypass;
+  std::mutex mExternalMu;  // readExternalPage is synchronized (:291)
 };
 
 // Page payload of the benchmarks and replays: 64-bit word k of page (file, index) is the k-th

@@ -41,6 +41,38 @@ APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, doubl
  * and deletes the rest from the store.  The store stays the caller's (apc_manager_close does not close it). */
 APS_API int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
                                     apc_manager** out);
+/* Everything LocalCacheManager.create reads from the configuration, in one place.  Exactly one of `over`,
+ * n_shards > 0, or neither (a single new store on store.device) selects the page store. */
+typedef struct apc_options {
+  aps_config store;             /* GpuPageStoreOptions: page size, cache size, device, ... */
+  const char* evictor;          /* alluxio.user.client.cache.evictor.class: "LRU" | "LFU" (| "FIFO", the test double) */
+  double lfu_logbase;           /* alluxio.user.client.cache.evictor.lfu.logbase */
+  uint32_t n_shards;            /* > 0: one cache over this many GPU stores (see apc_manager_create_sharded) */
+  const int32_t* shard_devices; /* n_shards CUDA ordinals */
+  aps_store* over;              /* non-NULL: adopt this store and restore from its pages (not closed by the manager) */
+  int32_t async_write_threads;  /* alluxio.user.client.cache.async.write.enabled/.threads: 0 = synchronous puts.
+                                 * Otherwise put() queues the page on a pool of this many threads that accepts a task
+                                 * only while a thread is free (ThreadPoolExecutor over a SynchronousQueue,
+                                 * CACHE/LocalCacheManager.java:156-161): a put of an id already queued, or one that
+                                 * finds every thread busy, returns false (:221-243). */
+  int32_t async_restore;        /* alluxio.user.client.cache.async.restore.enabled: create returns at once in state
+                                 * READ_ONLY (gets served, puts refused, :208-212) and turns READ_WRITE when the
+                                 * restore thread is done (:126-133) */
+} apc_options;
+APS_API int apc_manager_create_ex(const apc_options* options, apc_manager** out);
+/* Waits for the restore thread and for every queued asynchronous put (tests; orderly shutdown). */
+APS_API void apc_wait_async(apc_manager* m);
+APS_API int64_t apc_put_async_rejections(apc_manager* m); /* Client.CachePutAsyncRejectionErrors */
+APS_API int64_t apc_put_not_ready_errors(apc_manager* m); /* Client.CachePutNotReadyErrors */
+
+/* CacheManager.Factory.get / clear (CACHE/CacheManager.java:69-127): the process-wide manager, created by the
+ * first caller.  A caller that arrives while another thread is still creating it receives *out = NULL (Java
+ * null) and status APS_OK; a failed creation is counted (Client.CacheCreateErrors) and reported.  The manager
+ * belongs to the factory: release it with apc_factory_clear, never apc_manager_close. */
+APS_API int apc_factory_get(const apc_options* options, apc_manager** out);
+APS_API void apc_factory_clear(void);
+APS_API int64_t apc_factory_create_errors(void);
+
 /* ONE cache over several GPUs: the manager, its meta store, its evictor and its byte budget
  * (cfg->cache_bytes) stay single and global, as in the reference (CACHE/LocalCacheManager.java:261); the pages
  * live in n_shards GPU stores, page -> shard aps_shard_of(key, n_shards) on device devices[shard].  put and
@@ -55,7 +87,8 @@ APS_API uint32_t apc_shard_count(apc_manager* m);
 APS_API aps_store* apc_shard_store(apc_manager* m, uint32_t shard);
 APS_API uint32_t apc_shard_of(apc_manager* m, const char* file_id, int64_t page_index);
 APS_API int apc_manager_close(apc_manager* m);
-/* CacheManager.put(PageId, byte[]) -> boolean, CACHE/LocalCacheManager.java:206-347 */
+/* CacheManager.put(PageId, byte[]) -> boolean, CACHE/LocalCacheManager.java:206-347.  put and delete never
+ * throw in this mirror, so they are also their NoExceptionCacheManager forms (CACHE/NoExceptionCacheManager.java:37-46,81-90). */
 APS_API int apc_put(apc_manager* m, const char* file_id, int64_t page_index, const void* page, int32_t len);
 /* CacheManager.get(PageId, pageOffset, bytesToRead, buffer, offsetInBuffer) -> bytes read, 0 on a
  * miss, -1 on error, CACHE/LocalCacheManager.java:360-399 */
@@ -87,6 +120,28 @@ typedef int (*apc_external_read)(void* user, int64_t file_pos, void* dst, int32_
 APS_API int32_t apc_positioned_read(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst,
                                     int32_t len, apc_external_read external, void* user, int64_t* bytes_from_cache,
                                     int64_t* bytes_from_external);
+
+/* LocalCacheFileSystem.openFile (CACHE/LocalCacheFileSystem.java:51-70) + LocalCacheFileInStream
+ * (CACHE/LocalCacheFileInStream.java:43-330) as an object with a position.  m == NULL or a manager in state
+ * NOT_IN_USE yields the delegated file system's own stream (every read goes to `external`, the cache is not
+ * touched).  read / positioned_read return bytes read, -1 at end of file, APC_GET_ILLEGAL_ARGUMENT for negative
+ * or out-of-buffer arguments, -3 where the reference throws IOException (external read came up short).
+ * seek returns 0 or APC_GET_ILLEGAL_ARGUMENT (position negative or beyond the file); seek / skip on a closed
+ * stream return -4 (IllegalStateException, :262-264). */
+typedef struct apc_stream apc_stream;
+APS_API apc_stream* apc_file_open(apc_manager* m, const char* file_id, int64_t file_len, apc_external_read external,
+                                  void* user);
+APS_API int32_t apc_stream_read(apc_stream* s, void* b, int32_t b_len, int32_t off, int32_t len);
+APS_API int32_t apc_stream_positioned_read(apc_stream* s, int64_t pos, void* b, int32_t b_len, int32_t off, int32_t len);
+APS_API int64_t apc_stream_skip(apc_stream* s, int64_t n);
+APS_API int apc_stream_seek(apc_stream* s, int64_t pos);
+APS_API int64_t apc_stream_remaining(apc_stream* s);
+APS_API int64_t apc_stream_get_pos(apc_stream* s);
+APS_API int apc_stream_bypass(apc_stream* s);
+/* BytesReadCache, BytesRequestedExternal, BytesReadExternal of this stream (:312-330) */
+APS_API void apc_stream_counters(apc_stream* s, int64_t* out3);
+APS_API void apc_stream_close(apc_stream* s);
+APS_API void apc_stream_destroy(apc_stream* s);
 
 /* The same read with ONE batched store call for all resident pages it touches. */
 APS_API int32_t apc_positioned_read_batched(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst,
