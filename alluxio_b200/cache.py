@@ -16,12 +16,14 @@ EXTERNAL_READ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_int3
 class apc_options(C.Structure):
     _fields_ = [("store", capi.aps_config), ("evictor", C.c_char_p), ("lfu_logbase", C.c_double), ("n_shards", C.c_uint32),
                 ("shard_devices", C.POINTER(C.c_int32)), ("over", C.c_void_p), ("async_write_threads", C.c_int32),
-                ("async_restore", C.c_int32)]
+                ("async_restore", C.c_int32), ("timeout_ms", C.c_int64), ("timeout_threads", C.c_int32)]
 
 
 SIGNATURES = {
     "apc_manager_create_ex": (C.c_int, [C.POINTER(apc_options), C.POINTER(_vp)]),
     "apc_wait_async": (None, [_vp]),
+    "apc_store_timeout_counters": (C.c_int, [_vp, _vp]),
+    "apc_set_store_delays": (C.c_int, [_vp, _i32, _i32, _i32]),
     "apc_put_async_rejections": (_i64, [_vp]),
     "apc_put_not_ready_errors": (_i64, [_vp]),
     "apc_factory_get": (C.c_int, [C.POINTER(apc_options), C.POINTER(_vp)]),
@@ -208,7 +210,8 @@ class LocalCacheManager:
 
     @staticmethod
     def _options(page_size, cache_size, evictor="LRU", lfu_logbase=2.0, device=0, slab_slots=0, crc=True, max_batch=0,
-                 shard_devices=None, over=None, async_write_threads=0, async_restore=False):
+                 shard_devices=None, over=None, async_write_threads=0, async_restore=False, timeout_ms=-1,
+                 timeout_threads=0):
         o = apc_options()
         o.store = capi.aps_config(device=device, page_size=page_size, cache_bytes=cache_size, slab_slots=slab_slots,
                                   table_capacity=0, max_batch=max_batch, flags=capi.APS_FLAG_CRC if crc else 0)
@@ -220,6 +223,7 @@ class LocalCacheManager:
         if over is not None:
             o.over = over.handle
         o.async_write_threads, o.async_restore = async_write_threads, int(async_restore)
+        o.timeout_ms, o.timeout_threads = timeout_ms, timeout_threads
         return o, keep
 
     @classmethod
@@ -232,6 +236,16 @@ class LocalCacheManager:
         capi.check(lib().apc_manager_create_ex(C.byref(o), C.byref(h)), "apc_manager_create_ex")
         self._h, self.page_size, self._keep = h, page_size, kw.get("over")
         return self
+
+    def store_timeouts(self):
+        """Client.CacheStore{Put,Get,Delete}Timeout and ...ThreadsRejected of the TimeBoundPageStore wrapper."""
+        import numpy as np
+        v = np.zeros(4, np.int64)
+        capi.check(lib().apc_store_timeout_counters(self._h, v.ctypes.data), "no timeout configured")
+        return dict(zip(("put", "get", "delete", "rejected"), v.tolist()))
+
+    def set_store_delays(self, put_ms=0, get_ms=0, delete_ms=0):
+        capi.check(lib().apc_set_store_delays(self._h, put_ms, get_ms, delete_ms), "no timeout configured")
 
     def wait_async(self):
         lib().apc_wait_async(self._h)

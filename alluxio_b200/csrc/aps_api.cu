@@ -509,6 +509,7 @@ const char* aps_strerror(int code) {
     case APS_EFAULT: return "injected fault";
     case APS_ELIMIT: return "request exceeds the fixed scratch of the no-allocation entry point";
     case APS_EIO: return "snapshot file could not be read or written";
+    case APS_ETIMEOUT: return "store call timed out or all store threads busy";
     default: return "unknown error";
   }
 }

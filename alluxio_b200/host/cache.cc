@@ -2,6 +2,7 @@
 #include "cache.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 
@@ -518,6 +519,80 @@ void HandOffPool::Work() {
   }
 }
 
+// ================================================================================ TimeBoundPageStore
+
+TimeBoundPageStore::TimeBoundPageStore(std::unique_ptr<PageStore> store, int64_t timeoutMs, int threads)
+    : mStore(std::move(store)), mTimeoutMs(timeoutMs), mPool(new HandOffPool(std::max(1, threads))) {}
+
+int TimeBoundPageStore::Bounded(std::function<int()> call, std::atomic<int64_t>* timeouts) {
+  struct Outcome {
+    std::mutex mu;
+    std::condition_variable cv;
+    bool done = false;
+    int rc = APS_OK;
+  };
+  auto out = std::make_shared<Outcome>();
+  if (!mPool->TrySubmit([out, call] {
+        const int rc = call();
+        std::lock_guard<std::mutex> lk(out->mu);
+        out->rc = rc;
+        out->done = true;
+        out->cv.notify_all();
+      })) {
+    storeThreadsRejected++;
+    return APS_ETIMEOUT;
+  }
+  std::unique_lock<std::mutex> lk(out->mu);
+  if (!out->cv.wait_for(lk, std::chrono::milliseconds(mTimeoutMs), [&] { return out->done; })) {
+    (*timeouts)++;
+    return APS_ETIMEOUT;
+  }
+  return out->rc;
+}
+
+static void Nap(int32_t ms) {
+  if (ms > 0) std::this_thread::sleep_for(std::chrono::milliseconds(ms));
+}
+
+int TimeBoundPageStore::Put(const Key& k, const void* page, int32_t len) {
+  auto bytes = std::make_shared<std::vector<uint8_t>>((const uint8_t*)page, (const uint8_t*)page + std::max(len, 0));
+  auto store = mStore;
+  const int32_t delay = putDelayMs.load();
+  return Bounded([store, k, bytes, len, delay] {
+    Nap(delay);
+    return store->Put(k, bytes->data(), len);
+  }, &storePutTimeout);
+}
+int TimeBoundPageStore::Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) {
+  *bytesRead = 0;
+  if (room < 0) return APS_EINVAL;
+  struct Landing {
+    std::vector<uint8_t> bytes;
+    int32_t got = 0;
+  };
+  auto land = std::make_shared<Landing>();
+  land->bytes.resize((size_t)std::max(0, std::min(room, std::max(bytesToRead, 0))));
+  auto store = mStore;
+  const int32_t delay = getDelayMs.load();
+  const int rc = Bounded([store, k, pageOffset, bytesToRead, land, delay] {
+    Nap(delay);
+    return store->Get(k, pageOffset, bytesToRead, land->bytes.data(), (int32_t)land->bytes.size(), &land->got);
+  }, &storeGetTimeout);
+  if (rc == APS_OK) {  // only a call that finished in time touches the caller's buffer
+    memcpy(dst, land->bytes.data(), (size_t)land->got);
+    *bytesRead = land->got;
+  }
+  return rc;
+}
+int TimeBoundPageStore::Delete(const Key& k) {
+  auto store = mStore;
+  const int32_t delay = deleteDelayMs.load();
+  return Bounded([store, k, delay] {
+    Nap(delay);
+    return store->Delete(k);
+  }, &storeDeleteTimeout);
+}
+
 LocalCacheManager::LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore> meta, std::unique_ptr<PageStore> store,
                                      ManagerOptions options)
     : mOptions(options), mPageSize(pageSize), mCacheSize(store->GetCacheSize()), mMetaStore(std::move(meta)),
@@ -599,12 +674,14 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
       if (enoughSpace) {
         mMetaStore->AddPage(k, PageMeta{len, lockId});
       } else if (!mMetaStore->Evict(&victim, &victimMeta)) {
+        metrics.putEvictionErrors++;
         return false;  // :265-271
       }
     }
     if (enoughSpace) {  // :274-285
       if (mPageStore->Put(k, page, len) == APS_OK) return true;
       UndoAddPage(k);
+      metrics.putStoreWriteErrors++;
       return false;
     }
   }
@@ -625,6 +702,7 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
   }
   if (mPageStore->Delete(victim) != APS_OK) {  // :318-330 the victim is deleted whatever enoughSpace says
     if (enoughSpace) UndoAddPage(k);
+    metrics.putStoreDeleteErrors++;
     return false;
   }
   if (logEvictions) evicted.push_back(victim);
@@ -636,6 +714,7 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
   }
   if (mPageStore->Put(k, page, len) == APS_OK) return true;
   UndoAddPage(k);  // :339-344
+  metrics.putStoreWriteErrors++;
   return false;
 }
 
@@ -863,6 +942,7 @@ struct apc_manager {
   std::unique_ptr<LocalCacheManager> mgr;
   GpuPageStore* gpu = nullptr;             // single store, owned by mgr
   ShardedGpuPageStore* sharded = nullptr;  // or several, owned by mgr
+  TimeBoundPageStore* bound = nullptr;     // the wrapper around either, when a timeout is configured
 };
 struct apc_evictor {
   std::unique_ptr<CacheEvictor> ev;
@@ -943,12 +1023,32 @@ int apc_manager_create_ex(const apc_options* o, apc_manager** out) {
     m->gpu = gs.get();
     store = std::move(gs);
   }
+  if (o->timeout_ms > 0) {  // PageStore.create wraps the store when a timeout is set (CACHE/PageStore.java:72-75)
+    auto* tb = new TimeBoundPageStore(std::move(store), o->timeout_ms, o->timeout_threads > 0 ? o->timeout_threads : 32);
+    m->bound = tb;
+    store.reset(tb);
+  }
   m->mgr.reset(new LocalCacheManager(o->store.page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))),
                                      std::move(store), mo));
   *out = m.release();
   return APS_OK;
 }
 void apc_wait_async(apc_manager* m) { m->mgr->WaitAsync(); }
+int apc_store_timeout_counters(apc_manager* m, int64_t* out4) {
+  if (!m->bound) return APS_EINVAL;
+  out4[0] = m->bound->storePutTimeout.load();
+  out4[1] = m->bound->storeGetTimeout.load();
+  out4[2] = m->bound->storeDeleteTimeout.load();
+  out4[3] = m->bound->storeThreadsRejected.load();
+  return APS_OK;
+}
+int apc_set_store_delays(apc_manager* m, int32_t put_ms, int32_t get_ms, int32_t delete_ms) {
+  if (!m->bound) return APS_EINVAL;
+  m->bound->putDelayMs = put_ms;
+  m->bound->getDelayMs = get_ms;
+  m->bound->deleteDelayMs = delete_ms;
+  return APS_OK;
+}
 int64_t apc_put_async_rejections(apc_manager* m) { return m->mgr->putAsyncRejectionErrors.load(); }
 int64_t apc_put_not_ready_errors(apc_manager* m) { return m->mgr->putNotReadyErrors.load(); }
 

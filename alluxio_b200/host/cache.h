@@ -190,14 +190,6 @@ class ShardedGpuPageStore : public PageStore {
   uint64_t mCacheBytes = 0;
 };
 
-// Counters of the reference's Client.Cache* metrics that live in this layer
-// (core/common/src/main/java/alluxio/metrics/MetricKey.java:778-995; LocalCacheManager.java:557-627).
-struct CacheMetrics {
-  std::atomic<int64_t> bytesReadCache{0}, bytesRequestedExternal{0}, bytesReadExternal{0}, bytesWrittenCache{0},
-      bytesEvicted{0}, pagesEvicted{0}, getErrors{0}, putErrors{0}, deleteErrors{0}, putEvictionErrors{0},
-      putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0};
-};
-
 // new ThreadPoolExecutor(n, n, 60 s, new SynchronousQueue<>()) of CACHE/LocalCacheManager.java:156-161: a task
 // is accepted only while a worker is free to take it, otherwise the submit is rejected at once.
 class HandOffPool {
@@ -214,6 +206,44 @@ class HandOffPool {
   std::vector<std::thread> mWorkers;
   int mRunning = 0;
   bool mStop = false;
+};
+
+// CACHE/TimeBoundPageStore.java:38-159: every put / get / delete of the wrapped store runs on a fixed pool over
+// a synchronous hand-off and is abandoned after timeoutMs (IOException); a call that finds every thread busy is
+// refused at once (IOException).  The reference cancels the abandoned call by interrupt; a CUDA call cannot be
+// interrupted, so here it runs to its end on private copies of the caller's buffers and its result is dropped.
+// The delays are the test double of CTEST/HangingPageStore.java, shortened from "forever".
+class TimeBoundPageStore : public PageStore {
+ public:
+  TimeBoundPageStore(std::unique_ptr<PageStore> store, int64_t timeoutMs, int threads);
+  int Put(const Key& k, const void* page, int32_t len) override;
+  int Get(const Key& k, int32_t pageOffset, int32_t bytesToRead, void* dst, int32_t room, int32_t* bytesRead) override;
+  int Delete(const Key& k) override;
+  int GetPages(std::vector<std::pair<Key, int64_t>>* out) override { return mStore->GetPages(out); }
+  int64_t GetCacheSize() const override { return mStore->GetCacheSize(); }
+  int GetBatch(uint32_t n, const aps_get_req* r, aps_result* res) override { return mStore->GetBatch(n, r, res); }
+  int PutBatch(uint32_t n, const aps_put_req* r, aps_result* res) override { return mStore->PutBatch(n, r, res); }
+  int DeleteBatch(uint32_t n, const aps_key* k, aps_result* res) override { return mStore->DeleteBatch(n, k, res); }
+  int FillPages(void* d, uint64_t stride, uint32_t len, uint32_t n, const uint64_t* f, const uint64_t* i, uint64_t seed) override {
+    return mStore->FillPages(d, stride, len, n, f, i, seed);
+  }
+  int SetFaults(uint32_t mask) override { return mStore->SetFaults(mask); }
+  int32_t StagingDevice() const override { return mStore->StagingDevice(); }
+  std::atomic<int64_t> storePutTimeout{0}, storeGetTimeout{0}, storeDeleteTimeout{0}, storeThreadsRejected{0};
+  std::atomic<int32_t> putDelayMs{0}, getDelayMs{0}, deleteDelayMs{0};  // HangingPageStore
+ private:
+  int Bounded(std::function<int()> call, std::atomic<int64_t>* timeouts);
+  std::shared_ptr<PageStore> mStore;  // shared with calls that outlive their timeout
+  int64_t mTimeoutMs;
+  std::shared_ptr<HandOffPool> mPool;
+};
+
+// Counters of the reference's Client.Cache* metrics that live in this layer
+// (core/common/src/main/java/alluxio/metrics/MetricKey.java:778-995; LocalCacheManager.java:557-627).
+struct CacheMetrics {
+  std::atomic<int64_t> bytesReadCache{0}, bytesRequestedExternal{0}, bytesReadExternal{0}, bytesWrittenCache{0},
+      bytesEvicted{0}, pagesEvicted{0}, getErrors{0}, putErrors{0}, deleteErrors{0}, putEvictionErrors{0},
+      putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0};
 };
 
 // ---- CACHE/LocalCacheManager.java:75-627 -----------------------------------------------------------------

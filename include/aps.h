@@ -50,6 +50,7 @@ extern "C" {
 #define APS_EFAULT 8     /* injected fault (APS_FAULT_* below) */
 #define APS_ELIMIT 9     /* request larger than the fixed scratch of aps_crc32c_noalloc */
 #define APS_EIO 10       /* a snapshot file could not be read or written */
+#define APS_ETIMEOUT 11  /* host layer: a store call outlived its time bound, or every store thread was busy */
 
 /* PageId on the device: CACHE/PageId.java:23-74 is (String fileId, long pageIndex).  The file id
  * is carried as 128 bits; the host side maps strings to 128 bits without collisions (decimal,

@@ -58,10 +58,19 @@ typedef struct apc_options {
   int32_t async_restore;        /* alluxio.user.client.cache.async.restore.enabled: create returns at once in state
                                  * READ_ONLY (gets served, puts refused, :208-212) and turns READ_WRITE when the
                                  * restore thread is done (:126-133) */
+  int64_t timeout_ms;           /* alluxio.user.client.cache.timeout.duration: > 0 wraps the store in TimeBoundPageStore
+                                 * (CACHE/TimeBoundPageStore.java:38-159; PageStore.create, CACHE/PageStore.java:72-75):
+                                 * a put/get/delete that takes longer, or finds all timeout_threads busy, fails like an
+                                 * IOException.  <= 0 (the reference's default -1): no wrapper. */
+  int32_t timeout_threads;      /* alluxio.user.client.cache.timeout.threads (0 = the default 32) */
 } apc_options;
 APS_API int apc_manager_create_ex(const apc_options* options, apc_manager** out);
 /* Waits for the restore thread and for every queued asynchronous put (tests; orderly shutdown). */
 APS_API void apc_wait_async(apc_manager* m);
+/* Client.CacheStorePutTimeout, ...GetTimeout, ...DeleteTimeout, ...ThreadsRejected; APS_EINVAL without a timeout. */
+APS_API int apc_store_timeout_counters(apc_manager* m, int64_t* out4);
+/* Test double of CTEST/HangingPageStore.java: the wrapped store's put / get / delete first sleep this long. */
+APS_API int apc_set_store_delays(apc_manager* m, int32_t put_ms, int32_t get_ms, int32_t delete_ms);
 APS_API int64_t apc_put_async_rejections(apc_manager* m); /* Client.CachePutAsyncRejectionErrors */
 APS_API int64_t apc_put_not_ready_errors(apc_manager* m); /* Client.CachePutNotReadyErrors */
 

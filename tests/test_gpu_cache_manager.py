@@ -118,6 +118,7 @@ def test_store_faults_leave_no_state():
     assert not m.put(p1, PAGE1)
     assert m.get(p1, PAGE_SIZE, buf) == 0
     assert not m.put(p1, PAGE1)
+    assert m.metrics()["PutStoreWriteErrors"] == 2 and m.metrics()["PutErrors"] == 2
     m.set_store_faulty()
     assert m.put(p1, PAGE1)
     assert m.get(p1, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1
@@ -126,6 +127,7 @@ def test_store_faults_leave_no_state():
     m.set_store_faulty(delete=True)
     assert m.put(p1, PAGE1)
     assert not m.put(p2, PAGE2)
+    assert m.metrics()["PutStoreDeleteErrors"] == 1 and m.metrics()["PagesEvicted"] == 0
     m.set_store_faulty()
     assert m.put(p1, PAGE1)
     assert m.get(p1, PAGE_SIZE, buf) == PAGE_SIZE and bytes(buf) == PAGE1

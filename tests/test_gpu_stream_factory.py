@@ -186,3 +186,56 @@ def test_factory_is_a_singleton_and_null_while_creating():
     fresh = CacheManagerFactory.get(PS, 256 * PS)
     assert fresh.pages() == 0
     CacheManagerFactory.clear()
+
+
+def test_time_bound_page_store():
+    """CTEST/TimeBoundPageStoreTest.java: put / get / delete pass through; a call that outlives the bound fails like
+    an IOException and is counted; more concurrent calls than store threads are refused."""
+    m = _manager(timeout_ms=150, timeout_threads=2)
+    p = PID("0L", 0)
+    page, buf = increasing(PS), bytearray(PS)
+    assert m.put(p, page)                                   # put / get / delete
+    assert m.get(p, PS, buf) == PS and bytes(buf) == page
+    assert m.delete(p) and m.get(p, PS, buf) == 0
+    assert m.store_timeouts() == {"put": 0, "get": 0, "delete": 0, "rejected": 0}
+    m.set_store_delays(put_ms=600)                          # putTimeout: the manager sees a failed store write
+    assert not m.put(p, page)
+    assert m.store_timeouts()["put"] == 1 and m.metrics()["PutStoreWriteErrors"] == 1 and m.pages() == 0
+    m.set_store_delays()
+    import time
+    time.sleep(0.7)                                         # let the abandoned put finish inside the store
+    q = PID("0L", 1)
+    assert m.put(q, page)
+    m.set_store_delays(get_ms=600)                          # getTimeout: -1, and the page is dropped from the meta store
+    assert m.get(q, PS, buf) == -1
+    assert m.store_timeouts()["get"] == 1 and m.pages() == 0
+    m.set_store_delays()
+    time.sleep(0.7)
+    r = PID("0L", 2)
+    assert m.put(r, page)
+    m.set_store_delays(delete_ms=600)                       # deleteTimeout
+    assert not m.delete(r)
+    assert m.store_timeouts()["delete"] == 1
+    m.set_store_delays()
+    time.sleep(0.7)
+    # concurrentPutWithSmallThreadPool: two store threads, six callers at once, each call slower than the bound
+    m.set_store_delays(put_ms=400)
+    results = []
+    barrier = threading.Barrier(6)
+
+    def worker(k):
+        barrier.wait()
+        results.append(m.put(PID("7", k), page))
+
+    ts = [threading.Thread(target=worker, args=(k,)) for k in range(6)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    t = m.store_timeouts()
+    assert not any(results) and t["rejected"] == 4 and t["put"] == 1 + 2
+    m.set_store_delays()
+    time.sleep(0.6)
+    m.close()
+    plain = _manager()                                      # no timeout configured: no wrapper, as with the default -1
+    with pytest.raises(Exception):
+        plain.store_timeouts()
+    plain.close()
