@@ -220,6 +220,7 @@ struct aps_store {
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
   bool use_steal = true;  // APS_NO_STEAL=1 turns intra-CTA work stealing off
+  bool use_table_image = true;  // APS_NO_TABLE_IMAGE=1: build the shared-memory CRC tables with plain loads
   std::atomic<uint64_t> launches{0};
   // optional timing of the copy kernel (aps_profile_*): event pairs recorded around each launch
   bool prof_on = false;
@@ -260,7 +261,7 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.acc = s->d_acc;
   a.done = s->d_done;
   a.tables = s->dc->d_tables;
-  a.table_image = getenv("APS_NO_TABLE_IMAGE") ? nullptr : s->dc->d_table_image;
+  a.table_image = s->use_table_image ? s->dc->d_table_image : nullptr;
   a.rowshift = s->d_rowshift;
   a.error_flag = s->d_error;
   a.timeline = s->d_timeline;
@@ -536,6 +537,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   s->dc = dc;
   s->use_pdl = getenv("APS_NO_PDL") == nullptr;
   s->use_steal = getenv("APS_NO_STEAL") == nullptr;
+  s->use_table_image = getenv("APS_NO_TABLE_IMAGE") == nullptr;
   uint64_t slots = cfg->slab_slots;
   if (slots == 0) {
     uint64_t base = (cfg->cache_bytes + cfg->page_size - 1) / cfg->page_size;
@@ -887,7 +889,7 @@ int aps_iterate(aps_store* s, aps_iter_cb cb, void* user) {
 int aps_compact(aps_store* s) {
   int rc = check_open(s);
   if (rc) return rc;
-  if (s->n_shards > 1) return APS_EINVAL;  // peers hold pointers into the current table
+  if (s->n_shards > 0) return APS_EINVAL;  // attached shard tables (own copy included) point into the current table
   DeviceGuard g(s->cfg.device);
   std::lock_guard<std::mutex> lk(s->mu);
   Entry* fresh = nullptr;

@@ -149,7 +149,12 @@ APS_API int aps_delete_batch(aps_store* s, uint32_t n, const aps_key* keys, aps_
 
 /* Device-resident forms: d_reqs / d_res / d_keys are DEVICE arrays that are already in HBM.
  * Fully asynchronous on `stream`: nothing is copied to or from the host and the call does not
- * wait.  This is what the kernel-only benchmark times. */
+ * wait.  This is what the kernel-only benchmark times.
+ * All calls on one store share that store's scratch (job list, CRC accumulators, staging): two of
+ * them must never RUN on the GPU at the same time.  Host forms wait before they return and are
+ * serialised by the store's mutex; device forms are ordered by their stream, so put them all on one
+ * stream (or order the streams with events), and do not mix them with host forms from another
+ * thread.  Use one store per thread, or one stream per store, when in doubt. */
 APS_API int aps_get_batch_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream);
 APS_API int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_result* d_res, aps_stream stream);
 APS_API int aps_delete_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, aps_result* d_res, aps_stream stream);
