@@ -158,9 +158,14 @@ __device__ __forceinline__ Claim claim_rows(unsigned long long* range, uint32_t 
 // lane per row).  Software pipelined: while the rows of one group are stored and folded, the loads of
 // the next claimed group are already in flight.  Returns the zero-init CRC of the rows it processed
 // (same value in every lane, when kCrc); *row_end receives the first row it did NOT process.
-template <bool kCrc, int G>
+struct NoGate {
+  __device__ __forceinline__ void operator()() const {}
+};
+// `gate` runs once the first loads are in flight and before anything is stored: the copy kernel uses it to
+// wait for the previous kernel in the stream (programmatic dependent launch) as late as it safely can.
+template <bool kCrc, int G, typename Gate = NoGate>
 __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst, unsigned long long* range, uint32_t row_lo,
-                                                uint32_t lane, uint32_t* row_end, uint32_t tables_bar) {
+                                                uint32_t lane, uint32_t* row_end, uint32_t tables_bar, Gate gate = Gate()) {
   const uint4* s = reinterpret_cast<const uint4*>(src) + lane;  // src/dst point at row 0 of the job
   uint4* d = reinterpret_cast<uint4*>(dst) + lane;
   const bool store = dst != nullptr;
@@ -189,6 +194,7 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   load(A, ca);
   // the first loads are in flight; only now make sure the CRC tables have landed in shared memory
   if (kCrc && tables_bar) mbar_wait(tables_bar, 0);
+  gate();
   while (ca.cnt) {
     Claim cb = claim_rows<G>(range, lane);
     load(B, cb);
@@ -249,6 +255,9 @@ struct CopyArgs {
   uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
   const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
   uint32_t n_slow;           // how many SMs that is
+  int early;                 // kGet, non-zero: requests, table and slab are known not to change under the previous kernel
+                             // in the stream, so they may be read before waiting for it (see the kernel's dependency
+                             // gate); early - 1 = rows to prefetch into L2 while waiting
 };
 
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -287,7 +296,14 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   // Programmatic dependent launch: let the next kernel in the stream be scheduled as soon as SMs free
   // up, and wait here until everything launched before this kernel has completed and is visible.
   asm volatile("griddepcontrol.launch_dependents;");
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // Dependency gate.  Normally a kernel waits right here.  When the host knows that the previous kernel in
+  // the stream was another get of this store (a.early), nothing this kernel READS can change under it -- the
+  // requests, the table and the slab -- so every warp resolves its first page and puts its first loads in
+  // flight before it waits: the three dependent memory round trips of a task's start-up (request, bucket,
+  // first rows) then overlap the previous kernel's tail instead of following it.  Everything this kernel
+  // WRITES (pages, results, scratch, the rank counters) stays behind the gate.
+  bool dep_ok = !(kGet && a.early);
+  if (dep_ok) asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t n_items = a.n_jobs * a.tasks_per_job;
   // Task assignment.  n_items / grid tasks per CTA are fixed by blockIdx, so warps can start at once.  The
   // n_items % grid surplus tasks go to the CTAs with the lowest RANK: CTAs on fast SMs count up from 0,
@@ -297,12 +313,28 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   const uint32_t base_cnt = n_items / gridDim.x, extra = n_items % gridDim.x;
   const uint32_t surplus_warp = base_cnt % nwarps;
   uint32_t rank_reg = 0xFFFFFFFFu;
-  if (warp == surplus_warp && lane == 0) {
-    uint32_t smid;
-    asm("mov.u32 %0, %%smid;" : "=r"(smid));
-    const bool slow = a.sm_slow[smid & 255u] != 0;
-    rank_reg = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
-  }
+  auto ask_rank = [&]() {  // the counters are re-armed by the previous launch's last CTA: only behind the gate
+    if (warp == surplus_warp && lane == 0) {
+      uint32_t smid;
+      asm("mov.u32 %0, %%smid;" : "=r"(smid));
+      const bool slow = a.sm_slow[smid & 255u] != 0;
+      rank_reg = slow ? (gridDim.x - 1u - atomicAdd(&a.sched[1], 1u)) : atomicAdd(&a.sched[0], 1u);
+    }
+  };
+  const uint8_t* pf_ptr = nullptr;  // rows this warp will load right after the gate ...
+  uint32_t pf_lines = 0;            // ... as a count of 128-byte lines
+  auto gate = [&]() {
+    if (!dep_ok) {
+      // while this warp waits for its predecessor, pull its next rows into L2: DRAM is under-used during the
+      // previous kernel's tail, and the loads that follow the gate then hit L2.  (Read-ahead of the same kind
+      // INSIDE the streaming loop was measured too and only hurts: 0.80 at 32 rows ahead.)
+      for (uint32_t l = lane; l < pf_lines; l += 32u) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_ptr + (size_t)l * 128u));
+      asm volatile("griddepcontrol.wait;" ::: "memory");
+      dep_ok = true;
+      ask_rank();
+    }
+  };
+  if (dep_ok) ask_rank();
   if (lane == 0) s_range[warp] = 0;
   __shared__ __align__(8) unsigned long long s_tables_bar;
   uint32_t tables_bar = 0;
@@ -374,12 +406,15 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     bool publish = false;
     uint32_t item = 0xFFFFFFFFu;
     bool last_item = false;
+    bool report = false;  // kGet, task 0 of a page that needs no finisher: its result is written behind the gate
+    int32_t report_status = 0;
     if (local < base_cnt) {
       item = blockIdx.x * base_cnt + local;
       local += nwarps;
       last_item = local >= base_cnt && !surplus_pending;
     } else if (surplus_pending) {
       surplus_pending = false;
+      gate();
       const uint32_t rank = __shfl_sync(0xFFFFFFFFu, rank_reg, 0);
       if (rank < extra) {
         item = base_cnt * gridDim.x + rank;
@@ -418,8 +453,10 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           atomicAdd(&a.table.counters[kCtrLookups], 1ull);
           atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
           if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
-          if (!kCrc || j.n == 0) a.res[job] = aps_result{status, 0};  // otherwise the finisher reports
+          report = !kCrc || j.n == 0;  // otherwise the finisher reports
+          report_status = status;
         }
+        report = __shfl_sync(0xFFFFFFFFu, (int)report, 0) != 0;
       } else {
         j = a.jobs[job];
       }
@@ -427,6 +464,10 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       row_lo = min(rows_full, c * a.rows_per_task);
       row_hi = min(rows_full, row_lo + a.rows_per_task);
       tail_mine = c == 0 && (j.n % kRowBytes) != 0;
+      if (report) {
+        gate();
+        if (lane == 0) a.res[job] = aps_result{report_status, 0};
+      }
       if (row_lo >= row_hi && !tail_mine) continue;
       publish = last_item;  // only a warp's final task is open to stealing (its descriptor stays valid)
     } else {
@@ -485,16 +526,23 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         }
         __syncwarp();
         uint32_t row_end = row_lo;
-        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end, tables_bar);
+        if (!dep_ok) {
+          const uint32_t ahead = row_hi - row_lo > (uint32_t)G ? min(row_hi - row_lo - (uint32_t)G, (uint32_t)a.early - 1u) : 0u;
+          pf_ptr = j.src + (size_t)(row_lo + G) * kRowBytes;
+          pf_lines = ahead * (kRowBytes / 128u);
+        }
+        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end, tables_bar, gate);
         rows_done = row_end - row_lo;
         end_byte = row_end * kRowBytes;
       } else {
+        gate();
         const uint32_t nb = (row_hi - row_lo) * kRowBytes;
         crc = warp_bytes<kCrc>(j.src + (size_t)row_lo * kRowBytes, j.dst ? j.dst + (size_t)row_lo * kRowBytes : nullptr, nb, lane);
         rows_done = row_hi - row_lo;
         end_byte = row_hi * kRowBytes;
       }
     }
+    gate();  // a task made of a sub-row tail only has not passed it yet
     if (!kCrc) {
       if (tail_mine) {
         const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
@@ -535,6 +583,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       a.done[job] = 0;
     }
   }
+  gate();  // a warp that found nothing to do arrives here without having waited
   if (warp == surplus_warp && lane == 0) {
     // this CTA holds its rank (the answer was consumed above or is awaited here); the last CTA to say so
     // re-arms the counters for the next launch

@@ -203,6 +203,9 @@ def run_ours(args):
                           table_capacity=0, max_batch=BATCH,
                           flags=0 if os.environ.get("APS_BENCH_NOCRC") == "1" else capi.APS_FLAG_CRC)
     with_crc = cfg.flags != 0
+    # the request pool below is written once, long before the timed steps: the promise APS_FLAG_STABLE_REQS asks for
+    if os.environ.get("APS_BENCH_NO_EARLY") != "1":
+        cfg.flags |= capi.APS_FLAG_STABLE_REQS
     h = C.c_void_p()
     capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "aps_open")
     # one explicit non-default stream for everything: torch copies, our kernels and the timing events
@@ -500,7 +503,7 @@ def run_ours(args):
     # ---- the same three paths with the checksum off (BASELINE configs[1]: "each with CRC off/on"): a second
     # store opened without APS_FLAG_CRC over the same resident set, after the first one released its HBM
     if world == 1 and with_crc and not quick:
-        cfg.flags = 0
+        cfg.flags = cfg.flags & capi.APS_FLAG_STABLE_REQS
         h2 = C.c_void_p()
         capi.check(L.aps_open(C.byref(cfg), C.byref(h2)), "aps_open (no CRC)")
         populate(h2)

@@ -63,6 +63,11 @@ typedef struct aps_key {
 
 #define APS_FLAG_CRC 1u        /* compute CRC32C inside every copy, record it at put, verify whole-page gets */
 #define APS_FLAG_TMA_COPY 2u   /* when CRC is off, move pages with bulk-async (TMA) copies instead of LDG/STG */
+#define APS_FLAG_STABLE_REQS 4u /* a promise by the caller of the device forms: a request array is complete in HBM before
+                                 * the call that uses it is enqueued (it is not produced by earlier work on the same
+                                 * stream).  Back-to-back gets on one stream then overlap: a get resolves its pages and
+                                 * starts loading while the previous get is still finishing, and only waits for it
+                                 * before its first store.  Without the flag every kernel waits before it reads anything. */
 
 /* Replaces LocalPageStoreOptions / PageStoreOptions (CACHE/store/PageStoreOptions.java:23-182). */
 typedef struct aps_config {
