@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(HERE, "libaps.so")
 (APS_OK, APS_ENOTFOUND, APS_EINVAL, APS_ENOSPC, APS_ECUDA, APS_ECORRUPT, APS_ECLOSED, APS_ENOMEM, APS_EFAULT,
  APS_ELIMIT, APS_EIO, APS_ETIMEOUT) = range(12)
 APS_NOALLOC_MAX_RANGES, APS_NOALLOC_MAX_LEN = 1024, 4 << 20
-APS_FLAG_CRC, APS_FLAG_TMA_COPY, APS_FLAG_STABLE_REQS = 1, 2, 4
+APS_FLAG_CRC, APS_FLAG_TMA_COPY, APS_FLAG_STABLE_REQS, APS_FLAG_DEVICE_CLOCK = 1, 2, 4, 8
 APS_FAULT_PUT, APS_FAULT_DELETE = 1, 2
 
 
@@ -45,7 +45,8 @@ class aps_shard_handle(C.Structure):
 
 class aps_stats_t(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("pages", "bytes", "slots_free", "table_capacity", "tombstones", "lookups",
-                                           "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches", "slow_sms")]
+                                           "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches", "slow_sms",
+                                           "clock_evictions")]
 
 
 ITER_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.POINTER(aps_key), C.c_uint32)
@@ -87,6 +88,7 @@ SIGNATURES = {
     "aps_compact": (C.c_int, [_vp]),
     "aps_snapshot_save": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64)]),
     "aps_snapshot_load": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64), C.POINTER(_u64)]),
+    "aps_clock_evict_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),
     "aps_profile_begin": (C.c_int, [_vp, _u32]),

@@ -212,6 +212,7 @@ struct aps_store {
   uint32_t n_shards = 0, my_shard = 0;
   std::vector<void*> ipc_ptrs;  // peer allocations opened through CUDA IPC (closed in aps_close)
   uint32_t* d_done = nullptr;
+  uint32_t* d_clock = nullptr;  // APS_FLAG_DEVICE_CLOCK: {hand, cursor, need, found, CTAs finished}
   int* d_error = nullptr;
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
   aps_result* d_res = nullptr;
@@ -343,6 +344,18 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
 
 inline dim3 tile_grid(uint32_t n) { return dim3((n * 8 + 255) / 256); }
 
+// CLOCK sweep: evicts `fixed` pages, or (fixed == 0) as many as `incoming` new pages lack free slots.
+int clock_evict(aps_store* s, uint32_t incoming, uint32_t fixed, aps_key* d_victims, uint32_t victims_cap, cudaStream_t st) {
+  clock_need_kernel<<<1, 1, 0, st>>>(s->table, incoming, fixed, s->d_clock);
+  // never more windows in flight than half a turn of the hand, so that a page keeps its second chance
+  const unsigned grid = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(s->slots / 512, (uint64_t)s->dc->num_sms * 8));
+  clock_evict_kernel<<<grid, 256, 0, st>>>(s->table, (uint32_t)s->slots, s->d_clock, d_victims, victims_cap);
+  count_launch(s, 2);
+  CUDA_TRY(cudaGetLastError());
+  s->last_was_get = false;
+  return APS_OK;
+}
+
 int check_open(aps_store* s) {
   if (!s) return APS_EINVAL;
   if (s->closed) return APS_ECLOSED;
@@ -394,6 +407,9 @@ void free_store(aps_store* s) {
   for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
   s->ipc_ptrs.clear();
   cudaFree(s->d_done);
+  cudaFree(s->d_clock);
+  cudaFree(s->table.slot_ref);
+  cudaFree(s->table.slot_entry);
   cudaFree(s->d_error);
   cudaFree(s->d_reqs);
   cudaFree(s->d_res);
@@ -602,6 +618,14 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   }
   OPEN_TRY(cudaMalloc(&s->d_done, (uint64_t)mb * sizeof(uint32_t)));
   OPEN_TRY(cudaMalloc(&s->d_error, sizeof(int)));
+  if (cfg->flags & APS_FLAG_DEVICE_CLOCK) {
+    OPEN_TRY(cudaMalloc(&s->table.slot_ref, slots));
+    OPEN_TRY(cudaMalloc(&s->table.slot_entry, slots * sizeof(uint64_t)));
+    OPEN_TRY(cudaMalloc(&s->d_clock, 8 * sizeof(uint32_t)));
+    OPEN_TRY(cudaMemset(s->table.slot_ref, 0, slots));
+    OPEN_TRY(cudaMemset(s->table.slot_entry, 0xFF, slots * sizeof(uint64_t)));
+    OPEN_TRY(cudaMemset(s->d_clock, 0, 8 * sizeof(uint32_t)));
+  }
   OPEN_TRY(cudaMalloc(&s->d_reqs, (uint64_t)mb * sizeof(aps_get_req)));
   OPEN_TRY(cudaMalloc(&s->d_res, (uint64_t)mb * sizeof(aps_result)));
   OPEN_TRY(cudaHostAlloc(&s->h_stage, (uint64_t)mb * (sizeof(aps_get_req) + sizeof(aps_result)), cudaHostAllocDefault));
@@ -677,6 +701,10 @@ int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_r
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   s->last_was_get = false;
+  if (s->d_clock) {  // make room on the device: evict as many pages as this batch lacks free slots
+    rc = clock_evict(s, n, 0, nullptr, 0, st);
+    if (rc) return rc;
+  }
   put_resolve_kernel<<<tile_grid(n), kK1Threads, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
@@ -935,6 +963,19 @@ int aps_compact(aps_store* s) {
   return APS_OK;
 }
 
+int aps_clock_evict_dev(aps_store* s, uint32_t n, aps_key* d_victims, uint32_t* d_count, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!s->d_clock) return APS_EINVAL;  // the store was opened without APS_FLAG_DEVICE_CLOCK
+  if (n == 0) return APS_OK;
+  DeviceGuard g(s->cfg.device);
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  rc = clock_evict(s, 0, n, d_victims, n, st);
+  if (rc) return rc;
+  if (d_count) CUDA_TRY(cudaMemcpyAsync(d_count, s->d_clock + 5, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+  return APS_OK;
+}
+
 int aps_stats(aps_store* s, aps_stats_t* out) {
   int rc = check_open(s);
   if (rc) return rc;
@@ -957,6 +998,7 @@ int aps_stats(aps_store* s, aps_stats_t* out) {
   out->crc_mismatches = c[kCtrCrcMismatch];
   out->kernel_launches = s->launches.load();
   out->slow_sms = (uint64_t)s->dc->n_slow;
+  out->clock_evictions = c[kCtrEvicted];
   return APS_OK;
 }
 

@@ -44,7 +44,7 @@ __host__ __device__ __forceinline__ uint32_t shard_of(const aps_key& k, uint32_t
   return (uint32_t)((hash_key(k) >> 32) % n_shards);
 }
 
-enum Counter { kCtrPages = 0, kCtrBytes, kCtrTombs, kCtrLookups, kCtrProbes, kCtrBytesCopied, kCtrCrcMismatch, kNumCounters };
+enum Counter { kCtrPages = 0, kCtrBytes, kCtrTombs, kCtrLookups, kCtrProbes, kCtrBytesCopied, kCtrCrcMismatch, kCtrEvicted, kNumCounters };
 
 struct Table {
   Entry* entries;
@@ -55,7 +55,11 @@ struct Table {
   unsigned long long* counters;
   uint8_t* slab;
   uint32_t page_size;
+  // opt-in device-side CLOCK eviction (APS_FLAG_DEVICE_CLOCK); both null otherwise
+  uint8_t* slot_ref;     // per slab slot: 1 = referenced since the hand last passed
+  uint64_t* slot_entry;  // per slab slot: index of the table entry that owns it, ~0 = free
 };
+constexpr uint64_t kNoEntry = ~0ull;
 
 __device__ __forceinline__ void load_entry(const Entry* e, uint64_t& k0, uint64_t& k1, uint64_t& k2, uint64_t& meta) {
   // .cg: always observe L2, entries are written by other SMs in earlier (or the same) launches

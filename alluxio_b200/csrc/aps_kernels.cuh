@@ -448,6 +448,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;  // which shard's slot_crc to check
           j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
           status = (int32_t)j.n;
+          if (c == 0 && lane == 0 && tb.slot_ref) tb.slot_ref[j.slot] = 1;  // CLOCK: referenced (a store that commutes)
         }
         if (c == 0 && lane == 0) {
           atomicAdd(&a.table.counters[kCtrLookups], 1ull);
@@ -922,6 +923,7 @@ __global__ void __launch_bounds__(kK1Threads) put_resolve_kernel(Table t, const 
       slot = meta_slot(c.was);
       if (sub == 0) {
         t.entries[c.entry_idx].meta = meta_make(slot, rq.len);
+        if (t.slot_ref) t.slot_ref[slot] = 1;
         acct_add(acct, kCtrBytes, (unsigned long long)rq.len - (unsigned long long)meta_len(c.was));
       }
     } else if (!err) {
@@ -932,6 +934,10 @@ __global__ void __launch_bounds__(kK1Threads) put_resolve_kernel(Table t, const 
           e->k0 = rq.key.file_hi; e->k1 = rq.key.file_lo; e->k2 = rq.key.page_index;
           __threadfence();
           e->meta = meta_make(slot, rq.len);
+          if (t.slot_entry) {
+            t.slot_entry[slot] = c.entry_idx;
+            t.slot_ref[slot] = 1;
+          }
           acct_add(acct, kCtrPages, 1ull);
           acct_add(acct, kCtrBytes, (unsigned long long)rq.len);
           if (c.was == kMetaTomb) acct_add(acct, kCtrTombs, ~0ull);
@@ -980,6 +986,7 @@ __global__ void __launch_bounds__(kK1Threads) delete_kernel(Table t, const aps_k
   }
   block_return_slots(acct, t);
   if (live && sub == 0) {
+    if (rank >= 0 && t.slot_entry) t.slot_entry[meta_slot(pr.meta)] = kNoEntry;
     if (rank >= 0) t.free_slots[acct.base + rank] = meta_slot(pr.meta);
     res[i] = aps_result{pr.meta ? 0 : -APS_ENOTFOUND, 0};
   }
@@ -1040,6 +1047,7 @@ __global__ void rehash_kernel(Table t, const Entry* old, uint64_t n_old) {
           e->k0 = k0; e->k1 = k1; e->k2 = k2;
           __threadfence();
           e->meta = meta;
+          if (t.slot_entry) t.slot_entry[meta_slot(meta)] = cand;
         }
         return;
       }
@@ -1053,6 +1061,78 @@ __global__ void rehash_kernel(Table t, const Entry* old, uint64_t n_old) {
 __global__ void init_free_slots_kernel(uint32_t* free_slots, uint64_t n) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) free_slots[i] = (uint32_t)(n - 1 - i);  // slot 0 is handed out first
+}
+
+// ------------------------------------------------------------------------------------------------
+// Opt-in eviction on the device: CLOCK, the classic one-bit approximation of LRU.
+// A get or put sets the slot's reference bit; the hand sweeps the slots in index order, clears set
+// bits and evicts pages whose bit is already clear.  It cannot reproduce the reference's exact LRU /
+// LFU victim order, so it is never used for the parity runs -- it is for caches whose accesses stay
+// on the GPU, where a host-side policy (3.5 M accesses/s) would be the bottleneck.
+//   ctl[0] = hand (slot index)  ctl[1] = cursor (slots handed out to CTAs in this sweep)
+//   ctl[2] = need               ctl[3] = candidates seen  ctl[4] = CTAs finished   ctl[5] = evicted (result)
+// ------------------------------------------------------------------------------------------------
+__global__ void clock_need_kernel(Table t, uint32_t n_incoming, uint32_t n_fixed, uint32_t* ctl) {
+  const int free_now = max(*t.free_top, 0);
+  ctl[2] = n_fixed ? n_fixed : ((int)n_incoming > free_now ? n_incoming - (uint32_t)free_now : 0u);
+  ctl[3] = 0;
+  ctl[1] = 0;
+  ctl[4] = 0;
+}
+
+__global__ void __launch_bounds__(256) clock_evict_kernel(Table t, uint32_t n_slots, uint32_t* ctl, aps_key* victims,
+                                                          uint32_t victims_cap) {
+  __shared__ uint32_t s_base;
+  const uint32_t need = ctl[2], hand = ctl[0];
+  if (need) {
+    for (;;) {
+      if (threadIdx.x == 0) {
+        // stop handing out windows once enough victims exist, or after two full turns of the hand (the
+        // first turn clears every bit, so the second finds a victim in every occupied slot)
+        s_base = (*(volatile uint32_t*)&ctl[3] >= need) ? 0xFFFFFFFFu : atomicAdd(&ctl[1], 256u);
+      }
+      __syncthreads();
+      const uint32_t base = s_base;
+      __syncthreads();
+      if (base == 0xFFFFFFFFu || base >= 2u * n_slots + 256u) break;
+      const uint32_t slot = (uint32_t)(((uint64_t)hand + base + threadIdx.x) % n_slots);
+      const uint64_t e = t.slot_entry[slot];
+      if (e == kNoEntry) continue;
+      if (t.slot_ref[slot]) {
+        t.slot_ref[slot] = 0;
+        continue;
+      }
+      // On a small store the windows of the second turn can overlap those of the first that are still in
+      // flight: whoever swaps the owner out first evicts the page, the other sees a free slot.
+      if (atomicCAS((unsigned long long*)&t.slot_entry[slot], (unsigned long long)e, (unsigned long long)kNoEntry) != e) continue;
+      const uint32_t idx = atomicAdd(&ctl[3], 1u);
+      if (idx >= need) {  // enough already: this page stays (its bit is clear, it goes first next time)
+        t.slot_entry[slot] = e;
+        continue;
+      }
+      Entry* ent = t.entries + e;
+      const uint64_t meta = ent->meta;
+      if (victims && idx < victims_cap) victims[idx] = aps_key{ent->k0, ent->k1, ent->k2};
+      bool has_empty = false;
+      const Entry* bucket = t.entries + (e & ~(uint64_t)(kBucketEntries - 1));
+      for (uint32_t q = 0; q < kBucketEntries; ++q) has_empty |= __ldcg(&bucket[q].meta) == kMetaEmpty;
+      ent->meta = has_empty ? kMetaEmpty : kMetaTomb;  // same rule as tile_erase
+      t.free_slots[atomicAdd(t.free_top, 1)] = slot;
+      atomicAdd(&t.counters[kCtrPages], ~0ull);
+      atomicAdd(&t.counters[kCtrBytes], 0ull - (unsigned long long)meta_len(meta));
+      atomicAdd(&t.counters[kCtrEvicted], 1ull);
+      if (!has_empty) atomicAdd(&t.counters[kCtrTombs], 1ull);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&ctl[4], 1u) == gridDim.x - 1u) {  // last CTA out: the hand moves past what was swept
+      const uint32_t swept = min(ctl[1], 2u * n_slots);
+      ctl[0] = (uint32_t)(((uint64_t)hand + swept) % n_slots);
+      ctl[5] = min(ctl[3], need);  // pages actually evicted (candidates beyond `need` were left alone)
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -69,6 +69,14 @@ typedef struct aps_key {
                                  * starts loading while the previous get is still finishing, and only waits for it
                                  * before its first store.  Without the flag every kernel waits before it reads anything. */
 
+#define APS_FLAG_DEVICE_CLOCK 8u /* opt-in, SURVEY.md 8f-3: the store evicts by itself.  Every get and put sets a
+                                 * reference bit on the page's slot; a put batch that finds fewer free slots than it has
+                                 * new pages first runs a CLOCK sweep on the device (clear set bits, evict pages whose
+                                 * bit is clear) for the difference.  Capacity is then counted in slab slots, not bytes,
+                                 * and the victim order is CLOCK's, NOT the reference's LRU/LFU (CACHE/evictor/): never
+                                 * combine it with a host-side LocalCacheManager, whose meta store would go stale.
+                                 * For caches whose accesses stay on the GPU. */
+
 /* Replaces LocalPageStoreOptions / PageStoreOptions (CACHE/store/PageStoreOptions.java:23-182). */
 typedef struct aps_config {
   int32_t device;           /* CUDA ordinal */
@@ -230,6 +238,11 @@ APS_API int aps_crc32c_batch_dev(aps_store* s, uint32_t n, const void* const* d_
 APS_API int aps_crc32c_noalloc(int32_t device, uint32_t n, const void* const* d_data, const uint32_t* d_len,
                                uint32_t max_len, uint32_t* d_crc, aps_stream stream);
 
+/* Explicit CLOCK sweep on a store opened with APS_FLAG_DEVICE_CLOCK: evicts n pages (fewer if the store holds
+ * fewer).  d_victims (optional, DEVICE array of n keys) receives their ids, d_count (optional, DEVICE) how many.
+ * No counterpart in the reference, whose eviction is decided by CacheEvictor on the host. */
+APS_API int aps_clock_evict_dev(aps_store* s, uint32_t n, aps_key* d_victims, uint32_t* d_count, aps_stream stream);
+
 /* ---- warm restart --------------------------------------------------------------
  * LocalPageStore's pages are files, so they survive a restart and LocalCacheManager.restore finds them
  * through getPages() (CACHE/LocalCacheManager.java:466-509; CACHE/store/LocalPageStore.java:193-199).
@@ -274,6 +287,7 @@ typedef struct aps_stats_t {
   uint64_t crc_mismatches;  /* whole-page gets whose CRC differed from the one recorded at put */
   uint64_t kernel_launches; /* kernels this store has launched */
   uint64_t slow_sms;        /* SMs the open-time calibration classed as slow (they get one task less per launch) */
+  uint64_t clock_evictions; /* pages evicted by the device-side CLOCK sweep (APS_FLAG_DEVICE_CLOCK) */
 } aps_stats_t;
 APS_API int aps_stats(aps_store* s, aps_stats_t* out);
 
