@@ -283,9 +283,11 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   // the same stream -- then the table and the slab cannot change under it -- and only when the caller has
   // promised that request arrays are complete before the call is enqueued (APS_FLAG_STABLE_REQS).
   const bool is_get = d_get_reqs != nullptr;
-  a.early = (is_get && !sharded && (s->cfg.flags & APS_FLAG_STABLE_REQS) && s->last_was_get && s->last_stream == st &&
-             s->use_pdl && !s->d_timeline) ? 1 + (int)s->prefetch_rows : 0;
-  s->last_was_get = is_get && !sharded;
+  // (A sharded get also reads its peers' tables and slabs.  Those are not ordered against this stream in any case --
+  // keeping puts on one GPU apart from gets on another is the caller's job -- so reading them early changes nothing.)
+  a.early = (is_get && (s->cfg.flags & APS_FLAG_STABLE_REQS) && s->last_was_get && s->last_stream == st && s->use_pdl &&
+             !s->d_timeline) ? 1 + (sharded ? 0 : (int)s->prefetch_rows) : 0;  // no L2 prefetch of peer memory: measured 18x slower
+  s->last_was_get = is_get;
   s->last_stream = st;
   if (use_tma_variant() || s->use_tma) {
     // bulk-async form: chunks of 16 rows, a contiguous weighted slice of the chunk space per CTA
