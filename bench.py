@@ -601,7 +601,8 @@ def run_ours(args):
                      "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
         "e2e": {"value": round(world * e2e_steps * step_bytes / e2e_s / 1e9, 2), "unit": UNIT,
                 "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
-                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound)",
+                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound; gathered in HBM by the fused "
+                        "kernel, then moved by the copy engine)",
                 "pcie_memcpy_d2h_GBps": None if pcie_gbps is None else round(pcie_gbps, 2),
                 "frac_of_pcie_memcpy": None if pcie_gbps is None else round(e2e_steps * step_bytes / e2e_s / 1e9 / pcie_gbps, 4)},
         "gpu_launches": int(launches), "clocks": clocks, "aux": aux,

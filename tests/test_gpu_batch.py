@@ -279,3 +279,58 @@ def test_crc_disabled_store_copies_identically():
     for i in range(8):
         assert np.array_equal(host[i * ps:i * ps + lens[i]], data[i * ps:i * ps + lens[i]])
     store.close()
+
+
+def test_batched_get_into_pinned_host_memory_staged_and_direct(monkeypatch):
+    """Large host-destination batches go through an HBM staging area and the copy engine; small ones, or with
+    APS_NO_D2H_STAGE=1, are stored by the kernel directly.  Same bytes, same results, nothing written past len."""
+    import ctypes as C
+    import os
+    import torch
+    import gpu_util as gu
+    from alluxio_b200 import capi
+    from oracle import binding as orc
+    L = capi.lib()
+    page, n = 256 * 1024, 48                                    # 12 MiB per batch: above the staging threshold
+    outs = []
+    for direct in (False, True):
+        if direct:
+            monkeypatch.setenv("APS_NO_D2H_STAGE", "1")
+        else:
+            monkeypatch.delenv("APS_NO_D2H_STAGE", raising=False)
+        cfg = capi.aps_config(device=0, page_size=page, cache_bytes=n * page, slab_slots=n + 8, table_capacity=0,
+                              max_batch=n, flags=capi.APS_FLAG_CRC)
+        h = C.c_void_p()
+        capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "open")
+        ids = np.arange(n, dtype=np.uint64)
+        lens = np.where(ids % 5 == 2, 1000 + 7 * ids, page).astype(np.uint32)   # some short pages
+        stage = torch.empty(n * page, dtype=torch.uint8, device="cuda:0")
+        gu.fill_pages(stage, page, page, ids // 8, ids % 8, 55)
+        pr = np.zeros(n, gu.PUT_REQ)
+        pr["file_lo"], pr["page_index"], pr["len"] = ids // 8, ids % 8, lens
+        pr["src"] = stage.data_ptr() + ids * page
+        res = np.zeros(n, gu.RESULT)
+        capi.check(L.aps_put_batch(h, n, pr.ctypes.data, res.ctypes.data, None), "put")
+        host = torch.full((n * page + 4096,), 0xEE, dtype=torch.uint8).pin_memory()
+        rq = np.zeros(n, gu.GET_REQ)
+        rq["file_lo"], rq["page_index"], rq["nbytes"] = ids // 8, ids % 8, page
+        rq["file_lo"][7] = 9999                                                  # one miss in the middle of a run
+        order = np.arange(n)
+        order[10], order[11] = 11, 10                                            # two destinations swapped: not adjacent
+        rq["dst"] = host.data_ptr() + order.astype(np.uint64) * page
+        capi.check(L.aps_get_batch(h, n, rq.ctypes.data, res.ctypes.data, None), "get")
+        outs.append((res.copy(), host.numpy().copy()))
+        for i in range(n):
+            want_len = -capi.APS_ENOTFOUND if i == 7 else int(lens[i])
+            assert res["len"][i] == want_len
+            at = int(order[i]) * page
+            got = host.numpy()[at:at + page]
+            if i == 7:
+                assert (got == 0xEE).all()
+                continue
+            want = orc.fill_page(55, int(ids[i]) // 8, int(ids[i]) % 8, page)[:lens[i]]
+            assert np.array_equal(got[:lens[i]], want) and (got[lens[i]:] == 0xEE).all()
+            assert res["crc"][i] == orc.crc32c(want)
+        assert (host.numpy()[n * page:] == 0xEE).all()
+        capi.check(L.aps_close(h))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
