@@ -577,6 +577,8 @@ def run_ours(args):
                     "algorithmic_bytes_per_launch": int(remote_frac * step_bytes),
                     "remote_fraction": round(remote_frac, 4), "avg_launch_ms": round(ms_total / K, 5),
                     "launches_timed": int(launches), "frac_of_nominal_900": round(nv_achieved / 900.0, 4),
+                    "all_to_all_pull_ceiling_GBps": 630.0,  # tools/micro/p2p_all_bw.cu, every GPU reading all its peers
+                    "frac_of_pull_ceiling": round(nv_achieved / 630.0, 4),
                     "hbm_traffic_GBps_per_gpu": round(achieved, 1)}
     else:
         roofline = None

@@ -239,3 +239,42 @@ def test_time_bound_page_store():
     with pytest.raises(Exception):
         plain.store_timeouts()
     plain.close()
+
+
+def test_async_cache_same_page_is_refused_while_pending():
+    """LocalCacheManagerTest.asyncCacheSamePage (:563-580): a put of an id that is still queued returns false and is
+    not an async rejection; the first put lands."""
+    m = _manager(cache_size=256 * PS, slab_slots=256, async_write_threads=2, timeout_ms=5000)
+    m.set_store_delays(put_ms=300)                          # HangingPageStore, shortened: the worker sits in the store
+    p = PID("0L", 0)
+    assert m.put(p, increasing(PS))
+    assert not m.put(p, increasing(255, PS))                # same id, still pending
+    assert m.put(PID("0L", 1), increasing(PS))              # another id takes the second worker
+    assert not m.put(PID("0L", 2), increasing(PS))          # both workers busy: rejected
+    assert m.put_async_rejections() == 1
+    m.wait_async()
+    m.set_store_delays()
+    buf = bytearray(PS)
+    assert m.get(p, PS, buf) == PS and bytes(buf) == increasing(PS)          # the first put's bytes
+    assert m.pages() == 2
+    m.close()
+
+
+def test_oversized_buffers_and_several_files():
+    """LocalCacheFileInStreamTest.readOversizedBuffer / readSmallPageOversizedBuffer / positionReadOversizedBuffer /
+    readMultipleFiles: a buffer larger than the file returns the file; files do not see each other's pages."""
+    m = _manager()
+    files = {str(100 + k): np.random.default_rng(k).integers(0, 256, n, dtype=np.uint8).tobytes()
+             for k, n in enumerate((PS, PS // 3, 2 * PS + 17, 5))}
+    streams = {f: m.open_file(f, len(d), External(d)) for f, d in files.items()}
+    for f, d in files.items():
+        b = bytearray(len(d) * 2 + 7)
+        assert streams[f].read(b) == len(d) and bytes(b[:len(d)]) == d and streams[f].read(b) == -1
+        assert streams[f].positioned_read(0, b) == len(d) and bytes(b[:len(d)]) == d
+        assert streams[f].positioned_read(len(d) - 1, b, 3) == 1 and b[3] == d[-1]
+    for f, d in files.items():                              # second pass: from the cache, still each file's own bytes
+        s = m.open_file(f, len(d), lambda pos, n: (_ for _ in ()).throw(AssertionError("external read on a cached file")))
+        b = bytearray(len(d))
+        assert s.read(b) == len(d) and bytes(b) == d
+    assert m.pages() == sum((len(d) + PS - 1) // PS for d in files.values())
+    m.close()
