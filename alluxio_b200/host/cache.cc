@@ -159,11 +159,12 @@ class RecencyEvictor : public CacheEvictor {
   void UpdateOnPut(const Key& k) override { Touch(k, /*keepPlaceIfPresent=*/!mOnPut); }
   void UpdateOnDelete(const Key& k) override {
     std::lock_guard<std::mutex> g(mMu);
-    auto it = mWhere.find(k);
-    if (it == mWhere.end()) return;
-    ListUnlink(mPool, mList, it->second);
-    mPool.Free(it->second);
-    mWhere.erase(it);
+    const int32_t* at = mWhere.Find(k);
+    if (!at) return;
+    const int32_t n = *at;
+    ListUnlink(mPool, mList, n);
+    mPool.Free(n);
+    mWhere.Erase(k);
   }
   bool Evict(Key* victim) override {
     std::lock_guard<std::mutex> g(mMu);
@@ -173,30 +174,28 @@ class RecencyEvictor : public CacheEvictor {
   }
   void Reset() override {
     std::lock_guard<std::mutex> g(mMu);
-    mWhere.clear();
+    mWhere.Clear();
     mPool = NodePool();
     mList = ListHead();
   }
  private:
   void Touch(const Key& k, bool keepPlaceIfPresent) {
     std::lock_guard<std::mutex> g(mMu);
-    auto it = mWhere.find(k);
-    int32_t n;
-    if (it != mWhere.end()) {
-      if (keepPlaceIfPresent) return;
-      n = it->second;
-      ListUnlink(mPool, mList, n);
+    bool inserted;
+    int32_t* at = mWhere.Emplace(k, -1, &inserted);
+    if (inserted) {
+      *at = mPool.Alloc(k);
     } else {
-      n = mPool.Alloc(k);
-      mWhere.emplace(k, n);
+      if (keepPlaceIfPresent) return;
+      ListUnlink(mPool, mList, *at);
     }
-    ListPushBack(mPool, mList, n);
+    ListPushBack(mPool, mList, *at);
   }
   const bool mOnGet, mOnPut;
   std::mutex mMu;
   NodePool mPool;
   ListHead mList;
-  std::unordered_map<Key, int32_t, KeyHash> mWhere;
+  FlatMap<int32_t> mWhere;
 };
 
 // CACHE/evictor/LFUCacheEvictor.java:35-161: ids grouped by bucket = (int)(ln(count)/ln(base)), LRU
@@ -206,7 +205,8 @@ class LFUEvictor : public CacheEvictor {
   explicit LFUEvictor(double logBase) : mDivisor(std::log(logBase)) {}
   void UpdateOnGet(const Key& k) override {
     std::lock_guard<std::mutex> g(mMu);
-    Entry& e = mEntries[k];  // count starts at 0
+    bool inserted;
+    Entry& e = *mEntries.Emplace(k, Entry(), &inserted);  // count starts at 0
     const int newCount = ++e.count;
     const int newBucket = Bucket(newCount);
     if (newCount > 1) {
@@ -231,11 +231,11 @@ class LFUEvictor : public CacheEvictor {
   void UpdateOnPut(const Key& k) override { UpdateOnGet(k); }
   void UpdateOnDelete(const Key& k) override {
     std::lock_guard<std::mutex> g(mMu);
-    auto it = mEntries.find(k);
-    if (it == mEntries.end()) return;
-    const int bucket = Bucket(it->second.count);
-    const int32_t node = it->second.node;
-    mEntries.erase(it);
+    const Entry* e = mEntries.Find(k);
+    if (!e) return;
+    const int bucket = Bucket(e->count);
+    const int32_t node = e->node;
+    mEntries.Erase(k);
     const bool left = Detach(node, bucket);
     mPool.Free(node);
     if (!left && bucket == mMinBucket && !mBuckets.empty())
@@ -250,7 +250,7 @@ class LFUEvictor : public CacheEvictor {
   }
   void Reset() override {
     std::lock_guard<std::mutex> g(mMu);
-    mEntries.clear();
+    mEntries.Clear();
     mBuckets.clear();
     mPool = NodePool();
     mMinBucket = -1;
@@ -273,7 +273,7 @@ class LFUEvictor : public CacheEvictor {
   std::mutex mMu;
   const double mDivisor;
   NodePool mPool;
-  std::unordered_map<Key, Entry, KeyHash> mEntries;
+  FlatMap<Entry> mEntries;
   std::map<int, ListHead> mBuckets;
   int mMinBucket = -1;
 };
@@ -290,41 +290,42 @@ std::unique_ptr<CacheEvictor> CacheEvictor::Create(const std::string& kind, doub
 // ================================================================================ meta store
 
 void MetaStore::AddPage(const Key& k, const PageMeta& m) {  // DefaultMetaStore.java:56-63
-  mPages[k] = m;
+  bool inserted;
+  *mPages.Emplace(k, m, &inserted) = m;
   mBytes += m.size;
   mCount += 1;
   mEvictor->UpdateOnPut(k);
 }
 bool MetaStore::GetPageInfo(const Key& k, PageMeta* out) {  // :66-72
-  auto it = mPages.find(k);
-  if (it == mPages.end()) return false;
+  const PageMeta* pm = mPages.Find(k);
+  if (!pm) return false;
+  *out = *pm;
   mEvictor->UpdateOnGet(k);
-  *out = it->second;
   return true;
 }
 bool MetaStore::RemovePage(const Key& k) {  // :75-85
-  auto it = mPages.find(k);
-  if (it == mPages.end()) return false;
-  mBytes -= it->second.size;
+  const PageMeta* pm = mPages.Find(k);
+  if (!pm) return false;
+  mBytes -= pm->size;
   mCount -= 1;
-  mPages.erase(it);
+  mPages.Erase(k);
   mEvictor->UpdateOnDelete(k);
   return true;
 }
 void MetaStore::Reset() {  // :98-105
-  mPages.clear();
+  mPages.Clear();
   mBytes = 0;
   mCount = 0;
   mEvictor->Reset();
 }
 bool MetaStore::Evict(Key* victim, PageMeta* meta) {  // :108-122
   if (!mEvictor->Evict(victim)) return false;
-  auto it = mPages.find(*victim);
-  if (it == mPages.end()) {
+  const PageMeta* pm = mPages.Find(*victim);
+  if (!pm) {
     mEvictor->UpdateOnDelete(*victim);  // heal an evictor that named an unknown page
     return false;
   }
-  *meta = it->second;
+  *meta = *pm;
   return true;
 }
 
@@ -1401,7 +1402,9 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
   std::vector<aps_get_req> gets;
   std::vector<uint64_t> put_files, put_pages;
   std::vector<aps_result> res;
-  std::unordered_set<Key, KeyHash> pendingPuts, pendingGets;
+  // "is this id part of the window that has not been flushed yet?" is answered by the page's own meta entry: the
+  // replay stamps it with the window number on every put and hit (no side table, no extra hash probe)
+  uint32_t epoch = 1;
   int64_t ops[5] = {0, 0, 0, 0, 0};
   double tStore = 0;
   bool failed = false;
@@ -1430,7 +1433,7 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
       ops[2] += (int64_t)gets.size();
     }
     dels.clear(); puts.clear(); gets.clear(); put_files.clear(); put_pages.clear();
-    pendingPuts.clear(); pendingGets.clear();
+    ++epoch;
     tStore += Secs(t0, Clock::now());
   };
   const auto tBegin = Clock::now();
@@ -1439,15 +1442,15 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
     const Key key{0, (uint64_t)file[k], (uint64_t)page[k]};  // decimal file ids encode as (0, value)
     const int32_t len = page_len[k];
     put_ok[k] = 255;
-    if (meta->HasPage(key)) {  // LocalCacheManager.get: hit
+    if (PageMeta* pm = meta->Find(key)) {  // LocalCacheManager.get: hit
       hit[k] = 1;
       gets.push_back(aps_get_req{aps_key{key.hi, key.lo, key.idx}, 0, (uint32_t)len, (uint8_t*)d_sink + (size_t)gets.size() * ps});
-      pendingGets.insert(key);
+      pm->epoch = epoch;
     } else {  // miss -> put (LocalCacheManager.putInternal, single-threaded reading)
       hit[k] = 0;
       bool enough = meta->Bytes() + len <= cacheSize, doPut = false;
       if (enough) {
-        meta->AddPage(key, PageMeta{len, 0});
+        meta->AddPage(key, PageMeta{len, 0, epoch});
         doPut = true;
       } else {
         Key victim;
@@ -1456,9 +1459,9 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
           put_ok[k] = 0;
         } else {
           meta->RemovePage(victim);
+          if (vm.epoch == epoch) flush();  // the victim was put or read in this window: keep per-id order
           enough = meta->Bytes() + len <= cacheSize;
-          if (enough) meta->AddPage(key, PageMeta{len, 0});
-          if (pendingPuts.count(victim) || pendingGets.count(victim)) flush();  // keep per-id order
+          if (enough) meta->AddPage(key, PageMeta{len, 0, epoch});
           dels.push_back(aps_key{victim.hi, victim.lo, victim.idx});
           if (nv < victims_cap) {
             victim_file[nv] = (int64_t)victim.lo;
@@ -1474,7 +1477,6 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
         puts.push_back(aps_put_req{aps_key{key.hi, key.lo, key.idx}, (uint32_t)len, 0, (uint8_t*)d_put + (size_t)puts.size() * ps});
         put_files.push_back((uint64_t)file[k]);
         put_pages.push_back((uint64_t)page[k]);
-        pendingPuts.insert(key);
       }
     }
     if (dels.size() >= window || puts.size() >= window || gets.size() >= window) flush();

@@ -43,6 +43,85 @@ struct KeyHash {
   }
 };
 
+// Open-addressing map from Key to a small value: linear probing over a power-of-two array kept at most half
+// full, deletion by backward shift (no tombstones).  The policy state of a cache with millions of pages is
+// probed tens of millions of times per second; node-based std::unordered_map costs a cache miss per node.
+template <typename V>
+class FlatMap {
+ public:
+  FlatMap() { Rebuild(16); }
+  V* Find(const Key& k) {
+    for (size_t i = KeyHash()(k) & mMask;; i = (i + 1) & mMask) {
+      Slot& s = mSlots[i];
+      if (!s.used) return nullptr;
+      if (s.key == k) return &s.val;
+    }
+  }
+  const V* Find(const Key& k) const { return const_cast<FlatMap*>(this)->Find(k); }
+  // Returns the value for k, inserting `init` if absent; *inserted tells which.
+  V* Emplace(const Key& k, const V& init, bool* inserted) {
+    if ((mSize + 1) * 2 > mSlots.size()) Rebuild(mSlots.size() * 2);
+    for (size_t i = KeyHash()(k) & mMask;; i = (i + 1) & mMask) {
+      Slot& s = mSlots[i];
+      if (!s.used) {
+        s.used = true;
+        s.key = k;
+        s.val = init;
+        ++mSize;
+        *inserted = true;
+        return &s.val;
+      }
+      if (s.key == k) {
+        *inserted = false;
+        return &s.val;
+      }
+    }
+  }
+  bool Erase(const Key& k) {
+    size_t i = KeyHash()(k) & mMask;
+    for (;; i = (i + 1) & mMask) {
+      if (!mSlots[i].used) return false;
+      if (mSlots[i].key == k) break;
+    }
+    // shift the rest of the cluster back so that every key stays reachable from its home slot
+    size_t hole = i;
+    for (size_t j = (i + 1) & mMask; mSlots[j].used; j = (j + 1) & mMask) {
+      const size_t home = KeyHash()(mSlots[j].key) & mMask;
+      const bool movable = ((j - home) & mMask) >= ((j - hole) & mMask);
+      if (movable) {
+        mSlots[hole] = mSlots[j];
+        hole = j;
+      }
+    }
+    mSlots[hole].used = false;
+    --mSize;
+    return true;
+  }
+  void Clear() {
+    mSlots.clear();
+    Rebuild(16);
+  }
+  size_t Size() const { return mSize; }
+ private:
+  struct Slot {
+    Key key;
+    V val;
+    bool used = false;
+  };
+  void Rebuild(size_t capacity) {
+    std::vector<Slot> old;
+    old.swap(mSlots);
+    mSlots.assign(capacity, Slot());
+    mMask = capacity - 1;
+    mSize = 0;
+    bool ins;
+    for (const Slot& s : old)
+      if (s.used) Emplace(s.key, s.val, &ins);
+  }
+  std::vector<Slot> mSlots;
+  size_t mMask = 0, mSize = 0;
+};
+
 int32_t JavaStringHashCode(const std::string& utf8);  // String.hashCode over UTF-16 units
 
 // String file id -> 128 bits, collision free: decimal longs -> (0, v); 32 lower-case hex
@@ -93,12 +172,14 @@ class CacheEvictor {
 // ---- CACHE/DefaultMetaStore.java:33-132 ----------------------------------------------------------------
 struct PageMeta {
   int64_t size;
-  int32_t lockId;  // LocalCacheManager.getPageLockId of this page, kept so a victim's lock is known
+  int32_t lockId;      // LocalCacheManager.getPageLockId of this page, kept so a victim's lock is known
+  uint32_t epoch = 0;  // batched replay: the flush window in which the page was last put or read
 };
 class MetaStore {
  public:
   explicit MetaStore(std::unique_ptr<CacheEvictor> e) : mEvictor(std::move(e)) {}
-  bool HasPage(const Key& k) const { return mPages.find(k) != mPages.end(); }
+  bool HasPage(const Key& k) const { return mPages.Find(k) != nullptr; }
+  PageMeta* Find(const Key& k) { return mPages.Find(k); }  // hasPage with the entry in hand: no evictor update
   void AddPage(const Key& k, const PageMeta& m);
   bool GetPageInfo(const Key& k, PageMeta* out);  // false == PageNotFoundException; refreshes the evictor
   bool RemovePage(const Key& k);                  // false == PageNotFoundException
@@ -107,7 +188,7 @@ class MetaStore {
   void Reset();
   bool Evict(Key* victim, PageMeta* meta);  // false == null
  private:
-  std::unordered_map<Key, PageMeta, KeyHash> mPages;
+  FlatMap<PageMeta> mPages;
   std::atomic<int64_t> mBytes{0}, mCount{0};
   std::unique_ptr<CacheEvictor> mEvictor;
 };
