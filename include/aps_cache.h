@@ -174,7 +174,9 @@ APS_API int64_t apc_replay(apc_manager* m, int64_t n, const int64_t* file, const
  * every `window` accesses, or earlier when an operation would be reordered against a pending one on the
  * same id.  This is how the host-side evictor drives GPU hash-table inserts and erases at speed.
  * store_ops[0..2] receive the numbers of deletes, puts and gets issued, store_ops[3] the number of flushes,
- * store_ops[4] the gets whose length or status was not the expected one (must be 0). */
+ * store_ops[4] the gets whose length or status was not the expected one (must be 0).  The batches of one window
+ * are issued by a worker thread while the caller's thread decides the next window; windows reach the store in
+ * order.  seconds_host = time the policy itself took, seconds_store = time the worker spent in store calls. */
 APS_API int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* file, const int64_t* page,
                                    const int32_t* page_len, uint64_t seed, uint32_t window, uint8_t* hit, uint8_t* put_ok,
                                    int64_t* victim_file, int64_t* victim_page, int64_t victims_cap, int64_t* final_pages,
