@@ -73,11 +73,11 @@ typedef void (*CopyKernelFn)(CopyArgs);
 struct CopyVariant {
   const char* name;
   uint32_t threads;
-  CopyKernelFn crc, plain, get_crc, get_plain;
+  CopyKernelFn crc, plain, get_crc, get_plain, put_crc, put_plain;
 };
 #define APS_VARIANT(T, G)                                                                                  \
   {#T "x" #G, T, copy_kernel<true, T, G, false>, copy_kernel<false, T, G, false>, copy_kernel<true, T, G, true>, \
-   copy_kernel<false, T, G, true>}
+   copy_kernel<false, T, G, true>, copy_kernel<true, T, G, false, true>, copy_kernel<false, T, G, false, true>}
 const CopyVariant kCopyVariants[] = {
     APS_VARIANT(512, 4), APS_VARIANT(1024, 4), APS_VARIANT(1024, 2), APS_VARIANT(512, 8),
     APS_VARIANT(512, 2), APS_VARIANT(256, 8),
@@ -163,6 +163,7 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
     for (const CopyVariant& v : kCopyVariants) {
       CUDA_TRY(cudaFuncSetAttribute(v.crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
       CUDA_TRY(cudaFuncSetAttribute(v.get_crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
+      CUDA_TRY(cudaFuncSetAttribute(v.put_crc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem));
     }
     {
       int optin = 0;
@@ -212,6 +213,9 @@ struct aps_store {
   uint32_t n_shards = 0, my_shard = 0;
   std::vector<void*> ipc_ptrs;  // peer allocations opened through CUDA IPC (closed in aps_close)
   uint32_t* d_done = nullptr;
+  unsigned long long* d_jslot = nullptr;  // fused put: per-job hand-over word (see copy_kernel, kPut)
+  uint32_t put_epoch = 0;
+  bool fused_put = true;  // APS_NO_FUSED_PUT=1: resolve puts in a kernel of their own, as the bulk-async variant does
   uint32_t* d_clock = nullptr;  // APS_FLAG_DEVICE_CLOCK: {hand, cursor, need, found, CTAs finished}
   int* d_error = nullptr;
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
@@ -247,7 +251,7 @@ inline void count_launch(aps_store* s, uint64_t k = 1) {
 }
 
 int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_result* d_res, uint32_t* d_crc_out,
-                cudaStream_t st, bool sharded = false) {
+                cudaStream_t st, bool sharded = false, const aps_put_req* d_put_reqs = nullptr) {
   const bool crc = (s->cfg.flags & APS_FLAG_CRC) != 0 || d_crc_out != nullptr;
   const CopyVariant& v = copy_variant();
   const uint32_t warps_per_block = v.threads / 32;
@@ -262,6 +266,12 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   CopyArgs a{};
   a.jobs = s->d_jobs;
   a.reqs = d_get_reqs;
+  a.preqs = d_put_reqs;
+  a.jslot = s->d_jslot;
+  if (d_put_reqs) {
+    if (++s->put_epoch == 0) s->put_epoch = 1;
+    a.epoch = s->put_epoch;
+  }
   a.table = s->table;
   a.crc_on = (s->cfg.flags & APS_FLAG_CRC) != 0;
   a.n_jobs = n;
@@ -325,7 +335,8 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   {
     // Programmatic dependent launch: back-to-back copy kernels overlap launch latency; each kernel
     // still waits (griddepcontrol.wait) for all earlier work before it touches any data.
-    CopyKernelFn fn = d_get_reqs ? (crc ? v.get_crc : v.get_plain) : (crc ? v.crc : v.plain);
+    CopyKernelFn fn = d_get_reqs ? (crc ? v.get_crc : v.get_plain)
+                      : d_put_reqs ? (crc ? v.put_crc : v.put_plain) : (crc ? v.crc : v.plain);
     cudaLaunchConfig_t lc{};
     lc.gridDim = dim3(grid);
     lc.blockDim = dim3(v.threads);
@@ -412,6 +423,7 @@ void free_store(aps_store* s) {
   for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
   s->ipc_ptrs.clear();
   cudaFree(s->d_done);
+  cudaFree(s->d_jslot);
   cudaFree(s->d_clock);
   cudaFree(s->d_d2h_stage);
   cudaFree(s->table.slot_ref);
@@ -576,6 +588,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   s->use_steal = getenv("APS_NO_STEAL") == nullptr;
   s->use_table_image = getenv("APS_NO_TABLE_IMAGE") == nullptr;
   s->use_d2h_stage = getenv("APS_NO_D2H_STAGE") == nullptr;
+  s->fused_put = getenv("APS_NO_FUSED_PUT") == nullptr;
   if (const char* pf = getenv("APS_PF_ROWS")) s->prefetch_rows = (uint32_t)std::min(256, std::max(0, atoi(pf)));
   s->use_tma = (cfg->flags & APS_FLAG_TMA_COPY) != 0 && (cfg->flags & APS_FLAG_CRC) == 0;
   uint64_t slots = cfg->slab_slots;
@@ -624,6 +637,8 @@ int aps_open(const aps_config* cfg, aps_store** out) {
     OPEN_TRY(cudaMemcpy(s->d_rowshift, rs.data(), rs.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
   }
   OPEN_TRY(cudaMalloc(&s->d_done, (uint64_t)mb * sizeof(uint32_t)));
+  OPEN_TRY(cudaMalloc(&s->d_jslot, (uint64_t)mb * sizeof(unsigned long long)));
+  OPEN_TRY(cudaMemset(s->d_jslot, 0, (uint64_t)mb * sizeof(unsigned long long)));
   OPEN_TRY(cudaMalloc(&s->d_error, sizeof(int)));
   if (cfg->flags & APS_FLAG_DEVICE_CLOCK) {
     OPEN_TRY(cudaMalloc(&s->table.slot_ref, slots));
@@ -712,6 +727,8 @@ int aps_put_batch_dev(aps_store* s, uint32_t n, const aps_put_req* d_reqs, aps_r
     rc = clock_evict(s, n, 0, nullptr, 0, st);
     if (rc) return rc;
   }
+  if (s->fused_put && !use_tma_variant() && !s->use_tma)  // insert + scatter + CRC in one launch
+    return launch_copy(s, n, nullptr, d_res, nullptr, st, false, d_reqs);
   put_resolve_kernel<<<tile_grid(n), kK1Threads, 0, st>>>(s->table, d_reqs, n, s->d_jobs, d_res, (s->cfg.flags & APS_FLAG_CRC) != 0);
   count_launch(s);
   CUDA_TRY(cudaGetLastError());

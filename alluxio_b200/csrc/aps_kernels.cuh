@@ -234,6 +234,9 @@ constexpr uint32_t kMaxTasksPerJob = 128;
 struct CopyArgs {
   const Job* jobs;           // kGet == false: jobs prepared by a resolve kernel
   const aps_get_req* reqs;   // kGet == true: requests, resolved in this kernel
+  const aps_put_req* preqs;  // kPut == true: put requests; task 0 of a page inserts it, the others wait for its slot
+  unsigned long long* jslot; // kPut scratch, one word per job: launch epoch << 32 | (slot + 1, or 0x80000000 | status)
+  uint32_t epoch;            // kPut: this launch's number (never 0), so the words above need no reset
   Table table;
   int crc_on;
   uint32_t n_jobs;
@@ -283,8 +286,9 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
 // job's accumulator.  Warps that run out of work take the back half of the longest remaining range
 // in their CTA (finish times of equal streams differ by ~10 % on a saturated memory system).  The
 // warp that completes a job's last row applies init/xorout and verifies or records the page CRC.
-template <bool kCrc, int kThreads, int G, bool kGet>
+template <bool kCrc, int kThreads, int G, bool kGet, bool kPut = false>
 __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
+  static_assert(!(kGet && kPut), "a launch is a get, a put, or a list of prepared jobs");
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr uint32_t nwarps = kThreads / 32;
   __shared__ unsigned long long s_range[nwarps];  // published ranges: open to stealing
@@ -458,6 +462,85 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           report_status = status;
         }
         report = __shfl_sync(0xFFFFFFFFu, (int)report, 0) != 0;
+      } else if (kPut) {
+        // Fused insert (LocalPageStore.put's "create the file"): task 0 of a page claims a table entry and a slab
+        // slot with the first eight lanes and publishes the outcome; the page's other tasks, which start at the
+        // same moment on other warps, pick it up from a.jslot.  Task 0 never waits for anybody, and a page's task
+        // 0 always precedes its other tasks in every warp's list, so the waiting cannot cycle.
+        const aps_put_req rq = a.preqs[job];
+        const Table& t = a.table;
+        unsigned long long word = 0;
+        if (c == 0) {
+          int err = 0;
+          uint32_t slot = kNoSlot;
+          if (rq.len > t.page_size) {
+            err = APS_EINVAL;
+          } else {
+            EntryClaim cl{kClaimFull, 0, 0};
+            if (lane < 8) cl = tile_claim(t, rq.key, lane, 0);
+            __syncwarp();
+            cl.kind = __shfl_sync(0xFFFFFFFFu, cl.kind, 0);
+            if (cl.kind == kClaimFull) {
+              err = APS_ENOSPC;
+            } else if (lane == 0) {
+              Entry* e = t.entries + cl.entry_idx;
+              if (cl.kind == kClaimReplace) {  // PageStore.put overwrites: same slot, new length
+                slot = meta_slot(cl.was);
+                e->meta = meta_make(slot, rq.len);
+                if (t.slot_ref) t.slot_ref[slot] = 1;
+                atomicAdd(&t.counters[kCtrBytes], (unsigned long long)rq.len - (unsigned long long)meta_len(cl.was));
+              } else {
+                const int idx = atomicSub(t.free_top, 1) - 1;
+                if (idx < 0) {
+                  atomicAdd(t.free_top, 1);
+                  e->meta = cl.was;  // no slab slot left: give the entry back
+                } else {
+                  slot = t.free_slots[idx];
+                  e->k0 = rq.key.file_hi; e->k1 = rq.key.file_lo; e->k2 = rq.key.page_index;
+                  __threadfence();
+                  e->meta = meta_make(slot, rq.len);
+                  if (t.slot_entry) {
+                    t.slot_entry[slot] = cl.entry_idx;
+                    t.slot_ref[slot] = 1;
+                  }
+                  atomicAdd(&t.counters[kCtrPages], 1ull);
+                  atomicAdd(&t.counters[kCtrBytes], (unsigned long long)rq.len);
+                  if (cl.was == kMetaTomb) atomicAdd(&t.counters[kCtrTombs], ~0ull);
+                }
+              }
+            }
+            slot = __shfl_sync(0xFFFFFFFFu, slot, 0);
+            if (!err && slot == kNoSlot) err = APS_ENOSPC;
+          }
+          word = ((unsigned long long)a.epoch << 32) | (err ? (0x80000000u | (uint32_t)err) : slot + 1u);
+          if (lane == 0) {
+            if (!err) {
+              if (rq.len == 0) t.slot_crc[slot] = 0;  // CRC32C of the empty string
+              else atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)rq.len);
+            }
+            __threadfence();
+            *(volatile unsigned long long*)&a.jslot[job] = word;
+            report = err != 0 || !kCrc || rq.len == 0;  // otherwise the finisher reports
+            report_status = err ? -err : (int32_t)rq.len;
+          }
+          report = __shfl_sync(0xFFFFFFFFu, (int)report, 0) != 0;
+        } else {
+          if (lane == 0) {
+            do word = *(volatile unsigned long long*)&a.jslot[job];
+            while ((uint32_t)(word >> 32) != a.epoch);
+            __threadfence();
+          }
+          word = __shfl_sync(0xFFFFFFFFu, word, 0);
+        }
+        const uint32_t v = (uint32_t)word;
+        j = Job{nullptr, nullptr, 0, 0, 0, 0};
+        if (!(v & 0x80000000u)) {
+          j.src = (const uint8_t*)rq.src;
+          j.slot = v - 1u;
+          j.dst = t.slab + (uint64_t)j.slot * t.page_size;
+          j.n = rq.len;
+          j.flags = a.crc_on ? kJobRecord : 0u;
+        }
       } else {
         j = a.jobs[job];
       }
