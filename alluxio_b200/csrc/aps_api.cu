@@ -218,6 +218,7 @@ struct aps_store {
   bool fused_put = true;  // APS_NO_FUSED_PUT=1: resolve puts in a kernel of their own, as the bulk-async variant does
   uint32_t* d_clock = nullptr;  // APS_FLAG_DEVICE_CLOCK: {hand, cursor, need, found, CTAs finished}
   int* d_error = nullptr;
+  int* h_error = nullptr;  // pinned and device-visible: the copy kernels' error flag, read after a sync without a copy
   void* d_reqs = nullptr;  // staging for host-array calls (max_batch * sizeof(aps_get_req))
   aps_result* d_res = nullptr;
   uint8_t* h_stage = nullptr;   // pinned: requests, then results
@@ -284,7 +285,7 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.tables = s->dc->d_tables;
   a.table_image = s->use_table_image ? s->dc->d_table_image : nullptr;
   a.rowshift = s->d_rowshift;
-  a.error_flag = s->d_error;
+  a.error_flag = s->h_error;
   a.timeline = s->d_timeline;
   a.steal = s->use_steal ? 1 : 0;
   a.sched = s->d_sched;
@@ -397,9 +398,8 @@ bool distinct_keys(uint32_t n, GetKey key_of) {
 }
 
 int check_device_error(aps_store* s, cudaStream_t st) {
-  int err = 0;
-  CUDA_TRY(cudaMemcpyAsync(&err, s->d_error, sizeof(int), cudaMemcpyDeviceToHost, st));
   CUDA_TRY(cudaStreamSynchronize(st));
+  const int err = *(volatile int*)s->h_error;
   if (err) {
     snprintf(tl_cuda_error, sizeof(tl_cuda_error), "copy kernel: shared-memory window not at the expected address");
     return APS_ECUDA;
@@ -429,6 +429,7 @@ void free_store(aps_store* s) {
   cudaFree(s->table.slot_ref);
   cudaFree(s->table.slot_entry);
   cudaFree(s->d_error);
+  if (s->h_error) cudaFreeHost(s->h_error);
   cudaFree(s->d_reqs);
   cudaFree(s->d_res);
   for (cudaEvent_t e : s->prof_events) cudaEventDestroy(e);
@@ -640,6 +641,8 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaMalloc(&s->d_jslot, (uint64_t)mb * sizeof(unsigned long long)));
   OPEN_TRY(cudaMemset(s->d_jslot, 0, (uint64_t)mb * sizeof(unsigned long long)));
   OPEN_TRY(cudaMalloc(&s->d_error, sizeof(int)));
+  OPEN_TRY(cudaHostAlloc(&s->h_error, sizeof(int), cudaHostAllocDefault));
+  *s->h_error = 0;
   if (cfg->flags & APS_FLAG_DEVICE_CLOCK) {
     OPEN_TRY(cudaMalloc(&s->table.slot_ref, slots));
     OPEN_TRY(cudaMalloc(&s->table.slot_entry, slots * sizeof(uint64_t)));
@@ -886,10 +889,15 @@ int aps_delete_batch(aps_store* s, uint32_t n, const aps_key* keys, aps_result* 
   aps_key* h_keys = reinterpret_cast<aps_key*>(s->h_stage);
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   memcpy(h_keys, keys, (size_t)n * sizeof(aps_key));
-  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_keys, (size_t)n * sizeof(aps_key), cudaMemcpyHostToDevice, st));
-  rc = aps_delete_batch_dev(s, n, (const aps_key*)s->d_reqs, s->d_res, st);
-  if (rc) return rc;
-  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+  if (n <= 8) {  // a handful of ids (PageStore.delete is one): let the kernel use the pinned staging area in place
+    rc = aps_delete_batch_dev(s, n, h_keys, h_res, st);
+    if (rc) return rc;
+  } else {
+    CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_keys, (size_t)n * sizeof(aps_key), cudaMemcpyHostToDevice, st));
+    rc = aps_delete_batch_dev(s, n, (const aps_key*)s->d_reqs, s->d_res, st);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+  }
   CUDA_TRY(cudaStreamSynchronize(st));
   memcpy(res, h_res, (size_t)n * sizeof(aps_result));
   return APS_OK;
@@ -921,11 +929,17 @@ int aps_put(aps_store* s, const aps_key* key, const void* src, uint32_t len) {
   }
   aps_put_req* h_req = reinterpret_cast<aps_put_req*>(s->h_stage);
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
+  // One page, one launch, no staging copies: the kernel reads the request from, and writes the result to, the
+  // pinned staging area itself (page-locked host memory is device-visible), so a call costs a launch and a sync.
   *h_req = rq;
-  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
-  rc = aps_put_batch_dev(s, 1, (const aps_put_req*)s->d_reqs, s->d_res, s->stream);
+  rc = s->fused_put ? aps_put_batch_dev(s, 1, h_req, h_res, s->stream) : APS_EINVAL;
+  if (!s->fused_put) {
+    CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
+    rc = aps_put_batch_dev(s, 1, (const aps_put_req*)s->d_reqs, s->d_res, s->stream);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, sizeof(aps_result), cudaMemcpyDeviceToHost, s->stream));
+  }
   if (rc) return rc;
-  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, sizeof(aps_result), cudaMemcpyDeviceToHost, s->stream));
   rc = check_device_error(s, s->stream);
   if (rc) return rc;
   return h_res->len < 0 ? -h_res->len : APS_OK;
@@ -947,10 +961,8 @@ int aps_get(aps_store* s, const aps_key* key, uint32_t page_off, uint32_t bytes_
   aps_get_req* h_req = reinterpret_cast<aps_get_req*>(s->h_stage);
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   *h_req = rq;
-  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
-  rc = aps_get_batch_dev(s, 1, (const aps_get_req*)s->d_reqs, s->d_res, s->stream);
+  rc = aps_get_batch_dev(s, 1, h_req, h_res, s->stream);  // request and result stay in the pinned staging area (see aps_put)
   if (rc) return rc;
-  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, sizeof(aps_result), cudaMemcpyDeviceToHost, s->stream));
   rc = check_device_error(s, s->stream);
   if (rc) return rc;
   if (h_res->len < 0) return -h_res->len;
