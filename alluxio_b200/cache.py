@@ -84,6 +84,8 @@ SIGNATURES = {
     "apc_meta_evict": (C.c_int, [_vp, _vp, C.c_size_t, C.POINTER(_i64), C.POINTER(_i64)]),
     "apc_file_key": (None, [_vp, _cp, C.POINTER(_u64), C.POINTER(_u64)]),
     "apc_java_string_hashcode": (_i32, [_cp]),
+    "apc_hadoop_file_identifier": (None, [_cp, _vp]),
+    "apc_file_key_of": (None, [_cp, C.POINTER(_u64), C.POINTER(_u64)]),
 }
 
 _lib = None
@@ -514,3 +516,16 @@ class LocalCacheFileInStream:
                 self._h = None
         except Exception:
             pass
+
+
+def hadoop_file_identifier(path):
+    """HadoopUtils.toAlluxioUriStatus: md5 hex of the path string."""
+    out = C.create_string_buffer(33)
+    lib().apc_hadoop_file_identifier(path.encode("utf-8"), out)
+    return out.value.decode()
+
+
+def file_key_of(file_id):
+    hi, lo = C.c_uint64(), C.c_uint64()
+    lib().apc_file_key_of(str(file_id).encode(), C.byref(hi), C.byref(lo))
+    return hi.value, lo.value

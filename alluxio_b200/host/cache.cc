@@ -114,6 +114,54 @@ std::string FileKeyCodec::Decode(uint64_t hi, uint64_t lo) {
   return buf;
 }
 
+// ---- HadoopUtils.toAlluxioUriStatus (core/client/hdfs/src/main/java/alluxio/hadoop/HadoopUtils.java:225-238):
+// behind the Hadoop-compatible file system (how Presto reaches the cache) a file's identifier is the lower-case hex
+// MD5 of its path string, which FileKeyCodec maps onto the 128-bit key exactly.  RFC 1321, one-shot, host side.
+namespace {
+inline uint32_t Rotl32(uint32_t x, int s) { return (x << s) | (x >> (32 - s)); }
+void Md5(const uint8_t* data, size_t len, uint8_t out[16]) {
+  static const int kShift[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9,  14, 20, 5, 9,
+                                 14, 20, 5, 9,  14, 20, 5, 9,  14, 20, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23,
+                                 4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+  uint32_t k[64];
+  for (int i = 0; i < 64; ++i) k[i] = (uint32_t)(int64_t)std::floor(std::fabs(std::sin((double)(i + 1))) * 4294967296.0);
+  uint32_t h[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+  std::vector<uint8_t> msg(data, data + len);
+  msg.push_back(0x80);
+  while (msg.size() % 64 != 56) msg.push_back(0);
+  const uint64_t bits = (uint64_t)len * 8;
+  for (int i = 0; i < 8; ++i) msg.push_back((uint8_t)(bits >> (8 * i)));
+  for (size_t off = 0; off < msg.size(); off += 64) {
+    uint32_t m[16];
+    memcpy(m, msg.data() + off, 64);  // little endian host
+    uint32_t a = h[0], b = h[1], c = h[2], d = h[3];
+    for (int i = 0; i < 64; ++i) {
+      uint32_t f;
+      int g;
+      if (i < 16) { f = (b & c) | (~b & d); g = i; }
+      else if (i < 32) { f = (d & b) | (~d & c); g = (5 * i + 1) & 15; }
+      else if (i < 48) { f = b ^ c ^ d; g = (3 * i + 5) & 15; }
+      else { f = c ^ (b | ~d); g = (7 * i) & 15; }
+      const uint32_t t = d;
+      d = c;
+      c = b;
+      b = b + Rotl32(a + f + k[i] + m[g], kShift[i]);
+      a = t;
+    }
+    h[0] += a; h[1] += b; h[2] += c; h[3] += d;
+  }
+  memcpy(out, h, 16);
+}
+}  // namespace
+
+std::string HadoopFileIdentifier(const std::string& pathUtf8) {
+  uint8_t d[16];
+  Md5((const uint8_t*)pathUtf8.data(), pathUtf8.size(), d);
+  char buf[33];
+  for (int i = 0; i < 16; ++i) snprintf(buf + 2 * i, 3, "%02x", d[i]);
+  return buf;
+}
+
 // ================================================================================ node pool
 
 int32_t NodePool::Alloc(const Key& k) {
@@ -1233,6 +1281,14 @@ int apc_set_store_faults(apc_manager* m, uint32_t mask) { return m->mgr->store()
 aps_store* apc_store(apc_manager* m) { return apc_shard_store(m, 0); }
 void apc_file_key(apc_manager* m, const char* f, uint64_t* hi, uint64_t* lo) { m->mgr->codec()->Encode(f, hi, lo); }
 int32_t apc_java_string_hashcode(const char* utf8) { return JavaStringHashCode(utf8); }
+void apc_hadoop_file_identifier(const char* path_utf8, char* out33) {
+  const std::string id = HadoopFileIdentifier(path_utf8 ? path_utf8 : "");
+  memcpy(out33, id.c_str(), 33);
+}
+void apc_file_key_of(const char* file_id, uint64_t* hi, uint64_t* lo) {
+  FileKeyCodec c;  // decimal and 32-hex ids need no state; anything else would be interned per codec
+  c.Encode(file_id, hi, lo);
+}
 
 // CACHE/LocalCacheFileInStream.java:175-223 + readExternalPage :291-310
 int32_t apc_positioned_read(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst, int32_t len,

@@ -123,6 +123,7 @@ class FlatMap {
 };
 
 int32_t JavaStringHashCode(const std::string& utf8);  // String.hashCode over UTF-16 units
+std::string HadoopFileIdentifier(const std::string& pathUtf8);  // md5 hex of the path, HadoopUtils.java:225-238
 
 // String file id -> 128 bits, collision free: decimal longs -> (0, v); 32 lower-case hex
 // chars -> (hi, lo) unless hi is 0 or all ones; anything else interned -> (all ones, n).

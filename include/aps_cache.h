@@ -206,6 +206,12 @@ APS_API int apc_meta_evict(apc_meta* m, char* file_out, size_t cap, int64_t* ind
 /* String file id -> 128-bit key, and Java's String.hashCode for the lock striping. */
 APS_API void apc_file_key(apc_manager* m, const char* file_id, uint64_t* hi, uint64_t* lo);
 APS_API int32_t apc_java_string_hashcode(const char* utf8);
+/* The file identifier the Hadoop-compatible client gives a file: lower-case hex MD5 of its path
+ * string (core/client/hdfs/src/main/java/alluxio/hadoop/HadoopUtils.java:225-238).  out33 receives 32 characters
+ * and a terminator.  Such ids map onto the 128-bit device key exactly: (hi, lo) are the digest's two halves. */
+APS_API void apc_hadoop_file_identifier(const char* path_utf8, char* out33);
+/* apc_file_key without a manager, for ids that need no interning (decimal longs, 32-hex). */
+APS_API void apc_file_key_of(const char* file_id, uint64_t* hi, uint64_t* lo);
 
 #ifdef __cplusplus
 }

@@ -108,3 +108,20 @@ def test_java_string_hashcode_and_file_keys_agree_with_the_python_codec():
     assert py.encode("0123")[0] == 2**64 - 1          # not canonical -> interned
     assert py.encode("d41d8cd98f00b204e9800998ecf8427e") == (0xd41d8cd98f00b204, 0xe9800998ecf8427e)
     assert py.encode("0000000000000000ffffffffffffffff")[0] == 2**64 - 1  # reserved high word -> interned
+
+
+def test_hadoop_file_identifier_is_md5_hex_of_the_path_and_maps_exactly():
+    """behind the Hadoop-compatible client the file id is md5(path) in hex
+    (core/client/hdfs/.../HadoopUtils.java:225-238); its 32 hex characters are the 128-bit device key."""
+    import hashlib
+    from alluxio_b200.cache import file_key_of, hadoop_file_identifier
+    paths = ["", "/", "hdfs://nn:8020/warehouse/t/part-00000.parquet", "s3a://bucket/kéy with spaces/ü", "x" * 55, "y" * 56,
+             "z" * 64, "w" * 1000]
+    for p in paths:
+        want = hashlib.md5(p.encode("utf-8")).hexdigest()
+        got = hadoop_file_identifier(p)
+        assert got == want
+        hi, lo = file_key_of(got)
+        assert (hi, lo) == (int(want[:16], 16), int(want[16:], 16))
+    assert file_key_of("12345") == (0, 12345)
+    assert file_key_of("-1") == (0, (1 << 64) - 1)
