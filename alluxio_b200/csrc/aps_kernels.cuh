@@ -6,7 +6,8 @@
 namespace aps {
 
 // ------------------------------------------------------------------------------------------------
-// Copy jobs: the resolve kernels turn requests into jobs, the copy kernel executes them.
+// Copy jobs: what a warp-task executes.  Gets and puts build theirs inside the copy kernel (lookup / insert fused);
+// the stand-alone checksum pass and the bulk-async variant's puts prepare them in a small kernel of their own.
 // ------------------------------------------------------------------------------------------------
 struct Job {
   const uint8_t* src;
@@ -232,7 +233,7 @@ __device__ __forceinline__ uint32_t warp_bytes(const uint8_t* src, uint8_t* dst,
 constexpr uint32_t kMaxTasksPerJob = 128;
 
 struct CopyArgs {
-  const Job* jobs;           // kGet == false: jobs prepared by a resolve kernel
+  const Job* jobs;           // neither kGet nor kPut: jobs prepared by an earlier kernel
   const aps_get_req* reqs;   // kGet == true: requests, resolved in this kernel
   const aps_put_req* preqs;  // kPut == true: put requests; task 0 of a page inserts it, the others wait for its slot
   unsigned long long* jslot; // kPut scratch, one word per job: launch epoch << 32 | (slot + 1, or 0x80000000 | status)
@@ -276,10 +277,10 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
   return sh;
 }
 
-// K2 + K3 (+ K1 lookup when kGet).  Persistent grid: one CTA per SM.  A job (one page request) is
+// K2 + K3 (+ K1: lookup when kGet, insert when kPut).  Persistent grid: one CTA per SM.  A job (one page request) is
 // cut into tasks_per_job warp-tasks of rows_per_task 512-byte rows, sized by the host so that one
 // round of all warps of the chip covers the batch (no wave quantisation).  A task resolves its
-// page (kGet: eight lanes probe the hash table), publishes its row range in shared memory and
+// page (kGet: eight lanes probe the hash table; kPut: task 0 inserts, its siblings wait for the slot), publishes its row range in shared memory and
 // streams the rows it claims from it (128-bit loads and stores per lane, next group in flight while
 // the current one is folded).  It reduces the four per-lane CRC words to the zero-init CRC of the
 // segment, shifts it by the bytes that follow it in the page (GF(2) multiply) and XORs it into the
