@@ -3,6 +3,7 @@
 //   pull: every GPU reads 2 KiB chunks round-robin from all its peers and writes them to local memory (what
 //         aps_get_batch_sharded does: the requester reads the owner's slab in place)
 //   push: every GPU reads local memory and writes the chunks round-robin into its peers' memory
+//   both: every GPU does both at once on two streams (half the chunks each): do the two directions of use add up?
 // Reports GB/s per GPU (bytes that crossed NVLink into / out of that GPU), min and mean over GPUs.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o p2p_all_bw p2p_all_bw.cu
 #include <cstdint>
@@ -61,7 +62,15 @@ int main() {
     CK(cudaEventCreate(&e0[g]));
     CK(cudaEventCreate(&e1[g]));
   }
-  for (int mode = 0; mode < 2; ++mode) {
+  std::vector<cudaStream_t> st2(n);
+  std::vector<uint8_t*> loc2(n);
+  for (int g = 0; g < n; ++g) {
+    CK(cudaSetDevice(g));
+    CK(cudaStreamCreate(&st2[g]));
+    CK(cudaMalloc(&loc2[g], bytes));
+    CK(cudaMemset(loc2[g], 0, bytes));
+  }
+  for (int mode = 0; mode < 3; ++mode) {
     for (int rep = 0; rep < 3; ++rep) {  // the last repetition is reported
       for (int g = 0; g < n; ++g) { CK(cudaSetDevice(g)); CK(cudaDeviceSynchronize()); }
       for (int g = 0; g < n; ++g) {
@@ -72,9 +81,25 @@ int main() {
           if (p != g) pr.p[k++] = buf[p] + (size_t)g * (bytes / n);  // every reader/writer gets its own 1/n slice of a peer
         const size_t chunks = (bytes / n) * (n - 1) / 2048;          // so that slices never overlap
         CK(cudaEventRecord(e0[g], st[g]));
-        for (int it = 0; it < 4; ++it) {
-          if (mode == 0) xfer<true><<<148, 512, 0, st[g]>>>(pr, loc[g], chunks);
-          else xfer<false><<<148, 512, 0, st[g]>>>(pr, loc[g], chunks);
+        if (mode == 2) {
+          // pull from the first half of every peer slice on one stream, push into the second half on another;
+          // 74 CTAs each so that the two kernels share the SMs
+          Peers hi = pr;
+          for (int k = 0; k < hi.n; ++k) hi.p[k] += (bytes / n) / 2;
+          CK(cudaStreamWaitEvent(st2[g], e0[g], 0));
+          for (int it = 0; it < 4; ++it) {
+            xfer<true><<<74, 512, 0, st[g]>>>(pr, loc[g], chunks / 2);
+            xfer<false><<<74, 512, 0, st2[g]>>>(hi, loc2[g], chunks / 2);
+          }
+          cudaEvent_t done;
+          CK(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+          CK(cudaEventRecord(done, st2[g]));
+          CK(cudaStreamWaitEvent(st[g], done, 0));
+        } else {
+          for (int it = 0; it < 4; ++it) {
+            if (mode == 0) xfer<true><<<148, 512, 0, st[g]>>>(pr, loc[g], chunks);
+            else xfer<false><<<148, 512, 0, st[g]>>>(pr, loc[g], chunks);
+          }
         }
         CK(cudaEventRecord(e1[g], st[g]));
       }
@@ -89,7 +114,7 @@ int main() {
         sum += gbps;
       }
       if (rep == 2)
-        printf("{\"mode\": \"%s\", \"gpus\": %d, \"per_gpu_GBps_min\": %.1f, \"per_gpu_GBps_mean\": %.1f}\n", mode == 0 ? "pull" : "push", n,
+        printf("{\"mode\": \"%s\", \"gpus\": %d, \"per_gpu_GBps_min\": %.1f, \"per_gpu_GBps_mean\": %.1f}\n", mode == 0 ? "pull" : mode == 1 ? "push" : "both", n,
                mn, sum / n);
     }
   }
