@@ -125,3 +125,47 @@ def test_hadoop_file_identifier_is_md5_hex_of_the_path_and_maps_exactly():
         assert (hi, lo) == (int(want[:16], 16), int(want[16:], 16))
     assert file_key_of("12345") == (0, 12345)
     assert file_key_of("-1") == (0, (1 << 64) - 1)
+
+
+def test_meta_store_random_ops_match_a_dict():
+    """The meta store and the LRU evictor keep their state in open-addressing maps with backward-shift deletion
+    (host/cache.h FlatMap): long random sequences of add / remove / lookup / evict against a plain model."""
+    import random
+    from collections import OrderedDict
+    from alluxio_b200.cache import MetaStore, PageNotFoundException
+    from alluxio_b200.page_store import PageId
+    rnd = random.Random(5)
+    m = MetaStore("LRU")
+    model = OrderedDict()          # id -> size, in recency order (put and getPageInfo refresh, hasPage does not)
+    ids = [PageId(str(f), i) for f in range(13) for i in range(40)]
+    for step in range(30000):
+        p = rnd.choice(ids)
+        k = (p.file_id, p.page_index)
+        op = rnd.random()
+        if op < 0.40:
+            if k not in model:
+                size = rnd.randrange(1, 5000)
+                m.add_page(p, size)
+                model[k] = size
+        elif op < 0.65:
+            if k in model:
+                m.remove_page(p)
+                del model[k]
+            else:
+                with pytest.raises(PageNotFoundException):
+                    m.remove_page(p)
+        elif op < 0.85:
+            assert m.has_page(p) == (k in model)
+            if k in model:
+                assert m.get_page_info(p)[1] == model[k]
+                model.move_to_end(k)
+        else:
+            v = m.evict()
+            if not model:
+                assert v is None
+            else:
+                head = next(iter(model))
+                assert (v[0].file_id, v[0].page_index) == head and v[1] == model[head]
+        if step % 997 == 0:
+            assert m.pages() == len(model) and m.bytes() == sum(model.values())
+    assert m.pages() == len(model) and m.bytes() == sum(model.values())
