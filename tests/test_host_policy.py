@@ -169,3 +169,32 @@ def test_meta_store_random_ops_match_a_dict():
         if step % 997 == 0:
             assert m.pages() == len(model) and m.bytes() == sum(model.values())
     assert m.pages() == len(model) and m.bytes() == sum(model.values())
+
+
+@pytest.mark.parametrize("kind,base", [("LRU", 2.0), ("LFU", 2.0), ("LFU", 1.5), ("LFU", 10.0)])
+def test_evictors_follow_the_oracle_through_random_sequences(kind, base):
+    """Product evictor against the oracle's restatement of the reference's, step by step: same victim after every
+    update, including deletes of unknown ids, repeated gets (LFU bucket moves) and resets."""
+    import random
+    from alluxio_b200.cache import CacheEvictor
+    from alluxio_b200.page_store import PageId
+    from oracle import binding as orc
+    rnd = random.Random(hash((kind, base)) & 0xFFFF)
+    ours, ref = CacheEvictor(kind, base), orc.Evictor(kind, base)
+    ids = [(str(f), i) for f in range(6) for i in range(25)]
+    for step in range(20000):
+        f, i = rnd.choice(ids)
+        a, b = PageId(f, i), orc.PageId(f, i)
+        op = rnd.random()
+        if op < 0.35:
+            ours.update_on_put(a); ref.update_on_put(b)
+        elif op < 0.75:
+            ours.update_on_get(a); ref.update_on_get(b)
+        elif op < 0.995:
+            ours.update_on_delete(a); ref.update_on_delete(b)
+        else:
+            ours.reset(); ref.reset()
+        va, vb = ours.evict(), ref.evict()
+        assert (va is None) == (vb is None), step
+        if va is not None:
+            assert (va.file_id, va.page_index) == (vb.file_id, vb.page_index), step
