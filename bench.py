@@ -551,6 +551,21 @@ def run_ours(args):
         threads = os.cpu_count() or 1
         gbps_c, _, desc = cpu_reference_run(steps=int(os.environ.get("APS_CPU_STEPS", "40")), warmup=2, threads=threads)
         cpu = {"value": round(gbps_c, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
+        # SURVEY.md 8d asks for one thread as well, and for the CPU CRC32C rate (not reference-derived: the reference
+        # has no CRC) so that the fused checksum has something on the host to stand beside
+        g1, _, _ = cpu_reference_run(steps=4, warmup=1, threads=1)
+        cpu["one_thread_value"] = round(g1, 3)
+        blob = orc.fill_page(DATA_SEED, 1, 1, 64 << 20)
+        rates = {}
+        for impl in ("sb8", "hw"):
+            try:
+                t0 = time.perf_counter()
+                orc.crc32c(blob, impl)
+                rates[impl] = round(blob.nbytes / (time.perf_counter() - t0) / 1e9, 2)
+            except Exception:
+                pass
+        cpu["crc32c_one_thread_GBps"] = rates
+        cpu["crc32c_note"] = "slicing-by-8 / SSE4.2 CRC32C of 64 MiB on one host core; not part of the reference path"
 
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(peaks_path):
