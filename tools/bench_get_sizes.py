@@ -34,7 +34,7 @@ def main():
         n_res, batch = resident_bytes // page, step_bytes // page
         fill_batch = min(n_res, max(batch, 4096))
         cfg = capi.aps_config(device=0, page_size=page, cache_bytes=n_res * page, slab_slots=n_res + 64, table_capacity=0,
-                              max_batch=fill_batch, flags=0 if os.environ.get('APS_SIZES_NOCRC') == '1' else capi.APS_FLAG_CRC)
+                              max_batch=fill_batch, flags=(0 if os.environ.get('APS_SIZES_NOCRC') == '1' else capi.APS_FLAG_CRC) | capi.APS_FLAG_STABLE_REQS)
         h = C.c_void_p()
         capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "open")
         stage = torch.empty(fill_batch * page, dtype=torch.uint8, device=dev)
@@ -71,7 +71,7 @@ def main():
         out = gu.from_dev(d_res, gu.RESULT)
         p = int(picks[3, 7])
         want = orc.fill_page(21, p // 4096, p % 4096, page)
-        ok = bool((out["len"] == page).all()) and (cfg.flags == 0 or int(out["crc"][7]) == orc.crc32c(want)) and \
+        ok = bool((out["len"] == page).all()) and (not (cfg.flags & capi.APS_FLAG_CRC) or int(out["crc"][7]) == orc.crc32c(want)) and \
             np.array_equal(dst[7 * page:8 * page].cpu().numpy(), want)
         l0 = L.aps_total_kernel_launches()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
