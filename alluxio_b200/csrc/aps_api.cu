@@ -229,6 +229,7 @@ struct aps_store {
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
   bool use_steal = true;  // APS_NO_STEAL=1 turns intra-CTA work stealing off
+  bool use_early = true;        // APS_NO_EARLY=1: every kernel waits for its predecessor before it reads anything
   bool use_table_image = true;  // APS_NO_TABLE_IMAGE=1: build the shared-memory CRC tables with plain loads
   uint32_t prefetch_rows = 48;  // rows a waiting warp prefetches into L2 (APS_PF_ROWS overrides; 0/16/32/48/64/96 rows
                                 // measured 0.892/0.900/0.913/0.9175/0.9165/0.908 of the HBM peak)
@@ -299,8 +300,9 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   const bool is_get = d_get_reqs != nullptr;
   // (A sharded get also reads its peers' tables and slabs.  Those are not ordered against this stream in any case --
   // keeping puts on one GPU apart from gets on another is the caller's job -- so reading them early changes nothing.)
-  a.early = (is_get && (s->cfg.flags & APS_FLAG_STABLE_REQS) && s->last_was_get && s->last_stream == st && s->use_pdl &&
-             !s->d_timeline) ? 1 + (sharded ? 0 : (int)s->prefetch_rows) : 0;  // no L2 prefetch of peer memory: measured 18x slower
+  a.early = (is_get && s->last_was_get && s->last_stream == st && s->use_pdl && !s->d_timeline && s->use_early)
+                ? 1 + (sharded ? 0 : (int)s->prefetch_rows) : 0;  // no L2 prefetch of peer memory: measured 18x slower
+  a.trust_reqs = (s->cfg.flags & APS_FLAG_STABLE_REQS) != 0;
   s->last_was_get = is_get;
   s->last_stream = st;
   if (use_tma_variant() || s->use_tma) {
@@ -592,6 +594,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   s->use_steal = getenv("APS_NO_STEAL") == nullptr;
   s->use_table_image = getenv("APS_NO_TABLE_IMAGE") == nullptr;
   s->use_d2h_stage = getenv("APS_NO_D2H_STAGE") == nullptr;
+  s->use_early = getenv("APS_NO_EARLY") == nullptr;
   s->fused_put = getenv("APS_NO_FUSED_PUT") == nullptr;
   if (const char* pf = getenv("APS_PF_ROWS")) s->prefetch_rows = (uint32_t)std::min(256, std::max(0, atoi(pf)));
   s->use_tma = (cfg->flags & APS_FLAG_TMA_COPY) != 0 && (cfg->flags & APS_FLAG_CRC) == 0;

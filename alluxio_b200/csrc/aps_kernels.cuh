@@ -238,6 +238,7 @@ struct CopyArgs {
   const aps_put_req* preqs;  // kPut == true: put requests; task 0 of a page inserts it, the others wait for its slot
   unsigned long long* jslot; // kPut scratch, one word per job: launch epoch << 32 | (slot + 1, or 0x80000000 | status)
   uint32_t epoch;            // kPut: this launch's number (never 0), so the words above need no reset
+  int trust_reqs;            // kGet with early: the caller promised that request arrays are final (APS_FLAG_STABLE_REQS)
   Table table;
   int crc_on;
   uint32_t n_jobs;
@@ -431,29 +432,51 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       const uint32_t c = item - job * a.tasks_per_job;
       if (kGet) {
         // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
-        const aps_get_req rq = a.reqs[job];
-        // sharded cache: the page lives on GPU shard_of(key); its table and slab are read in place over
-        // NVLink (P2P), so lookup, gather and CRC stay one kernel on the requesting GPU
-        const Table tb = a.n_shards > 1 ? a.shards[shard_of(rq.key, a.n_shards)] : a.table;
+        aps_get_req rq = a.reqs[job];
         Probe pr{0, 0, 0, 0};
-        if (lane < 8) pr = tile_lookup(tb, rq.key, lane, 0);
-        __syncwarp();
-        const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
         int32_t status = 0;
-        j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
-        if (!meta) {
-          status = -APS_ENOTFOUND;
-        } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
-          status = -APS_EINVAL;
-        } else {
-          const uint32_t plen = meta_len(meta);
-          j.slot = meta_slot(meta);
-          j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
-          j.src = tb.slab + (uint64_t)j.slot * tb.page_size + rq.page_off;
-          j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;  // which shard's slot_crc to check
-          j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
-          status = (int32_t)j.n;
-          if (c == 0 && lane == 0 && tb.slot_ref) tb.slot_ref[j.slot] = 1;  // CLOCK: referenced (a store that commutes)
+        for (;;) {
+          // sharded cache: the page lives on GPU shard_of(key); its table and slab are read in place over
+          // NVLink (P2P), so lookup, gather and CRC stay one kernel on the requesting GPU
+          const Table tb = a.n_shards > 1 ? a.shards[shard_of(rq.key, a.n_shards)] : a.table;
+          pr = Probe{0, 0, 0, 0};
+          if (lane < 8) pr = tile_lookup(tb, rq.key, lane, 0);
+          __syncwarp();
+          const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
+          status = 0;
+          j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
+          if (!meta) {
+            status = -APS_ENOTFOUND;
+          } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
+            status = -APS_EINVAL;
+          } else {
+            const uint32_t plen = meta_len(meta);
+            j.slot = meta_slot(meta);
+            j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
+            j.src = tb.slab + (uint64_t)j.slot * tb.page_size + rq.page_off;
+            j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;  // which shard's slot_crc to check
+            j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
+            status = (int32_t)j.n;
+            if (c == 0 && lane == 0 && tb.slot_ref) tb.slot_ref[j.slot] = 1;  // CLOCK: referenced (a store that commutes)
+          }
+          if (dep_ok || a.trust_reqs) break;
+          // Early, but the request array is not promised to be final yet (no APS_FLAG_STABLE_REQS): use what was read
+          // only to warm L2 with the rows this task will want, wait for the predecessor, then read the request again.
+          // If it is unchanged the resolution above stands; otherwise it is redone, now behind the gate.
+          if (j.n && a.n_shards <= 1) {
+            const uint32_t rows_full = j.n / kRowBytes, lo = min(rows_full, c * a.rows_per_task);
+            const uint32_t cnt = min(min(rows_full, lo + a.rows_per_task) - lo, (uint32_t)a.early - 1u + (uint32_t)G);
+            const uint8_t* p0 = j.src + (size_t)lo * kRowBytes;
+            for (uint32_t l = lane; l < cnt * (kRowBytes / 128u); l += 32u)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + (size_t)l * 128u));
+          }
+          gate();
+          const aps_get_req again = a.reqs[job];
+          const bool same = again.key.file_hi == rq.key.file_hi && again.key.file_lo == rq.key.file_lo &&
+                            again.key.page_index == rq.key.page_index && again.page_off == rq.page_off &&
+                            again.nbytes == rq.nbytes && again.dst == rq.dst;
+          if (same) break;
+          rq = again;
         }
         if (c == 0 && lane == 0) {
           atomicAdd(&a.table.counters[kCtrLookups], 1ull);

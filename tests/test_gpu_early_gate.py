@@ -46,11 +46,17 @@ def _get_reqs(files, idx, dst, nbytes=PAGE):
 
 
 @pytest.mark.parametrize("crc", [True, False])
-def test_interleavings_match_a_store_without_the_flag(crc):
+def test_interleavings_match_a_store_without_the_flag(crc, monkeypatch):
     L = capi.lib()
     base = capi.APS_FLAG_CRC if crc else 0
     outs = []
-    for flags in (base, base | capi.APS_FLAG_STABLE_REQS):
+    # three stores: every kernel waits first (APS_NO_EARLY=1); early with re-validated requests (the default); early
+    # with trusted requests (the flag)
+    for flags, no_early in ((base, True), (base, False), (base | capi.APS_FLAG_STABLE_REQS, False)):
+        if no_early:
+            monkeypatch.setenv("APS_NO_EARLY", "1")
+        else:
+            monkeypatch.delenv("APS_NO_EARLY", raising=False)
         h = _open(flags)
         stage = torch.empty(N * PAGE, dtype=torch.uint8, device="cuda:0")
         dst = torch.zeros(N * PAGE, dtype=torch.uint8, device="cuda:0")
@@ -92,11 +98,12 @@ def test_interleavings_match_a_store_without_the_flag(crc):
         capi.check(L.aps_stats(h, C.byref(st)))
         assert st.crc_mismatches == 0
         capi.check(L.aps_close(h))
-    (res0, snap0), (res1, snap1) = outs
-    for a, b in zip(res0, res1):
-        assert np.array_equal(a["len"], b["len"]) and np.array_equal(a["crc"], b["crc"])
-    for a, b in zip(snap0, snap1):
-        assert np.array_equal(a, b)
+    (res0, snap0), (res1, snap1) = outs[0], outs[2]
+    for other_res, other_snap in outs[1:]:
+        for a, b in zip(res0, other_res):
+            assert np.array_equal(a["len"], b["len"]) and np.array_equal(a["crc"], b["crc"])
+        for a, b in zip(snap0, other_snap):
+            assert np.array_equal(a, b)
     # and against the oracle: after "get A, get B" the destination holds B's pages
     lens = np.where(np.arange(N) % 7 == 3, 1000 + np.arange(N), PAGE)
     for i in (0, 3, 10, N - 1):
@@ -146,6 +153,41 @@ def test_many_back_to_back_gets_large_pages():
     got = dst.cpu().numpy().reshape(batch, page)
     src = stage.cpu().numpy().reshape(n_res, page)
     assert np.array_equal(got, src[picks[39].astype(np.int64)])                 # the last get's bytes
+    st = capi.aps_stats_t()
+    capi.check(L.aps_stats(h, C.byref(st)))
+    assert st.crc_mismatches == 0
+    capi.check(L.aps_close(h))
+
+
+def test_requests_rewritten_on_the_stream_between_gets_are_honoured():
+    """Without APS_FLAG_STABLE_REQS a get may read its requests early, but must not trust them: here the request
+    array is overwritten by a kernel on the same stream right before every get (the early read can only see the
+    previous batch), and every get must serve the batch that is current when its turn comes."""
+    L = capi.lib()
+    h = _open(capi.APS_FLAG_CRC)
+    stage = torch.empty(N * PAGE, dtype=torch.uint8, device="cuda:0")
+    files = np.arange(N, dtype=np.uint64) % 5
+    idx = np.arange(N, dtype=np.uint64)
+    lens = np.full(N, PAGE, np.uint32)
+    keep = [_put(h, files + 10 * s_, idx, lens, 40 + s_, stage) for s_ in range(4)]
+    dsts = [torch.zeros(N * PAGE, dtype=torch.uint8, device="cuda:0") for _ in range(4)]
+    batches = [_get_reqs(files + 10 * s_, idx, dsts[s_]) for s_ in range(4)]
+    live = torch.zeros_like(batches[0])
+    res = [torch.zeros(N * 8, dtype=torch.uint8, device="cuda:0") for _ in range(12)]
+    sp = gu.cur_stream()
+    torch.cuda.synchronize()
+    for k in range(12):
+        live.copy_(batches[k % 4])                          # a kernel on the same stream rewrites the requests ...
+        capi.check(L.aps_get_batch_dev(h, N, live.data_ptr(), res[k].data_ptr(), sp))   # ... that this get must use
+    torch.cuda.synchronize()
+    put_crc = [gu.from_dev(keep[s_][1], gu.RESULT)["crc"].copy() for s_ in range(4)]
+    for k in range(12):
+        r = gu.from_dev(res[k], gu.RESULT)
+        assert (r["len"] == PAGE).all() and np.array_equal(r["crc"], put_crc[k % 4]), k
+    for s_ in range(4):
+        got = dsts[s_].cpu().numpy()
+        for i in (0, N - 1):
+            assert np.array_equal(got[i * PAGE:(i + 1) * PAGE], orc.fill_page(40 + s_, int(files[i]) + 10 * s_, i, PAGE))
     st = capi.aps_stats_t()
     capi.check(L.aps_stats(h, C.byref(st)))
     assert st.crc_mismatches == 0
