@@ -303,6 +303,8 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.early = (is_get && s->last_was_get && s->last_stream == st && s->use_pdl && !s->d_timeline && s->use_early)
                 ? 1 + (sharded ? 0 : (int)s->prefetch_rows) : 0;  // no L2 prefetch of peer memory: measured 18x slower
   a.trust_reqs = (s->cfg.flags & APS_FLAG_STABLE_REQS) != 0;
+  // a fused put only prefetches its sources before it waits, which is safe after any predecessor
+  if (d_put_reqs && s->use_pdl && !s->d_timeline && s->use_early) a.early = 1 + (int)s->prefetch_rows;
   s->last_was_get = is_get;
   s->last_stream = st;
   if (use_tma_variant() || s->use_tma) {

@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   // flight before it waits: the three dependent memory round trips of a task's start-up (request, bucket,
   // first rows) then overlap the previous kernel's tail instead of following it.  Everything this kernel
   // WRITES (pages, results, scratch, the rank counters) stays behind the gate.
-  bool dep_ok = !(kGet && a.early);
+  bool dep_ok = !((kGet || kPut) && a.early);
   if (dep_ok) asm volatile("griddepcontrol.wait;" ::: "memory");
   const uint32_t n_items = a.n_jobs * a.tasks_per_job;
   // Task assignment.  n_items / grid tasks per CTA are fixed by blockIdx, so warps can start at once.  The
@@ -491,7 +491,21 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         // slot with the first eight lanes and publishes the outcome; the page's other tasks, which start at the
         // same moment on other warps, pick it up from a.jslot.  Task 0 never waits for anybody, and a page's task
         // 0 always precedes its other tasks in every warp's list, so the waiting cannot cycle.
-        const aps_put_req rq = a.preqs[job];
+        aps_put_req rq = a.preqs[job];
+        if (!dep_ok) {
+          // A put cannot touch the table before its predecessor is done, but it can warm L2 with the source rows this
+          // task will copy (a prefetch of whatever address the possibly unfinished request names is harmless), then
+          // wait, then read the request for good.
+          if (rq.src && rq.len <= a.table.page_size) {
+            const uint32_t rows_full = rq.len / kRowBytes, lo = min(rows_full, c * a.rows_per_task);
+            const uint32_t cnt = min(min(rows_full, lo + a.rows_per_task) - lo, (uint32_t)a.early - 1u + (uint32_t)G);
+            const uint8_t* p0 = (const uint8_t*)rq.src + (size_t)lo * kRowBytes;
+            for (uint32_t l = lane; l < cnt * (kRowBytes / 128u); l += 32u)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + (size_t)l * 128u));
+          }
+          gate();
+          rq = a.preqs[job];
+        }
         const Table& t = a.table;
         unsigned long long word = 0;
         if (c == 0) {
