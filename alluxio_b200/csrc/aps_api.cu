@@ -229,6 +229,8 @@ struct aps_store {
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
   bool use_steal = true;  // APS_NO_STEAL=1 turns intra-CTA work stealing off
+  bool host_form = false;       // set around launches made by the host-array entry points: their predecessor on the
+                                // stream is a copy, not a kernel, so there is nothing to overlap with
   bool use_early = true;        // APS_NO_EARLY=1: every kernel waits for its predecessor before it reads anything
   bool use_table_image = true;  // APS_NO_TABLE_IMAGE=1: build the shared-memory CRC tables with plain loads
   uint32_t prefetch_rows = 48;  // rows a waiting warp prefetches into L2 (APS_PF_ROWS overrides; 0/16/32/48/64/96 rows
@@ -300,11 +302,11 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   const bool is_get = d_get_reqs != nullptr;
   // (A sharded get also reads its peers' tables and slabs.  Those are not ordered against this stream in any case --
   // keeping puts on one GPU apart from gets on another is the caller's job -- so reading them early changes nothing.)
-  a.early = (is_get && s->last_was_get && s->last_stream == st && s->use_pdl && !s->d_timeline && s->use_early)
+  a.early = (is_get && s->last_was_get && s->last_stream == st && s->use_pdl && !s->d_timeline && s->use_early && !s->host_form)
                 ? 1 + (sharded ? 0 : (int)s->prefetch_rows) : 0;  // no L2 prefetch of peer memory: measured 18x slower
   a.trust_reqs = (s->cfg.flags & APS_FLAG_STABLE_REQS) != 0;
   // a fused put only prefetches its sources before it waits, which is safe after any predecessor
-  if (d_put_reqs && s->use_pdl && !s->d_timeline && s->use_early) a.early = 1 + (int)s->prefetch_rows;
+  if (d_put_reqs && s->use_pdl && !s->d_timeline && s->use_early && !s->host_form) a.early = 1 + (int)s->prefetch_rows;
   s->last_was_get = is_get;
   s->last_stream = st;
   if (use_tma_variant() || s->use_tma) {
@@ -838,8 +840,10 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   if (via_stage)
     for (uint32_t i = 0; i < n; ++i) h_reqs[i].dst = s->d_d2h_stage + (uint64_t)i * slot;
   CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
+  s->host_form = true;
   rc = sharded ? aps_get_batch_sharded_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st)
                : aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
+  s->host_form = false;
   if (rc) return rc;
   CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
   rc = check_device_error(s, st);  // also waits for the stream
@@ -876,7 +880,9 @@ int aps_put_batch(aps_store* s, uint32_t n, const aps_put_req* reqs, aps_result*
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_put_req));
   CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_put_req), cudaMemcpyHostToDevice, st));
+  s->host_form = true;
   rc = aps_put_batch_dev(s, n, (const aps_put_req*)s->d_reqs, s->d_res, st);
+  s->host_form = false;
   if (rc) return rc;
   CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
   rc = check_device_error(s, st);
@@ -940,7 +946,9 @@ int aps_put(aps_store* s, const aps_key* key, const void* src, uint32_t len) {
   // One page, one launch, no staging copies: the kernel reads the request from, and writes the result to, the
   // pinned staging area itself (page-locked host memory is device-visible), so a call costs a launch and a sync.
   *h_req = rq;
+  s->host_form = true;
   rc = s->fused_put ? aps_put_batch_dev(s, 1, h_req, h_res, s->stream) : APS_EINVAL;
+  s->host_form = false;
   if (!s->fused_put) {
     CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_req, sizeof(rq), cudaMemcpyHostToDevice, s->stream));
     rc = aps_put_batch_dev(s, 1, (const aps_put_req*)s->d_reqs, s->d_res, s->stream);
@@ -969,7 +977,9 @@ int aps_get(aps_store* s, const aps_key* key, uint32_t page_off, uint32_t bytes_
   aps_get_req* h_req = reinterpret_cast<aps_get_req*>(s->h_stage);
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   *h_req = rq;
+  s->host_form = true;
   rc = aps_get_batch_dev(s, 1, h_req, h_res, s->stream);  // request and result stay in the pinned staging area (see aps_put)
+  s->host_form = false;
   if (rc) return rc;
   rc = check_device_error(s, s->stream);
   if (rc) return rc;
