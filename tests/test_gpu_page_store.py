@@ -170,7 +170,7 @@ def test_no_space_is_an_io_exception():
     s.close()
 
 
-@pytest.mark.parametrize("page_size", [1024, 65536])
+@pytest.mark.parametrize("page_size", [48, 1024, 4112, 65536, 1000 * 16])
 def test_random_ops_match_oracle_local_page_store(page_size, tmp_path):
     """Same random put/get/delete sequence into GpuPageStore and the oracle's LocalPageStore:
     every status, length, byte and CRC must agree."""
@@ -179,7 +179,7 @@ def test_random_ops_match_oracle_local_page_store(page_size, tmp_path):
     gpu = GpuPageStore(page_size=page_size, cache_size=64 * page_size, slab_slots=128)
     ref = orc.PageStore.create_local(tmp_path, page_size=page_size, cache_size=64 * page_size)
     ids = [(str(f), i) for f in range(4) for i in range(12)]
-    lens = [0, 1, 15, 16, 17, 511, 512, 513, page_size - 1, page_size]
+    lens = [n for n in (0, 1, 15, 16, 17, 511, 512, 513, page_size - 1, page_size) if n <= page_size]
     resident = 0
     for step in range(600):
         f, i = ids[rng.integers(len(ids))]
