@@ -103,14 +103,14 @@ def test_full_pages_1mib_put_get_bytes_and_crc():
     store.close()
 
 
-def test_ragged_lengths_offsets_misses_and_unaligned_destinations():
+@pytest.mark.parametrize("ps", [65536, 4112, 16000, 48])
+def test_ragged_lengths_offsets_misses_and_unaligned_destinations(ps):
     from alluxio_b200 import capi
     from alluxio_b200.page_store import PageId
     torch = torch_mod()
-    ps = 65536
     store = make_store(page_size=ps, cache_size=64 * ps, slab_slots=128)
     rng = np.random.default_rng(2)
-    lens = [0, 1, 15, 16, 17, 511, 512, 513, 16383, 16384, 16385, 32768, ps - 1, ps, 40000, 4097]
+    lens = [n for n in (0, 1, 15, 16, 17, 511, 512, 513, 16383, 16384, 16385, 32768, ps - 1, ps, 40000, 4097) if n <= ps]
     n = len(lens)
     pids = [PageId("77", i) for i in range(n)]
     payload = [rng.integers(0, 256, l, dtype=np.uint8) for l in lens]
