@@ -10,6 +10,8 @@ import alluxio.client.file.cache.PageStore;
 import alluxio.exception.PageNotFoundException;
 
 import com.google.common.base.Preconditions;
+import org.slf4j.Logger;
+import org.slf4j.LoggerFactory;
 
 import java.io.IOException;
 import java.nio.ByteBuffer;
@@ -23,6 +25,8 @@ import java.util.stream.Stream;
  * C ABI of include/aps.h reached through the thin JNI shim integration/jni/aps_jni.c.
  */
 public class GpuPageStore implements PageStore {
+  private static final Logger LOG = LoggerFactory.getLogger(GpuPageStore.class);
+
   static {
     System.loadLibrary("aps_jni"); // links against libaps.so
   }
@@ -40,6 +44,7 @@ public class GpuPageStore implements PageStore {
   private final List<String> mInternedNames = new ArrayList<>();
   /** One pinned direct buffer per thread: byte[] <-> device staging without per-call allocation. */
   private final ThreadLocal<ByteBuffer> mStaging;
+  private final String mSnapshotPath;
 
   public GpuPageStore(GpuPageStoreOptions options) throws IOException {
     mCacheSize = options.getCacheSize();
@@ -52,6 +57,15 @@ public class GpuPageStore implements PageStore {
     }
     mHandle = handle[0];
     mStaging = ThreadLocal.withInitial(() -> nativeAllocPinned(mPageSize));
+    mSnapshotPath = options.getSnapshotPath();
+    if (mSnapshotPath != null && new java.io.File(mSnapshotPath).exists()) {
+      // warm restart: getPages() then lists these pages and LocalCacheManager.restore adopts them
+      long[] counts = new long[2];
+      rc = nativeSnapshotLoad(mHandle, mSnapshotPath, counts);
+      if (rc != OK) {
+        LOG.warn("ignoring snapshot {}: {}", mSnapshotPath, nativeStrError(rc));
+      }
+    }
   }
 
   /** PageId -> (fileHi, fileLo): disjoint ranges, so equal keys imply equal strings. */
@@ -157,6 +171,12 @@ public class GpuPageStore implements PageStore {
 
   @Override
   public void close() {
+    if (mSnapshotPath != null) {
+      int rc = nativeSnapshotSave(mHandle, mSnapshotPath);
+      if (rc != OK) {
+        LOG.warn("could not save snapshot {}: {}", mSnapshotPath, nativeStrError(rc));
+      }
+    }
     nativeClose(mHandle);
   }
 
@@ -172,4 +192,6 @@ public class GpuPageStore implements PageStore {
   private static native long[] nativeIterate(long handle);
   private static native ByteBuffer nativeAllocPinned(int bytes);
   private static native String nativeStrError(int code);
+  private static native int nativeSnapshotSave(long handle, String path);
+  private static native int nativeSnapshotLoad(long handle, String path, long[] loadedAndRejected);
 }

@@ -13,12 +13,16 @@ public class GpuPageStoreOptions extends PageStoreOptions {
   private long mTableCapacity = 0;  // 0 = 2 x slots, rounded up to a power of two
   private int mMaxBatch = 4096;
   private boolean mCrcEnabled = true;
+  /** alluxio.user.client.cache.gpu.snapshot.path: where close() saves and open loads the pages; null = volatile. */
+  private String mSnapshotPath = null;
 
   public GpuPageStoreOptions setDevice(int device) { mDevice = device; return this; }
   public GpuPageStoreOptions setSlabSlots(long slots) { mSlabSlots = slots; return this; }
   public GpuPageStoreOptions setTableCapacity(long entries) { mTableCapacity = entries; return this; }
   public GpuPageStoreOptions setMaxBatch(int n) { mMaxBatch = n; return this; }
   public GpuPageStoreOptions setCrcEnabled(boolean on) { mCrcEnabled = on; return this; }
+  public GpuPageStoreOptions setSnapshotPath(String path) { mSnapshotPath = path; return this; }
+  public String getSnapshotPath() { return mSnapshotPath; }
   public int getDevice() { return mDevice; }
   public long getSlabSlots() { return mSlabSlots; }
   public long getTableCapacity() { return mTableCapacity; }

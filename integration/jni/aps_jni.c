@@ -93,3 +93,28 @@ JNIEXPORT jobject JNICALL JFN(nativeAllocPinned)(JNIEnv* env, jclass cls, jint b
 JNIEXPORT jstring JNICALL JFN(nativeStrError)(JNIEnv* env, jclass cls, jint code) {
   return (*env)->NewStringUTF(env, aps_strerror(code));
 }
+
+JNIEXPORT jint JNICALL JFN(nativeSnapshotSave)(JNIEnv* env, jclass cls, jlong handle, jstring path) {
+  const char* p = (*env)->GetStringUTFChars(env, path, NULL);
+  int rc;
+  (void)cls;
+  if (!p) return APS_ENOMEM;
+  rc = aps_snapshot_save((aps_store*)(intptr_t)handle, p, NULL);
+  (*env)->ReleaseStringUTFChars(env, path, p);
+  return rc;
+}
+
+JNIEXPORT jint JNICALL JFN(nativeSnapshotLoad)(JNIEnv* env, jclass cls, jlong handle, jstring path, jlongArray counts) {
+  const char* p = (*env)->GetStringUTFChars(env, path, NULL);
+  uint64_t loaded = 0, rejected = 0;
+  jlong out[2];
+  int rc;
+  (void)cls;
+  if (!p) return APS_ENOMEM;
+  rc = aps_snapshot_load((aps_store*)(intptr_t)handle, p, &loaded, &rejected);
+  (*env)->ReleaseStringUTFChars(env, path, p);
+  out[0] = (jlong)loaded;
+  out[1] = (jlong)rejected;
+  (*env)->SetLongArrayRegion(env, counts, 0, 2, out);
+  return rc;
+}
