@@ -1,0 +1,21 @@
+/* Minimal stand-in for the JDK's jni.h (absent from this image), just enough to type-check integration/jni/aps_jni.c
+ * against include/aps.h in tests/test_c_abi.py.  Declares only what the shim uses; not a JNI implementation. */
+#include <stdint.h>
+typedef int32_t jint; typedef int64_t jlong; typedef signed char jbyte; typedef unsigned char jboolean;
+typedef void* jobject; typedef jobject jclass; typedef jobject jstring; typedef jobject jarray; typedef jarray jintArray;
+typedef jarray jlongArray; typedef jarray jbyteArray; typedef jint jsize;
+#define JNIEXPORT
+#define JNICALL
+struct JNINativeInterface_;
+typedef const struct JNINativeInterface_* JNIEnv;
+struct JNINativeInterface_ {
+  void* (*GetDirectBufferAddress)(JNIEnv*, jobject);
+  jlong (*GetDirectBufferCapacity)(JNIEnv*, jobject);
+  void (*SetIntArrayRegion)(JNIEnv*, jintArray, jsize, jsize, const jint*);
+  void (*SetLongArrayRegion)(JNIEnv*, jlongArray, jsize, jsize, const jlong*);
+  jlongArray (*NewLongArray)(JNIEnv*, jsize);
+  jobject (*NewDirectByteBuffer)(JNIEnv*, void*, jlong);
+  jstring (*NewStringUTF)(JNIEnv*, const char*);
+  const char* (*GetStringUTFChars)(JNIEnv*, jstring, jboolean*);
+  void (*ReleaseStringUTFChars)(JNIEnv*, jstring, const char*);
+};

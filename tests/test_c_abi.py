@@ -42,3 +42,14 @@ def test_c_example_links_against_libaps(tmp_path):
 def test_c_example_runs(tmp_path):
     out = subprocess.run([_build_example(tmp_path)], capture_output=True, timeout=120)
     assert out.returncode == 0 and out.stdout.strip() == b"ok", out.stderr
+
+
+def test_jni_shim_type_checks_against_the_abi(tmp_path):
+    """The JNI shim of INTEGRATION.md cannot be built for real here (no JDK), but its calls into include/aps.h can be
+    type-checked: compile it against a minimal stand-in jni.h."""
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime_api.h")):
+        pytest.skip("no CUDA headers")
+    subprocess.run([_gcc(), "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "tests", "jni_stub"), "-I",
+                    os.path.join(ROOT, "include"), "-I", cuda_inc, "-c", os.path.join(ROOT, "integration", "jni", "aps_jni.c"),
+                    "-o", str(tmp_path / "aps_jni.o")], check=True, capture_output=True)
