@@ -38,6 +38,7 @@ SIGNATURES = {
     "apc_stream_get_pos": (_i64, [_vp]),
     "apc_stream_bypass": (C.c_int, [_vp]),
     "apc_stream_counters": (None, [_vp, _vp]),
+    "apc_stream_set_batched": (None, [_vp, C.c_int]),
     "apc_stream_close": (None, [_vp]),
     "apc_stream_destroy": (None, [_vp]),
     "apc_manager_create": (C.c_int, [C.POINTER(capi.aps_config), _cp, _dbl, C.POINTER(_vp)]),
@@ -477,6 +478,10 @@ class LocalCacheFileInStream:
         r = lib().apc_stream_positioned_read(self._h, pos, C.addressof(cbuf), len(b), off, length)
         del cbuf
         return self._result(r, b, off)
+
+    def set_batched(self, on=True):
+        """one batched store call per read instead of one get per page."""
+        lib().apc_stream_set_batched(self._h, int(on))
 
     def skip(self, n):
         r = lib().apc_stream_skip(self._h, n)

@@ -882,12 +882,87 @@ bool LocalCacheManager::Restore() {  // :466-509
   return true;
 }
 
+// ================================================================================ batched read
+
+// One read of [pos, pos + len) of a file through the cache with ONE batched store call for all resident pages it
+// touches: page read-locks in id order, residency from the meta store, a single GetBatch into a pinned staging
+// area, the rest fetched whole from `external` and offered to the cache -- same bytes and cache effects as the
+// per-page loop of LocalCacheFileInStream.positionedRead (:175-223).  *stage is a pinned buffer the caller keeps
+// between calls (grown here when too small).
+int32_t BatchedRead(LocalCacheManager* mgr, const std::string& fileId, int64_t fileLen, int64_t pos, uint8_t* dst, int32_t len,
+                    ExternalRead external, void* user, void** stage, uint64_t* stageBytes, int64_t* fromCache,
+                    int64_t* fromExternal, int64_t* readExternal) {
+  if (len < 0 || pos < 0) return kGetIllegalArgument;
+  if (len == 0) return 0;
+  if (pos >= fileLen) return -1;
+  const int64_t ps = mgr->pageSize();
+  const int64_t toRead = std::min<int64_t>(len, fileLen - pos);
+  const int64_t firstPage = pos / ps, lastPage = (pos + toRead - 1) / ps;
+  const int32_t n = (int32_t)(lastPage - firstPage + 1);
+  if (*stageBytes < (uint64_t)toRead) {
+    if (*stage) aps_host_free_pinned(*stage);
+    *stage = nullptr;
+    *stageBytes = 0;
+    const uint64_t want = std::max<uint64_t>((uint64_t)toRead, 1u << 20);
+    if (aps_host_alloc_pinned(want, stage) != APS_OK) return -1;
+    *stageBytes = want;
+  }
+  std::vector<int32_t> off((size_t)n), ln((size_t)n), got((size_t)n);
+  std::vector<void*> dsts((size_t)n);
+  int64_t cur = pos, done = 0;
+  for (int32_t i = 0; i < n; ++i) {
+    off[(size_t)i] = (int32_t)(cur % ps);
+    ln[(size_t)i] = (int32_t)std::min<int64_t>(ps - off[(size_t)i], toRead - done);
+    dsts[(size_t)i] = (uint8_t*)*stage + done;
+    cur += ln[(size_t)i];
+    done += ln[(size_t)i];
+  }
+  mgr->GetMany(fileId, firstPage, n, off.data(), ln.data(), dsts.data(), got.data());
+  std::vector<uint8_t> page;
+  int32_t result = (int32_t)toRead;
+  done = 0;
+  for (int32_t i = 0; i < n && result >= 0; ++i) {
+    uint8_t* out = dst + done;
+    if (got[(size_t)i] > 0) {
+      memcpy(out, dsts[(size_t)i], (size_t)ln[(size_t)i]);
+      mgr->metrics.bytesReadCache += ln[(size_t)i];
+      *fromCache += ln[(size_t)i];
+    } else {
+      const int64_t pageStart = (firstPage + i) * ps;
+      const int32_t plen = (int32_t)std::min<int64_t>(ps, fileLen - pageStart);
+      page.resize((size_t)plen);
+      int32_t have = 0;
+      while (have < plen) {
+        const int r = external(user, pageStart + have, page.data() + have, plen - have);
+        if (r <= 0) break;
+        have += r;
+      }
+      mgr->metrics.bytesReadExternal += have;
+      *readExternal += have;
+      if (have != plen) {
+        result = -3;  // "Failed to read complete page from external storage"
+        break;
+      }
+      memcpy(out, page.data() + off[(size_t)i], (size_t)ln[(size_t)i]);
+      mgr->metrics.bytesRequestedExternal += ln[(size_t)i];
+      *fromExternal += ln[(size_t)i];
+      mgr->Put(fileId, firstPage + i, page.data(), plen);
+    }
+    done += ln[(size_t)i];
+  }
+  return result;
+}
+
 // ================================================================================ LocalCacheFileInStream
 
 LocalCacheFileInStream::LocalCacheFileInStream(LocalCacheManager* manager, const std::string& fileId, int64_t fileLength,
                                                ExternalRead external, void* user)
     : mManager(manager), mFileId(fileId), mLength(fileLength), mPageSize(manager ? manager->pageSize() : 1),
       mExternal(external), mUser(user), mBypass(!manager || manager->state() == NOT_IN_USE) {}
+
+LocalCacheFileInStream::~LocalCacheFileInStream() {
+  if (mStage) aps_host_free_pinned(mStage);
+}
 
 bool LocalCacheFileInStream::ReadExternalPage(int64_t pos, std::vector<uint8_t>* page) {  // :291-310
   std::lock_guard<std::mutex> lk(mExternalMu);
@@ -920,6 +995,12 @@ int32_t LocalCacheFileInStream::ReadAt(int64_t* position, void* b, int32_t bLen,
     }
     *position += total;
     return (int32_t)total;
+  }
+  if (mBatched) {  // one store call for every resident page of the read
+    const int32_t r = BatchedRead(mManager, mFileId, mLength, *position, (uint8_t*)b + off, len, mExternal, mUser, &mStage,
+                                  &mStageBytes, &bytesReadCache, &bytesRequestedExternal, &bytesReadExternal);
+    if (r > 0) *position += r;
+    return r;
   }
   int32_t total = 0;
   const int64_t toRead = std::min<int64_t>(len, mLength - *position);
@@ -1157,6 +1238,7 @@ void apc_stream_counters(apc_stream* s, int64_t* out3) {
   out3[1] = s->in->bytesRequestedExternal;
   out3[2] = s->in->bytesReadExternal;
 }
+void apc_stream_set_batched(apc_stream* s, int on) { s->in->SetBatched(on != 0); }
 void apc_stream_close(apc_stream* s) { s->in->Close(); }
 void apc_stream_destroy(apc_stream* s) { delete s; }
 
@@ -1207,60 +1289,15 @@ void apc_metrics_read(apc_manager* m, int64_t* out14) {
 // memory: a pageable dst is served through a pinned staging buffer.
 int32_t apc_positioned_read_batched(apc_manager* m, const char* file_id, int64_t file_len, int64_t pos, void* dst, int32_t len,
                                     apc_external_read external, void* user, int64_t* from_cache, int64_t* from_external) {
-  if (len < 0 || pos < 0) return APC_GET_ILLEGAL_ARGUMENT;
-  if (len == 0) return 0;
-  if (pos >= file_len) return -1;
-  LocalCacheManager* mgr = m->mgr.get();
-  const int64_t ps = mgr->pageSize();
-  const int64_t toRead = std::min<int64_t>(len, file_len - pos);
-  const int64_t firstPage = pos / ps, lastPage = (pos + toRead - 1) / ps;
-  const int32_t n = (int32_t)(lastPage - firstPage + 1);
   void* stage = nullptr;
-  if (aps_host_alloc_pinned((uint64_t)toRead, &stage) != APS_OK) return -1;
-  std::vector<int32_t> off((size_t)n), ln((size_t)n), got((size_t)n);
-  std::vector<void*> dsts((size_t)n);
-  int64_t cur = pos, done = 0;
-  for (int32_t i = 0; i < n; ++i) {
-    off[(size_t)i] = (int32_t)(cur % ps);
-    ln[(size_t)i] = (int32_t)std::min<int64_t>(ps - off[(size_t)i], toRead - done);
-    dsts[(size_t)i] = (uint8_t*)stage + done;
-    cur += ln[(size_t)i];
-    done += ln[(size_t)i];
-  }
-  mgr->GetMany(file_id, firstPage, n, off.data(), ln.data(), dsts.data(), got.data());
-  std::vector<uint8_t> page;
-  int32_t result = (int32_t)toRead;
-  done = 0;
-  for (int32_t i = 0; i < n && result >= 0; ++i) {
-    uint8_t* out = (uint8_t*)dst + done;
-    if (got[(size_t)i] > 0) {
-      memcpy(out, dsts[(size_t)i], (size_t)ln[(size_t)i]);
-      mgr->metrics.bytesReadCache += ln[(size_t)i];
-      if (from_cache) *from_cache += ln[(size_t)i];
-    } else {
-      const int64_t pageStart = (firstPage + i) * ps;
-      const int32_t plen = (int32_t)std::min<int64_t>(ps, file_len - pageStart);
-      page.resize((size_t)plen);
-      int32_t have = 0;
-      while (have < plen) {
-        const int r = external(user, pageStart + have, page.data() + have, plen - have);
-        if (r <= 0) break;
-        have += r;
-      }
-      mgr->metrics.bytesReadExternal += have;
-      if (have != plen) {
-        result = -1;
-        break;
-      }
-      memcpy(out, page.data() + off[(size_t)i], (size_t)ln[(size_t)i]);
-      mgr->metrics.bytesRequestedExternal += ln[(size_t)i];
-      if (from_external) *from_external += ln[(size_t)i];
-      mgr->Put(file_id, firstPage + i, page.data(), plen);
-    }
-    done += ln[(size_t)i];
-  }
-  aps_host_free_pinned(stage);
-  return result;
+  uint64_t stageBytes = 0;
+  int64_t fc = 0, fe = 0, re = 0;
+  const int32_t r = BatchedRead(m->mgr.get(), file_id, file_len, pos, (uint8_t*)dst, len, external, user, &stage, &stageBytes,
+                                &fc, &fe, &re);
+  if (stage) aps_host_free_pinned(stage);
+  if (from_cache) *from_cache += fc;
+  if (from_external) *from_external += fe;
+  return r;
 }
 
 int apc_manager_close(apc_manager* m) {

@@ -402,6 +402,9 @@ class LocalCacheFileInStream {
   int64_t Remaining() const { return mLength - mPosition; }
   int64_t GetPos() const { return mPosition; }
   void Close() { mClosed = true; }
+  ~LocalCacheFileInStream();
+  // serve every read with ONE batched store call for the resident pages it touches
+  void SetBatched(bool on) { mBatched = on && !mBypass; }
   bool bypass() const { return mBypass; }
   int64_t bytesReadCache = 0, bytesRequestedExternal = 0, bytesReadExternal = 0;
  private:
@@ -412,9 +415,15 @@ class LocalCacheFileInStream {
   int64_t mLength, mPageSize, mPosition = 0;
   ExternalRead mExternal;
   void* mUser;
-  bool mClosed = false, mBypass;
+  bool mClosed = false, mBypass, mBatched = false;
+  void* mStage = nullptr;  // pinned staging of the batched mode, kept between reads
+  uint64_t mStageBytes = 0;
   std::mutex mExternalMu;  // readExternalPage is synchronized (:291)
 };
+
+int32_t BatchedRead(LocalCacheManager* mgr, const std::string& fileId, int64_t fileLen, int64_t pos, uint8_t* dst, int32_t len,
+                    ExternalRead external, void* user, void** stage, uint64_t* stageBytes, int64_t* fromCache,
+                    int64_t* fromExternal, int64_t* readExternal);
 
 // Page payload of the benchmarks and replays: 64-bit word k of page (file, index) is the k-th
 // splitmix64 output for seed ^ (file << 32) ^ index.

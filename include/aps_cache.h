@@ -149,6 +149,9 @@ APS_API int64_t apc_stream_get_pos(apc_stream* s);
 APS_API int apc_stream_bypass(apc_stream* s);
 /* BytesReadCache, BytesRequestedExternal, BytesReadExternal of this stream (:312-330) */
 APS_API void apc_stream_counters(apc_stream* s, int64_t* out3);
+/* from now on every read of this stream makes ONE batched store call for all resident pages it
+ * touches (and keeps a pinned staging buffer between reads) instead of one CacheManager.get per page. */
+APS_API void apc_stream_set_batched(apc_stream* s, int on);
 APS_API void apc_stream_close(apc_stream* s);
 APS_API void apc_stream_destroy(apc_stream* s);
 

@@ -278,3 +278,31 @@ def test_oversized_buffers_and_several_files():
         assert s.read(b) == len(d) and bytes(b) == d
     assert m.pages() == sum((len(d) + PS - 1) // PS for d in files.values())
     m.close()
+
+
+def test_batched_stream_reads_equal_per_page_reads():
+    """SURVEY.md 8f-1 on the stream object: with set_batched() every read is one batched store call; bytes, position,
+    counters and cache contents must be those of the per-page loop."""
+    file_len = 9 * PS + 321
+    data = np.random.default_rng(21).integers(0, 256, file_len, dtype=np.uint8).tobytes()
+    ma, mb = _manager(), _manager()
+    ea, eb = External(data), External(data)
+    sa, sb = ma.open_file("55", file_len, ea), mb.open_file("55", file_len, eb)
+    sb.set_batched()
+    rng = np.random.default_rng(22)
+    for _ in range(60):
+        if rng.integers(4) == 0:
+            pos = int(rng.integers(0, file_len + 1))
+            sa.seek(pos); sb.seek(pos)
+        n = int(rng.integers(0, 4 * PS))
+        ba, bb = bytearray(n + 3), bytearray(n + 3)
+        ra, rb = sa.read(ba, 3, n), sb.read(bb, 3, n)
+        assert ra == rb and ba == bb and sa.get_pos() == sb.get_pos()
+        if ra > 0:
+            assert bytes(ba[3:3 + ra]) == data[sa.get_pos() - ra:sa.get_pos()]
+    assert sa.counters() == sb.counters()
+    assert (ma.pages(), ma.bytes()) == (mb.pages(), mb.bytes())
+    assert ea.bytes == eb.bytes
+    one = bytearray(2 * PS)
+    assert sb.positioned_read(PS - 5, one) == 2 * PS and bytes(one) == data[PS - 5:3 * PS - 5]
+    ma.close(); mb.close()
