@@ -1114,18 +1114,46 @@ __global__ void __launch_bounds__(kK1Threads) delete_kernel(Table t, const aps_k
   acct_flush(acct, t);
 }
 
+// Membership only.  A lookup needs no agreement on an entry (inserts and erases do, hence their eight-lane tiles),
+// so a key gets kLookupLanes lanes that read 8 / kLookupLanes entries each: the per-warp instruction stream (hash,
+// ballots, bookkeeping -- 65 % of the issue slots with eight lanes per key) is shared by more keys.
+constexpr uint32_t kLookupLanes = 4;
 __global__ void __launch_bounds__(kK1Threads) lookup_kernel(Table t, const aps_key* keys, uint32_t n, int32_t* len_out) {
   __shared__ BlockAcct acct;
   acct_init(acct);
+  constexpr uint32_t L = kLookupLanes, E = kBucketEntries / L;
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t i = gid >> 3, sub = gid & 7u, tshift = threadIdx.x & 24u;
+  const uint32_t i = gid / L, sub = gid % L, gshift = (threadIdx.x & 31u) & ~(L - 1u), gmask = ((1u << L) - 1u) << gshift;
   if (i < n) {
     const aps_key key = keys[i];
-    Probe pr = tile_lookup(t, key, sub, tshift);
+    uint64_t b = hash_key(key) & t.bucket_mask;
+    uint64_t found = 0;
+    uint32_t nb = 0;
+    for (uint64_t p = 0; p <= t.bucket_mask; ++p) {
+      uint64_t k0[E], k1[E], k2[E], m[E];
+#pragma unroll
+      for (uint32_t q = 0; q < E; ++q) load_entry(t.entries + b * kBucketEntries + sub * E + q, k0[q], k1[q], k2[q], m[q]);
+      ++nb;
+      uint64_t mine = 0;
+      bool empty = false;
+#pragma unroll
+      for (uint32_t q = 0; q < E; ++q) {
+        if ((m[q] >> 63) && k0[q] == key.file_hi && k1[q] == key.file_lo && k2[q] == key.page_index) mine = m[q];
+        empty |= m[q] == kMetaEmpty;
+      }
+      const uint32_t bm = (__ballot_sync(gmask, mine != 0) >> gshift) & ((1u << L) - 1u);
+      const uint32_t be = (__ballot_sync(gmask, empty) >> gshift) & ((1u << L) - 1u);
+      if (bm) {
+        found = __shfl_sync(gmask, mine, gshift + (__ffs(bm) - 1));
+        break;
+      }
+      if (be) break;
+      b = (b + 1) & t.bucket_mask;
+    }
     if (sub == 0) {
       acct_add(acct, kCtrLookups, 1ull);
-      acct_add(acct, kCtrProbes, (unsigned long long)pr.nbuckets);
-      len_out[i] = pr.meta ? (int32_t)meta_len(pr.meta) : -1;
+      acct_add(acct, kCtrProbes, (unsigned long long)nb);
+      len_out[i] = found ? (int32_t)meta_len(found) : -1;
     }
   }
   acct_flush(acct, t);
