@@ -56,6 +56,8 @@ SIGNATURES = {
     "apc_get": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
     "apc_delete": (C.c_int, [_vp, _cp, _i64]),
     "apc_state": (C.c_int, [_vp]),
+    "apc_manager_snapshot_save": (C.c_int, [_vp, _cp, C.POINTER(_u64)]),
+    "apc_manager_create_over_snapshot": (C.c_int, [_vp, C.c_uint32, _cp, _dbl, _cp, C.POINTER(_vp)]),
     "apc_bytes": (_i64, [_vp]),
     "apc_pages": (_i64, [_vp]),
     "apc_page_lock_id": (_i32, [_vp, _cp, _i64]),
@@ -284,6 +286,24 @@ class LocalCacheManager:
         capi.check(lib().apc_manager_create_over(store.handle, page_size, evictor.encode(), lfu_logbase, C.byref(h)))
         self._h, self.page_size, self._keep = h, page_size, store
         return self
+
+    @classmethod
+    def over_snapshot(cls, store, page_size, path, evictor="LRU", lfu_logbase=2.0):
+        """Warm restart: loads the snapshot at `path` into the freshly opened `store`, takes over the table of interned
+        file ids it carries and runs the reference's restore over the loaded pages."""
+        import os
+        self = cls.__new__(cls)
+        h = C.c_void_p()
+        capi.check(lib().apc_manager_create_over_snapshot(store.handle, page_size, evictor.encode(), lfu_logbase,
+                                                          os.fsencode(path), C.byref(h)), "restore from %s" % path)
+        self._h, self.page_size, self._keep = h, page_size, store
+        return self
+
+    def save_snapshot(self, path):
+        import os
+        n = _u64()
+        capi.check(lib().apc_manager_snapshot_save(self._h, os.fsencode(path), C.byref(n)), "snapshot save %s" % path)
+        return n.value
 
     METRIC_NAMES = ("BytesReadCache", "BytesRequestedExternal", "BytesReadExternal", "BytesWrittenCache", "BytesEvicted",
                     "PagesEvicted", "GetErrors", "PutErrors", "DeleteErrors", "PutEvictionErrors", "PutStoreWriteErrors",

@@ -88,6 +88,8 @@ SIGNATURES = {
     "aps_compact": (C.c_int, [_vp]),
     "aps_snapshot_save": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64)]),
     "aps_snapshot_load": (C.c_int, [_vp, C.c_char_p, C.POINTER(_u64), C.POINTER(_u64)]),
+    "aps_snapshot_save_names": (C.c_int, [_vp, C.c_char_p, C.c_uint32, C.POINTER(C.c_char_p), C.POINTER(_u64)]),
+    "aps_snapshot_names": (C.c_int, [C.c_char_p, _vp, _vp]),
     "aps_clock_evict_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_stats": (C.c_int, [_vp, C.POINTER(aps_stats_t)]),
     "aps_set_faults": (C.c_int, [_vp, _u32]),

@@ -461,8 +461,8 @@ int calibrate_sms(aps_store* s) {
   const uint32_t n = (uint32_t)n64;
   std::vector<Job> jobs(n);
   for (uint32_t i = 0; i < n; ++i)
-    jobs[i] = Job{s->table.slab + (uint64_t)i * s->cfg.page_size, s->table.slab + (uint64_t)(n + i) * s->cfg.page_size,
-                  s->cfg.page_size, 0, 0, 0};
+    jobs[i] = Job{s->table.slab + (uint64_t)i * s->table.page_size, s->table.slab + (uint64_t)(n + i) * s->table.page_size,
+                  s->table.page_size, 0, 0, 0};
   CUDA_TRY(cudaMemcpy(s->d_jobs, jobs.data(), n * sizeof(Job), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMalloc(&s->d_timeline, kTimelineWords * sizeof(unsigned long long)));
   std::vector<unsigned long long> tl(kTimelineWords);
@@ -577,7 +577,10 @@ const char* aps_strerror(int code) {
 int aps_open(const aps_config* cfg, aps_store** out) {
   if (!cfg || !out) return APS_EINVAL;
   *out = nullptr;
-  if (cfg->page_size == 0 || (cfg->page_size & 15u) || cfg->page_size > (1u << 30)) return APS_EINVAL;
+  // any page size the reference accepts (alluxio.user.client.cache.page.size is a free byte count, PropertyKey.java:3704);
+  // slab slots are spaced at the next multiple of 16 so that whole-page copies stay on the 128-bit path
+  if (cfg->page_size == 0 || cfg->page_size > (1u << 30)) return APS_EINVAL;
+  const uint32_t stride = (cfg->page_size + 15u) & ~15u;
   int ndev = 0;
   CUDA_TRY(cudaGetDeviceCount(&ndev));
   if (cfg->device < 0 || cfg->device >= ndev) return APS_EINVAL;
@@ -613,7 +616,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   if (s->cfg.max_batch == 0) s->cfg.max_batch = 4096;
   s->slots = slots;
   s->n_entries = entries;
-  s->page_rows = (cfg->page_size + kRowBytes - 1) / kRowBytes;
+  s->page_rows = (stride + kRowBytes - 1) / kRowBytes;
   const uint32_t mb = s->cfg.max_batch;
 
 #define OPEN_TRY(expr)                                                                                    \
@@ -629,7 +632,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   } while (0)
 
   OPEN_TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-  OPEN_TRY(cudaMalloc(&s->table.slab, slots * (uint64_t)cfg->page_size));
+  OPEN_TRY(cudaMalloc(&s->table.slab, slots * (uint64_t)stride));
   OPEN_TRY(cudaMalloc(&s->table.entries, entries * sizeof(Entry)));
   OPEN_TRY(cudaMalloc(&s->table.free_slots, slots * sizeof(uint32_t)));
   OPEN_TRY(cudaMalloc(&s->table.free_top, sizeof(int32_t)));
@@ -664,9 +667,10 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   OPEN_TRY(cudaMalloc(&s->d_reqs, (uint64_t)mb * sizeof(aps_get_req)));
   OPEN_TRY(cudaMalloc(&s->d_res, (uint64_t)mb * sizeof(aps_result)));
   OPEN_TRY(cudaHostAlloc(&s->h_stage, (uint64_t)mb * (sizeof(aps_get_req) + sizeof(aps_result)), cudaHostAllocDefault));
-  OPEN_TRY(cudaHostAlloc(&s->h_bounce, cfg->page_size, cudaHostAllocDefault));
+  OPEN_TRY(cudaHostAlloc(&s->h_bounce, stride, cudaHostAllocDefault));
   s->table.bucket_mask = entries / kBucketEntries - 1;
-  s->table.page_size = cfg->page_size;
+  s->table.page_size = stride;
+  s->table.max_len = cfg->page_size;
   const int32_t top = (int32_t)slots;
   OPEN_TRY(cudaMemsetAsync(s->table.entries, 0, entries * sizeof(Entry), s->stream));
   OPEN_TRY(cudaMemsetAsync(s->table.slot_crc, 0, slots * sizeof(uint32_t), s->stream));
@@ -693,17 +697,17 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   return APS_OK;
 }
 
+// PageStore is AutoCloseable and SURVEY 8b asks for an idempotent close.  The handle itself (a few hundred bytes of host
+// memory, no device resources) is therefore never freed: after the first close it stays behind as a tombstone, so a
+// second close returns APS_OK and any other call on it returns APS_ECLOSED instead of reading freed memory.
 int aps_close(aps_store* s) {
   if (!s) return APS_EINVAL;
-  {
-    std::lock_guard<std::mutex> lk(s->mu);
-    if (s->closed) return APS_ECLOSED;
-    s->closed = true;
-    DeviceGuard g(s->cfg.device);
-    cudaStreamSynchronize(s->stream);
-    free_store(s);
-  }
-  delete s;
+  std::lock_guard<std::mutex> lk(s->mu);
+  if (s->closed) return APS_OK;
+  s->closed = true;
+  DeviceGuard g(s->cfg.device);
+  cudaStreamSynchronize(s->stream);
+  free_store(s);
   return APS_OK;
 }
 
@@ -1247,10 +1251,6 @@ int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_cta
   if (!enable && s->d_timeline) {
     CUDA_TRY(cudaDeviceSynchronize());
     cudaFree(s->d_timeline);
-  cudaFree(s->d_sched);
-  cudaFree(s->d_shards);
-  for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
-  s->ipc_ptrs.clear();
     s->d_timeline = nullptr;
   }
   return APS_OK;

@@ -54,10 +54,11 @@ struct Table {
   uint32_t* slot_crc;    // CRC32C recorded at put, per slab slot
   unsigned long long* counters;
   uint8_t* slab;
-  uint32_t page_size;
+  uint32_t page_size;    // bytes between slab slots: the configured page size rounded up to a multiple of 16
   // opt-in device-side CLOCK eviction (APS_FLAG_DEVICE_CLOCK); both null otherwise
   uint8_t* slot_ref;     // per slab slot: 1 = referenced since the hand last passed
   uint64_t* slot_entry;  // per slab slot: index of the table entry that owns it, ~0 = free
+  uint32_t max_len;      // longest page a put may store = alluxio.user.client.cache.page.size as configured (any value)
 };
 constexpr uint64_t kNoEntry = ~0ull;
 

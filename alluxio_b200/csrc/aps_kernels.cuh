@@ -235,8 +235,8 @@ constexpr uint32_t kMaxTasksPerJob = 128;
 struct CopyArgs {
   const Job* jobs;           // neither kGet nor kPut: jobs prepared by an earlier kernel
   const aps_get_req* reqs;   // kGet == true: requests, resolved in this kernel
-  const aps_put_req* preqs;  // kPut == true: put requests; task 0 of a page inserts it, the others wait for its slot
-  unsigned long long* jslot; // kPut scratch, one word per job: launch epoch << 32 | (slot + 1, or 0x80000000 | status)
+  const aps_put_req* preqs;  // kPut == true: put requests; the first task of a page to arrive inserts it, the others pick its slot up
+  unsigned long long* jslot; // kPut scratch, one word per job: launch epoch << 32 | (0 = insert in progress, slot + 1, or 0x80000000 | status)
   uint32_t epoch;            // kPut: this launch's number (never 0), so the words above need no reset
   int trust_reqs;            // kGet with early: the caller promised that request arrays are final (APS_FLAG_STABLE_REQS)
   Table table;
@@ -281,7 +281,7 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
 // K2 + K3 (+ K1: lookup when kGet, insert when kPut).  Persistent grid: one CTA per SM.  A job (one page request) is
 // cut into tasks_per_job warp-tasks of rows_per_task 512-byte rows, sized by the host so that one
 // round of all warps of the chip covers the batch (no wave quantisation).  A task resolves its
-// page (kGet: eight lanes probe the hash table; kPut: task 0 inserts, its siblings wait for the slot), publishes its row range in shared memory and
+// page (kGet: eight lanes probe the hash table; kPut: the first of the page's tasks to arrive inserts, the others pick the slot up), publishes its row range in shared memory and
 // streams the rows it claims from it (128-bit loads and stores per lane, next group in flight while
 // the current one is folded).  It reduces the four per-lane CRC words to the zero-init CRC of the
 // segment, shifts it by the bytes that follow it in the page (GF(2) multiply) and XORs it into the
@@ -487,10 +487,13 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         }
         report = __shfl_sync(0xFFFFFFFFu, (int)report, 0) != 0;
       } else if (kPut) {
-        // Fused insert (LocalPageStore.put's "create the file"): task 0 of a page claims a table entry and a slab
-        // slot with the first eight lanes and publishes the outcome; the page's other tasks, which start at the
-        // same moment on other warps, pick it up from a.jslot.  Task 0 never waits for anybody, and a page's task
-        // 0 always precedes its other tasks in every warp's list, so the waiting cannot cycle.
+        // Fused insert (LocalPageStore.put's "create the file").  The page's tasks start at the same moment on different
+        // warps, possibly in different CTAs.  Whichever of them ARRIVES FIRST takes the page's hand-over word
+        // (a.jslot[job]: stale epoch -> this epoch, value 0) with a compare-and-swap, claims a table entry and a slab
+        // slot with the first eight lanes and publishes the outcome; the others pick it up from the word.  A waiting warp
+        // therefore only ever waits for a warp that is already running (the winner never waits for anybody), so the
+        // kernel makes progress whatever part of its grid is resident -- a second kernel holding SMs (another store's put
+        // on the same device) cannot deadlock it.
         aps_put_req rq = a.preqs[job];
         if (!dep_ok) {
           // A put cannot touch the table before its predecessor is done, but it can warm L2 with the source rows this
@@ -508,10 +511,21 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         }
         const Table& t = a.table;
         unsigned long long word = 0;
-        if (c == 0) {
+        int inserter = 0;
+        if (lane == 0) {
+          const unsigned long long mine = (unsigned long long)a.epoch << 32;  // this launch, outcome pending
+          word = *(volatile unsigned long long*)&a.jslot[job];
+          while ((uint32_t)(word >> 32) != a.epoch) {
+            const unsigned long long seen = atomicCAS(&a.jslot[job], word, mine);
+            if (seen == word) { inserter = 1; word = mine; break; }
+            word = seen;
+          }
+        }
+        inserter = __shfl_sync(0xFFFFFFFFu, inserter, 0);
+        if (inserter) {
           int err = 0;
           uint32_t slot = kNoSlot;
-          if (rq.len > t.page_size) {
+          if (rq.len > t.max_len) {
             err = APS_EINVAL;
           } else {
             EntryClaim cl{kClaimFull, 0, 0};
@@ -564,8 +578,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           report = __shfl_sync(0xFFFFFFFFu, (int)report, 0) != 0;
         } else {
           if (lane == 0) {
-            do word = *(volatile unsigned long long*)&a.jslot[job];
-            while ((uint32_t)(word >> 32) != a.epoch);
+            while ((uint32_t)word == 0u) word = *(volatile unsigned long long*)&a.jslot[job];  // the winner is running
             __threadfence();
           }
           word = __shfl_sync(0xFFFFFFFFu, word, 0);
@@ -1029,7 +1042,7 @@ __global__ void __launch_bounds__(kK1Threads) put_resolve_kernel(Table t, const 
   int err = 0, rank = -1;
   if (live) {
     rq = reqs[i];
-    if (rq.len > t.page_size) err = APS_EINVAL;
+    if (rq.len > t.max_len) err = APS_EINVAL;
     else {
       c = tile_claim(t, rq.key, sub, tshift);
       if (c.kind == kClaimFull) err = APS_ENOSPC;

@@ -36,7 +36,7 @@ struct Scratch {
   uint32_t acc[kMaxRanges];      // per-range XOR accumulator        -- must be zero when a call starts
   uint32_t done[kMaxRanges];     // per-range finished-row counter    -- must be zero when a call starts
   uint32_t sched[4];             // CTA rank counters of the kernel   -- must be zero when a call starts
-  int error_flag;                // kernel could not place its tables -- must be zero when a call starts
+  int error_flag;                // kernel could not place its tables (ruled out on the host at set-up) -- zeroed per call
   uint32_t pad[3];
   uint8_t sm_slow[256];          // all zero: no SM speed classes here (set once)
   CrcTables tables;              // GF(2) fold tables (set once)
@@ -113,6 +113,18 @@ int setup_device(int dev, PerDevice** out) {
     if (cudaFuncSetAttribute(kKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCopyDynSmem) != cudaSuccess)
       return APS_ECUDA;
     if (cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return APS_ECUDA;
+    // The kernel keeps its CRC tables at fixed shared-memory addresses and gives up (sets Scratch::error_flag, writes
+    // no checksum) if the dynamic window does not start below them.  This call cannot wait for the kernel to find
+    // that out, so the condition is decided here, from what fixes it: the kernel's static shared memory plus the
+    // per-block reserve.  If it does not hold, no call on this device is ever launched.
+    cudaFuncAttributes fa{};
+    int reserved = 0;
+    if (cudaFuncGetAttributes(&fa, kKernel) != cudaSuccess) return APS_ECUDA;
+    if (cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev) != cudaSuccess) return APS_ECUDA;
+    if (fa.sharedSizeBytes + (size_t)reserved > kSmemG) return APS_ECUDA;
+    // The set-up copies above ran on the legacy default stream; the caller's stream may be a non-blocking one that
+    // does not order itself after it.  Wait here, once, so that the first call's kernels see the tables.
+    if (cudaDeviceSynchronize() != cudaSuccess) return APS_ECUDA;
     d.scratch = sc;
     d.ready = true;
   }

@@ -103,6 +103,19 @@ void FileKeyCodec::Encode(const std::string& fileId, uint64_t* hi, uint64_t* lo)
   *lo = it->second;
 }
 
+std::vector<std::string> FileKeyCodec::Names() {
+  std::lock_guard<std::mutex> g(mMu);
+  return mNames;
+}
+
+void FileKeyCodec::AdoptNames(const std::vector<std::string>& names) {
+  std::lock_guard<std::mutex> g(mMu);
+  for (size_t i = mNames.size(); i < names.size(); ++i) {
+    mIds.emplace(names[i], (uint64_t)i);
+    mNames.push_back(names[i]);
+  }
+}
+
 std::string FileKeyCodec::Decode(uint64_t hi, uint64_t lo) {
   if (hi == 0) return std::to_string((int64_t)lo);
   if (hi == ~0ull) {
@@ -647,6 +660,7 @@ LocalCacheManager::LocalCacheManager(int64_t pageSize, std::unique_ptr<MetaStore
     : mOptions(options), mPageSize(pageSize), mCacheSize(store->GetCacheSize()), mMetaStore(std::move(meta)),
       mPageStore(std::move(store)), mState(READ_ONLY) {  // LocalCacheManager.java:145-166
   if (mOptions.asyncWriteThreads > 0) mAsyncCacheExecutor.reset(new HandOffPool(mOptions.asyncWriteThreads));
+  mCodec.AdoptNames(mOptions.internedNames);  // before restore decodes the ids the store lists
   if (mOptions.asyncRestore) mInitService = std::thread([this] { RestoreOrInit(); });  // :126-133, READ_ONLY meanwhile
   else RestoreOrInit();                                                                // :134
 }
@@ -788,7 +802,10 @@ int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int
   int32_t got = 0;
   const int rc = mPageStore->Get(k, pageOffset, bytesToRead, (uint8_t*)buffer + offsetInBuffer, bufLen - offsetInBuffer, &got);
   if (rc == APS_EINVAL) return kGetIllegalArgument;  // IllegalArgumentException is not caught by getPage (:550)
-  if (rc != APS_OK || got != bytesToRead) {           // :544-549, :384-395
+  // getPage (:540-555) turns a failed or short read into -1; get (:383-395) then treats ANY bytesRead <= 0 as an
+  // error -- which includes a successful read of zero bytes -- removes the page from the meta store and returns -1
+  const int32_t bytesRead = (rc != APS_OK || got != bytesToRead) ? -1 : bytesToRead;
+  if (bytesRead <= 0) {
     std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
     mMetaStore->RemovePage(k);
     metrics.getErrors++;
@@ -829,9 +846,9 @@ void LocalCacheManager::GetMany(const std::string& fileId, int64_t firstPage, in
   const int rc = mPageStore->GetBatch((uint32_t)reqs.size(), reqs.data(), res.data());
   for (size_t r = 0; r < reqs.size(); ++r) {
     const int32_t i = which[r];
-    if (rc == APS_OK && res[r].len == len[i]) {
+    if (rc == APS_OK && res[r].len == len[i] && len[i] > 0) {
       got[i] = len[i];
-    } else {  // inconsistent with the meta store: drop the page, as get() does
+    } else {  // inconsistent with the meta store, or a read of zero bytes (bytesRead <= 0, :384): drop the page, as get() does
       std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
       mMetaStore->RemovePage(keys[r]);
       metrics.getErrors++;
@@ -1264,6 +1281,38 @@ int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* ev
   return APS_OK;
 }
 
+// Warm restart with ids that are neither decimal nor 32-hex: they reach the store as indices into this process's intern
+// table, which the snapshot therefore has to carry (aps_snapshot_save_names / aps_snapshot_names).
+static int CollectName(void* user, uint32_t, const char* name) {
+  static_cast<std::vector<std::string>*>(user)->push_back(name);
+  return 0;
+}
+int apc_manager_create_over_snapshot(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
+                                     const char* snapshot_path, apc_manager** out) {
+  if (!store || !evictor || !out || !snapshot_path) return APS_EINVAL;
+  *out = nullptr;
+  auto ev = CacheEvictor::Create(evictor, lfu_logbase);
+  if (!ev) return APS_EINVAL;
+  ManagerOptions mo;
+  int rc = aps_snapshot_names(snapshot_path, CollectName, &mo.internedNames);
+  if (rc != APS_OK) return rc;
+  rc = aps_snapshot_load(store, snapshot_path, nullptr, nullptr);
+  if (rc != APS_OK) return rc;
+  std::unique_ptr<GpuPageStore> gs = GpuPageStore::Adopt(store);
+  apc_manager* m = new apc_manager();
+  m->gpu = gs.get();
+  m->mgr.reset(new LocalCacheManager(page_size, std::unique_ptr<MetaStore>(new MetaStore(std::move(ev))), std::move(gs), mo));
+  *out = m;
+  return APS_OK;
+}
+int apc_manager_snapshot_save(apc_manager* m, const char* path, uint64_t* pages_out) {
+  if (!m || !m->gpu || !path) return APS_EINVAL;
+  const std::vector<std::string> names = m->mgr->codec()->Names();
+  std::vector<const char*> ptrs;
+  for (const std::string& n : names) ptrs.push_back(n.c_str());
+  return aps_snapshot_save_names(m->gpu->handle(), path, (uint32_t)ptrs.size(), ptrs.data(), pages_out);
+}
+
 // NoExceptionCacheManager (CACHE/NoExceptionCacheManager.java:37-79): nothing escapes; errors are counted.
 int32_t apc_get_noexcept(apc_manager* m, const char* f, int64_t i, int32_t page_offset, int32_t bytes_to_read, void* buffer,
                          int32_t buffer_len, int32_t offset_in_buffer) {
@@ -1577,7 +1626,15 @@ extern "C" int64_t apc_replay_batched(apc_manager* m, int64_t n, const int64_t* 
     const Key key{0, (uint64_t)file[k], (uint64_t)page[k]};  // decimal file ids encode as (0, value)
     const int32_t len = page_len[k];
     put_ok[k] = 255;
-    if (PageMeta* pm = meta->Find(key)) {  // LocalCacheManager.get: hit
+    PageMeta* pm = meta->Find(key);
+    if (pm && len == 0) {
+      // get of zero bytes from a resident page: bytesRead <= 0 counts as a failed read (LocalCacheManager.java:383-395),
+      // the page leaves the meta store (not the page store) and the caller falls through to the miss path
+      if (pm->epoch == epoch) flush();  // its put is still queued in this window: keep per-id order in the store
+      meta->RemovePage(key);
+      pm = nullptr;
+    }
+    if (pm) {  // LocalCacheManager.get: hit
       hit[k] = 1;
       gets.push_back(aps_get_req{aps_key{key.hi, key.lo, key.idx}, 0, (uint32_t)len, (uint8_t*)d_sink + (size_t)gets.size() * ps});
       pm->epoch = epoch;

@@ -131,6 +131,9 @@ class FileKeyCodec {
  public:
   void Encode(const std::string& fileId, uint64_t* hi, uint64_t* lo);
   std::string Decode(uint64_t hi, uint64_t lo);
+  // Warm restart: the interned ids in index order, and their adoption into a still empty table (aps_snapshot_names).
+  std::vector<std::string> Names();
+  void AdoptNames(const std::vector<std::string>& names);
  private:
   std::mutex mMu;
   std::unordered_map<std::string, uint64_t> mIds;
@@ -335,6 +338,7 @@ constexpr int32_t kGetIllegalArgument = -2;
 struct ManagerOptions {
   int asyncWriteThreads = 0;  // alluxio.user.client.cache.async.write.enabled / .threads (0 = synchronous puts)
   bool asyncRestore = false;  // alluxio.user.client.cache.async.restore.enabled
+  std::vector<std::string> internedNames;  // intern table of the process that wrote the snapshot being restored
 };
 
 class LocalCacheManager {

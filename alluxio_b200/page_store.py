@@ -78,6 +78,22 @@ class FileKeyCodec:
                 self._names.append(file_id)
             return _INTERNED_HI, n
 
+    def names(self):
+        """The interned ids in index order (what a snapshot has to carry, see save_snapshot)."""
+        with self._lock:
+            return list(self._names)
+
+    def adopt_names(self, names):
+        """After a restart: take over the intern table a snapshot carries.  The table here must be empty or agree."""
+        with self._lock:
+            for i, nm in enumerate(names):
+                if i < len(self._names):
+                    if self._names[i] != nm:
+                        raise ValueError("snapshot name table disagrees with ids already interned: %r vs %r" % (self._names[i], nm))
+                else:
+                    self._ids[nm] = i
+                    self._names.append(nm)
+
     def decode(self, hi, lo):
         if hi == 0:
             return str(lo - (1 << 64) if lo >> 63 else lo)
@@ -210,13 +226,23 @@ class GpuPageStore:
     def save_snapshot(self, path):
         """Warm restart, SURVEY.md 8f-4: writes every resident page to `path`; returns the number written."""
         n = C.c_uint64()
-        self._raise(capi.lib().aps_snapshot_save(self.handle, os.fsencode(path), C.byref(n)), "snapshot save %s" % path)
+        # ids that are neither decimal nor 32-hex live in this process's intern table: the snapshot carries it, so that
+        # getPages() returns the same ids after a restart as LocalPageStore's directory walk would
+        names = [nm.encode("utf-8") for nm in self.codec.names()]
+        arr = (C.c_char_p * max(1, len(names)))(*names)
+        self._raise(capi.lib().aps_snapshot_save_names(self.handle, os.fsencode(path), len(names), arr, C.byref(n)),
+                    "snapshot save %s" % path)
         return n.value
 
     def load_snapshot(self, path):
         """Puts the pages of a snapshot into this store; returns (loaded, rejected).  getPages() lists them
         afterwards, which is what LocalCacheManager.restore walks (LocalCacheManager.java:466-509)."""
         n, r = C.c_uint64(), C.c_uint64()
+        names = []
+        cb_t = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.c_char_p)
+        cb = cb_t(lambda user, index, name: names.append(name.decode("utf-8")) or 0)
+        self._raise(capi.lib().aps_snapshot_names(os.fsencode(path), C.cast(cb, C.c_void_p), None), "snapshot names %s" % path)
+        self.codec.adopt_names(names)
         self._raise(capi.lib().aps_snapshot_load(self.handle, os.fsencode(path), C.byref(n), C.byref(r)),
                     "snapshot load %s" % path)
         return n.value, r.value

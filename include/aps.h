@@ -82,7 +82,7 @@ typedef struct aps_key {
 /* Replaces LocalPageStoreOptions / PageStoreOptions (CACHE/store/PageStoreOptions.java:23-182). */
 typedef struct aps_config {
   int32_t device;           /* CUDA ordinal */
-  uint32_t page_size;       /* bytes per slab slot = alluxio.user.client.cache.page.size; multiple of 16 */
+  uint32_t page_size;       /* alluxio.user.client.cache.page.size: any byte count up to 1 GiB (slab slots are spaced at the next multiple of 16) */
   uint64_t cache_bytes;     /* alluxio.user.client.cache.size; what getCacheSize() reports */
   uint64_t slab_slots;      /* slots in the HBM slab; 0 = ceil(cache_bytes / page_size) + 1/8 slack (min 64) */
   uint64_t table_capacity;  /* hash-table entries; 0 = next power of two >= 2 * slab_slots (min 1024) */
@@ -97,7 +97,9 @@ typedef void* aps_stream;           /* a cudaStream_t, or NULL for the store's o
  * create are the same thing: the store starts empty (getPages() yields nothing, which
  * LocalCacheManager.restore accepts, CACHE/LocalCacheManager.java:466-509). */
 APS_API int aps_open(const aps_config* cfg, aps_store** out);
-/* AutoCloseable.close (CACHE/PageStore.java:37).  Idempotent on a live handle; frees it. */
+/* AutoCloseable.close (CACHE/PageStore.java:37).  Frees every device and pinned-host resource of the store.  Idempotent:
+ * the handle itself stays valid as a small tombstone for the life of the process, so a second close returns APS_OK and
+ * any other call on a closed handle returns APS_ECLOSED. */
 APS_API int aps_close(aps_store* s);
 
 /* ---- single-page operations: exactly the PageStore contract, host pointers ------------------ */
@@ -257,6 +259,16 @@ APS_API int aps_clock_evict_dev(aps_store* s, uint32_t n, aps_key* d_victims, ui
  * APS_ECORRUPT (not a snapshot, truncated), APS_EINVAL (page size differs). */
 APS_API int aps_snapshot_save(aps_store* s, const char* path, uint64_t* pages_out);
 APS_API int aps_snapshot_load(aps_store* s, const char* path, uint64_t* pages_out, uint64_t* rejected_out);
+/* File ids that are neither decimal longs nor 32 hex digits (UUIDs, raw paths) reach the store as (2^64-1, n), n
+ * being an index into an intern table of the CALLING process; LocalPageStore keeps the id in the file path instead
+ * (CACHE/store/LocalPageStore.java:139-147,177-191), so its getPages() returns the same ids after a restart.  To get
+ * the same here the caller hands its table to aps_snapshot_save_names (names[i] = the id interned as n = i, UTF-8),
+ * and after a restart reads it back with aps_snapshot_names into its empty table BEFORE it lists the loaded pages.
+ * Pages whose interned index has no name (all of them with plain aps_snapshot_save) are left out of the file. */
+typedef int (*aps_name_cb)(void* user, uint32_t index, const char* name); /* non-zero return stops the walk */
+APS_API int aps_snapshot_save_names(aps_store* s, const char* path, uint32_t n_names, const char* const* names,
+                                    uint64_t* pages_out);
+APS_API int aps_snapshot_names(const char* path, aps_name_cb cb, void* user);
 
 /* ---- synthetic data, stats, diagnostics ---------------------------------------------------------*/
 

@@ -41,6 +41,14 @@ APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, doubl
  * and deletes the rest from the store.  The store stays the caller's (apc_manager_close does not close it). */
 APS_API int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
                                     apc_manager** out);
+/* Warm restart through the manager.  apc_manager_snapshot_save writes the store's pages together with
+ * the manager's table of interned file ids (ids that are neither decimal longs nor 32 hex digits);
+ * apc_manager_create_over_snapshot loads such a file into the freshly opened `store`, takes the table over and then runs
+ * the reference's restore, so that getPages() yields the ids LocalPageStore's directory walk would
+ * (CACHE/store/LocalPageStore.java:177-199, CACHE/LocalCacheManager.java:466-509). */
+APS_API int apc_manager_snapshot_save(apc_manager* m, const char* path, uint64_t* pages_out);
+APS_API int apc_manager_create_over_snapshot(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
+                                             const char* snapshot_path, apc_manager** out);
 /* Everything LocalCacheManager.create reads from the configuration, in one place.  Exactly one of `over`,
  * n_shards > 0, or neither (a single new store on store.device) selects the page store. */
 typedef struct apc_options {

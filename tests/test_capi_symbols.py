@@ -44,8 +44,9 @@ def test_open_rejects_bad_config_and_fails_loudly_without_gpu():
     import torch
     L = capi.lib()
     h = C.c_void_p()
-    bad = capi.aps_config(device=0, page_size=100, cache_bytes=1 << 20)  # not a multiple of 16
-    assert L.aps_open(C.byref(bad), C.byref(h)) == capi.APS_EINVAL
+    for bad_size in (0, (1 << 30) + 1):  # (any size in between is accepted: the reference's page size is a free byte count)
+        bad = capi.aps_config(device=0, page_size=bad_size, cache_bytes=1 << 20)
+        assert L.aps_open(C.byref(bad), C.byref(h)) == capi.APS_EINVAL
     if torch.cuda.is_available():
         pytest.skip("a GPU is present; the no-device branch cannot be shown here")
     cfg = capi.aps_config(device=0, page_size=4096, cache_bytes=1 << 20)

@@ -110,6 +110,32 @@ def test_partial_pages_large_ids_and_short_read_drops_page():
     m.close()
 
 
+def test_get_of_zero_bytes_is_an_error_and_drops_the_page():
+    """LocalCacheManager.get treats bytesRead <= 0 as a failed read (LocalCacheManager.java:383-395): asking a resident
+    page for 0 bytes returns -1 and removes the page from the meta store.  Result and residency afterwards must equal
+    the oracle's, for a full page, for an empty page and through the batched read path."""
+    ostore = orc.PageStore.open_mem(PAGE_SIZE, CACHE_SIZE)
+    om = orc.LocalCacheManager(ostore, PAGE_SIZE, "LRU")
+    m = manager(evictor="LRU")
+    script = [("put", "7", 0, PAGE1), ("get", "7", 0, 0), ("get", "7", 0, PAGE_SIZE),      # dropped by the 0-byte get
+              ("put", "7", 0, PAGE2), ("get", "7", 0, PAGE_SIZE),                           # re-admitted: store overwritten
+              ("put", "8", 3, b""), ("get", "8", 3, 0), ("get", "8", 3, 0),                 # empty page: -1, then a miss
+              ("put", "9", 1, PAGE1), ("get", "9", 1, 10), ("get", "9", 1, 0), ("delete", "9", 1, None)]
+    for op, f, i, arg in script:
+        if op == "put":
+            assert m.put(PID(f, i), arg) == om.put(orc.PageId(f, i), arg)
+        elif op == "delete":
+            assert m.delete(PID(f, i)) == om.delete(orc.PageId(f, i))
+        else:
+            b1, b2 = bytearray(max(arg, 1)), bytearray(max(arg, 1))
+            r1, r2 = m.get(PID(f, i), arg, b1), om.get(orc.PageId(f, i), arg, b2)
+            assert r1 == r2, (op, f, i, arg, r1, r2)
+            if r1 > 0:
+                assert bytes(b1[:r1]) == bytes(b2[:r2])
+        assert (m.pages(), m.bytes()) == (om.pages(), om.bytes())
+    m.close()
+
+
 def test_store_faults_leave_no_state():
     m = manager()
     p1, p2 = PID(*PAGE_ID1), PID(*PAGE_ID2)
@@ -186,6 +212,7 @@ def test_replay_matches_oracle_element_by_element(evictor):
     ids = rng.permutation(n_ids)[rng.choice(n_ids, size=n_acc, p=pz)]
     files, pages = ids // 100, ids % 100
     lens = np.where(pages == 99, 1000 + files, ps).astype(np.int32)   # last page of every file is short
+    lens[(pages == 98) & (files % 3 == 0)] = 0   # empty pages: a get of 0 bytes counts as a failed read and drops the page
     cache_bytes = cap_pages * ps
     want = orc.replay(evictor, ps, cache_bytes, files, pages, lens)
     m = manager(cache_size=cache_bytes, evictor=evictor, page_size=ps, slab_slots=cap_pages + 128)
@@ -213,6 +240,7 @@ def test_batched_replay_equals_oracle_and_single_page_replay(evictor):
     ids = rng.permutation(n_ids)[rng.choice(n_ids, size=n_acc, p=pz)]
     files, pages = ids // 100, ids % 100
     lens = np.where(pages == 99, 2000 + files, ps).astype(np.int32)
+    lens[(pages == 98) & (files % 3 == 0)] = 0   # empty pages (LocalCacheManager.java:383-395: bytesRead <= 0 is an error)
     cache_bytes = cap_pages * ps
     want = orc.replay(evictor, ps, cache_bytes, files, pages, lens)
     m = manager(cache_size=cache_bytes, evictor=evictor, page_size=ps, slab_slots=cap_pages + 256, max_batch=1024)

@@ -170,7 +170,7 @@ def test_no_space_is_an_io_exception():
     s.close()
 
 
-@pytest.mark.parametrize("page_size", [48, 1024, 4112, 65536, 1000 * 16])
+@pytest.mark.parametrize("page_size", [48, 100, 1024, 4099, 4112, 65536, 1000 * 16])
 def test_random_ops_match_oracle_local_page_store(page_size, tmp_path):
     """Same random put/get/delete sequence into GpuPageStore and the oracle's LocalPageStore:
     every status, length, byte and CRC must agree."""

@@ -129,3 +129,57 @@ def test_snapshot_without_crc_and_empty_store(tmp_path):
         assert b.get(pid, buf) == len(data) and bytes(buf[:len(data)]) == data
     a.close()
     b.close()
+
+
+def test_interned_file_ids_survive_a_restart(tmp_path):
+    """File ids that are neither decimal longs nor 32 hex digits (UUIDs, raw paths) are interned by the calling process.
+    LocalPageStore keeps the id in the page's path, so getPages() returns it after a restart
+    (CACHE/store/LocalPageStore.java:177-199); the snapshot carries the intern table to give the same answer."""
+    from alluxio_b200.cache import LocalCacheManager
+    ids = ["/data/warehouse/part-0001.parquet", "123e4567-e89b-12d3-a456-426614174000", "7", "%032x" % 0xabcdef0123456789abcdef]
+    # (a) through the Python mirror of GpuPageStore
+    path = str(tmp_path / "a.snap")
+    a = _store()
+    want = {}
+    for k, f in enumerate(ids * 3):
+        want[_pid(f, k)] = orc.fill_page(5, k, k, 100 + k).tobytes()
+        a.put(_pid(f, k), want[_pid(f, k)])
+    assert a.save_snapshot(path) == len(want)
+    a.close()
+    b = _store()                       # a fresh process would start with an empty intern table, as this store does
+    b.put(_pid("some/other/name", 0), b"x")   # ... unless it interned something else first: then the tables must agree
+    with pytest.raises(ValueError):
+        b.load_snapshot(path)
+    b.close()
+    b = _store()
+    assert b.load_snapshot(path) == (len(want), 0)
+    assert dict(b.get_pages()) == {p: len(d) for p, d in want.items()}
+    for pid, data in want.items():
+        buf = bytearray(PAGE)
+        assert b.get(pid, buf) == len(data) and bytes(buf[:len(data)]) == data
+    b.close()
+    # (b) through the native manager: save with its table, restore into a new store + manager
+    path2 = str(tmp_path / "b.snap")
+    m = LocalCacheManager(PAGE, 256 * PAGE, evictor="LRU")
+    for k, f in enumerate(ids * 2):
+        assert m.put(_pid(f, k), want[_pid(f, k)])
+    assert m.save_snapshot(path2) == 2 * len(ids)
+    m.close()
+    c = _store(cache_pages=256)
+    m2 = LocalCacheManager.over_snapshot(c, PAGE, path2, evictor="LRU")
+    assert m2.state() == m2.READ_WRITE and m2.pages() == 2 * len(ids)
+    for k, f in enumerate(ids * 2):
+        data, buf = want[_pid(f, k)], bytearray(PAGE)
+        assert m2.get(_pid(f, k), len(data), buf) == len(data) and bytes(buf[:len(data)]) == data
+    m2.close()
+    c.close()
+    # (c) a snapshot written WITHOUT a table leaves interned ids out instead of restoring them under a wrong id
+    from alluxio_b200 import capi
+    import ctypes as C
+    d = _store()
+    for k, f in enumerate(ids):
+        d.put(_pid(f, k), b"abc")
+    n = C.c_uint64()
+    capi.check(capi.lib().aps_snapshot_save(d.handle, os.fsencode(str(tmp_path / "c.snap")), C.byref(n)))
+    assert n.value == 2                # the decimal and the 32-hex id
+    d.close()

@@ -181,7 +181,7 @@ def test_factory_is_a_singleton_and_null_while_creating():
     errs = CacheManagerFactory.create_errors()
     CacheManagerFactory.clear()
     with pytest.raises(Exception):                          # a failed creation is reported and counted
-        CacheManagerFactory.get(PS + 1, 256 * PS)           # page size not a multiple of 16
+        CacheManagerFactory.get(0, 256 * PS)                # a page size of zero is not a configuration
     assert CacheManagerFactory.create_errors() == errs + 1
     fresh = CacheManagerFactory.get(PS, 256 * PS)
     assert fresh.pages() == 0
