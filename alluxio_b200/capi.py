@@ -43,6 +43,10 @@ class aps_shard_handle(C.Structure):
     _fields_ = [("opaque", C.c_ubyte * 256)]
 
 
+class aps_push_handle(C.Structure):
+    _fields_ = [("opaque", C.c_ubyte * 192)]
+
+
 class aps_stats_t(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in ("pages", "bytes", "slots_free", "table_capacity", "tombstones", "lookups",
                                            "probe_buckets", "bytes_copied", "crc_mismatches", "kernel_launches", "slow_sms",
@@ -74,6 +78,14 @@ SIGNATURES = {
     "aps_shard_attach_local": (C.c_int, [_vp, _u32, _u32, _vp]),
     "aps_get_batch_sharded_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_get_batch_sharded": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
+    "aps_push_setup": (C.c_int, [_vp, _u64, _u32]),
+    "aps_push_landing": (_vp, [_vp, C.POINTER(_u64)]),
+    "aps_push_export": (C.c_int, [_vp, C.POINTER(aps_push_handle)]),
+    "aps_push_attach": (C.c_int, [_vp, _u32, _u32, C.POINTER(aps_push_handle)]),
+    "aps_push_attach_local": (C.c_int, [_vp, _u32, _u32, _vp]),
+    "aps_get_batch_push_begin_dev": (C.c_int, [_vp, _u32, _vp, _vp]),
+    "aps_get_batch_push_end_dev": (C.c_int, [_vp, _vp, _vp]),
+    "aps_get_batch_push_dev": (C.c_int, [_vp, _u32, _vp, _vp, _vp]),
     "aps_md5_batch_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp]),
     "aps_md5_batch": (C.c_int, [_i32, _u32, _vp, _vp, _vp]),
     "aps_md5_stream_dev": (C.c_int, [_i32, _u32, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp]),

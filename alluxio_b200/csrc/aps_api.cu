@@ -176,6 +176,8 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
         g_tma.dyn_crc = g_tma.dyn_plain = dyn;
       }
     }
+    CUDA_TRY(cudaFuncSetAttribute(copy_kernel<true, 512, 4, true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)kCopyDynSmem));
     CUDA_TRY(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, dev));
     CUDA_TRY(cudaMalloc(&d.d_sm_slow, 256));
     CUDA_TRY(cudaMemset(d.d_sm_slow, 0, 256));
@@ -240,6 +242,25 @@ struct aps_store {
   // predecessor was a get too (see launch_copy)
   bool last_was_get = false;
   cudaStream_t last_stream = nullptr;
+  // push transport of the sharded multi-get (aps_push_*): everything is null until aps_push_setup
+  struct Push {
+    uint8_t* landing = nullptr;       // peers write pages here
+    uint64_t landing_bytes = 0;
+    uint8_t* ctrl = nullptr;          // inboxes | done words | result slots, one allocation (exported to the peers)
+    uint64_t ctrl_bytes = 0, off_done = 0, off_results = 0;
+    uint32_t cap = 0, depth = 0, n_shards = 0, me = 0;
+    bool attached = false;
+    PushServe* d_serve = nullptr;     // the owner-side maps, in device memory
+    uint8_t* peer_ctrl[kPushMaxShards] = {};  // peers' control blocks as mapped here
+    uint32_t* d_acc = nullptr;        // the serve kernel's own scratch: it runs next to this store's other kernels
+    uint32_t* d_done = nullptr;
+    uint32_t* d_sched = nullptr;
+    uint32_t* d_served = nullptr;
+    cudaStream_t serve_stream = nullptr;
+    uint32_t seq_begun = 0, seq_ended = 0;
+    uint32_t n_of[4] = {};            // batch size of the rounds in flight, by slot
+    std::vector<void*> ipc_ptrs;
+  } push;
   std::atomic<uint64_t> launches{0};
   // optional timing of the copy kernel (aps_profile_*): event pairs recorded around each launch
   bool prof_on = false;
@@ -432,6 +453,19 @@ void free_store(aps_store* s) {
   for (void* p : s->ipc_ptrs) cudaIpcCloseMemHandle(p);
   s->ipc_ptrs.clear();
   cudaFree(s->d_done);
+  if (s->push.serve_stream) {
+    cudaStreamSynchronize(s->push.serve_stream);
+    cudaStreamDestroy(s->push.serve_stream);
+  }
+  for (void* p : s->push.ipc_ptrs) cudaIpcCloseMemHandle(p);
+  s->push.ipc_ptrs.clear();
+  cudaFree(s->push.landing);
+  cudaFree(s->push.ctrl);
+  cudaFree(s->push.d_serve);
+  cudaFree(s->push.d_acc);
+  cudaFree(s->push.d_done);
+  cudaFree(s->push.d_sched);
+  cudaFree(s->push.d_served);
   cudaFree(s->d_jslot);
   cudaFree(s->d_clock);
   cudaFree(s->d_d2h_stage);
@@ -1236,6 +1270,239 @@ int aps_get_batch_sharded_dev(aps_store* s, uint32_t n, const aps_get_req* d_req
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   return launch_copy(s, n, d_reqs, d_res, nullptr, st, /*sharded=*/true);
+}
+
+// ---------------------------------------------------------------- push transport (owner-side serve kernels)
+
+namespace {
+struct PushHandleBlob {
+  cudaIpcMemHandle_t landing, ctrl;
+  uint64_t landing_bytes;
+  uint32_t cap, depth;
+  int32_t device;
+  uint32_t magic;
+};
+static_assert(sizeof(PushHandleBlob) <= sizeof(aps_push_handle), "handle blob must fit the opaque handle");
+constexpr uint32_t kPushMagic = 0x41505055u;  // "APPU"
+
+// Control block of one store (sized for kPushMaxShards so that it can be exported before the shard count is known):
+//   [0, off_done)            inboxes [depth][n_shards] x (PushInboxHead + cap x PushReq), written by the requesters
+//   [off_done, off_results)  done words, one per owner, written by the owners
+//   [off_results, end)       result slots [depth][cap], written by the owners
+void push_layout(aps_store::Push& p) {
+  p.off_done = (uint64_t)p.depth * kPushMaxShards * push_inbox_stride(p.cap);
+  p.off_done = (p.off_done + 255u) & ~255ull;
+  p.off_results = p.off_done + 256;
+  p.ctrl_bytes = p.off_results + (uint64_t)p.depth * p.cap * sizeof(aps_result);
+}
+
+int push_install(aps_store* s, uint32_t n_shards, uint32_t me, uint8_t* const* landing, uint8_t* const* ctrl) {
+  aps_store::Push& p = s->push;
+  PushServe h{};
+  h.n_shards = n_shards;
+  h.me = me;
+  h.cap = p.cap;
+  h.depth = p.depth;
+  h.inbox = p.ctrl;
+  h.served = p.d_served;
+  for (uint32_t r = 0; r < n_shards; ++r) {
+    h.landing[r] = landing[r];
+    h.results[r] = reinterpret_cast<aps_result*>(ctrl[r] + p.off_results);
+    h.done[r] = reinterpret_cast<unsigned long long*>(ctrl[r] + p.off_done) + me;
+    p.peer_ctrl[r] = ctrl[r];
+  }
+  CUDA_TRY(cudaMemcpy(p.d_serve, &h, sizeof(h), cudaMemcpyHostToDevice));
+  p.n_shards = n_shards;
+  p.me = me;
+  p.attached = true;
+  return APS_OK;
+}
+}  // namespace
+
+int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (landing_bytes == 0 || depth == 0 || depth > 4 || !(s->cfg.flags & APS_FLAG_CRC)) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  aps_store::Push& p = s->push;
+  if (p.ctrl) return APS_EINVAL;  // once per store
+  p.cap = s->cfg.max_batch;
+  p.depth = depth;
+  p.landing_bytes = landing_bytes;
+  push_layout(p);
+  const uint64_t jobs = (uint64_t)kPushMaxShards * p.cap;  // an owner may be asked for every request of every peer
+  cudaError_t e;
+  if ((e = cudaMalloc(&p.landing, landing_bytes)) != cudaSuccess || (e = cudaMalloc(&p.ctrl, p.ctrl_bytes)) != cudaSuccess ||
+      (e = cudaMemset(p.ctrl, 0, p.ctrl_bytes)) != cudaSuccess || (e = cudaMalloc(&p.d_serve, sizeof(PushServe))) != cudaSuccess ||
+      (e = cudaMalloc(&p.d_acc, jobs * sizeof(uint32_t))) != cudaSuccess || (e = cudaMemset(p.d_acc, 0, jobs * sizeof(uint32_t))) != cudaSuccess ||
+      (e = cudaMalloc(&p.d_done, jobs * sizeof(uint32_t))) != cudaSuccess || (e = cudaMemset(p.d_done, 0, jobs * sizeof(uint32_t))) != cudaSuccess ||
+      (e = cudaMalloc(&p.d_sched, 4 * sizeof(uint32_t))) != cudaSuccess || (e = cudaMemset(p.d_sched, 0, 4 * sizeof(uint32_t))) != cudaSuccess ||
+      (e = cudaMalloc(&p.d_served, kPushMaxShards * sizeof(uint32_t))) != cudaSuccess ||
+      (e = cudaMemset(p.d_served, 0, kPushMaxShards * sizeof(uint32_t))) != cudaSuccess ||
+      (e = cudaStreamCreateWithFlags(&p.serve_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaDeviceSynchronize()) != cudaSuccess) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "aps_push_setup: %s", cudaGetErrorString(e));
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? APS_ENOMEM : APS_ECUDA;
+  }
+  return APS_OK;
+}
+
+void* aps_push_landing(aps_store* s, uint64_t* bytes_out) {
+  if (!s || s->closed) return nullptr;
+  if (bytes_out) *bytes_out = s->push.landing_bytes;
+  return s->push.landing;
+}
+
+int aps_push_export(aps_store* s, aps_push_handle* out) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!out || !s->push.ctrl) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  PushHandleBlob b{};
+  CUDA_TRY(cudaIpcGetMemHandle(&b.landing, s->push.landing));
+  CUDA_TRY(cudaIpcGetMemHandle(&b.ctrl, s->push.ctrl));
+  b.landing_bytes = s->push.landing_bytes;
+  b.cap = s->push.cap;
+  b.depth = s->push.depth;
+  b.device = s->cfg.device;
+  b.magic = kPushMagic;
+  memset(out, 0, sizeof(*out));
+  memcpy(out, &b, sizeof(b));
+  return APS_OK;
+}
+
+int aps_push_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const aps_push_handle* handles) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!handles || n_shards == 0 || n_shards > kPushMaxShards || my_shard >= n_shards || !s->push.ctrl) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  uint8_t *landing[kPushMaxShards] = {}, *ctrl[kPushMaxShards] = {};
+  for (uint32_t i = 0; i < n_shards; ++i) {
+    if (i == my_shard) {
+      landing[i] = s->push.landing;
+      ctrl[i] = s->push.ctrl;
+      continue;
+    }
+    PushHandleBlob b;
+    memcpy(&b, &handles[i], sizeof(b));
+    if (b.magic != kPushMagic || b.cap != s->push.cap || b.depth != s->push.depth) return APS_EINVAL;
+    void *l = nullptr, *c = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&l, b.landing, cudaIpcMemLazyEnablePeerAccess));
+    s->push.ipc_ptrs.push_back(l);
+    CUDA_TRY(cudaIpcOpenMemHandle(&c, b.ctrl, cudaIpcMemLazyEnablePeerAccess));
+    s->push.ipc_ptrs.push_back(c);
+    landing[i] = (uint8_t*)l;
+    ctrl[i] = (uint8_t*)c;
+  }
+  return push_install(s, n_shards, my_shard, landing, ctrl);
+}
+
+int aps_push_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, aps_store* const* stores) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  if (!stores || n_shards == 0 || n_shards > kPushMaxShards || my_shard >= n_shards || !s->push.ctrl) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  uint8_t *landing[kPushMaxShards] = {}, *ctrl[kPushMaxShards] = {};
+  for (uint32_t i = 0; i < n_shards; ++i) {
+    aps_store* p = i == my_shard ? s : stores[i];
+    if (!p || p->closed || !p->push.ctrl || p->push.cap != s->push.cap || p->push.depth != s->push.depth) return APS_EINVAL;
+    if (p->cfg.device != s->cfg.device) {
+      cudaError_t e = cudaDeviceEnablePeerAccess(p->cfg.device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        snprintf(tl_cuda_error, sizeof(tl_cuda_error), "cudaDeviceEnablePeerAccess(%d): %s", p->cfg.device, cudaGetErrorString(e));
+        return APS_ECUDA;
+      }
+      cudaGetLastError();
+    }
+    landing[i] = p->push.landing;
+    ctrl[i] = p->push.ctrl;
+  }
+  return push_install(s, n_shards, my_shard, landing, ctrl);
+}
+
+int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  aps_store::Push& p = s->push;
+  if (!p.attached || n > p.cap || (n && !d_reqs)) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  if (p.seq_begun - p.seq_ended >= p.depth) return APS_EINVAL;  // more multi-gets in flight than the store was set up for
+  const uint32_t seq = ++p.seq_begun;
+  p.n_of[seq % p.depth] = n;
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  // requester side: route the batch to the owners' inboxes (a collective round even when n == 0)
+  PushPostArgs pa{};
+  pa.reqs = d_reqs;
+  pa.n = n;
+  pa.n_shards = p.n_shards;
+  pa.me = p.me;
+  pa.cap = p.cap;
+  pa.depth = p.depth;
+  pa.seq = seq;
+  for (uint32_t o = 0; o < p.n_shards; ++o) pa.peer_inbox[o] = p.peer_ctrl[o];
+  pa.landing = p.landing;
+  pa.landing_bytes = p.landing_bytes;
+  pa.my_results = reinterpret_cast<aps_result*>(p.ctrl + p.off_results);
+  push_post_kernel<<<1, 256, 0, st>>>(pa);
+  CUDA_TRY(cudaGetLastError());
+  // owner side: serve what the peers post for this round.  One CTA per SM but one: the SM left over runs the small
+  // post and wait kernels of this GPU, which the serve kernels of this and the other GPUs wait for.  Plain stream order
+  // (no programmatic launch) keeps two serve kernels from holding every SM between them.
+  CopyArgs a{};
+  a.table = s->table;
+  a.crc_on = 1;
+  a.res = nullptr;
+  a.acc = p.d_acc;
+  a.done = p.d_done;
+  a.tables = s->dc->d_tables;
+  a.table_image = s->use_table_image ? s->dc->d_table_image : nullptr;
+  a.rowshift = s->d_rowshift;
+  a.error_flag = s->h_error;
+  a.steal = s->use_steal ? 1 : 0;
+  a.sched = p.d_sched;
+  a.sm_slow = s->dc->d_sm_slow;
+  a.n_slow = (uint32_t)s->dc->n_slow;
+  a.push = p.d_serve;
+  a.push_seq = seq;
+  a.serve_rows = s->page_rows;
+  const uint32_t grid = (uint32_t)std::max(1, s->dc->num_sms - 1);
+  const uint32_t warps = grid * 16u;
+  a.serve_warps = warps > (uint32_t)s->dc->n_slow + p.cap ? warps - (uint32_t)s->dc->n_slow : warps;
+  copy_kernel<true, 512, 4, true, false, true><<<grid, 512, kCopyDynSmem, p.serve_stream>>>(a);
+  CUDA_TRY(cudaGetLastError());
+  count_launch(s, 2);
+  return APS_OK;
+}
+
+int aps_get_batch_push_end_dev(aps_store* s, aps_result* d_res, aps_stream stream) {
+  int rc = check_open(s);
+  if (rc) return rc;
+  aps_store::Push& p = s->push;
+  if (!p.attached) return APS_EINVAL;
+  DeviceGuard g(s->cfg.device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  if (p.seq_ended == p.seq_begun) return APS_EINVAL;  // nothing in flight
+  const uint32_t seq = ++p.seq_ended;
+  const uint32_t n = p.n_of[seq % p.depth];
+  if (n && !d_res) return APS_EINVAL;
+  cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+  push_wait_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const unsigned long long*>(p.ctrl + p.off_done), p.n_shards, seq,
+                                      reinterpret_cast<const aps_result*>(p.ctrl + p.off_results) + (size_t)(seq % p.depth) * p.cap,
+                                      d_res, n, s->h_error);
+  CUDA_TRY(cudaGetLastError());
+  count_launch(s);
+  return APS_OK;
+}
+
+int aps_get_batch_push_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream) {
+  int rc = aps_get_batch_push_begin_dev(s, n, d_reqs, stream);
+  if (rc) return rc;
+  return aps_get_batch_push_end_dev(s, d_res, stream);
 }
 
 int aps_debug_timeline(aps_store* s, int enable, uint64_t* out, uint32_t max_ctas) {

@@ -232,6 +232,39 @@ __device__ __forceinline__ uint32_t warp_bytes(const uint8_t* src, uint8_t* dst,
 
 constexpr uint32_t kMaxTasksPerJob = 128;
 
+// ------------------------------------------------------------------------------------------------
+// Push transport of the sharded multi-get.  SM stores into peer memory run ~11 % faster over
+// NVLink than SM loads from it when every GPU is busy (700 against 626 GB/s per GPU, tools/micro/p2p_transports.cu),
+// so the OWNER of a page moves it: a requester posts its requests into each owner's inbox, the owner's serve kernel
+// (this copy kernel with kServe) looks the pages up in its own table, streams them from its own slab into the
+// requester's landing buffer with the CRC32C check fused in, writes each result into the requester's result array and,
+// after the last page of that requester, raises the requester's done word.  All cross-GPU words are plain device
+// memory mapped into the peers (CUDA IPC or peer access); ordering is fence.sys + one flag word per direction.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t kPushMaxShards = 8;
+struct PushReq {       // 48 bytes, three 16-byte stores
+  aps_key key;
+  uint32_t page_off, nbytes;
+  uint64_t dst_off;    // destination, as an offset into the REQUESTER's landing buffer
+  uint32_t res_idx;    // index of the request in the requester's batch
+  uint32_t pad;
+};
+static_assert(sizeof(PushReq) == 48, "PushReq layout");
+struct PushInboxHead {  // followed by `cap` PushReq
+  unsigned long long post;  // sequence number << 32 | number of requests; written last by the requester's post kernel
+  unsigned long long pad;
+};
+struct PushServe {     // one per store, in device memory; everything an owner needs to serve its peers
+  uint32_t n_shards, me, cap, depth;
+  uint8_t* inbox;                          // my inboxes: [depth][n_shards] x (PushInboxHead + cap * PushReq)
+  uint8_t* landing[kPushMaxShards];        // requester r's landing buffer as mapped here
+  aps_result* results[kPushMaxShards];     // requester r's result slots [depth][cap] as mapped here
+  unsigned long long* done[kPushMaxShards];  // requester r's done word for owner `me` as mapped here
+  uint32_t* served;                        // scratch [n_shards]: pages finished per requester in this launch (self-resetting)
+};
+__host__ __device__ __forceinline__ size_t push_inbox_stride(uint32_t cap) { return sizeof(PushInboxHead) + (size_t)cap * sizeof(PushReq); }
+constexpr unsigned long long kPushTimeoutNs = 30ull * 1000 * 1000 * 1000;  // a peer that never posts: give up, flag it
+
 struct CopyArgs {
   const Job* jobs;           // neither kGet nor kPut: jobs prepared by an earlier kernel
   const aps_get_req* reqs;   // kGet == true: requests, resolved in this kernel
@@ -260,6 +293,10 @@ struct CopyArgs {
   uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
   const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
   uint32_t n_slow;           // how many SMs that is
+  const PushServe* push;     // kServe: the push transport's maps (device memory)
+  uint32_t push_seq;         // kServe: which posting to serve
+  uint32_t serve_rows;       // kServe: 512-byte rows of a full page ...
+  uint32_t serve_warps;      // ... and the warps of the grid: the job split is computed in the kernel, once the posts are in
   int early;                 // kGet, non-zero: requests, table and slab are known not to change under the previous kernel
                              // in the stream, so they may be read before waiting for it (see the kernel's dependency
                              // gate); early - 1 = rows to prefetch into L2 while waiting
@@ -278,6 +315,26 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
   return sh;
 }
 
+// kServe: hand one page's result to its requester and count the page; whoever delivers the requester's last page raises
+// the requester's done word.  `tag` is Job::pad (requester, index in the requester's batch); lane r of the calling warp
+// holds requester r's request count (cnt).  Every warp that stored part of the page fenced at system scope before it
+// added its rows to the page's row counter, and the caller observed that counter complete, so the fences below make the
+// whole page visible to the requester before the result, and every result before the done word.
+__device__ __forceinline__ void push_deliver(const PushServe& ps, uint32_t seq, uint32_t tag, aps_result r, uint32_t lane,
+                                             uint32_t cnt) {
+  const uint32_t who = (tag >> 24) & 0x7Fu, idx = tag & 0x00FFFFFFu;
+  const uint32_t want = __shfl_sync(0xFFFFFFFFu, cnt, who);
+  if (lane == 0) {
+    ps.results[who][(size_t)(seq % ps.depth) * ps.cap + idx] = r;
+    __threadfence_system();
+    if (atomicAdd(&ps.served[who], 1u) + 1u == want) {
+      ps.served[who] = 0;  // re-armed for the next launch (launches of one store's serve stream do not overlap)
+      __threadfence_system();
+      *(volatile unsigned long long*)ps.done[who] = seq;
+    }
+  }
+}
+
 // K2 + K3 (+ K1: lookup when kGet, insert when kPut).  Persistent grid: one CTA per SM.  A job (one page request) is
 // cut into tasks_per_job warp-tasks of rows_per_task 512-byte rows, sized by the host so that one
 // round of all warps of the chip covers the batch (no wave quantisation).  A task resolves its
@@ -288,9 +345,10 @@ __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t
 // job's accumulator.  Warps that run out of work take the back half of the longest remaining range
 // in their CTA (finish times of equal streams differ by ~10 % on a saturated memory system).  The
 // warp that completes a job's last row applies init/xorout and verifies or records the page CRC.
-template <bool kCrc, int kThreads, int G, bool kGet, bool kPut = false>
+template <bool kCrc, int kThreads, int G, bool kGet, bool kPut = false, bool kServe = false>
 __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   static_assert(!(kGet && kPut), "a launch is a get, a put, or a list of prepared jobs");
+  static_assert(!kServe || (kGet && kCrc), "the serve kernel is a get with the checksum on");
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr uint32_t nwarps = kThreads / 32;
   __shared__ unsigned long long s_range[nwarps];  // published ranges: open to stealing
@@ -310,6 +368,47 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   // WRITES (pages, results, scratch, the rank counters) stays behind the gate.
   bool dep_ok = !((kGet || kPut) && a.early);
   if (dep_ok) asm volatile("griddepcontrol.wait;" ::: "memory");
+  // kServe: the batch is what the peers have posted.  Lane r of every warp waits for requester r's posting of this
+  // sequence number and keeps its request count and the exclusive prefix; the job split follows from the total.
+  uint32_t srv_cnt = 0, srv_pre = 0;
+  if (kServe) {
+    const PushServe& ps = *a.push;
+    if (lane < ps.n_shards) {
+      const volatile unsigned long long* word = (const volatile unsigned long long*)(
+          ps.inbox + ((size_t)(a.push_seq % ps.depth) * ps.n_shards + lane) * push_inbox_stride(ps.cap));
+      const unsigned long long t0 = globaltimer_ns();
+      unsigned long long w = *word;
+      while ((uint32_t)(w >> 32) != a.push_seq) {
+        if (globaltimer_ns() - t0 > kPushTimeoutNs) {  // the peer never posted (it failed, or skipped a collective call)
+          *a.error_flag = 3;
+          w = (unsigned long long)a.push_seq << 32;
+          break;
+        }
+        __nanosleep(100);
+        w = *word;
+      }
+      srv_cnt = min((uint32_t)w, ps.cap);
+    }
+    __threadfence_system();  // acquire: the requests were written before the posting word
+    uint32_t incl = srv_cnt;
+#pragma unroll
+    for (int o = 1; o < (int)kPushMaxShards; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+      if (lane >= (uint32_t)o) incl += up;
+    }
+    srv_pre = incl - srv_cnt;
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, kPushMaxShards - 1);
+    a.n_jobs = total;
+    uint32_t tpj = max(1u, a.serve_warps / max(total, 1u));
+    tpj = min(tpj, min(kMaxTasksPerJob, max(1u, a.serve_rows / 8u)));
+    a.rows_per_task = (a.serve_rows + tpj - 1u) / tpj;
+    a.tasks_per_job = (a.serve_rows + a.rows_per_task - 1u) / a.rows_per_task;
+    // a requester that asked this owner for nothing still waits for its done word
+    if (blockIdx.x == 0 && warp == 0 && lane < ps.n_shards && srv_cnt == 0) {
+      __threadfence_system();
+      *(volatile unsigned long long*)ps.done[lane] = a.push_seq;
+    }
+  }
   const uint32_t n_items = a.n_jobs * a.tasks_per_job;
   // Task assignment.  n_items / grid tasks per CTA are fixed by blockIdx, so warps can start at once.  The
   // n_items % grid surplus tasks go to the CTAs with the lowest RANK: CTAs on fast SMs count up from 0,
@@ -432,7 +531,27 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       const uint32_t c = item - job * a.tasks_per_job;
       if (kGet) {
         // every task of a page probes for itself (the bucket is an L2 hit after the first); task 0 reports
-        aps_get_req rq = a.reqs[job];
+        aps_get_req rq;
+        uint32_t srv_tag = 0;  // kServe: 0x80000000 | requester << 24 | index in the requester's batch
+        if (kServe) {
+          const PushServe& ps = *a.push;
+          const uint32_t owner_mask = __ballot_sync(0xFFFFFFFFu, lane < ps.n_shards && srv_pre <= job && srv_cnt != 0);
+          const uint32_t r = 31u - (uint32_t)__clz((int)owner_mask);  // the last requester whose range starts at or before job
+          const uint32_t i = job - __shfl_sync(0xFFFFFFFFu, srv_pre, r);
+          const PushReq* q = reinterpret_cast<const PushReq*>(
+              ps.inbox + ((size_t)(a.push_seq % ps.depth) * ps.n_shards + r) * push_inbox_stride(ps.cap) + sizeof(PushInboxHead)) + i;
+          const uint4 q0 = __ldcg(reinterpret_cast<const uint4*>(q)), q1 = __ldcg(reinterpret_cast<const uint4*>(q) + 1),
+                      q2 = __ldcg(reinterpret_cast<const uint4*>(q) + 2);
+          rq.key.file_hi = (uint64_t)q0.x | ((uint64_t)q0.y << 32);
+          rq.key.file_lo = (uint64_t)q0.z | ((uint64_t)q0.w << 32);
+          rq.key.page_index = (uint64_t)q1.x | ((uint64_t)q1.y << 32);
+          rq.page_off = q1.z;
+          rq.nbytes = q1.w;
+          rq.dst = ps.landing[r] + ((uint64_t)q2.x | ((uint64_t)q2.y << 32));
+          srv_tag = 0x80000000u | (r << 24) | (q2.z & 0x00FFFFFFu);
+        } else {
+          rq = a.reqs[job];
+        }
         Probe pr{0, 0, 0, 0};
         int32_t status = 0;
         for (;;) {
@@ -444,7 +563,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
           __syncwarp();
           const uint64_t meta = __shfl_sync(0xFFFFFFFFu, pr.meta, 0);
           status = 0;
-          j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, 0};
+          j = Job{nullptr, (uint8_t*)rq.dst, 0, 0, 0, kServe ? srv_tag : 0u};
           if (!meta) {
             status = -APS_ENOTFOUND;
           } else if (rq.page_off > meta_len(meta)) {  // LocalPageStore.java:99-100
@@ -454,7 +573,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
             j.slot = meta_slot(meta);
             j.n = min(plen - rq.page_off, rq.nbytes);  // LocalPageStore.java:109-110
             j.src = tb.slab + (uint64_t)j.slot * tb.page_size + rq.page_off;
-            j.pad = a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u;  // which shard's slot_crc to check
+            j.pad = kServe ? srv_tag : (a.n_shards > 1 ? shard_of(rq.key, a.n_shards) + 1u : 0u);  // which shard's slot_crc to check
             j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
             status = (int32_t)j.n;
             if (c == 0 && lane == 0 && tb.slot_ref) tb.slot_ref[j.slot] = 1;  // CLOCK: referenced (a store that commutes)
@@ -601,7 +720,11 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       tail_mine = c == 0 && (j.n % kRowBytes) != 0;
       if (report) {
         gate();
-        if (lane == 0) a.res[job] = aps_result{report_status, 0};
+        if (kServe) {
+          push_deliver(*a.push, a.push_seq, j.pad, aps_result{report_status, 0}, lane, srv_cnt);
+        } else if (lane == 0) {
+          a.res[job] = aps_result{report_status, 0};
+        }
       }
       if (row_lo >= row_hi && !tail_mine) continue;
       publish = last_item;  // only a warp's final task is open to stealing (its descriptor stays valid)
@@ -695,6 +818,10 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     }
     const uint32_t target = (j.n + kRowBytes - 1) / kRowBytes;
     uint32_t prev = 0;
+    if (kServe) {  // every lane's stores into the requester's memory are ordered before the row count that announces them
+      __threadfence_system();
+      __syncwarp();
+    }
     if (lane == 0) {
       atomicXor(&a.acc[job], contrib);
       __threadfence();
@@ -702,6 +829,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     }
     prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
     if (prev + units != target) continue;
+    aps_result fin{0, 0};
     if (lane == 0) {  // this segment completed the job
       __threadfence();
       const uint32_t x = atomicExch(&a.acc[job], 0u);
@@ -709,14 +837,16 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       bool corrupt = false;
       if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
       if (j.flags & kJobOutCrc) a.crc_out[job] = full;
-      const uint32_t* recorded = (kGet && j.pad) ? a.shards[j.pad - 1u].slot_crc : a.table.slot_crc;
+      const uint32_t* recorded = (kGet && !kServe && j.pad) ? a.shards[j.pad - 1u].slot_crc : a.table.slot_crc;
       if ((j.flags & kJobVerify) && __ldcg(&recorded[j.slot]) != full) {
         corrupt = true;
         atomicAdd(&a.table.counters[kCtrCrcMismatch], 1ull);
       }
-      if (a.res) a.res[job] = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
+      fin = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
+      if (!kServe && a.res) a.res[job] = fin;
       a.done[job] = 0;
     }
+    if (kServe) push_deliver(*a.push, a.push_seq, j.pad, fin, lane, srv_cnt);
   }
   gate();  // a warp that found nothing to do arrives here without having waited
   if (warp == surplus_warp && lane == 0) {
@@ -1170,6 +1300,81 @@ __global__ void __launch_bounds__(kK1Threads) lookup_kernel(Table t, const aps_k
     }
   }
   acct_flush(acct, t);
+}
+
+// Push transport, requester side (one small CTA each; they run next to the serve kernel, which leaves one SM free).
+// push_post_kernel routes a batch: request i goes into the inbox that requester `me` has on the GPU owning its page,
+// at a position taken from a per-owner counter, then one posting word per owner (sequence number << 32 | count)
+// announces them.  A destination outside the landing buffer cannot be written by a peer: that request is answered
+// -APS_EINVAL on the spot and not posted.
+struct PushPostArgs {
+  const aps_get_req* reqs;
+  uint32_t n, n_shards, me, cap, depth, seq;
+  uint8_t* peer_inbox[kPushMaxShards];  // owner o's inbox array as mapped here
+  const uint8_t* landing;               // my landing buffer
+  uint64_t landing_bytes;
+  aps_result* my_results;               // my result slots [depth][cap]
+};
+__global__ void __launch_bounds__(256) push_post_kernel(PushPostArgs p) {
+  __shared__ uint32_t s_cnt[kPushMaxShards];
+  if (threadIdx.x < kPushMaxShards) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t slot = p.seq % p.depth;
+  for (uint32_t i = threadIdx.x; i < p.n; i += blockDim.x) {
+    const aps_get_req rq = p.reqs[i];
+    const uint8_t* d = (const uint8_t*)rq.dst;
+    if (rq.nbytes && (d < p.landing || d + rq.nbytes > p.landing + p.landing_bytes)) {
+      p.my_results[(size_t)slot * p.cap + i] = aps_result{-APS_EINVAL, 0};
+      continue;
+    }
+    const uint32_t owner = shard_of(rq.key, p.n_shards);
+    const uint32_t pos = atomicAdd(&s_cnt[owner], 1u);
+    uint4* q = reinterpret_cast<uint4*>(p.peer_inbox[owner] + ((size_t)slot * p.n_shards + p.me) * push_inbox_stride(p.cap) +
+                                        sizeof(PushInboxHead) + (size_t)pos * sizeof(PushReq));
+    const uint64_t off = rq.nbytes ? (uint64_t)(d - p.landing) : 0;
+    q[0] = make_uint4((uint32_t)rq.key.file_hi, (uint32_t)(rq.key.file_hi >> 32), (uint32_t)rq.key.file_lo, (uint32_t)(rq.key.file_lo >> 32));
+    q[1] = make_uint4((uint32_t)rq.key.page_index, (uint32_t)(rq.key.page_index >> 32), rq.page_off, rq.nbytes);
+    q[2] = make_uint4((uint32_t)off, (uint32_t)(off >> 32), i, 0u);
+  }
+  __threadfence_system();  // every thread: its requests are out before the posting words
+  __syncthreads();
+  if (threadIdx.x < p.n_shards) {
+    volatile unsigned long long* word = (volatile unsigned long long*)(
+        p.peer_inbox[threadIdx.x] + ((size_t)slot * p.n_shards + p.me) * push_inbox_stride(p.cap));
+    *word = ((unsigned long long)p.seq << 32) | s_cnt[threadIdx.x];
+  }
+}
+
+// push_wait_kernel: the stream-ordered end of a pushed multi-get.  Waits until every owner has raised this GPU's done
+// word for `seq` (the pages are then in the landing buffer), then copies the results into the caller's array.
+__global__ void __launch_bounds__(256) push_wait_kernel(const unsigned long long* done, uint32_t n_shards, uint32_t seq,
+                                                        const aps_result* slot_results, aps_result* res, uint32_t n, int* error_flag) {
+  __shared__ int s_ok;
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if (threadIdx.x < n_shards) {
+    const volatile unsigned long long* word = (const volatile unsigned long long*)&done[threadIdx.x];
+    const unsigned long long t0 = globaltimer_ns();
+    while (*word < (unsigned long long)seq) {  // sequence numbers only grow
+      if (globaltimer_ns() - t0 > kPushTimeoutNs) {
+        *error_flag = 4;
+        s_ok = 0;
+        break;
+      }
+      __nanosleep(200);
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+    aps_result r{-APS_ETIMEOUT, 0};
+    if (s_ok) {
+      const unsigned long long v = __ldcg(reinterpret_cast<const unsigned long long*>(&slot_results[i]));  // written by a peer: from L2
+      r.len = (int32_t)(uint32_t)v;
+      r.crc = (uint32_t)(v >> 32);
+    }
+    res[i] = r;
+  }
 }
 
 // jobs for the stand-alone checksum pass

@@ -200,6 +200,36 @@ APS_API int aps_get_batch_sharded_dev(aps_store* s, uint32_t n, const aps_get_re
 /* As aps_get_batch (host arrays, waits), served from the owning shards. */
 APS_API int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream);
 
+/* ---- push transport for the sharded multi-get (additive; no counterpart in the reference, whose cache is
+ * process-local: CACHE/LocalCacheManager.java has no remote tier) --------------------------------------------------
+ * Over NVLink with every GPU busy, stores into a peer run faster than loads from it (700 against 626 GB/s per GPU
+ * measured, tools/micro/p2p_transports.cu), so here the OWNER moves a page: a multi-get posts its requests to the
+ * owning GPUs, each owner's serve kernel looks the pages up in its own table and streams them from its own slab into
+ * the requester's LANDING BUFFER with the CRC32C check fused in, and the requester's stream waits for the owners' done
+ * words.  Destinations must therefore lie in memory the peers can write: the landing buffer allocated by
+ * aps_push_setup (requests with a destination outside it are answered -APS_EINVAL).  The store must have APS_FLAG_CRC.
+ *   set-up:  aps_push_setup on every store, exchange aps_push_handle blobs (CUDA IPC), aps_push_attach; or
+ *            aps_push_attach_local for stores of one process.  depth = multi-gets a store may have in flight (1..4).
+ *   use:     aps_get_batch_push_begin_dev posts batch k and starts this GPU's serve kernel for round k (on a stream of
+ *            the store's own); aps_get_batch_push_end_dev makes `stream` wait until the oldest batch in flight has
+ *            landed and writes its results.  aps_get_batch_push_dev = begin + end.  A caller that wants two batches in
+ *            flight issues begin(k+1) before end(k), with different destination ranges.
+ * COLLECTIVE: every store of the shard set must issue the same sequence of begin calls (an owner's round k waits for
+ * round k's posting of every peer; a peer that never calls makes the others time out after 30 s with -APS_ETIMEOUT
+ * results).  begin and end calls of one store must be ordered among themselves (one stream, or events).  Puts and
+ * deletes on an owner are not ordered against the serve kernels: keep them apart, as for aps_get_batch_sharded_dev. */
+typedef struct aps_push_handle {
+  unsigned char opaque[192];
+} aps_push_handle;
+APS_API int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth);
+APS_API void* aps_push_landing(aps_store* s, uint64_t* bytes_out);
+APS_API int aps_push_export(aps_store* s, aps_push_handle* out);
+APS_API int aps_push_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const aps_push_handle* handles);
+APS_API int aps_push_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, aps_store* const* stores);
+APS_API int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_stream stream);
+APS_API int aps_get_batch_push_end_dev(aps_store* s, aps_result* d_res, aps_stream stream);
+APS_API int aps_get_batch_push_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_result* d_res, aps_stream stream);
+
 /* ---- checksum path: `alluxio fs checksum` ------------------------------------------------------
  * ChecksumCommand.calculateChecksum (shell/src/main/java/alluxio/cli/fs/command/
  * ChecksumCommand.java:83-90) = DigestUtils.md5Hex over the file's bytes.  One digest per file,

@@ -39,3 +39,14 @@ def fill_pages(dst, stride, page_len, files, indices, seed, device=0):
     capi.check(capi.lib().aps_fill_pages_dev(device, dst.data_ptr(), stride, page_len, len(files), f.data_ptr(),
                                              i.data_ptr(), seed, cur_stream()), "aps_fill_pages_dev")
     torch.cuda.synchronize()
+
+
+class _RawDeviceMemory:
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+def raw_tensor(ptr, nbytes, device="cuda:0"):
+    """A uint8 tensor over device memory somebody else allocated (e.g. the library's landing buffer); no copy."""
+    with torch.cuda.device(device):
+        return torch.as_tensor(_RawDeviceMemory(ptr, nbytes), device=device)
