@@ -249,6 +249,7 @@ struct aps_store {
     uint8_t* ctrl = nullptr;          // inboxes | done words | result slots, one allocation (exported to the peers)
     uint64_t ctrl_bytes = 0, off_done = 0, off_results = 0;
     uint32_t cap = 0, depth = 0, n_shards = 0, me = 0;
+    uint32_t sharing = 1;             // shards whose serve kernels run on this device (they split the SMs)
     bool attached = false;
     PushServe* d_serve = nullptr;     // the owner-side maps, in device memory
     uint8_t* peer_ctrl[kPushMaxShards] = {};  // peers' control blocks as mapped here
@@ -1281,6 +1282,7 @@ struct PushHandleBlob {
   uint32_t cap, depth;
   int32_t device;
   uint32_t magic;
+  char pci[16];  // PCI bus id of the exporting store's GPU: ordinals mean nothing across processes
 };
 static_assert(sizeof(PushHandleBlob) <= sizeof(aps_push_handle), "handle blob must fit the opaque handle");
 constexpr uint32_t kPushMagic = 0x41505055u;  // "APPU"
@@ -1296,8 +1298,9 @@ void push_layout(aps_store::Push& p) {
   p.ctrl_bytes = p.off_results + (uint64_t)p.depth * p.cap * sizeof(aps_result);
 }
 
-int push_install(aps_store* s, uint32_t n_shards, uint32_t me, uint8_t* const* landing, uint8_t* const* ctrl) {
+int push_install(aps_store* s, uint32_t n_shards, uint32_t me, uint8_t* const* landing, uint8_t* const* ctrl, uint32_t sharing) {
   aps_store::Push& p = s->push;
+  p.sharing = std::max(1u, sharing);
   PushServe h{};
   h.n_shards = n_shards;
   h.me = me;
@@ -1327,6 +1330,15 @@ int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth) {
   std::lock_guard<std::mutex> lk(s->mu);
   aps_store::Push& p = s->push;
   if (p.ctrl) return APS_EINVAL;  // once per store
+  {
+    // The three kernels of a round wait for each other across streams and GPUs.  With lazy module loading the FIRST
+    // launch of a kernel may have to wait for the device to go idle, which it never does while a serve kernel spins
+    // for a posting that this very launch would lead to.  Load them now.
+    cudaFuncAttributes fa{};
+    CUDA_TRY(cudaFuncGetAttributes(&fa, push_post_kernel));
+    CUDA_TRY(cudaFuncGetAttributes(&fa, push_wait_kernel));
+    CUDA_TRY(cudaFuncGetAttributes(&fa, copy_kernel<true, 512, 4, true, false, true>));
+  }
   p.cap = s->cfg.max_batch;
   p.depth = depth;
   p.landing_bytes = landing_bytes;
@@ -1368,6 +1380,7 @@ int aps_push_export(aps_store* s, aps_push_handle* out) {
   b.depth = s->push.depth;
   b.device = s->cfg.device;
   b.magic = kPushMagic;
+  CUDA_TRY(cudaDeviceGetPCIBusId(b.pci, sizeof(b.pci), s->cfg.device));
   memset(out, 0, sizeof(*out));
   memcpy(out, &b, sizeof(b));
   return APS_OK;
@@ -1380,6 +1393,9 @@ int aps_push_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const ap
   DeviceGuard g(s->cfg.device);
   std::lock_guard<std::mutex> lk(s->mu);
   uint8_t *landing[kPushMaxShards] = {}, *ctrl[kPushMaxShards] = {};
+  uint32_t sharing = 1;
+  char my_pci[16] = "";
+  CUDA_TRY(cudaDeviceGetPCIBusId(my_pci, sizeof(my_pci), s->cfg.device));
   for (uint32_t i = 0; i < n_shards; ++i) {
     if (i == my_shard) {
       landing[i] = s->push.landing;
@@ -1396,8 +1412,9 @@ int aps_push_attach(aps_store* s, uint32_t n_shards, uint32_t my_shard, const ap
     s->push.ipc_ptrs.push_back(c);
     landing[i] = (uint8_t*)l;
     ctrl[i] = (uint8_t*)c;
+    if (strncmp(b.pci, my_pci, sizeof(my_pci)) == 0) ++sharing;
   }
-  return push_install(s, n_shards, my_shard, landing, ctrl);
+  return push_install(s, n_shards, my_shard, landing, ctrl, sharing);
 }
 
 int aps_push_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, aps_store* const* stores) {
@@ -1407,6 +1424,7 @@ int aps_push_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, ap
   DeviceGuard g(s->cfg.device);
   std::lock_guard<std::mutex> lk(s->mu);
   uint8_t *landing[kPushMaxShards] = {}, *ctrl[kPushMaxShards] = {};
+  uint32_t sharing = 1;
   for (uint32_t i = 0; i < n_shards; ++i) {
     aps_store* p = i == my_shard ? s : stores[i];
     if (!p || p->closed || !p->push.ctrl || p->push.cap != s->push.cap || p->push.depth != s->push.depth) return APS_EINVAL;
@@ -1420,8 +1438,9 @@ int aps_push_attach_local(aps_store* s, uint32_t n_shards, uint32_t my_shard, ap
     }
     landing[i] = p->push.landing;
     ctrl[i] = p->push.ctrl;
+    if (i != my_shard && p->cfg.device == s->cfg.device) ++sharing;
   }
-  return push_install(s, n_shards, my_shard, landing, ctrl);
+  return push_install(s, n_shards, my_shard, landing, ctrl, sharing);
 }
 
 int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_reqs, aps_stream stream) {
@@ -1470,7 +1489,10 @@ int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_
   a.push = p.d_serve;
   a.push_seq = seq;
   a.serve_rows = s->page_rows;
-  const uint32_t grid = (uint32_t)std::max(1, s->dc->num_sms - 1);
+  static const int spare = [] { const char* e = getenv("APS_SERVE_SPARE_SMS"); return e ? std::max(0, atoi(e)) : 1; }();
+  // several shards on ONE device (tests, small deployments) split the SMs, so that their serve kernels together never
+  // hold every SM while they wait for a posting
+  const uint32_t grid = (uint32_t)std::max(1, (s->dc->num_sms - spare) / (int)p.sharing);
   const uint32_t warps = grid * 16u;
   a.serve_warps = warps > (uint32_t)s->dc->n_slow + p.cap ? warps - (uint32_t)s->dc->n_slow : warps;
   copy_kernel<true, 512, 4, true, false, true><<<grid, 512, kCopyDynSmem, p.serve_stream>>>(a);

@@ -371,6 +371,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
   // kServe: the batch is what the peers have posted.  Lane r of every warp waits for requester r's posting of this
   // sequence number and keeps its request count and the exclusive prefix; the job split follows from the total.
   uint32_t srv_cnt = 0, srv_pre = 0;
+  bool srv_lost = false;  // this lane's requester never posted: it gets no done word, so its own wait reports the time-out
   if (kServe) {
     const PushServe& ps = *a.push;
     if (lane < ps.n_shards) {
@@ -382,6 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
         if (globaltimer_ns() - t0 > kPushTimeoutNs) {  // the peer never posted (it failed, or skipped a collective call)
           *a.error_flag = 3;
           w = (unsigned long long)a.push_seq << 32;
+          srv_lost = true;
           break;
         }
         __nanosleep(100);
@@ -404,7 +406,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     a.rows_per_task = (a.serve_rows + tpj - 1u) / tpj;
     a.tasks_per_job = (a.serve_rows + a.rows_per_task - 1u) / a.rows_per_task;
     // a requester that asked this owner for nothing still waits for its done word
-    if (blockIdx.x == 0 && warp == 0 && lane < ps.n_shards && srv_cnt == 0) {
+    if (blockIdx.x == 0 && warp == 0 && lane < ps.n_shards && srv_cnt == 0 && !srv_lost) {
       __threadfence_system();
       *(volatile unsigned long long*)ps.done[lane] = a.push_seq;
     }

@@ -162,7 +162,8 @@ def _run_push(n_shards, devices, depth, rounds=4):
         streams[r].synchronize()
         res = from_dev(d_res[r, k], RESULT)
         host = _copy_from_device(land[r][0] + (k % depth) * nreq * ps, nreq * ps, devs[r])
-        assert res[-1]["len"] == -capi.APS_ENOTFOUND
+        assert res[-1]["len"] == -capi.APS_ENOTFOUND, (r, k, res["len"][-8:].tolist(), int((res["len"] == 0).sum()),
+                                                       int((res["len"] == -capi.APS_ETIMEOUT).sum()), time.time() - t_round)
         remote = 0
         for q, i in enumerate(picks[r][k]):
             if k == 1 and q == 7:
@@ -177,8 +178,11 @@ def _run_push(n_shards, devices, depth, rounds=4):
             remote += owners[i] != r
         assert remote > 0
 
+    import time
+    t_round = time.time()
     if depth == 1:
         for k in range(rounds):
+            t_round = time.time()
             for r in range(n_shards):
                 capi.check(L.aps_get_batch_push_dev(stores[r].handle, nreq, d_reqs[r, k].data_ptr(), d_res[r, k].data_ptr(), sp(r)), "push get")
             for r in range(n_shards):
