@@ -227,6 +227,10 @@ struct aps_store {
   uint8_t* h_bounce = nullptr;  // pinned: one page, for pageable single-page callers
   uint8_t* d_d2h_stage = nullptr;  // HBM staging for batched gets whose destinations are in host memory (grown on demand)
   uint64_t d2h_stage_bytes = 0;
+  bool d2h_stage_failed = false;
+  cudaStream_t copy_stream = nullptr;  // the copy engine's stream for staged host-destination gets
+  cudaEvent_t chunk_ev[8] = {};
+  std::vector<std::pair<const void*, bool>> ptr_kind;  // is_pinned_host's memo
   bool use_d2h_stage = true;       // APS_NO_D2H_STAGE=1: let the kernel store into host memory directly
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
@@ -470,6 +474,9 @@ void free_store(aps_store* s) {
   cudaFree(s->d_jslot);
   cudaFree(s->d_clock);
   cudaFree(s->d_d2h_stage);
+  if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+  for (cudaEvent_t e : s->chunk_ev)
+    if (e) cudaEventDestroy(e);
   cudaFree(s->table.slot_ref);
   cudaFree(s->table.slot_entry);
   cudaFree(s->d_error);
@@ -844,14 +851,30 @@ int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   return get_batch_host(s, n, reqs, res, stream, true);
 }
 
+// Is `p` page-locked host memory?  Asked once per distinct pointer (a reader hands the same few pinned buffers back
+// again and again); the driver call costs microseconds that the batched path does not have to spare.
+static bool is_pinned_host(aps_store* s, const void* p) {
+  for (const auto& e : s->ptr_kind)
+    if (e.first == p) return e.second;
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) cudaGetLastError();
+  const bool host = at.type == cudaMemoryTypeHost;
+  if (s->ptr_kind.size() >= 16) s->ptr_kind.erase(s->ptr_kind.begin());
+  s->ptr_kind.emplace_back(p, host);
+  return host;
+}
+
 static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream, bool sharded) {
   int rc = check_open(s);
   if (rc) return rc;
   if (n == 0) return APS_OK;
   if (!reqs || !res) return APS_EINVAL;
-  if (n > s->cfg.max_batch) {  // larger than the staging area: serve it in pieces
-    for (uint32_t lo = 0; lo < n; lo += s->cfg.max_batch) {
-      rc = get_batch_host(s, std::min(s->cfg.max_batch, n - lo), reqs + lo, res + lo, stream, sharded);
+  const uint64_t slot = ((uint64_t)s->table.page_size + 255u) & ~255ull;
+  // one call serves at most max_batch requests and at most 1 GiB of staging slots; more is served in pieces
+  const uint32_t limit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(s->cfg.max_batch, (1ull << 30) / slot));
+  if (n > limit) {
+    for (uint32_t lo = 0; lo < n; lo += limit) {
+      rc = get_batch_host(s, std::min(limit, n - lo), reqs + lo, res + lo, stream, sharded);
       if (rc) return rc;
     }
     return APS_OK;
@@ -864,46 +887,78 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_get_req));
   // Destinations in pinned HOST memory: stores issued by SMs cross PCIe at ~0.91 of what the copy engines reach
   // (52 against 57 GB/s measured), so large batches are gathered into an HBM staging area at HBM speed and handed
-  // to the copy engine, which also coalesces neighbouring destinations into one transfer.
-  const uint64_t slot = ((uint64_t)s->cfg.page_size + 255u) & ~255ull;
-  bool via_stage = s->use_d2h_stage && (uint64_t)n * s->cfg.page_size >= (8ull << 20) && (uint64_t)n * slot <= (1ull << 30);
-  if (via_stage) {
-    cudaPointerAttributes at{};
-    if (cudaPointerGetAttributes(&at, reqs[0].dst) != cudaSuccess) cudaGetLastError();
-    via_stage = at.type == cudaMemoryTypeHost;
+  // to the copy engine, which also coalesces neighbouring destinations into one transfer.  The staging area is
+  // allocated once (for the largest batch one call serves) and kept.
+  const uint64_t stage_want = (uint64_t)limit * slot;
+  bool via_stage = s->use_d2h_stage && (uint64_t)n * s->cfg.page_size >= (8ull << 20) && is_pinned_host(s, reqs[0].dst);
+  if (via_stage && !s->d_d2h_stage && !s->d2h_stage_failed) {
+    if (cudaMalloc(&s->d_d2h_stage, stage_want) == cudaSuccess &&
+        cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) == cudaSuccess) {
+      s->d2h_stage_bytes = stage_want;
+      for (cudaEvent_t& e : s->chunk_ev)
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) s->d2h_stage_failed = true;
+    } else {
+      cudaGetLastError();
+      s->d2h_stage_failed = true;  // no room for it: store straight into host memory, and do not ask again
+    }
   }
-  if (via_stage && s->d2h_stage_bytes < (uint64_t)n * slot) {
-    cudaFree(s->d_d2h_stage);
-    s->d_d2h_stage = nullptr;
-    s->d2h_stage_bytes = 0;
-    if (cudaMalloc(&s->d_d2h_stage, (uint64_t)n * slot) == cudaSuccess) s->d2h_stage_bytes = (uint64_t)n * slot;
-    else { cudaGetLastError(); via_stage = false; }  // no room for it: store straight into host memory as before
+  via_stage = via_stage && s->d_d2h_stage && !s->d2h_stage_failed;
+  if (!via_stage) {
+    CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
+    s->host_form = true;
+    rc = sharded ? aps_get_batch_sharded_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st)
+                 : aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
+    s->host_form = false;
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
+    rc = check_device_error(s, st);  // also waits for the stream
+    if (rc) return rc;
+    memcpy(res, h_res, (size_t)n * sizeof(aps_result));
+    return APS_OK;
   }
-  if (via_stage)
-    for (uint32_t i = 0; i < n; ++i) h_reqs[i].dst = s->d_d2h_stage + (uint64_t)i * slot;
+  // Pipelined: the batch is cut into chunks of ~32 MiB.  All gather kernels (and the copies of their results) are
+  // enqueued at once; the host then follows them chunk by chunk -- as soon as chunk k's results are in, its pages are
+  // handed to the copy engine on a second stream while the SMs gather chunk k+1.  The link idles only while the first
+  // chunk is gathered (~10 us of a 4.7 ms batch of 256 MiB).
+  for (uint32_t i = 0; i < n; ++i) h_reqs[i].dst = s->d_d2h_stage + (uint64_t)i * slot;
   CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
+  constexpr uint32_t kMaxChunks = 8;
+  const uint32_t per = std::max<uint32_t>(1, std::max<uint32_t>((n + kMaxChunks - 1) / kMaxChunks, (uint32_t)((32ull << 20) / slot)));
+  const uint32_t n_chunks = (n + per - 1) / per;
   s->host_form = true;
-  rc = sharded ? aps_get_batch_sharded_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st)
-               : aps_get_batch_dev(s, n, (const aps_get_req*)s->d_reqs, s->d_res, st);
+  for (uint32_t c = 0; c < n_chunks && rc == APS_OK; ++c) {
+    const uint32_t lo = c * per, cnt = std::min(per, n - lo);
+    const aps_get_req* dq = (const aps_get_req*)s->d_reqs + lo;
+    rc = sharded ? aps_get_batch_sharded_dev(s, cnt, dq, s->d_res + lo, st) : aps_get_batch_dev(s, cnt, dq, s->d_res + lo, st);
+    if (rc == APS_OK && cudaMemcpyAsync(h_res + lo, s->d_res + lo, (size_t)cnt * sizeof(aps_result), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+      rc = APS_ECUDA;
+    if (rc == APS_OK && cudaEventRecord(s->chunk_ev[c], st) != cudaSuccess) rc = APS_ECUDA;
+  }
   s->host_form = false;
-  if (rc) return rc;
-  CUDA_TRY(cudaMemcpyAsync(h_res, s->d_res, (size_t)n * sizeof(aps_result), cudaMemcpyDeviceToHost, st));
-  rc = check_device_error(s, st);  // also waits for the stream
-  if (rc) return rc;
-  if (via_stage) {
+  if (rc) {
+    cudaStreamSynchronize(st);
+    return rc;
+  }
+  for (uint32_t c = 0; c < n_chunks; ++c) {
+    const uint32_t lo = c * per, hi = std::min(n, lo + per);
+    CUDA_TRY(cudaEventSynchronize(s->chunk_ev[c]));
     // exactly the bytes each get returned, runs of requests that are adjacent on both sides as one copy
-    uint32_t i = 0;
-    while (i < n) {
+    uint32_t i = lo;
+    while (i < hi) {
       if (h_res[i].len <= 0) { ++i; continue; }
       uint64_t bytes = (uint64_t)h_res[i].len;
       uint32_t j = i + 1;
-      while (j < n && bytes == (uint64_t)(j - i) * slot && h_res[j].len > 0 &&
+      while (j < hi && bytes == (uint64_t)(j - i) * slot && h_res[j].len > 0 &&
              (uint8_t*)reqs[j].dst == (uint8_t*)reqs[i].dst + bytes)
         bytes += (uint64_t)h_res[j++].len;
-      CUDA_TRY(cudaMemcpyAsync(reqs[i].dst, s->d_d2h_stage + (uint64_t)i * slot, bytes, cudaMemcpyDefault, st));
+      CUDA_TRY(cudaMemcpyAsync(reqs[i].dst, s->d_d2h_stage + (uint64_t)i * slot, bytes, cudaMemcpyDefault, s->copy_stream));
       i = j;
     }
-    CUDA_TRY(cudaStreamSynchronize(st));
+  }
+  CUDA_TRY(cudaStreamSynchronize(s->copy_stream));
+  if (*(volatile int*)s->h_error) {
+    snprintf(tl_cuda_error, sizeof(tl_cuda_error), "copy kernel: shared-memory window not at the expected address");
+    return APS_ECUDA;
   }
   memcpy(res, h_res, (size_t)n * sizeof(aps_result));
   return APS_OK;

@@ -1,15 +1,16 @@
 #!/usr/bin/env python
-"""Benchmark of the page-cache hot path (BASELINE.json configs[1]).
+"""Benchmark of the page-cache hot path (BASELINE.json configs[1]; configs[4] when --gpus > 1).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-One step = one batched get of 256 x 1 MiB pages, drawn uniformly from a 64 GiB HBM-resident set,
-with the CRC32C integrity check fused into the copy.  `value` times the device-resident form
-(requests and destinations already in HBM) with CUDA events; `e2e` times the host-facing C-ABI call
-aps_get_batch() with host request arrays and PINNED HOST destinations, so every page crosses PCIe
-inside the timed region.  N > 1: one process per GPU (torchrun), one shard per GPU, no data-path
-collective (weak scaling).  `--impl reference` times the CPU restatement of the reference's
-LocalCacheManager + LocalPageStore on the host cores for the same workload.
+One step = one batched get of 256 x 1 MiB pages, drawn uniformly from the HBM-resident set (64 GiB on one GPU,
+128 GiB per GPU when sharded), with the CRC32C integrity check fused into the copy.  `value` times the
+device-resident form (requests and destinations already in HBM) with CUDA events; `e2e` times the host-facing C-ABI
+call aps_get_batch() with host request arrays and PINNED HOST destinations, so every page crosses PCIe inside the
+timed region.  N > 1: one process per GPU (torchrun), one shard per GPU, every GPU asks for ids from the whole id
+space (weak scaling, (N-1)/N of the bytes cross NVLink).  `--impl reference` times the CPU restatement of the
+reference's LocalCacheManager + LocalPageStore (BASELINE configs[0]: 8 GiB = 64 files x 128 pages, uniform gets,
+mt19937_64 seed 1) on the host cores, on tmpfs and on local disk, with all host threads and with one.
 """
 import argparse
 import ctypes as C
@@ -17,6 +18,7 @@ import json
 import os
 import shutil
 import statistics
+import subprocess
 import sys
 import tempfile
 import threading
@@ -31,45 +33,94 @@ BATCH = 256
 DATA_SEED = 0xA11C10
 METRIC = "batched_page_get_fused_crc32c_GBps"
 UNIT = "GB/s"
+N_DST = 4  # destination buffers the timed steps rotate through (4 x 256 MiB = 1 GiB, far beyond the 126 MB L2)
+
+# BASELINE configs[0] (SURVEY.md 8d cfg 1): the reference's own CPU-runnable case
+CFG0_FILES, CFG0_PAGES_PER_FILE, CFG0_GETS, CFG0_SEED = 64, 128, 65536, 1
 
 
-def workload_name(resident_pages):
-    return ("GpuPageStore on 1 B200 per rank: 1 MiB pages, %d GiB resident in HBM, uniform random batched get of "
-            "%d pages with fused CRC32C (BASELINE configs[1])" % (resident_pages * PAGE >> 30, BATCH))
+def config_block(world, resident, t_pop=None, transport=None):
+    """The `config` object; both arms print the same keys."""
+    if world == 1:
+        workload = ("GpuPageStore on 1 B200: 1 MiB pages, %d GiB resident in HBM, uniform random batched get of %d pages "
+                    "with fused CRC32C (BASELINE configs[1])" % (resident * PAGE >> 30, BATCH))
+    else:
+        workload = ("hash-sharded cache over %d B200: 1 MiB pages, %d GiB per GPU (%d GiB aggregate), every GPU issues batched "
+                    "gets of %d uniform ids over the whole id space, served by the owning GPU over NVLink with fused CRC32C "
+                    "(BASELINE configs[4])" % (world, resident * PAGE >> 30, world * resident * PAGE >> 30, BATCH))
+    return {"workload": workload, "page_bytes": PAGE, "resident_pages": resident, "batch_pages": BATCH,
+            "populate_s": t_pop,
+            "l2": "inputs larger than L2: each step reads 256 MiB drawn at random from the resident set and writes 256 MiB into "
+                  "one of %d destination buffers used in rotation (%d MiB in all)" % (N_DST, N_DST * BATCH),
+            "request_pool": "one request batch per step (warm-up + timed), none reused",
+            "shards": "single store" if world == 1 else
+                      "one store per GPU; owner = hash(PageId) mod n; transport: %s" % (transport or "see roofline.kernel"),
+            "reference_arm": "BASELINE configs[0]: LocalCacheManager + LocalPageStore port, %d files x %d pages of 1 MiB (8 GiB), "
+                             "uniform whole-page gets, mt19937_64 seed %d, steps of %d gets"
+                             % (CFG0_FILES, CFG0_PAGES_PER_FILE, CFG0_SEED, BATCH)}
 
 
 # ------------------------------------------------------------------------------------------------ CPU legs
 
-def cpu_sample_dir():
-    for base in ("/dev/shm", tempfile.gettempdir()):
+def fs_type(path):
+    best, kind = "", "?"
+    try:
+        real = os.path.realpath(path)
+        for line in open("/proc/mounts"):
+            parts = line.split()
+            if len(parts) >= 3 and (real == parts[1] or real.startswith(parts[1].rstrip("/") + "/")) and len(parts[1]) > len(best):
+                best, kind = parts[1], parts[2]
+    except OSError:
+        pass
+    return kind
+
+
+def cpu_dirs():
+    """(label, directory, fs) candidates: tmpfs, and the box's local disk (the first non-tmpfs writable place)."""
+    out, seen = [], set()
+    for base in ("/dev/shm", tempfile.gettempdir(), ROOT, os.path.expanduser("~")):
         try:
-            if shutil.disk_usage(base).free > 3 << 30:
-                return tempfile.mkdtemp(prefix="aps_cpu_", dir=base), base
+            kind = fs_type(base)
+            label = "tmpfs" if kind in ("tmpfs", "ramfs") else "disk"
+            if label in seen or not os.access(base, os.W_OK):
+                continue
+            seen.add(label)
+            out.append((label, base, kind))
         except OSError:
             pass
-    return tempfile.mkdtemp(prefix="aps_cpu_"), tempfile.gettempdir()
+    return out
 
 
-def cpu_reference_run(steps, warmup, threads, sample_pages=2048, gets_per_step=BATCH):
-    """Reference CPU path (oracle port of LocalCacheManager.get -> LocalPageStore.get, one file per
-    page on a real directory) on `threads` host threads.  Returns (GB/s, ms_per_step, description)."""
+def cpu_config0(base, threads_list, gets=CFG0_GETS, step_gets=None, steps=0, warmup=0):
+    """BASELINE configs[0] on `base`: populate 64 x 128 pages of 1 MiB through the oracle's LocalPageStore, then uniform
+    whole-page gets through LocalCacheManager.get.  Returns {"threads": {t: GB/s over `gets` gets}, "steps": (GB/s, ms)}.
+    A smaller file set is used (and named) only when `base` lacks room."""
     from oracle import binding as orc
-    root, base = cpu_sample_dir()
+    n_files, ppf = CFG0_FILES, CFG0_PAGES_PER_FILE
+    free = shutil.disk_usage(base).free
+    while n_files * ppf * PAGE + (1 << 30) > free and ppf > 8:
+        ppf //= 2
+    root = tempfile.mkdtemp(prefix="aps_cfg0_", dir=base)
     try:
-        n_files = 16
-        ppf = sample_pages // n_files
-        orc.bench_local_get(root, PAGE, n_files, ppf, True, 64, DATA_SEED, 1, threads)  # populate + touch
-        for w in range(warmup):
-            orc.bench_local_get(root, PAGE, n_files, ppf, False, gets_per_step, DATA_SEED, 100 + w, threads)
-        secs, nbytes = 0.0, 0
-        for k in range(steps):
-            s, b = orc.bench_local_get(root, PAGE, n_files, ppf, False, gets_per_step, DATA_SEED, 1000 + k, threads)
-            secs += s
-            nbytes += b
-        desc = ("%d uniform random whole-page gets per step over a %d GiB file set (%d x 1 MiB page files under %s, "
-                "resident in the OS page cache: the reference's best case)" %
-                (gets_per_step, sample_pages * PAGE >> 30, sample_pages, base))
-        return nbytes / secs / 1e9, secs / max(1, steps) * 1e3, desc
+        t0 = time.time()
+        orc.bench_local_get(root, PAGE, n_files, ppf, True, 64, DATA_SEED, CFG0_SEED, max(threads_list))  # populate + touch
+        out = {"file_set_GiB": n_files * ppf * PAGE / 2**30, "files": n_files, "pages_per_file": ppf,
+               "populate_s": round(time.time() - t0, 1), "threads": {}}
+        for t in threads_list:
+            n = gets if t > 1 else max(BATCH, gets // 8)  # one thread: an eighth of the gets keeps the run bounded
+            s, b = orc.bench_local_get(root, PAGE, n_files, ppf, False, n, DATA_SEED, CFG0_SEED, t)
+            out["threads"][t] = {"GBps": round(b / s / 1e9, 3), "gets": n}
+        if steps:
+            t = max(threads_list)
+            for w in range(warmup):
+                orc.bench_local_get(root, PAGE, n_files, ppf, False, step_gets, DATA_SEED, CFG0_SEED + 100000 + w, t)
+            secs = nbytes = 0
+            for k in range(steps):  # thread j of step k draws from mt19937_64(seed 1 + k * threads + j): disjoint streams
+                s, b = orc.bench_local_get(root, PAGE, n_files, ppf, False, step_gets, DATA_SEED, CFG0_SEED + k * t, t)
+                secs += s
+                nbytes += b
+            out["steps"] = (nbytes / secs / 1e9, secs / steps * 1e3)
+        return out
     finally:
         shutil.rmtree(root, ignore_errors=True)
 
@@ -81,14 +132,31 @@ def run_reference(args):
     from oracle import binding as orc
     orc.build()
     threads = os.cpu_count() or 1
-    steps = max(1, min(args.steps, 200))
-    gbps, ms, desc = cpu_reference_run(steps, min(args.warmup, 5), threads)
+    steps, warmup = max(1, min(args.steps, 256)), min(args.warmup, 5)
+    dirs = cpu_dirs()
+    results = {}
+    for label, base, kind in dirs:
+        try:
+            results[label] = cpu_config0(base, [threads, 1], step_gets=BATCH, steps=steps if label == dirs[0][0] else 0, warmup=warmup)
+            results[label]["dir"], results[label]["fs"] = base, kind
+        except Exception as e:  # noqa: BLE001
+            results[label] = {"unavailable": repr(e)[:200], "dir": base, "fs": kind}
+    head = results[dirs[0][0]]
+    gbps, ms = head["steps"]
+    desc = ("%d steps of %d uniform random whole-page gets over BASELINE configs[0]'s file set (%d files x %d pages of 1 MiB = "
+            "%.0f GiB under %s [%s], resident in the OS page cache: the reference's best case), %d threads"
+            % (steps, BATCH, head["files"], head["pages_per_file"], head["file_set_GiB"], head["dir"], head["fs"], threads))
+    full = {label: ({"dir": r["dir"], "fs": r["fs"], "file_set_GiB": r["file_set_GiB"], "populate_s": r["populate_s"],
+                     "all_threads_GBps": r["threads"][threads]["GBps"], "all_threads_gets": r["threads"][threads]["gets"],
+                     "one_thread_GBps": r["threads"][1]["GBps"], "one_thread_gets": r["threads"][1]["gets"]}
+                    if "threads" in r else r) for label, r in results.items()}
     line = {
         "impl": "reference", "metric": METRIC, "value": round(gbps, 3), "unit": UNIT, "n_gpus": args.gpus,
-        "steps": steps, "warmup": min(args.warmup, 5), "ms_per_step": round(ms, 3), "higher_is_better": True,
+        "steps": steps, "warmup": warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(65536), "page_bytes": PAGE, "batch_pages": BATCH},
-        "cpu_baseline": {"value": round(gbps, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+        "config": config_block(args.gpus, 131072 if args.gpus > 1 else 65536),
+        "cpu_baseline": {"value": round(gbps, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc,
+                         "configs0_65536_gets_seed1": full},
         "e2e": {"value": round(gbps, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference is Java and cannot be built here (no JVM); this is the oracle's C++ port of "
                 "LocalCacheManager+LocalPageStore, CRC not included because the reference has none",
@@ -96,6 +164,8 @@ def run_reference(args):
     print(json.dumps(line))
     return 0
 
+
+# ------------------------------------------------------------------------------------------------ clocks
 
 # ------------------------------------------------------------------------------------------------ clocks
 
@@ -156,7 +226,20 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+
 # ------------------------------------------------------------------------------------------------ GPU arm
+
+def run_tool(name, argv, timeout=900):
+    """Runs tools/<name> in its own process (after the main store released its HBM) and returns its JSON line."""
+    try:
+        out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", name)] + argv, capture_output=True, timeout=timeout)
+        for line in reversed(out.stdout.decode().splitlines()):
+            if line.startswith("{"):
+                return json.loads(line)
+        return {"unavailable": (out.stderr.decode() or "no output")[-300:]}
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": repr(e)[:300]}
+
 
 def run_ours(args):
     import numpy as np
@@ -164,6 +247,7 @@ def run_ours(args):
     import torch.distributed as dist
     from alluxio_b200 import capi
     from alluxio_b200 import build as build_mod
+    from alluxio_b200 import sharding
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -179,10 +263,16 @@ def run_ours(args):
     L = capi.lib()
     dev = torch.device("cuda", local_rank)
     K, W = args.steps, max(3, args.warmup)
+    quick = os.environ.get("APS_BENCH_QUICK") == "1"  # kernel sweeps: skip the slow PCIe, CPU and auxiliary legs
+    # several GPUs: "push" = the owners store the pages into the requester's landing buffer (aps_get_batch_push_*),
+    # "pull" = the requester's kernel reads the owners' slabs in place (aps_get_batch_sharded_dev)
+    transport = os.environ.get("APS_BENCH_TRANSPORT", "push") if world > 1 else "local"
+    depth = int(os.environ.get("APS_BENCH_DEPTH", "2")) if transport == "push" else 1
 
-    resident = int(os.environ.get("APS_BENCH_PAGES", "65536"))  # pages per GPU
+    # pages per GPU: configs[1] = 64 GiB on one GPU; configs[4] = 128 GiB per GPU (1 TiB at 8)
+    resident = int(os.environ.get("APS_BENCH_PAGES", "131072" if world > 1 else "65536"))
     free_b, _ = torch.cuda.mem_get_info(dev)
-    while resident * PAGE + (8 << 30) > free_b and resident > 1024:
+    while resident * PAGE + (10 << 30) > free_b and resident > 1024:
         resident //= 2  # a smaller GPU slice: stated in config.workload
     if world > 1:
         t = torch.tensor([resident], dtype=torch.int64, device=dev)
@@ -190,12 +280,10 @@ def run_ours(args):
         resident = int(t.item())
     # Global id space: world * resident pages; page g is (file g // 1024, index g % 1024).  With several
     # GPUs the cache is sharded: GPU aps_shard_of(key) owns the page (hash routing).
-    from alluxio_b200 import sharding
     total_pages = world * resident
     gids = np.arange(total_pages, dtype=np.uint64)
     if world > 1:
-        mine = sharding.owned_by(rank, world, gids // np.uint64(1024), gids % np.uint64(1024))
-        owned = gids[mine]
+        owned = gids[sharding.owned_by(rank, world, gids // np.uint64(1024), gids % np.uint64(1024))]
     else:
         owned = gids
     slots = int(len(owned)) + 64
@@ -209,33 +297,41 @@ def run_ours(args):
     h = C.c_void_p()
     capi.check(L.aps_open(C.byref(cfg), C.byref(h)), "aps_open")
     # one explicit non-default stream for everything: torch copies, our kernels and the timing events
-    # (a NULL aps_stream would mean "the store's own stream", which torch events cannot see)
     stream = torch.cuda.Stream(dev)
     torch.cuda.set_stream(stream)
     sp = C.c_void_p(stream.cuda_stream)
     assert sp.value, "need a real stream handle"
 
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    from gpu_util import GET_REQ, PUT_REQ, RESULT
+    from gpu_util import GET_REQ, KEY, PUT_REQ, RESULT, raw_tensor
+    from oracle import binding as orc
+
+    def ids_to_dev(ids):
+        return (torch.from_numpy((ids // np.uint64(1024)).view(np.int64)).to(dev),
+                torch.from_numpy((ids % np.uint64(1024)).view(np.int64)).to(dev))
+
+    def put_reqs_for(ids, src_ptr):
+        r = np.zeros(len(ids), PUT_REQ)
+        r["file_lo"], r["page_index"], r["len"] = ids // np.uint64(1024), ids % np.uint64(1024), PAGE
+        r["src"] = src_ptr + np.arange(len(ids), dtype=np.uint64) * PAGE
+        return torch.from_numpy(r.view(np.uint8).reshape(-1)).to(dev)
 
     # ---- populate the pages this GPU owns: generate on the device, put 256 at a time
     stage = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
     d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
+
+    def fill_stage(ids):
+        d_files, d_idx = ids_to_dev(ids)
+        capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, len(ids), d_files.data_ptr(),
+                                        d_idx.data_ptr(), DATA_SEED, sp), "fill")
+
     def populate(store):
         first = None
         for b0 in range(0, len(owned), BATCH):
             ids = owned[b0:b0 + BATCH]
-            nb = len(ids)
-            files, idx = ids // np.uint64(1024), ids % np.uint64(1024)
-            d_files = torch.from_numpy(files.view(np.int64)).to(dev)
-            d_idx = torch.from_numpy(idx.view(np.int64)).to(dev)
-            capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, nb, d_files.data_ptr(),
-                                            d_idx.data_ptr(), DATA_SEED, sp), "fill")
-            reqs = np.zeros(nb, PUT_REQ)
-            reqs["file_lo"], reqs["page_index"], reqs["len"] = files, idx, PAGE
-            reqs["src"] = stage.data_ptr() + np.arange(nb, dtype=np.uint64) * PAGE
-            d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
-            capi.check(L.aps_put_batch_dev(store, nb, d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
+            fill_stage(ids)
+            d_reqs = put_reqs_for(ids, stage.data_ptr())
+            capi.check(L.aps_put_batch_dev(store, len(ids), d_reqs.data_ptr(), d_res.data_ptr(), sp), "put")
             if b0 == 0:
                 torch.cuda.synchronize(dev)
                 first = d_res.cpu().numpy().view(RESULT).copy()
@@ -245,17 +341,18 @@ def run_ours(args):
     t_pop = time.time()
     first_put_res = populate(h)
     t_pop = time.time() - t_pop
-
-    # ---- parity spot check against the oracle (the checker; never the thing measured)
-    from oracle import binding as orc
-    for i in (0, 1, 255):
+    for i in (0, 1, 255):  # put CRCs against the oracle (the checker; never the thing measured)
         g = int(owned[i])
         want = orc.crc32c(orc.fill_page(DATA_SEED, g // 1024, g % 1024, PAGE))
         assert (not with_crc or int(first_put_res[i]["crc"]) == want) and int(first_put_res[i]["len"]) == PAGE, \
             "put CRC differs from oracle"
 
-    # ---- several GPUs: map every peer's table and slab (CUDA IPC handles travel over torch.distributed)
+    # ---- destination buffers: N_DST x 256 MiB used in rotation.  With the push transport they are the store's landing
+    # buffer (memory the peers can write); otherwise a plain device allocation.
+    dst_bytes = N_DST * BATCH * PAGE
     if world > 1:
+        # map every peer's table and slab (pull) and its landing buffer and mailboxes (push); CUDA IPC handles travel
+        # over torch.distributed
         hnd = capi.aps_shard_handle()
         capi.check(L.aps_shard_export(h, C.byref(hnd)), "shard_export")
         blobs = [None] * world
@@ -264,86 +361,83 @@ def run_ours(args):
         for i, bl in enumerate(blobs):
             C.memmove(C.addressof(arr[i]), bl, 256)
         capi.check(L.aps_shard_attach(h, world, rank, arr), "shard_attach")
+    if transport == "push":
+        capi.check(L.aps_push_setup(h, dst_bytes, depth), "push_setup")
+        ph = capi.aps_push_handle()
+        capi.check(L.aps_push_export(h, C.byref(ph)), "push_export")
+        blobs = [None] * world
+        dist.all_gather_object(blobs, bytes(ph.opaque))
+        parr = (capi.aps_push_handle * world)()
+        for i, bl in enumerate(blobs):
+            C.memmove(C.addressof(parr[i]), bl, 192)
+        capi.check(L.aps_push_attach(h, world, rank, parr), "push_attach")
+        nb = C.c_uint64()
+        dst = raw_tensor(L.aps_push_landing(h, C.byref(nb)), dst_bytes, dev)
+    else:
+        dst = torch.empty(dst_bytes, dtype=torch.uint8, device=dev)
+    if world > 1:
         dist.barrier()
 
-    # ---- request pool: uniform random page ids over the whole (global) id space, seed 2 + rank
+    # ---- request pool: one batch per step (warm-up + timed), uniform random page ids over the whole (global) id space,
+    # seed 2 + rank; batch p writes into destination buffer p % N_DST
     rng = np.random.default_rng(2 + rank)
-    pool = min(K + W, 512)
-    dst = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
+    pool = W + K
     picks = rng.integers(0, total_pages, size=(pool, BATCH)).astype(np.uint64)
     reqs = np.zeros((pool, BATCH), GET_REQ)
     reqs["file_lo"], reqs["page_index"] = picks // np.uint64(1024), picks % np.uint64(1024)
     reqs["page_off"], reqs["nbytes"] = 0, PAGE
-    reqs["dst"] = dst.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
+    reqs["dst"] = (dst.data_ptr() + (np.arange(pool, dtype=np.uint64)[:, None] % np.uint64(N_DST)) * np.uint64(BATCH * PAGE)
+                   + np.arange(BATCH, dtype=np.uint64)[None, :] * np.uint64(PAGE))
     d_reqs = torch.from_numpy(reqs.view(np.uint8).reshape(-1)).to(dev)
-    d_res = torch.zeros(BATCH * 8, dtype=torch.uint8, device=dev)
-    req_bytes = BATCH * GET_REQ.itemsize
+    d_res_all = torch.zeros(pool * BATCH * 8, dtype=torch.uint8, device=dev)  # every step keeps its own results
+    req_bytes, res_bytes = BATCH * GET_REQ.itemsize, BATCH * RESULT.itemsize
     if world > 1:
         pick_owner = sharding.shard_of_keys(np.zeros(picks.size, np.uint64), (picks // np.uint64(1024)).reshape(-1),
                                             (picks % np.uint64(1024)).reshape(-1), world)
         remote_frac = float((pick_owner != rank).mean())
     else:
         remote_frac = 0.0
-    get_dev = L.aps_get_batch_sharded_dev if world > 1 else L.aps_get_batch_dev
     get_host = L.aps_get_batch_sharded if world > 1 else L.aps_get_batch
 
-    def step_dev(k):
-        capi.check(get_dev(h, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+    def reqs_at(p):
+        return d_reqs.data_ptr() + p * req_bytes
 
-    for k in range(W):
-        step_dev(k)
+    def res_at(p):
+        return d_res_all.data_ptr() + p * res_bytes
+
+    def run_steps(p0, n):
+        """Steps p0 .. p0+n-1 of the pool, back to back on `stream`."""
+        if transport == "push":
+            # `depth` multi-gets in flight: begin(p + depth - 1) is issued before end(p)
+            for p in range(p0, min(p0 + depth - 1, p0 + n)):
+                capi.check(L.aps_get_batch_push_begin_dev(h, BATCH, reqs_at(p), sp), "push begin")
+            for p in range(p0, p0 + n):
+                if p + depth - 1 < p0 + n:
+                    capi.check(L.aps_get_batch_push_begin_dev(h, BATCH, reqs_at(p + depth - 1), sp), "push begin")
+                capi.check(L.aps_get_batch_push_end_dev(h, res_at(p), sp), "push end")
+        elif transport == "pull":
+            for p in range(p0, p0 + n):
+                capi.check(L.aps_get_batch_sharded_dev(h, BATCH, reqs_at(p), res_at(p), sp), "sharded get")
+        else:
+            for p in range(p0, p0 + n):
+                capi.check(L.aps_get_batch_dev(h, BATCH, reqs_at(p), res_at(p), sp), "get")
+
+    run_steps(0, W)
     torch.cuda.synchronize(dev)
-    # correctness of the last warm-up step, against the oracle, before anything is timed
-    res = d_res.cpu().numpy().view(RESULT)
-    k_last = (W - 1) % pool
-    for i in (0, 17, 255):
-        p = int(picks[k_last, i])
+    if world > 1:
+        dist.barrier()
+    # ---- parity of one FULL step (the last warm-up step), before anything is timed: all 256 pages and all 256 CRCs
+    # against the oracle's generator and CRC32C
+    p_chk = W - 1
+    res = d_res_all[p_chk * res_bytes:(p_chk + 1) * res_bytes].cpu().numpy().view(RESULT)
+    got = dst[(p_chk % N_DST) * BATCH * PAGE:(p_chk % N_DST + 1) * BATCH * PAGE].cpu().numpy()
+    for i in range(BATCH):
+        p = int(picks[p_chk, i])
         page = orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE)
-        assert int(res[i]["len"]) == PAGE and (not with_crc or int(res[i]["crc"]) == orc.crc32c(page)), \
-            "get CRC differs from oracle"
-        assert np.array_equal(dst[i * PAGE:(i + 1) * PAGE].cpu().numpy(), page), "get bytes differ from oracle"
-
-    if os.environ.get("APS_BENCH_TIMELINE") == "1":  # diagnostic: per-CTA / per-warp timestamps of single launches
-        none = np.uint64(0xFFFFFFFFFFFFFFFF)
-        per_sm = []
-        capi.check(L.aps_debug_timeline(h, 1, None, 0))
-        for rep in range(4):
-            for k in range(3):
-                step_dev(rep * 3 + k)
-            raw = np.zeros(1024 + 256 * 32 + 256, np.uint64)
-            capi.check(L.aps_debug_timeline(h, 1, raw.ctypes.data, raw.size))
-            tl = raw[:1024].reshape(256, 4)
-            live = tl[:, 0] != none
-            tl = tl[live].astype(np.int64)
-            t0 = tl[:, 0].min()
-            rel = (tl - t0) / 1e3
-            smid = raw[1024 + 256 * 32:][live].astype(np.int64)
-            per_sm.append(dict(zip(smid.tolist(), rel[:, 3].tolist())))
-            if rep:
-                continue
-            print("timeline us: ctas=%d start[min/med/max]=%.1f/%.1f/%.1f tables=%.1f/%.1f/%.1f firstwarp=%.1f/%.1f/%.1f "
-                  "end=%.1f/%.1f/%.1f" % ((len(rel),) + tuple(x for c in range(4) for x in
-                                                              (rel[:, c].min(), np.median(rel[:, c]), rel[:, c].max()))),
-                  file=sys.stderr)
-            w = raw[1024:1024 + 256 * 32].reshape(256, 32)[live]
-            w = np.where(w == none, 0, w).astype(np.int64)
-            nw = int((w[0] != 0).sum())
-            wrel = (w[:, :nw] - t0) / 1e3
-            print("timeline warp end spread within CTA (max-min) median %.1f us; CTA end: p10 %.1f p50 %.1f p90 %.1f max %.1f"
-                  % (np.median(wrel.max(axis=1) - wrel.min(axis=1)), *np.percentile(rel[:, 3], [10, 50, 90, 100])),
-                  file=sys.stderr)
-        common = sorted(set.intersection(*[set(d) for d in per_sm]))
-        m = np.array([[d[sm] for sm in common] for d in per_sm])
-        m = m - np.median(m, axis=1, keepdims=True)
-        cc = np.corrcoef(m)
-        print("timeline per-SM end offset: correlation between launches %s; SMs seen %d (ids %d..%d)" %
-              (np.round(cc[0, 1:], 2).tolist(), len(common), common[0], common[-1]), file=sys.stderr)
-        off = np.sort(m.mean(axis=0))
-        print("timeline per-SM mean end offset us, sorted (every 6th): " + " ".join("%.1f" % x for x in off[::6]), file=sys.stderr)
-        capi.check(L.aps_debug_timeline(h, 0, None, 0))
-        slow = np.argsort(-m.mean(axis=0))[:8]
-        print("timeline slowest SMs (id: mean offset us over 4 launches): " +
-              ", ".join("%d: %+.1f" % (common[i], m[:, i].mean()) for i in slow), file=sys.stderr)
+        assert int(res[i]["len"]) == PAGE, "get %d returned %d" % (i, int(res[i]["len"]))
+        assert not with_crc or int(res[i]["crc"]) == orc.crc32c(page), "get CRC differs from oracle (request %d)" % i
+        assert np.array_equal(got[i * PAGE:(i + 1) * PAGE], page), "get bytes differ from oracle (request %d)" % i
+    parity_pages = BATCH
 
     sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None))
     sampler.start()
@@ -355,45 +449,50 @@ def run_ours(args):
     torch.cuda.synchronize(dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
-    for k in range(K):
-        step_dev(W + k)
+    run_steps(W, K)
     ev1.record(stream)
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
     ms_total = ev0.elapsed_time(ev1)
     launches = L.aps_total_kernel_launches() - launches0
-    assert launches == K, "a get step must be exactly one kernel launch (lookup + gather + CRC fused)"
-    res = d_res.cpu().numpy().view(RESULT)
+    per_step = 3 if transport == "push" else 1  # push: post + serve + wait; otherwise lookup + gather + CRC in ONE launch
+    assert launches == per_step * K, "unexpected number of kernel launches per step: %d for %d steps" % (launches, K)
+    res = d_res_all[W * res_bytes:].cpu().numpy().view(RESULT)
     assert (res["len"] == PAGE).all(), "a timed get did not return a full page"
+    if with_crc:  # CRCs of one timed step against the oracle (bytes of a full step were checked above)
+        for i in (0, 101, 255):
+            p = int(picks[W + K - 1, i])
+            assert int(res[(K - 1) * BATCH + i]["crc"]) == orc.crc32c(orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE))
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
 
     # ---- end to end: host request arrays, pinned host destinations, results read back
-    quick = os.environ.get("APS_BENCH_QUICK") == "1"  # kernel sweeps: skip the slow PCIe and CPU legs
     e2e_steps = 2 if quick else max(1, min(K, 100))
-    pinned = torch.empty(BATCH * PAGE, dtype=torch.uint8).pin_memory()
-    h_reqs = reqs.copy()
-    h_reqs["dst"] = pinned.data_ptr() + np.arange(BATCH, dtype=np.uint64)[None, :] * PAGE
+    pinned = [torch.empty(BATCH * PAGE, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    n_h = e2e_steps + 3
+    h_reqs = reqs[:n_h].copy() if n_h <= pool else np.resize(reqs, (n_h, BATCH)).copy()
+    for p in range(n_h):
+        h_reqs[p]["dst"] = pinned[p % 2].data_ptr() + np.arange(BATCH, dtype=np.uint64) * PAGE
     h_res = np.zeros(BATCH, RESULT)
 
-    def step_host(k):
-        capi.check(get_host(h, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+    def step_host(p):
+        capi.check(get_host(h, BATCH, h_reqs[p].ctypes.data, h_res.ctypes.data, sp), "get_batch")
 
-    for k in range(3):
-        step_host(k)
-    p = int(picks[2 % pool, 5])
-    page = orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE)
-    assert np.array_equal(pinned.numpy()[5 * PAGE:6 * PAGE], page)
+    for p in range(3):
+        step_host(p)
+    pg = int(picks[2 % pool, 5])
+    page = orc.fill_page(DATA_SEED, pg // 1024, pg % 1024, PAGE)
+    assert np.array_equal(pinned[0].numpy()[5 * PAGE:6 * PAGE], page)
     assert not with_crc or int(h_res[5]["crc"]) == orc.crc32c(page)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
-    for k in range(e2e_steps):
-        step_host(3 + k)
+    for p in range(e2e_steps):
+        step_host(3 + p)
     torch.cuda.synchronize(dev)
     e2e_s = time.perf_counter() - t0
     if world > 1:
@@ -401,93 +500,63 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     assert (h_res["len"] == PAGE).all()
-    # what the link allows: a plain copy-engine transfer of the same 256 MiB from HBM to the pinned buffer
+    # what the box allows: a plain copy-engine transfer of the same 256 MiB from HBM to the pinned buffer, started on
+    # every rank at the same moment (barrier), so that at N > 1 the GPUs compete for the host side as the e2e steps do
     pcie_gbps = None
     if not quick:
         dsrc = dst[:BATCH * PAGE]
         for _ in range(2):
-            pinned.copy_(dsrc, non_blocking=True)
+            pinned[0].copy_(dsrc, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize(dev)
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         c0.record(stream)
-        for _ in range(5):
-            pinned.copy_(dsrc, non_blocking=True)
+        for i in range(8):
+            pinned[i % 2].copy_(dsrc, non_blocking=True)
         c1.record(stream)
         torch.cuda.synchronize(dev)
-        pcie_gbps = 5 * BATCH * PAGE / (c0.elapsed_time(c1) * 1e-3) / 1e9
+        ms_c = c0.elapsed_time(c1)
+        if world > 1:
+            t = torch.tensor([ms_c], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_c = float(t.item())
+        pcie_gbps = 8 * BATCH * PAGE / (ms_c * 1e-3) / 1e9
 
-    # ---- auxiliary numbers (not the headline): put with CRC
+    # ---- auxiliary numbers (not the headline): puts of FRESH pages with the fused CRC.  Each timed put follows an
+    # untimed delete of the same 256 ids and an untimed refill of the source buffer, so every put inserts (claims a
+    # table entry and a slab slot) and writes slots that are not in L2; only the put kernels are inside the event pairs.
     aux = {}
-    aux_steps = max(1, min(K, 50))
-    put_reqs = np.zeros(BATCH, PUT_REQ)
-    ids = owned[:BATCH]
-    put_reqs["file_lo"], put_reqs["page_index"], put_reqs["len"] = ids // np.uint64(1024), ids % np.uint64(1024), PAGE
-    put_reqs["src"] = stage.data_ptr() + np.arange(BATCH, dtype=np.uint64) * PAGE  # re-put this GPU's first 256 pages
-    files0 = torch.from_numpy((ids // np.uint64(1024)).view(np.int64)).to(dev)
-    idx0 = torch.from_numpy((ids % np.uint64(1024)).view(np.int64)).to(dev)
-    capi.check(L.aps_fill_pages_dev(local_rank, stage.data_ptr(), PAGE, PAGE, BATCH, files0.data_ptr(), idx0.data_ptr(),
-                                    DATA_SEED, sp), "fill")
-    d_put = torch.from_numpy(put_reqs.view(np.uint8).reshape(-1)).to(dev)
-    for _ in range(3):
-        capi.check(L.aps_put_batch_dev(h, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
-    torch.cuda.synchronize(dev)
-    ev0.record(stream)
-    for _ in range(aux_steps):
-        capi.check(L.aps_put_batch_dev(h, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
-    ev1.record(stream)
-    torch.cuda.synchronize(dev)
-    aux["put_fused_crc32c_GBps"] = round(aux_steps * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
-    aux["put_note"] = "re-puts one resident 256 MiB batch (source and slots cached in L2 between steps): upper bound"
+    aux_steps = max(1, min(K, 50, len(owned) // BATCH - 1))
 
-    # ---- several GPUs: the same multi-get through NCCL (all-to-all of keys, owner-side gather into a send
-    # buffer, all-to-all of pages): the plain-collective baseline that the fused P2P kernel is compared with
-    if world > 1 and not quick:
-        nccl_steps = max(1, min(K, 50))
-        sendbuf = torch.empty(2 * BATCH * PAGE, dtype=torch.uint8, device=dev)   # pages this GPU serves per step
-        recvbuf = torch.empty(BATCH * PAGE, dtype=torch.uint8, device=dev)
-        srv_res = torch.zeros(2 * BATCH * 8, dtype=torch.uint8, device=dev)
+    def fresh_puts(store, n_steps):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_steps)]
+        first_crc = None
+        for s_ in range(n_steps + 1):  # step 0 is a warm-up
+            ids = owned[len(owned) - (s_ + 1) * BATCH:len(owned) - s_ * BATCH]
+            keys = np.zeros(BATCH, KEY)
+            keys["file_lo"], keys["page_index"] = ids // np.uint64(1024), ids % np.uint64(1024)
+            d_keys = torch.from_numpy(keys.view(np.uint8).reshape(-1)).to(dev)
+            d_put = put_reqs_for(ids, stage.data_ptr())
+            capi.check(L.aps_delete_batch_dev(store, BATCH, d_keys.data_ptr(), d_res.data_ptr(), sp), "delete")
+            fill_stage(ids)
+            if s_:
+                evs[s_ - 1][0].record(stream)
+            capi.check(L.aps_put_batch_dev(store, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
+            if s_:
+                evs[s_ - 1][1].record(stream)
+            if s_ == n_steps:
+                torch.cuda.synchronize(dev)
+                r = d_res.cpu().numpy().view(RESULT)
+                assert (r["len"] == PAGE).all(), "a fresh put failed"
+                first_crc = (int(ids[0]), int(r[0]["crc"]))
+        torch.cuda.synchronize(dev)
+        return n_steps * BATCH * PAGE / (sum(a.elapsed_time(b) for a, b in evs) * 1e-3) / 1e9, first_crc
 
-        def step_nccl(k):
-            pk = picks[k % pool]
-            own = sharding.shard_of_keys(np.zeros(BATCH, np.uint64), pk // np.uint64(1024), pk % np.uint64(1024), world)
-            order = np.argsort(own, kind="stable")
-            counts = np.bincount(own, minlength=world)
-            keys = torch.from_numpy(np.stack([pk[order] // np.uint64(1024), pk[order] % np.uint64(1024)], 1).astype(np.int64)).to(dev)
-            cnt_out = torch.from_numpy(counts.astype(np.int64)).to(dev)
-            cnt_in = torch.empty_like(cnt_out)
-            dist.all_to_all_single(cnt_in, cnt_out)
-            n_in = cnt_in.cpu().tolist()
-            n_srv = int(sum(n_in))
-            assert n_srv <= 2 * BATCH, "request skew beyond the serve buffer"
-            keys_in = torch.empty((n_srv, 2), dtype=torch.int64, device=dev)
-            dist.all_to_all_single(keys_in, keys, output_split_sizes=n_in, input_split_sizes=counts.tolist())
-            # owner side: one local batched get straight into the send buffer
-            rq = torch.zeros((n_srv, 5), dtype=torch.int64, device=dev)
-            rq[:, 1], rq[:, 2] = keys_in[:, 0], keys_in[:, 1]
-            rq[:, 3] = PAGE << 32                                   # page_off = 0, nbytes = PAGE
-            rq[:, 4] = sendbuf.data_ptr() + torch.arange(n_srv, device=dev, dtype=torch.int64) * PAGE
-            for lo in range(0, n_srv, BATCH):
-                m = min(BATCH, n_srv - lo)
-                capi.check(L.aps_get_batch_dev(h, m, rq.data_ptr() + lo * 40, srv_res.data_ptr() + lo * 8, sp), "serve")
-            dist.all_to_all_single(recvbuf[:BATCH * PAGE], sendbuf[:n_srv * PAGE],
-                                   output_split_sizes=[int(c) * PAGE for c in counts], input_split_sizes=[c * PAGE for c in n_in])
-            return order
-
-        order = step_nccl(0)
-        torch.cuda.synchronize(dev)
-        p0 = int(picks[0, order[3]])
-        assert np.array_equal(recvbuf[3 * PAGE:4 * PAGE].cpu().numpy(), orc.fill_page(DATA_SEED, p0 // 1024, p0 % 1024, PAGE))
-        dist.barrier()
-        torch.cuda.synchronize(dev)
-        t0 = time.perf_counter()
-        for k in range(nccl_steps):
-            step_nccl(1 + k)
-        torch.cuda.synchronize(dev)
-        dist.barrier()
-        t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        aux["nccl_all_to_all_GBps"] = round(world * nccl_steps * BATCH * PAGE / float(t.item()) / 1e9, 1)
-        aux["nccl_note"] = "same multi-get via torch.distributed all_to_all_single (keys, then pages served by aps_get_batch_dev)"
+    put_gbps, (gid0, crc0) = fresh_puts(h, aux_steps)
+    assert not with_crc or crc0 == orc.crc32c(orc.fill_page(DATA_SEED, gid0 // 1024, gid0 % 1024, PAGE)), "put CRC differs from oracle"
+    aux["put_fresh_fused_crc32c_GBps" if with_crc else "put_fresh_GBps"] = round(put_gbps, 1)
 
     clocks = sampler.stop()
     stats = capi.aps_stats_t()
@@ -498,45 +567,46 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         remote_frac = float(t.item()) / world
         dist.barrier()  # peers may still be reading this GPU's slab
+    del dst
     capi.check(L.aps_close(h), "close")
 
-    # ---- the same three paths with the checksum off (BASELINE configs[1]: "each with CRC off/on"): a second
-    # store opened without APS_FLAG_CRC over the same resident set, after the first one released its HBM
+    # ---- the same paths with the checksum off (BASELINE configs[1]: "each with CRC off/on"): a second store opened
+    # without APS_FLAG_CRC over the same resident set, after the first one released its HBM
     if world == 1 and with_crc and not quick:
         cfg.flags = cfg.flags & capi.APS_FLAG_STABLE_REQS
         h2 = C.c_void_p()
         capi.check(L.aps_open(C.byref(cfg), C.byref(h2)), "aps_open (no CRC)")
         populate(h2)
+        dst2 = torch.empty(dst_bytes, dtype=torch.uint8, device=dev)
+        reqs2 = reqs.copy()
+        reqs2["dst"] = (dst2.data_ptr() + (np.arange(pool, dtype=np.uint64)[:, None] % np.uint64(N_DST)) * np.uint64(BATCH * PAGE)
+                        + np.arange(BATCH, dtype=np.uint64)[None, :] * np.uint64(PAGE))
+        d_reqs2 = torch.from_numpy(reqs2.view(np.uint8).reshape(-1)).to(dev)
         n2 = max(1, min(K, 200))
-        for k in range(5):
-            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs.data_ptr() + (k % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+        for p in range(W):
+            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs2.data_ptr() + p * req_bytes, res_at(p), sp), "get")
         torch.cuda.synchronize(dev)
         ev0.record(stream)
-        for k in range(n2):
-            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs.data_ptr() + ((5 + k) % pool) * req_bytes, d_res.data_ptr(), sp), "get")
+        for p in range(W, W + n2):
+            capi.check(L.aps_get_batch_dev(h2, BATCH, d_reqs2.data_ptr() + p * req_bytes, res_at(p), sp), "get")
         ev1.record(stream)
         torch.cuda.synchronize(dev)
         aux["get_nocrc_GBps"] = round(n2 * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
-        p = int(picks[(5 + n2 - 1) % pool, 9])
-        assert np.array_equal(dst[9 * PAGE:10 * PAGE].cpu().numpy(), orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE))
-        for _ in range(3):
-            capi.check(L.aps_put_batch_dev(h2, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
-        torch.cuda.synchronize(dev)
-        ev0.record(stream)
-        for _ in range(aux_steps):
-            capi.check(L.aps_put_batch_dev(h2, BATCH, d_put.data_ptr(), d_res.data_ptr(), sp), "put")
-        ev1.record(stream)
-        torch.cuda.synchronize(dev)
-        aux["put_nocrc_GBps"] = round(aux_steps * BATCH * PAGE / (ev0.elapsed_time(ev1) * 1e-3) / 1e9, 1)
+        p_last = W + n2 - 1
+        pg = int(picks[p_last, 9])
+        off = (p_last % N_DST) * BATCH * PAGE + 9 * PAGE
+        assert np.array_equal(dst2[off:off + PAGE].cpu().numpy(), orc.fill_page(DATA_SEED, pg // 1024, pg % 1024, PAGE))
+        aux["put_fresh_nocrc_GBps"] = round(fresh_puts(h2, aux_steps)[0], 1)
         n3 = max(1, min(K, 30))
-        for k in range(2):
-            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[k % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+        for p in range(2):
+            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[p].ctypes.data, h_res.ctypes.data, sp), "get_batch")
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
-        for k in range(n3):
-            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[(2 + k) % pool].ctypes.data, h_res.ctypes.data, sp), "get_batch")
+        for p in range(n3):
+            capi.check(L.aps_get_batch(h2, BATCH, h_reqs[(2 + p) % n_h].ctypes.data, h_res.ctypes.data, sp), "get_batch")
         torch.cuda.synchronize(dev)
         aux["e2e_get_nocrc_GBps"] = round(n3 * BATCH * PAGE / (time.perf_counter() - t0) / 1e9, 2)
+        del dst2
         capi.check(L.aps_close(h2), "close")
 
     if rank != 0:
@@ -544,17 +614,38 @@ def run_ours(args):
             dist.destroy_process_group()
         return 0
 
-    # ---- CPU baseline on a bounded sample (rank 0, N = 1 only)
+    # ---- the other BASELINE configs, measured by their own tools in separate processes once this one has released the
+    # GPU memory (rank 0, N = 1): K1 rates, configs[2] (small-page replay, checked against the oracle), configs[3] (MD5)
+    del stage, d_reqs, d_res_all
+    torch.cuda.empty_cache()
+    aux_level = os.environ.get("APS_BENCH_AUX", "full")
+    if world == 1 and not quick and aux_level != "0":
+        light = aux_level == "light"
+        tb = run_tool("bench_table.py", ["--reps", "4"])
+        aux["k1_table"] = {k: tb.get(k) for k in ("lookup_hit_Mops", "lookup_miss_Mops", "insert_churn_Mops", "erase_Mops",
+                                                  "buckets_per_hit", "roofline", "checks", "unavailable") if k in tb}
+        sm = run_tool("bench_small_pages.py", ["--accesses", "5000000" if light else "50000000"] + ([] if light else ["--check"]))
+        aux["configs2_small_pages"] = {k: sm.get(k) for k in ("config", "hit_ratio", "victims", "accesses_per_s_end_to_end",
+                                                              "store_Mops_per_s", "store_payload_GBps", "bad_gets", "crc_mismatches",
+                                                              "oracle", "unavailable") if k in sm}
+        md = run_tool("bench_md5.py", ["--files", "1024", "--check", "64"] if light else [])
+        aux["configs3_md5"] = {k: md.get(k) for k in ("config", "value", "unit", "roofline", "cpu_baseline", "e2e", "files_checked",
+                                                      "digest_mismatches", "md5sum_sample", "unavailable") if k in md}
+
+    # ---- CPU baseline: BASELINE configs[0] on tmpfs, all host threads and one (rank 0, N = 1 only)
     cpu = None
     if world == 1 and not args.no_cpu_baseline and not quick:
         orc.build()
         threads = os.cpu_count() or 1
-        gbps_c, _, desc = cpu_reference_run(steps=int(os.environ.get("APS_CPU_STEPS", "40")), warmup=2, threads=threads)
-        cpu = {"value": round(gbps_c, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": desc}
-        # SURVEY.md 8d asks for one thread as well, and for the CPU CRC32C rate (not reference-derived: the reference
-        # has no CRC) so that the fused checksum has something on the host to stand beside
-        g1, _, _ = cpu_reference_run(steps=4, warmup=1, threads=1)
-        cpu["one_thread_value"] = round(g1, 3)
+        label, base, kind = cpu_dirs()[0]
+        c0 = cpu_config0(base, [threads, 1], gets=int(os.environ.get("APS_CPU_GETS", str(CFG0_GETS))))
+        cpu = {"value": c0["threads"][threads]["GBps"], "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": "%d uniform random whole-page gets (mt19937_64 seed %d) over BASELINE configs[0]'s file set: %d files x %d "
+                         "pages of 1 MiB = %.0f GiB under %s [%s], resident in the OS page cache (the reference's best case)"
+                         % (c0["threads"][threads]["gets"], CFG0_SEED, c0["files"], c0["pages_per_file"], c0["file_set_GiB"], base, kind),
+               "one_thread_value": c0["threads"][1]["GBps"], "one_thread_gets": c0["threads"][1]["gets"]}
+        # the CPU CRC32C rate (not reference-derived: the reference has no CRC), so that the fused checksum has something
+        # on the host to stand beside
         blob = orc.fill_page(DATA_SEED, 1, 1, 64 << 20)
         rates = {}
         for impl in ("sb8", "hw"):
@@ -562,7 +653,7 @@ def run_ours(args):
                 t0 = time.perf_counter()
                 orc.crc32c(blob, impl)
                 rates[impl] = round(blob.nbytes / (time.perf_counter() - t0) / 1e9, 2)
-            except Exception:
+            except Exception:  # noqa: BLE001
                 pass
         cpu["crc32c_one_thread_GBps"] = rates
         cpu["crc32c_note"] = "slicing-by-8 / SSE4.2 CRC32C of 64 MiB on one host core; not part of the reference path"
@@ -577,51 +668,51 @@ def run_ours(args):
     if os.path.exists(tpath):
         traffic = json.load(open(tpath)).get("copy_kernel_crc_dram_bytes_per_launch")
     step_bytes = BATCH * PAGE
-    # One step is ONE launch of the fused kernel, so the kernel's average launch duration over the timed
-    # region is ms_total / K (CUDA events on the launching stream; launch gaps included: conservative).
+    # One step is ONE launch of the dominant kernel (the fused copy kernel; with the push transport the owner's serve
+    # kernel), so its average launch duration over the timed region is ms_total / K (CUDA events on the launching
+    # stream; launch gaps included: conservative).
     achieved = 2 * step_bytes / (ms_total / K * 1e-3) / 1e9
     value = world * K * step_bytes / (ms_total * 1e-3) / 1e9
     if world > 1:
         # cross-shard multi-get: the bytes that cross NVLink per GPU per step bound the step
-        nv_peak = 770.0  # measured peer-copy bandwidth per direction per GPU on this pool (B200_PROFILING.md); 900 nominal
         nv_achieved = remote_frac * step_bytes / (ms_total / K * 1e-3) / 1e9
-        roofline = {"bound": "nvlink", "achieved": round(nv_achieved, 1), "peak": nv_peak, "unit": "GB/s",
-                    "frac": round(nv_achieved / nv_peak, 4), "traffic": None,
+        ceil_name, ceil = ("all_to_all_push_ceiling_GBps", 697.0) if transport == "push" else ("all_to_all_pull_ceiling_GBps", 626.0)
+        kern = ("aps::copy_kernel<crc,512,4,get,serve>: each owner looks up, CRC-checks and STORES its pages into the requester's "
+                "landing buffer over NVLink (one serve launch per GPU per step, %d multi-gets in flight)" % depth) if transport == "push" \
+            else "aps::copy_kernel<crc,512,4,get> reading peer slabs over NVLink (lookup + gather + CRC, one launch per step)"
+        roofline = {"bound": "nvlink", "achieved": round(nv_achieved, 1), "peak": 770.0, "unit": "GB/s",
+                    "frac": round(nv_achieved / 770.0, 4), "traffic": None,
                     "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); nominal 900",
-                    "kernel": "aps::copy_kernel<crc,512,4,get> reading peer slabs over NVLink (lookup + gather + CRC, one launch per step)",
+                    "kernel": kern, "transport": transport, "pipeline_depth": depth,
                     "algorithmic_bytes_per_launch": int(remote_frac * step_bytes),
                     "remote_fraction": round(remote_frac, 4), "avg_launch_ms": round(ms_total / K, 5),
                     "launches_timed": int(launches), "frac_of_nominal_900": round(nv_achieved / 900.0, 4),
-                    "all_to_all_pull_ceiling_GBps": 630.0,  # tools/micro/p2p_all_bw.cu, every GPU reading all its peers
-                    "frac_of_pull_ceiling": round(nv_achieved / 630.0, 4),
+                    ceil_name: ceil,  # tools/micro/p2p_transports.cu, every GPU busy in both directions
+                    "frac_of_transport_ceiling": round(nv_achieved / ceil, 4),
                     "hbm_traffic_GBps_per_gpu": round(achieved, 1)}
     else:
-        roofline = None
+        roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                    "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                    "kernel": "aps::copy_kernel<crc, threads, group, get> (K1 lookup + K2 gather + K3 fused CRC32C, one launch per step)",
+                    "algorithmic_bytes_per_launch": 2 * step_bytes,
+                    "avg_launch_ms": round(ms_total / K, 5), "launches_timed": int(launches),
+                    "frac_of_nominal_8000": round(achieved / 8000.0, 4)}
+    e2e_gbps = world * e2e_steps * step_bytes / e2e_s / 1e9
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms_total / K, 5), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(resident) if world == 1 else
-                   ("hash-sharded cache over %d B200: 1 MiB pages, %d GiB per GPU (%d GiB aggregate), every GPU issues batched "
-                    "gets of %d uniform ids over the whole id space, served from the owning GPU over NVLink P2P with fused "
-                    "CRC32C (BASELINE configs[4])" % (world, resident * PAGE >> 30, world * resident * PAGE >> 30, BATCH)),
-                   "page_bytes": PAGE, "resident_pages": resident,
-                   "batch_pages": BATCH, "populate_s": round(t_pop, 2),
-                   "l2": "inputs larger than L2: each step reads 256 MiB drawn from the resident set and writes 256 MiB",
-                   "shards": "one store per GPU; owner = hash(PageId) mod n; gets read the owner's table and slab in place "
-                             "(P2P), no data-path collective" if world > 1 else "single store"},
-        "roofline": roofline if roofline is not None else {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "aps::copy_kernel<crc, threads, group, get> (K1 lookup + K2 gather + K3 fused CRC32C, one launch per step)",
-                     "algorithmic_bytes_per_launch": 2 * step_bytes,
-                     "avg_launch_ms": round(ms_total / K, 5), "launches_timed": int(launches),
-                     "frac_of_nominal_8000": round(achieved / 8000.0, 4)},
-        "e2e": {"value": round(world * e2e_steps * step_bytes / e2e_s / 1e9, 2), "unit": UNIT,
+        "config": config_block(world, resident, round(t_pop, 2), transport),
+        "roofline": roofline,
+        "parity_pages_checked": parity_pages,
+        "e2e": {"value": round(e2e_gbps, 2), "unit": UNIT,
                 "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
-                "steps": e2e_steps, "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound; gathered in HBM by the fused "
-                        "kernel, then moved by the copy engine)",
-                "pcie_memcpy_d2h_GBps": None if pcie_gbps is None else round(pcie_gbps, 2),
-                "frac_of_pcie_memcpy": None if pcie_gbps is None else round(e2e_steps * step_bytes / e2e_s / 1e9 / pcie_gbps, 4)},
+                "steps": e2e_steps,
+                "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound; gathered in HBM by the fused "
+                        "kernel in chunks while the copy engine moves the previous chunk)",
+                "host_d2h_ceiling_GBps": None if pcie_gbps is None else round(world * pcie_gbps, 2),
+                "host_d2h_ceiling_note": "plain cudaMemcpyAsync of 256 MiB HBM -> pinned host, all ranks at once (barrier), aggregate",
+                "frac_of_host_d2h_ceiling": None if pcie_gbps is None else round(e2e_gbps / (world * pcie_gbps), 4)},
         "gpu_launches": int(launches), "clocks": clocks, "aux": aux,
         "copy_variant": os.environ.get("APS_COPY_VARIANT", "default") + ("" if with_crc else " NOCRC"),
         "table": {"lookups": int(stats.lookups), "probe_buckets": int(stats.probe_buckets)},
