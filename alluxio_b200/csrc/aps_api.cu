@@ -230,7 +230,7 @@ struct aps_store {
   bool d2h_stage_failed = false;
   cudaStream_t copy_stream = nullptr;  // the copy engine's stream for staged host-destination gets
   cudaEvent_t chunk_ev[8] = {};
-  std::vector<std::pair<const void*, bool>> ptr_kind;  // is_pinned_host's memo
+  std::vector<std::pair<const void*, int>> ptr_kind;  // host_ptr_kind's memo
   bool use_d2h_stage = true;       // APS_NO_D2H_STAGE=1: let the kernel store into host memory directly
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
@@ -851,17 +851,35 @@ int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   return get_batch_host(s, n, reqs, res, stream, true);
 }
 
-// Is `p` page-locked host memory?  Asked once per distinct pointer (a reader hands the same few pinned buffers back
-// again and again); the driver call costs microseconds that the batched path does not have to spare.
-static bool is_pinned_host(aps_store* s, const void* p) {
+// What kind of memory is `p`?  Asked once per distinct pointer (a reader hands the same few buffers back again and
+// again); the driver call costs microseconds that the batched path does not have to spare.
+enum PtrKind { kPtrDevice = 0, kPtrPinned = 1, kPtrPageable = 2 };  // device / managed; page-locked host; plain host
+static int host_ptr_kind(aps_store* s, const void* p) {
   for (const auto& e : s->ptr_kind)
     if (e.first == p) return e.second;
   cudaPointerAttributes at{};
   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) cudaGetLastError();
-  const bool host = at.type == cudaMemoryTypeHost;
+  const int kind = at.type == cudaMemoryTypeHost ? kPtrPinned
+                   : (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) ? kPtrDevice : kPtrPageable;
   if (s->ptr_kind.size() >= 16) s->ptr_kind.erase(s->ptr_kind.begin());
-  s->ptr_kind.emplace_back(p, host);
-  return host;
+  s->ptr_kind.emplace_back(p, kind);
+  return kind;
+}
+
+// The HBM staging area of the host-array batched calls (one slot per request of the largest batch one call serves),
+// its copy stream and chunk events: allocated on first use and kept.
+static bool ensure_stage(aps_store* s, uint64_t bytes) {
+  if (s->d_d2h_stage) return true;
+  if (s->d2h_stage_failed) return false;
+  if (cudaMalloc(&s->d_d2h_stage, bytes) == cudaSuccess && cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) == cudaSuccess) {
+    s->d2h_stage_bytes = bytes;
+    for (cudaEvent_t& e : s->chunk_ev)
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) s->d2h_stage_failed = true;
+  } else {
+    cudaGetLastError();
+    s->d2h_stage_failed = true;  // no room for it; do not ask again
+  }
+  return s->d_d2h_stage && !s->d2h_stage_failed;
 }
 
 static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream, bool sharded) {
@@ -890,19 +908,15 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   // to the copy engine, which also coalesces neighbouring destinations into one transfer.  The staging area is
   // allocated once (for the largest batch one call serves) and kept.
   const uint64_t stage_want = (uint64_t)limit * slot;
-  bool via_stage = s->use_d2h_stage && (uint64_t)n * s->cfg.page_size >= (8ull << 20) && is_pinned_host(s, reqs[0].dst);
-  if (via_stage && !s->d_d2h_stage && !s->d2h_stage_failed) {
-    if (cudaMalloc(&s->d_d2h_stage, stage_want) == cudaSuccess &&
-        cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking) == cudaSuccess) {
-      s->d2h_stage_bytes = stage_want;
-      for (cudaEvent_t& e : s->chunk_ev)
-        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) s->d2h_stage_failed = true;
-    } else {
-      cudaGetLastError();
-      s->d2h_stage_failed = true;  // no room for it: store straight into host memory, and do not ask again
-    }
+  // Plain (pageable) host destinations -- a Java direct ByteBuffer from allocateDirect, a malloc'd array -- cannot be
+  // written by a kernel at all: they always go through the staging area and cudaMemcpy.  All destinations of one call
+  // must be of one kind.
+  const int kind = host_ptr_kind(s, reqs[0].dst);
+  bool via_stage = kind == kPtrPageable || (kind == kPtrPinned && s->use_d2h_stage && (uint64_t)n * s->cfg.page_size >= (8ull << 20));
+  if (via_stage && !ensure_stage(s, stage_want)) {
+    if (kind == kPtrPageable) return APS_ENOMEM;
+    via_stage = false;  // pinned: store straight into host memory
   }
-  via_stage = via_stage && s->d_d2h_stage && !s->d2h_stage_failed;
   if (!via_stage) {
     CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
     s->host_form = true;
@@ -971,11 +985,39 @@ int aps_put_batch(aps_store* s, uint32_t n, const aps_put_req* reqs, aps_result*
   if (n > s->cfg.max_batch || !reqs || !res) return APS_EINVAL;
   if (!distinct_keys(n, [&](uint32_t i) { return reqs[i].key; })) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
+  // Sources in plain (pageable) host memory -- a Java direct ByteBuffer, a malloc'd array -- cannot be read by a kernel:
+  // they are copied into the HBM staging area first.  All sources of one call must be of one kind.
+  const uint64_t slot = ((uint64_t)s->table.page_size + 255u) & ~255ull;
+  const uint32_t limit = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(s->cfg.max_batch, (1ull << 30) / slot));
+  const void* first_src = nullptr;
+  for (uint32_t i = 0; i < n && !first_src; ++i)
+    if (reqs[i].len) first_src = reqs[i].src;
+  bool pageable;
+  {
+    std::lock_guard<std::mutex> lk(s->mu);
+    pageable = first_src && host_ptr_kind(s, first_src) == kPtrPageable;
+  }
+  if (pageable && n > limit) {  // more than the staging area holds: in pieces
+    for (uint32_t lo = 0; lo < n; lo += limit) {
+      rc = aps_put_batch(s, std::min(limit, n - lo), reqs + lo, res + lo, stream);
+      if (rc) return rc;
+    }
+    return APS_OK;
+  }
   std::lock_guard<std::mutex> lk(s->mu);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
   aps_put_req* h_reqs = reinterpret_cast<aps_put_req*>(s->h_stage);
   aps_result* h_res = reinterpret_cast<aps_result*>(s->h_stage + (size_t)s->cfg.max_batch * sizeof(aps_get_req));
   memcpy(h_reqs, reqs, (size_t)n * sizeof(aps_put_req));
+  if (pageable) {
+    if (!ensure_stage(s, (uint64_t)limit * slot)) return APS_ENOMEM;
+    for (uint32_t i = 0; i < n; ++i) {
+      if (reqs[i].len > s->cfg.page_size) continue;  // refused by the kernel; nothing to stage
+      if (reqs[i].len)
+        CUDA_TRY(cudaMemcpyAsync(s->d_d2h_stage + (uint64_t)i * slot, reqs[i].src, reqs[i].len, cudaMemcpyHostToDevice, st));
+      h_reqs[i].src = s->d_d2h_stage + (uint64_t)i * slot;
+    }
+  }
   CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_put_req), cudaMemcpyHostToDevice, st));
   s->host_form = true;
   rc = aps_put_batch_dev(s, n, (const aps_put_req*)s->d_reqs, s->d_res, st);

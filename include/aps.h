@@ -150,15 +150,23 @@ typedef struct aps_put_req {
   aps_key key;
   uint32_t len;
   uint32_t reserved;
-  const void* src; /* device memory or pinned host memory */
+  const void* src; /* device memory or pinned host memory; host-array calls also take pageable host memory */
 } aps_put_req;
 
 /* Batched LocalPageStore.get.  reqs and res are HOST arrays; the call stages them, runs the
  * lookup + gather (+CRC) kernels on `stream`, copies the results back and waits for them.
- * Keys within one batch need not be distinct for gets.  n may exceed max_batch (served in pieces). */
+ * Keys within one batch need not be distinct for gets.  n may exceed max_batch (served in pieces).
+ * Destinations (all of one kind per call): device memory (written by the kernel), page-locked host memory
+ * (batches of 8 MiB and more are gathered in an HBM staging area in chunks while the copy engine moves the
+ * previous chunk; smaller ones are written by the kernel over PCIe), or plain pageable host memory -- a Java
+ * ByteBuffer.allocateDirect buffer, a malloc'd array -- which always goes through the staging area and
+ * cudaMemcpy.  The staging area (one slot per request of the largest batch, at most 1 GiB) is allocated on
+ * first use and kept until close. */
 APS_API int aps_get_batch(aps_store* s, uint32_t n, const aps_get_req* reqs, aps_result* res, aps_stream stream);
 
-/* Batched LocalPageStore.put.  Keys within one batch must be distinct (else APS_EINVAL). */
+/* Batched LocalPageStore.put.  Keys within one batch must be distinct (else APS_EINVAL).  Sources (all of one
+ * kind per call): device memory or page-locked host memory (read by the kernel in place), or plain pageable host
+ * memory (copied into the staging area first). */
 APS_API int aps_put_batch(aps_store* s, uint32_t n, const aps_put_req* reqs, aps_result* res, aps_stream stream);
 
 /* Batched LocalPageStore.delete; res[i].len is 0 or -APS_ENOTFOUND.  Keys must be distinct. */

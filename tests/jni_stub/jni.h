@@ -3,7 +3,8 @@
 #include <stdint.h>
 typedef int32_t jint; typedef int64_t jlong; typedef signed char jbyte; typedef unsigned char jboolean;
 typedef void* jobject; typedef jobject jclass; typedef jobject jstring; typedef jobject jarray; typedef jarray jintArray;
-typedef jarray jlongArray; typedef jarray jbyteArray; typedef jint jsize;
+typedef jarray jlongArray; typedef jarray jbyteArray; typedef jarray jobjectArray; typedef jint jsize;
+#define JNI_ABORT 2
 #define JNIEXPORT
 #define JNICALL
 struct JNINativeInterface_;
@@ -18,4 +19,15 @@ struct JNINativeInterface_ {
   jstring (*NewStringUTF)(JNIEnv*, const char*);
   const char* (*GetStringUTFChars)(JNIEnv*, jstring, jboolean*);
   void (*ReleaseStringUTFChars)(JNIEnv*, jstring, const char*);
+  jlong* (*GetLongArrayElements)(JNIEnv*, jlongArray, jboolean*);
+  void (*ReleaseLongArrayElements)(JNIEnv*, jlongArray, jlong*, jint);
+  jint* (*GetIntArrayElements)(JNIEnv*, jintArray, jboolean*);
+  void (*ReleaseIntArrayElements)(JNIEnv*, jintArray, jint*, jint);
+  jbyte* (*GetByteArrayElements)(JNIEnv*, jbyteArray, jboolean*);
+  void (*ReleaseByteArrayElements)(JNIEnv*, jbyteArray, jbyte*, jint);
+  jsize (*GetArrayLength)(JNIEnv*, jarray);
+  jobject (*GetObjectArrayElement)(JNIEnv*, jobjectArray, jsize);
+  void (*SetObjectArrayElement)(JNIEnv*, jobjectArray, jsize, jobject);
+  jobjectArray (*NewObjectArray)(JNIEnv*, jsize, jclass, jobject);
+  jclass (*FindClass)(JNIEnv*, const char*);
 };
