@@ -253,6 +253,7 @@ struct aps_store {
     uint8_t* ctrl = nullptr;          // inboxes | done words | result slots, one allocation (exported to the peers)
     uint64_t ctrl_bytes = 0, off_done = 0, off_results = 0;
     uint32_t cap = 0, depth = 0, n_shards = 0, me = 0;
+    unsigned long long timeout_ns = 30ull * 1000 * 1000 * 1000;  // APS_PUSH_TIMEOUT_MS overrides
     uint32_t sharing = 1;             // shards whose serve kernels run on this device (they split the SMs)
     bool attached = false;
     PushServe* d_serve = nullptr;     // the owner-side maps, in device memory
@@ -262,6 +263,8 @@ struct aps_store {
     uint32_t* d_sched = nullptr;
     uint32_t* d_served = nullptr;
     cudaStream_t serve_stream = nullptr;
+    cudaStream_t hp_stream = nullptr;  // highest priority: the post and wait kernels (see aps_get_batch_push_begin_dev)
+    cudaEvent_t ev_in = nullptr, ev_out = nullptr;
     uint32_t seq_begun = 0, seq_ended = 0;
     uint32_t n_of[4] = {};            // batch size of the rounds in flight, by slot
     std::vector<void*> ipc_ptrs;
@@ -462,6 +465,12 @@ void free_store(aps_store* s) {
     cudaStreamSynchronize(s->push.serve_stream);
     cudaStreamDestroy(s->push.serve_stream);
   }
+  if (s->push.hp_stream) {
+    cudaStreamSynchronize(s->push.hp_stream);
+    cudaStreamDestroy(s->push.hp_stream);
+  }
+  if (s->push.ev_in) cudaEventDestroy(s->push.ev_in);
+  if (s->push.ev_out) cudaEventDestroy(s->push.ev_out);
   for (void* p : s->push.ipc_ptrs) cudaIpcCloseMemHandle(p);
   s->push.ipc_ptrs.clear();
   cudaFree(s->push.landing);
@@ -930,22 +939,20 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
     memcpy(res, h_res, (size_t)n * sizeof(aps_result));
     return APS_OK;
   }
-  // Pipelined: the batch is cut into chunks of ~32 MiB.  All gather kernels (and the copies of their results) are
-  // enqueued at once; the host then follows them chunk by chunk -- as soon as chunk k's results are in, its pages are
-  // handed to the copy engine on a second stream while the SMs gather chunk k+1.  The link idles only while the first
-  // chunk is gathered (~10 us of a 4.7 ms batch of 256 MiB).
+  // Pipelined in two pieces: a small head (~8 MiB) whose only job is to get the link busy early, and the rest.  Both
+  // gather kernels are enqueued at once and read their requests from, and write their results to, the pinned staging
+  // area in place (no request or result copies).  The host follows them: as soon as a piece's results are in, its pages
+  // are handed to the copy engine on a second stream; the rest is gathered (~90 us for 248 MiB) while the head crosses
+  // PCIe (~150 us), so the link idles only while the head is gathered.  More pieces were measured and lose: every
+  // separate device-to-host copy costs a start-up gap (8 pieces of 32 MiB: 0.957 of the link, one piece: 0.97).
   for (uint32_t i = 0; i < n; ++i) h_reqs[i].dst = s->d_d2h_stage + (uint64_t)i * slot;
-  CUDA_TRY(cudaMemcpyAsync(s->d_reqs, h_reqs, (size_t)n * sizeof(aps_get_req), cudaMemcpyHostToDevice, st));
-  constexpr uint32_t kMaxChunks = 8;
-  const uint32_t per = std::max<uint32_t>(1, std::max<uint32_t>((n + kMaxChunks - 1) / kMaxChunks, (uint32_t)((32ull << 20) / slot)));
-  const uint32_t n_chunks = (n + per - 1) / per;
+  const uint32_t head = std::min<uint32_t>(n, std::max<uint32_t>(1, (uint32_t)((8ull << 20) / slot)));
+  const uint32_t cut[3] = {0, head, n};
+  const uint32_t n_chunks = head < n ? 2 : 1;
   s->host_form = true;
   for (uint32_t c = 0; c < n_chunks && rc == APS_OK; ++c) {
-    const uint32_t lo = c * per, cnt = std::min(per, n - lo);
-    const aps_get_req* dq = (const aps_get_req*)s->d_reqs + lo;
-    rc = sharded ? aps_get_batch_sharded_dev(s, cnt, dq, s->d_res + lo, st) : aps_get_batch_dev(s, cnt, dq, s->d_res + lo, st);
-    if (rc == APS_OK && cudaMemcpyAsync(h_res + lo, s->d_res + lo, (size_t)cnt * sizeof(aps_result), cudaMemcpyDeviceToHost, st) != cudaSuccess)
-      rc = APS_ECUDA;
+    const uint32_t lo = cut[c], cnt = cut[c + 1] - lo;
+    rc = sharded ? aps_get_batch_sharded_dev(s, cnt, h_reqs + lo, h_res + lo, st) : aps_get_batch_dev(s, cnt, h_reqs + lo, h_res + lo, st);
     if (rc == APS_OK && cudaEventRecord(s->chunk_ev[c], st) != cudaSuccess) rc = APS_ECUDA;
   }
   s->host_form = false;
@@ -954,7 +961,7 @@ static int get_batch_host(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
     return rc;
   }
   for (uint32_t c = 0; c < n_chunks; ++c) {
-    const uint32_t lo = c * per, hi = std::min(n, lo + per);
+    const uint32_t lo = cut[c], hi = cut[c + 1];
     CUDA_TRY(cudaEventSynchronize(s->chunk_ev[c]));
     // exactly the bytes each get returned, runs of requests that are adjacent on both sides as one copy
     uint32_t i = lo;
@@ -1405,6 +1412,7 @@ int push_install(aps_store* s, uint32_t n_shards, uint32_t me, uint8_t* const* l
   h.depth = p.depth;
   h.inbox = p.ctrl;
   h.served = p.d_served;
+  h.timeout_ns = p.timeout_ns;
   for (uint32_t r = 0; r < n_shards; ++r) {
     h.landing[r] = landing[r];
     h.results[r] = reinterpret_cast<aps_result*>(ctrl[r] + p.off_results);
@@ -1435,11 +1443,20 @@ int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth) {
     CUDA_TRY(cudaFuncGetAttributes(&fa, push_post_kernel));
     CUDA_TRY(cudaFuncGetAttributes(&fa, push_wait_kernel));
     CUDA_TRY(cudaFuncGetAttributes(&fa, copy_kernel<true, 512, 4, true, false, true>));
+    // The small kernels must be able to run BESIDE a serve CTA (serve kernels of consecutive rounds can hold every SM
+    // between them).  An SM is configured for one split of its L1 / shared memory at a time, and the serve kernel needs
+    // the largest shared part: ask for the same split, or the small kernels would wait for an SM to drain.
+    CUDA_TRY(cudaFuncSetAttribute(push_post_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_TRY(cudaFuncSetAttribute(push_wait_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_TRY(cudaFuncSetAttribute(copy_kernel<true, 512, 4, true, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                  cudaSharedmemCarveoutMaxShared));
+    if (const char* e = getenv("APS_PUSH_TIMEOUT_MS")) p.timeout_ns = (unsigned long long)std::max(1, atoi(e)) * 1000000ull;
   }
   p.cap = s->cfg.max_batch;
   p.depth = depth;
   p.landing_bytes = landing_bytes;
   push_layout(p);
+  int prio_least = 0, prio_greatest = 0;
   const uint64_t jobs = (uint64_t)kPushMaxShards * p.cap;  // an owner may be asked for every request of every peer
   cudaError_t e;
   if ((e = cudaMalloc(&p.landing, landing_bytes)) != cudaSuccess || (e = cudaMalloc(&p.ctrl, p.ctrl_bytes)) != cudaSuccess ||
@@ -1450,6 +1467,10 @@ int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth) {
       (e = cudaMalloc(&p.d_served, kPushMaxShards * sizeof(uint32_t))) != cudaSuccess ||
       (e = cudaMemset(p.d_served, 0, kPushMaxShards * sizeof(uint32_t))) != cudaSuccess ||
       (e = cudaStreamCreateWithFlags(&p.serve_stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest)) != cudaSuccess ||
+      (e = cudaStreamCreateWithPriority(&p.hp_stream, cudaStreamNonBlocking, prio_greatest)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&p.ev_in, cudaEventDisableTiming)) != cudaSuccess ||
+      (e = cudaEventCreateWithFlags(&p.ev_out, cudaEventDisableTiming)) != cudaSuccess ||
       (e = cudaDeviceSynchronize()) != cudaSuccess) {
     snprintf(tl_cuda_error, sizeof(tl_cuda_error), "aps_push_setup: %s", cudaGetErrorString(e));
     cudaGetLastError();
@@ -1564,11 +1585,17 @@ int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_
   pa.landing = p.landing;
   pa.landing_bytes = p.landing_bytes;
   pa.my_results = reinterpret_cast<aps_result*>(p.ctrl + p.off_results);
-  push_post_kernel<<<1, 256, 0, st>>>(pa);
+  // The post and wait kernels run on a stream of the HIGHEST priority, tied into the caller's stream with events.  The
+  // GPU hands out CTAs of equal priority in launch order: behind a serve kernel that still has CTAs to place (serve
+  // kernels of consecutive rounds overlap and hold every SM between them) a post kernel of the caller's priority would
+  // wait for the very serve kernels that wait for it.  With priority it is placed next, beside a serve CTA.
+  CUDA_TRY(cudaEventRecord(p.ev_in, st));
+  CUDA_TRY(cudaStreamWaitEvent(p.hp_stream, p.ev_in, 0));
+  push_post_kernel<<<1, 256, 0, p.hp_stream>>>(pa);
   CUDA_TRY(cudaGetLastError());
   // owner side: serve what the peers post for this round.  One CTA per SM but one: the SM left over runs the small
-  // post and wait kernels of this GPU, which the serve kernels of this and the other GPUs wait for.  Plain stream order
-  // (no programmatic launch) keeps two serve kernels from holding every SM between them.
+  // post and wait kernels of this GPU, which the serve kernels of this and the other GPUs wait for (and a serve CTA is
+  // compiled small enough for those kernels to fit beside it on any SM, see copy_kernel).
   CopyArgs a{};
   a.table = s->table;
   a.crc_on = 1;
@@ -1592,7 +1619,24 @@ int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_
   const uint32_t grid = (uint32_t)std::max(1, (s->dc->num_sms - spare) / (int)p.sharing);
   const uint32_t warps = grid * 16u;
   a.serve_warps = warps > (uint32_t)s->dc->n_slow + p.cap ? warps - (uint32_t)s->dc->n_slow : warps;
-  copy_kernel<true, 512, 4, true, false, true><<<grid, 512, kCopyDynSmem, p.serve_stream>>>(a);
+  // Consecutive rounds overlap (programmatic dependent launch): the CTAs of round k+1 land on SMs as round k's retire, fetch
+  // the CRC tables, pick up round k+1's postings, resolve their pages and warm L2 with their first rows, and only then
+  // wait for round k to finish; everything they write stays behind that wait.  (Postings are final once announced.)
+  a.early = s->use_pdl && s->use_early ? 1 + (int)s->prefetch_rows : 0;
+  a.trust_reqs = 1;
+  {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3(grid);
+    lc.blockDim = dim3(512);
+    lc.dynamicSmemBytes = kCopyDynSmem;
+    lc.stream = p.serve_stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = s->use_pdl ? 1 : 0;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&lc, copy_kernel<true, 512, 4, true, false, true>, a));
+  }
   CUDA_TRY(cudaGetLastError());
   count_launch(s, 2);
   return APS_OK;
@@ -1610,10 +1654,12 @@ int aps_get_batch_push_end_dev(aps_store* s, aps_result* d_res, aps_stream strea
   const uint32_t n = p.n_of[seq % p.depth];
   if (n && !d_res) return APS_EINVAL;
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  push_wait_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const unsigned long long*>(p.ctrl + p.off_done), p.n_shards, seq,
+  push_wait_kernel<<<1, 256, 0, p.hp_stream>>>(reinterpret_cast<const unsigned long long*>(p.ctrl + p.off_done), p.n_shards, seq,
                                       reinterpret_cast<const aps_result*>(p.ctrl + p.off_results) + (size_t)(seq % p.depth) * p.cap,
-                                      d_res, n, s->h_error);
+                                      d_res, n, s->h_error, p.timeout_ns);
   CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaEventRecord(p.ev_out, p.hp_stream));
+  CUDA_TRY(cudaStreamWaitEvent(st, p.ev_out, 0));  // `stream` continues once the batch has landed
   count_launch(s);
   return APS_OK;
 }

@@ -261,9 +261,9 @@ struct PushServe {     // one per store, in device memory; everything an owner n
   aps_result* results[kPushMaxShards];     // requester r's result slots [depth][cap] as mapped here
   unsigned long long* done[kPushMaxShards];  // requester r's done word for owner `me` as mapped here
   uint32_t* served;                        // scratch [n_shards]: pages finished per requester in this launch (self-resetting)
+  unsigned long long timeout_ns;           // how long a serve kernel waits for a peer's posting before it gives the peer up
 };
 __host__ __device__ __forceinline__ size_t push_inbox_stride(uint32_t cap) { return sizeof(PushInboxHead) + (size_t)cap * sizeof(PushReq); }
-constexpr unsigned long long kPushTimeoutNs = 30ull * 1000 * 1000 * 1000;  // a peer that never posts: give up, flag it
 
 struct CopyArgs {
   const Job* jobs;           // neither kGet nor kPut: jobs prepared by an earlier kernel
@@ -345,8 +345,11 @@ __device__ __forceinline__ void push_deliver(const PushServe& ps, uint32_t seq, 
 // job's accumulator.  Warps that run out of work take the back half of the longest remaining range
 // in their CTA (finish times of equal streams differ by ~10 % on a saturated memory system).  The
 // warp that completes a job's last row applies init/xorout and verifies or records the page CRC.
+// (kServe is compiled for at most 96 registers per thread -- bounds of 640 threads, launched with 512 -- so that a serve
+// CTA leaves room on its SM for the small post and wait kernels of the push transport, whatever SMs the serve kernels of
+// two consecutive rounds occupy between them.)
 template <bool kCrc, int kThreads, int G, bool kGet, bool kPut = false, bool kServe = false>
-__global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
+__global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyArgs a) {
   static_assert(!(kGet && kPut), "a launch is a get, a put, or a list of prepared jobs");
   static_assert(!kServe || (kGet && kCrc), "the serve kernel is a get with the checksum on");
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -380,7 +383,7 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
       const unsigned long long t0 = globaltimer_ns();
       unsigned long long w = *word;
       while ((uint32_t)(w >> 32) != a.push_seq) {
-        if (globaltimer_ns() - t0 > kPushTimeoutNs) {  // the peer never posted (it failed, or skipped a collective call)
+        if (globaltimer_ns() - t0 > ps.timeout_ns) {  // the peer never posted (it failed, or skipped a collective call)
           *a.error_flag = 3;
           w = (unsigned long long)a.push_seq << 32;
           srv_lost = true;
@@ -405,11 +408,6 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     tpj = min(tpj, min(kMaxTasksPerJob, max(1u, a.serve_rows / 8u)));
     a.rows_per_task = (a.serve_rows + tpj - 1u) / tpj;
     a.tasks_per_job = (a.serve_rows + a.rows_per_task - 1u) / a.rows_per_task;
-    // a requester that asked this owner for nothing still waits for its done word
-    if (blockIdx.x == 0 && warp == 0 && lane < ps.n_shards && srv_cnt == 0 && !srv_lost) {
-      __threadfence_system();
-      *(volatile unsigned long long*)ps.done[lane] = a.push_seq;
-    }
   }
   const uint32_t n_items = a.n_jobs * a.tasks_per_job;
   // Task assignment.  n_items / grid tasks per CTA are fixed by blockIdx, so warps can start at once.  The
@@ -851,6 +849,15 @@ __global__ void __launch_bounds__(kThreads, 1) copy_kernel(CopyArgs a) {
     if (kServe) push_deliver(*a.push, a.push_seq, j.pad, fin, lane, srv_cnt);
   }
   gate();  // a warp that found nothing to do arrives here without having waited
+  if (kServe) {
+    // a requester that asked this owner for nothing still waits for its done word (behind the gate: the previous round's
+    // serve kernel has finished, so done words go up in round order)
+    const PushServe& ps = *a.push;
+    if (blockIdx.x == 0 && warp == 0 && lane < ps.n_shards && srv_cnt == 0 && !srv_lost) {
+      __threadfence_system();
+      *(volatile unsigned long long*)ps.done[lane] = a.push_seq;
+    }
+  }
   if (warp == surplus_warp && lane == 0) {
     // this CTA holds its rank (the answer was consumed above or is awaited here); the last CTA to say so
     // re-arms the counters for the next launch
@@ -1350,7 +1357,8 @@ __global__ void __launch_bounds__(256) push_post_kernel(PushPostArgs p) {
 // push_wait_kernel: the stream-ordered end of a pushed multi-get.  Waits until every owner has raised this GPU's done
 // word for `seq` (the pages are then in the landing buffer), then copies the results into the caller's array.
 __global__ void __launch_bounds__(256) push_wait_kernel(const unsigned long long* done, uint32_t n_shards, uint32_t seq,
-                                                        const aps_result* slot_results, aps_result* res, uint32_t n, int* error_flag) {
+                                                        const aps_result* slot_results, aps_result* res, uint32_t n, int* error_flag,
+                                                        unsigned long long timeout_ns) {
   __shared__ int s_ok;
   if (threadIdx.x == 0) s_ok = 1;
   __syncthreads();
@@ -1358,7 +1366,7 @@ __global__ void __launch_bounds__(256) push_wait_kernel(const unsigned long long
     const volatile unsigned long long* word = (const volatile unsigned long long*)&done[threadIdx.x];
     const unsigned long long t0 = globaltimer_ns();
     while (*word < (unsigned long long)seq) {  // sequence numbers only grow
-      if (globaltimer_ns() - t0 > kPushTimeoutNs) {
+      if (globaltimer_ns() - t0 > timeout_ns) {
         *error_flag = 4;
         s_ok = 0;
         break;
