@@ -266,7 +266,7 @@ struct aps_store {
     cudaStream_t hp_stream = nullptr;  // highest priority: the post and wait kernels (see aps_get_batch_push_begin_dev)
     cudaEvent_t ev_in = nullptr, ev_out = nullptr;
     uint32_t seq_begun = 0, seq_ended = 0;
-    uint32_t n_of[4] = {};            // batch size of the rounds in flight, by slot
+    uint32_t n_of[8] = {};            // batch size of the rounds in flight, by slot
     std::vector<void*> ipc_ptrs;
   } push;
   std::atomic<uint64_t> launches{0};
@@ -1430,7 +1430,7 @@ int push_install(aps_store* s, uint32_t n_shards, uint32_t me, uint8_t* const* l
 int aps_push_setup(aps_store* s, uint64_t landing_bytes, uint32_t depth) {
   int rc = check_open(s);
   if (rc) return rc;
-  if (landing_bytes == 0 || depth == 0 || depth > 4 || !(s->cfg.flags & APS_FLAG_CRC)) return APS_EINVAL;
+  if (landing_bytes == 0 || depth == 0 || depth > 8 || !(s->cfg.flags & APS_FLAG_CRC)) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   std::lock_guard<std::mutex> lk(s->mu);
   aps_store::Push& p = s->push;
@@ -1610,9 +1610,15 @@ int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_
   a.sched = p.d_sched;
   a.sm_slow = s->dc->d_sm_slow;
   a.n_slow = (uint32_t)s->dc->n_slow;
+  a.timeline = s->d_timeline;  // diagnostics (aps_debug_timeline): stamps of the LAST round; launches are not separated
   a.push = p.d_serve;
   a.push_seq = seq;
   a.serve_rows = s->page_rows;
+  // With four or more shards the tasks are dealt to the CTAs round robin (the local requester's cheap tasks are then
+  // spread over all CTAs: 620 against 616 GB/s at 8 GPUs); with two, half of the tasks are local and whole CTAs of
+  // them finish early and start on the next round, which measured faster (632 against 610 GB/s).
+  static const int serve_flags = [] { const char* e = getenv("APS_SERVE_FLAGS"); return e ? atoi(e) : -1; }();
+  a.serve_flags = serve_flags >= 0 ? (uint32_t)serve_flags : (p.n_shards >= 4 ? 2u : 0u);
   static const int spare = [] { const char* e = getenv("APS_SERVE_SPARE_SMS"); return e ? std::max(0, atoi(e)) : 1; }();
   // several shards on ONE device (tests, small deployments) split the SMs, so that their serve kernels together never
   // hold every SM while they wait for a posting

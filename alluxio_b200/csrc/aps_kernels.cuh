@@ -296,6 +296,7 @@ struct CopyArgs {
   const PushServe* push;     // kServe: the push transport's maps (device memory)
   uint32_t push_seq;         // kServe: which posting to serve
   uint32_t serve_rows;       // kServe: 512-byte rows of a full page ...
+  uint32_t serve_flags;      // kServe experiments: 1 = no system fence per segment (UNSAFE, measurement only); 2 = tasks dealt round robin
   uint32_t serve_warps;      // ... and the warps of the grid: the job split is computed in the kernel, once the posts are in
   int early;                 // kGet, non-zero: requests, table and slab are known not to change under the previous kernel
                              // in the stream, so they may be read before waiting for it (see the kernel's dependency
@@ -436,6 +437,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
       for (uint32_t l = lane; l < pf_lines; l += 32u) asm volatile("prefetch.global.L2 [%0];" ::"l"(pf_ptr + (size_t)l * 128u));
       asm volatile("griddepcontrol.wait;" ::: "memory");
       dep_ok = true;
+      if (kServe && a.timeline && warp == 0 && lane == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();  // gate passed
       ask_rank();
     }
   };
@@ -498,7 +500,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
   } else {
     __syncthreads();
   }
-  if (a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();
+  if (!kServe && a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();
   uint32_t local = warp;  // this warp takes the CTA's fixed tasks local, local + nwarps, ...
   bool surplus_pending = warp == surplus_warp && extra > 0;
 
@@ -514,7 +516,10 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     bool report = false;  // kGet, task 0 of a page that needs no finisher: its result is written behind the gate
     int32_t report_status = 0;
     if (local < base_cnt) {
-      item = blockIdx.x * base_cnt + local;
+      // kServe with serve_flags & 2 deals the tasks out round robin: the job list is ordered by requester, and the requester that is this GPU
+      // itself has local (fast) destinations -- in blocks, the CTAs holding those would finish in a fraction of the time
+      // and leave NVLink to the others (measured at 2 GPUs: CTA end times from 96 to 219 us after the gate)
+      item = (kServe && (a.serve_flags & 2u)) ? local * gridDim.x + blockIdx.x : blockIdx.x * base_cnt + local;
       local += nwarps;
       last_item = local >= base_cnt && !surplus_pending;
     } else if (surplus_pending) {
@@ -818,7 +823,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     }
     const uint32_t target = (j.n + kRowBytes - 1) / kRowBytes;
     uint32_t prev = 0;
-    if (kServe) {  // every lane's stores into the requester's memory are ordered before the row count that announces them
+    if (kServe && !(a.serve_flags & 1u)) {  // every lane's stores into the requester's memory are ordered before the row count that announces them
       __threadfence_system();
       __syncwarp();
     }
@@ -870,7 +875,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
   }
   if (a.timeline) {
     if (lane == 0) a.timeline[1024 + blockIdx.x * 32 + warp] = globaltimer_ns();
-    if (lane == 0) atomicMin(&a.timeline[blockIdx.x * 4 + 2], globaltimer_ns());
+    if (lane == 0 && (!kServe || warp == 0)) { if (kServe) a.timeline[blockIdx.x * 4 + 2] = globaltimer_ns(); else atomicMin(&a.timeline[blockIdx.x * 4 + 2], globaltimer_ns()); }
     __syncthreads();
     if (threadIdx.x == 0) {
       a.timeline[blockIdx.x * 4 + 3] = globaltimer_ns();

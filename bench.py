@@ -33,7 +33,8 @@ BATCH = 256
 DATA_SEED = 0xA11C10
 METRIC = "batched_page_get_fused_crc32c_GBps"
 UNIT = "GB/s"
-N_DST = 4  # destination buffers the timed steps rotate through (4 x 256 MiB = 1 GiB, far beyond the 126 MB L2)
+N_DST = 4  # destination buffers the timed steps rotate through (4 x 256 MiB = 1 GiB, far beyond the 126 MB L2);
+           # with the push transport: as many as multi-gets are kept in flight, if that is more
 
 # BASELINE configs[0] (SURVEY.md 8d cfg 1): the reference's own CPU-runnable case
 CFG0_FILES, CFG0_PAGES_PER_FILE, CFG0_GETS, CFG0_SEED = 64, 128, 65536, 1
@@ -267,7 +268,9 @@ def run_ours(args):
     # several GPUs: "push" = the owners store the pages into the requester's landing buffer (aps_get_batch_push_*),
     # "pull" = the requester's kernel reads the owners' slabs in place (aps_get_batch_sharded_dev)
     transport = os.environ.get("APS_BENCH_TRANSPORT", "push") if world > 1 else "local"
-    depth = int(os.environ.get("APS_BENCH_DEPTH", "2")) if transport == "push" else 1
+    depth = int(os.environ.get("APS_BENCH_DEPTH", "6")) if transport == "push" else 1
+    global N_DST
+    N_DST = max(N_DST, depth)
 
     # pages per GPU: configs[1] = 64 GiB on one GPU; configs[4] = 128 GiB per GPU (1 TiB at 8)
     resident = int(os.environ.get("APS_BENCH_PAGES", "131072" if world > 1 else "65536"))
@@ -448,6 +451,9 @@ def run_ours(args):
         dist.barrier()
     torch.cuda.synchronize(dev)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    serve_tl = transport == "push" and os.environ.get("APS_BENCH_SERVE_TIMELINE") == "1"  # diagnostic, perturbs nothing
+    if serve_tl:
+        capi.check(L.aps_debug_timeline(h, 1, None, 0))
     ev0.record(stream)
     run_steps(W, K)
     ev1.record(stream)
@@ -455,6 +461,22 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
     ms_total = ev0.elapsed_time(ev1)
+    if serve_tl:
+        raw = np.zeros(1024 + 256 * 32 + 256, np.uint64)
+        capi.check(L.aps_debug_timeline(h, 1, raw.ctypes.data, raw.size))
+        tl = raw[:1024].reshape(256, 4)
+        live = (tl[:, 0] != np.uint64(0xFFFFFFFFFFFFFFFF)) & (tl[:, 0] != 0) & (tl[:, 3] != 0)
+        tl = tl[live].astype(np.int64)
+        t0 = tl[:, 1].min()  # the gate of the last round (= the round before it has completed)
+        rel = (tl - t0) / 1e3
+        wend = raw[1024:1024 + 256 * 32].reshape(256, 32)[live][:, :16].astype(np.int64)
+        wrel = (wend - t0) / 1e3
+        if rank == 0:
+            pct = lambda a: " ".join("%.1f" % x for x in np.percentile(a, [0, 10, 50, 90, 100]))
+            print("serve timeline (last round, us relative to its gate; p0 p10 p50 p90 p100): ctas=%d\n  cta resident: %s\n  gate passed: %s\n"
+                  "  cta end: %s\n  warp end: %s\n  within-CTA warp end spread (max-min): %s"
+                  % (len(rel), pct(rel[:, 0]), pct(rel[:, 1]), pct(rel[:, 3]), pct(wrel), pct(wrel.max(axis=1) - wrel.min(axis=1))), file=sys.stderr)
+        capi.check(L.aps_debug_timeline(h, 0, None, 0))
     launches = L.aps_total_kernel_launches() - launches0
     per_step = 3 if transport == "push" else 1  # push: post + serve + wait; otherwise lookup + gather + CRC in ONE launch
     assert launches == per_step * K, "unexpected number of kernel launches per step: %d for %d steps" % (launches, K)

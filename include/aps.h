@@ -217,7 +217,7 @@ APS_API int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* r
  * words.  Destinations must therefore lie in memory the peers can write: the landing buffer allocated by
  * aps_push_setup (requests with a destination outside it are answered -APS_EINVAL).  The store must have APS_FLAG_CRC.
  *   set-up:  aps_push_setup on every store, exchange aps_push_handle blobs (CUDA IPC), aps_push_attach; or
- *            aps_push_attach_local for stores of one process.  depth = multi-gets a store may have in flight (1..4).
+ *            aps_push_attach_local for stores of one process.  depth = multi-gets a store may have in flight (1..8).
  *   use:     aps_get_batch_push_begin_dev posts batch k and starts this GPU's serve kernel for round k (on a stream of
  *            the store's own); aps_get_batch_push_end_dev makes `stream` wait until the oldest batch in flight has
  *            landed and writes its results.  aps_get_batch_push_dev = begin + end.  A caller that wants two batches in
