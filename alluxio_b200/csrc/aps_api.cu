@@ -58,6 +58,7 @@ struct DeviceConsts {
   bool ready = false;
   CrcTables* d_tables = nullptr;
   uint8_t* d_table_image = nullptr;  // shared-memory image of the tables (bytes kSmemG..kSmemEnd of the window)
+  uint8_t* d_table_image4 = nullptr; // the same with the replicated tables carrying four rows ahead (kernels with kIndep)
   int num_sms = 0;
   // SM speed classes (see calibrate_sms): d_sm_slow[smid] = 1 for SMs that stream measurably slower
   uint8_t* d_sm_slow = nullptr;
@@ -72,11 +73,11 @@ DeviceConsts g_dev[64];
 typedef void (*CopyKernelFn)(CopyArgs);
 struct CopyVariant {
   const char* name;
-  uint32_t threads;
+  uint32_t threads, group;
   CopyKernelFn crc, plain, get_crc, get_plain, put_crc, put_plain;
 };
 #define APS_VARIANT(T, G)                                                                                  \
-  {#T "x" #G, T, copy_kernel<true, T, G, false>, copy_kernel<false, T, G, false>, copy_kernel<true, T, G, true>, \
+  {#T "x" #G, T, G, copy_kernel<true, T, G, false>, copy_kernel<false, T, G, false>, copy_kernel<true, T, G, true>, \
    copy_kernel<false, T, G, true>, copy_kernel<true, T, G, false, true>, copy_kernel<false, T, G, false, true>}
 const CopyVariant kCopyVariants[] = {
     APS_VARIANT(512, 4), APS_VARIANT(1024, 4), APS_VARIANT(1024, 2), APS_VARIANT(512, 8),
@@ -121,11 +122,12 @@ struct HostCrcConsts {
 const HostCrcConsts& host_crc_consts() {
   static const HostCrcConsts* c = [] {
     auto* h = new HostCrcConsts();
-    const uint32_t xrow = host_xpow8(kRowBytes), x4 = host_xpow8(4);
+    const uint32_t xrow = host_xpow8(kRowBytes), x4 = host_xpow8(4), xrow4 = host_xpow8(4 * kRowBytes);
     for (uint32_t j = 0; j < 4; ++j)
       for (uint32_t b = 0; b < 256; ++b) {
         h->tables.fold[j][b] = gf_mul(b << (8 * j), xrow);
         h->tables.z4[j][b] = gf_mul(b << (8 * j), x4);
+        h->tables.fold4[j][b] = gf_mul(b << (8 * j), xrow4);
       }
     for (int k = 0; k < 32; ++k) h->xpow8[k] = host_xpow8(1ull << k);
     // lane l holds bytes 16l..16l+15 of a 512-byte row; after the in-lane reduction its value
@@ -157,6 +159,14 @@ int ensure_device_consts(int dev, DeviceConsts** out) {
           }
       CUDA_TRY(cudaMalloc(&d.d_table_image, img.size()));
       CUDA_TRY(cudaMemcpy(d.d_table_image, img.data(), img.size(), cudaMemcpyHostToDevice));
+      for (uint32_t j = 0; j < 4; ++j)
+        for (uint32_t b = 0; b < 256; ++b)
+          for (uint32_t l = 0; l < 32; ++l) {
+            const uint32_t at = (kSmemF - kSmemG) + (j >> 1) * 0x10000u + b * 256u + (j & 1u) * 128u + l * 4u;
+            memcpy(img.data() + at, &h.tables.fold4[j][b], 4);
+          }
+      CUDA_TRY(cudaMalloc(&d.d_table_image4, img.size()));
+      CUDA_TRY(cudaMemcpy(d.d_table_image4, img.data(), img.size(), cudaMemcpyHostToDevice));
     }
     CUDA_TRY(cudaMemcpyToSymbol(c_xpow8, h.xpow8, sizeof(h.xpow8)));
     CUDA_TRY(cudaMemcpyToSymbol(c_lane_shift, h.lane_shift, sizeof(h.lane_shift)));
@@ -315,7 +325,7 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.acc = s->d_acc;
   a.done = s->d_done;
   a.tables = s->dc->d_tables;
-  a.table_image = s->use_table_image ? s->dc->d_table_image : nullptr;
+  a.table_image = s->use_table_image ? (v.group == 4 ? s->dc->d_table_image4 : s->dc->d_table_image) : nullptr;
   a.rowshift = s->d_rowshift;
   a.error_flag = s->h_error;
   a.timeline = s->d_timeline;

@@ -29,6 +29,7 @@ constexpr uint32_t kRowBytes = 512;  // one warp-wide 128-bit access
 //                       only ever touches bank l (conflict-free): address = 0x10000 + (j>>1)*0x10000
 //                       + b*256 + (j&1)*128 + lane*4.  The 64 KiB alignment lets one PRMT build the
 //                       address from a data byte (see fold_word).
+constexpr uint32_t kSmemP = 0x0E000u;  // plain x^(8*512) tables (4 KiB) of the kernels that fold four rows at a time, see stream_rows
 constexpr uint32_t kSmemG = 0x0F000u;
 constexpr uint32_t kSmemF = 0x10000u;
 constexpr uint32_t kSmemEnd = 0x30000u;
@@ -37,6 +38,7 @@ constexpr uint32_t kCopyDynSmem = kSmemEnd;  // requested size; the window start
 struct CrcTables {      // device-global copy, built once on the host
   uint32_t fold[4][256];  // F_j[b] = (b << 8j) * x^(8*512)
   uint32_t z4[4][256];    // G_j[b] = (b << 8j) * x^32
+  uint32_t fold4[4][256]; // (b << 8j) * x^(8*512*4): four rows ahead
 };
 
 __device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
@@ -61,6 +63,12 @@ __device__ __forceinline__ uint32_t fold_word(uint32_t s, uint32_t rb) {
   asm volatile("ld.shared.u32 %0, [%1+65536];" : "=r"(v2) : "r"(a2));
   asm volatile("ld.shared.u32 %0, [%1+65664];" : "=r"(v3) : "r"(a3));
   return v0 ^ v1 ^ v2 ^ v3;
+}
+
+// s * x^(8*512) from the plain (not replicated, so bank-conflicted, 4 KiB) tables at kSmemP: used a few times per segment
+__device__ __forceinline__ uint32_t fold1_plain(uint32_t r) {
+  return lds_u32(kSmemP + (r & 0xFFu) * 4u) ^ lds_u32(kSmemP + 1024u + ((r >> 8) & 0xFFu) * 4u) ^
+         lds_u32(kSmemP + 2048u + ((r >> 16) & 0xFFu) * 4u) ^ lds_u32(kSmemP + 3072u + (r >> 24) * 4u);
 }
 
 // r * x^32 (advance the register over four zero bytes) from the plain tables.
@@ -164,7 +172,12 @@ struct NoGate {
 };
 // `gate` runs once the first loads are in flight and before anything is stored: the copy kernel uses it to
 // wait for the previous kernel in the stream (programmatic dependent launch) as late as it safely can.
-template <bool kCrc, int G, typename Gate = NoGate>
+// kIndep (groups of four rows): the G rows of a group are folded into G INDEPENDENT states, each carried forward by a
+// whole group (the replicated tables then hold x^(8*512*G)), so that the sixteen table reads of a group do not wait for
+// each other (serially, row u+1 needs row u's result: four dependent shared-memory round trips per group and word).
+// The states are merged -- Horner with the plain one-row tables -- once, at the end of the segment, or just before a
+// last, incomplete group, whose rows then go through the one-row tables as well.
+template <bool kCrc, int G, bool kIndep, typename Gate = NoGate>
 __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst, unsigned long long* range, uint32_t row_lo,
                                                 uint32_t lane, uint32_t* row_end, uint32_t tables_bar, Gate gate = Gate()) {
   const uint4* s = reinterpret_cast<const uint4*>(src) + lane;  // src/dst point at row 0 of the job
@@ -172,6 +185,20 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   const bool store = dst != nullptr;
   const uint32_t rb = 0x00010000u | (lane << 2);
   uint32_t S0 = 0, S1 = 0, S2 = 0, S3 = 0;
+  constexpr int kChains = kIndep ? G : 1;
+  uint4 C[kChains];  // kIndep: chain u holds rows u, u + G, ... of the segment; chain 0 doubles as the merged state
+#pragma unroll
+  for (int u = 0; u < kChains; ++u) C[u] = make_uint4(0u, 0u, 0u, 0u);
+  bool merged = false;
+  auto merge = [&]() {  // C[0] = (((C0 * X + C1) * X + C2) * X + C3), X = x^(8*512)
+    if (merged) return;
+    merged = true;
+#pragma unroll
+    for (int u = 1; u < kChains; ++u) {
+      C[0].x = fold1_plain(C[0].x) ^ C[u].x; C[0].y = fold1_plain(C[0].y) ^ C[u].y;
+      C[0].z = fold1_plain(C[0].z) ^ C[u].z; C[0].w = fold1_plain(C[0].w) ^ C[u].w;
+    }
+  };
   uint4 A[G], B[G];
   auto load = [&](uint4(&buf)[G], const Claim& c) {
 #pragma unroll
@@ -184,10 +211,29 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
       for (int u = 0; u < G; ++u)
         if ((uint32_t)u < c.cnt) stg_stream(d + (size_t)(c.pos + u) * 32, buf[u]);
     }
-    if (kCrc) {
+    if (kCrc && !kIndep) {
 #pragma unroll
       for (int u = 0; u < G; ++u)
         if ((uint32_t)u < c.cnt) APS_FOLD_ROW(buf[u]);
+    }
+    if (kCrc && kIndep) {
+      if (c.cnt == (uint32_t)G) {
+#pragma unroll
+        for (int u = 0; u < kChains; ++u) {
+          C[u].x = fold_word(C[u].x, rb) ^ buf[u].x; C[u].y = fold_word(C[u].y, rb) ^ buf[u].y;
+          C[u].z = fold_word(C[u].z, rb) ^ buf[u].z; C[u].w = fold_word(C[u].w, rb) ^ buf[u].w;
+        }
+      } else if (c.cnt) {  // the last, incomplete group of the segment
+        merge();
+        for (uint32_t u = 0; u < c.cnt; ++u) {
+          uint4 v = buf[0];
+#pragma unroll
+          for (int q = 1; q < G; ++q)
+            if (u == (uint32_t)q) v = buf[q];
+          C[0].x = fold1_plain(C[0].x) ^ v.x; C[0].y = fold1_plain(C[0].y) ^ v.y;
+          C[0].z = fold1_plain(C[0].z) ^ v.z; C[0].w = fold1_plain(C[0].w) ^ v.w;
+        }
+      }
     }
   };
   uint32_t end = row_lo;
@@ -196,6 +242,8 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   // the first loads are in flight; only now make sure the CRC tables have landed in shared memory
   if (kCrc && tables_bar) mbar_wait(tables_bar, 0);
   gate();
+  // (A third buffer -- two groups in flight while one is stored and folded -- was measured and loses: 2,885 against
+  // 2,921 GB/s.  The warps do wait for loaded data at the first store of a group, but the memory system is what is busy.)
   while (ca.cnt) {
     Claim cb = claim_rows<G>(range, lane);
     load(B, cb);
@@ -209,6 +257,10 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   }
   *row_end = end;
   if (!kCrc) return 0;
+  if (kIndep) {
+    merge();
+    S0 = C[0].x; S1 = C[0].y; S2 = C[0].z; S3 = C[0].w;
+  }
   // lane words -> one register: t = Z4(Z4(Z4(S0)^S1)^S2)^S3, then shift to the end of the row
   uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
   return warp_xor(gf_mul(t, c_lane_shift[lane]));
@@ -353,6 +405,7 @@ template <bool kCrc, int kThreads, int G, bool kGet, bool kPut = false, bool kSe
 __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyArgs a) {
   static_assert(!(kGet && kPut), "a launch is a get, a put, or a list of prepared jobs");
   static_assert(!kServe || (kGet && kCrc), "the serve kernel is a get with the checksum on");
+  constexpr bool kIndep = kCrc && G == 4 && !kServe;  // fold the four rows of a group independently (stream_rows)
   extern __shared__ __align__(128) uint8_t smem_raw[];
   constexpr uint32_t nwarps = kThreads / 32;
   __shared__ unsigned long long s_range[nwarps];  // published ranges: open to stealing
@@ -449,9 +502,13 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     uint32_t dyn;
     asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn));
-    if (base > kSmemG || base + dyn < kSmemEnd) {
+    if (base > kSmemP || base + dyn < kSmemEnd) {
       if (threadIdx.x == 0) *a.error_flag = 1;
       return;
+    }
+    if (kIndep) {  // the plain one-row tables (4 KiB, L2-resident), visible after the barrier both branches below end with
+      const uint32_t* gfold1 = &a.tables->fold[0][0];
+      for (uint32_t idx = threadIdx.x; idx < 1024; idx += kThreads) sts_u32(kSmemP + idx * 4u, __ldg(&gfold1[idx]));
     }
     if (a.table_image) {
       // bulk-async copies of the ready-made table image; nobody waits here
@@ -470,7 +527,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     } else {
       // Each thread fetches its table entries up front (coalesced, independent loads); the warp then
       // broadcasts entry by entry and every lane writes its own replica.
-      const uint32_t* gfold = &a.tables->fold[0][0];
+      const uint32_t* gfold = kIndep ? &a.tables->fold4[0][0] : &a.tables->fold[0][0];
       const uint32_t* gz4 = &a.tables->z4[0][0];
       constexpr uint32_t kPerWarp = 1024 / nwarps;  // fold entries per warp
       static_assert(1024 % nwarps == 0 && kPerWarp % 32 == 0, "fold table split");
@@ -794,7 +851,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
           pf_ptr = j.src + (size_t)(row_lo + G) * kRowBytes;
           pf_lines = ahead * (kRowBytes / 128u);
         }
-        crc = stream_rows<kCrc, G>(j.src, j.dst, rp, row_lo, lane, &row_end, tables_bar, gate);
+        crc = stream_rows<kCrc, G, kIndep>(j.src, j.dst, rp, row_lo, lane, &row_end, tables_bar, gate);
         rows_done = row_end - row_lo;
         end_byte = row_end * kRowBytes;
       } else {

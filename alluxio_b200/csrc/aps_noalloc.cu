@@ -95,11 +95,12 @@ int setup_device(int dev, PerDevice** out) {
     static CrcTables tables;
     static uint32_t rowshift[kMaxRows + 1];
     uint32_t xp[32], ls[32];
-    const uint32_t xrow = host_xpow8(kRowBytes), x4 = host_xpow8(4);
+    const uint32_t xrow = host_xpow8(kRowBytes), x4 = host_xpow8(4), xrow4 = host_xpow8(4 * kRowBytes);
     for (uint32_t j = 0; j < 4; ++j)
       for (uint32_t b = 0; b < 256; ++b) {
         tables.fold[j][b] = gf_mul(b << (8 * j), xrow);
         tables.z4[j][b] = gf_mul(b << (8 * j), x4);
+        tables.fold4[j][b] = gf_mul(b << (8 * j), xrow4);
       }
     rowshift[0] = 0x80000000u;
     for (uint32_t k = 1; k <= kMaxRows; ++k) rowshift[k] = gf_mul(rowshift[k - 1], xrow);
@@ -121,7 +122,7 @@ int setup_device(int dev, PerDevice** out) {
     int reserved = 0;
     if (cudaFuncGetAttributes(&fa, kKernel) != cudaSuccess) return APS_ECUDA;
     if (cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev) != cudaSuccess) return APS_ECUDA;
-    if (fa.sharedSizeBytes + (size_t)reserved > kSmemG) return APS_ECUDA;
+    if (fa.sharedSizeBytes + (size_t)reserved > kSmemP) return APS_ECUDA;
     // The set-up copies above ran on the legacy default stream; the caller's stream may be a non-blocking one that
     // does not order itself after it.  Wait here, once, so that the first call's kernels see the tables.
     if (cudaDeviceSynchronize() != cudaSuccess) return APS_ECUDA;
