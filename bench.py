@@ -428,6 +428,7 @@ def run_ours(args):
     # The request pool above was built on the CPU while the GPU sat idle; W warm-up steps are half a millisecond of work.
     # Keep the GPU busy for ~50 ms first (synthetic-page fills into the staging buffer: not a step, nothing of the
     # workload) so that the warm-up and the timed steps run at steady clocks whatever K is.
+    sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None))  # NVML set-up: before, not between
     warm_ids = owned[:BATCH]
     t_w = time.time()
     while time.time() - t_w < 0.05:
@@ -438,13 +439,14 @@ def run_ours(args):
     torch.cuda.synchronize(dev)
     if world > 1:
         dist.barrier()
-    # ---- parity of one FULL step (the last warm-up step): its 256 pages and results are copied to the host now and compared
-    # with the oracle right after the timed region (a second of CPU checking here would let the GPU clock down before timing)
+    # ---- parity of one FULL step (the last warm-up step): its 256 pages are set aside on the device now and compared with the
+    # oracle right after the timed region (host copies and a second of CPU checking here would let the GPU clock down)
     p_chk = W - 1
-    res_chk = d_res_all[p_chk * res_bytes:(p_chk + 1) * res_bytes].cpu().numpy().view(RESULT).copy()
-    got_chk = dst[(p_chk % N_DST) * BATCH * PAGE:(p_chk % N_DST + 1) * BATCH * PAGE].cpu().numpy()
+    d_got_chk = dst[(p_chk % N_DST) * BATCH * PAGE:(p_chk % N_DST + 1) * BATCH * PAGE].clone()  # device copy now, host copy later
 
     def check_full_step():
+        res_chk = d_res_all[p_chk * res_bytes:(p_chk + 1) * res_bytes].cpu().numpy().view(RESULT)
+        got_chk = d_got_chk.cpu().numpy()
         for i in range(BATCH):
             p = int(picks[p_chk, i])
             page = orc.fill_page(DATA_SEED, p // 1024, p % 1024, PAGE)
@@ -453,7 +455,6 @@ def run_ours(args):
             assert np.array_equal(got_chk[i * PAGE:(i + 1) * PAGE], page), "get bytes differ from oracle (request %d)" % i
         return BATCH
 
-    sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(dev), "uuid", None))
     sampler.start()
 
     # ---- timed region: device-resident batched get with fused CRC (value + roofline)
