@@ -837,7 +837,14 @@ int aps_lookup_batch_dev(aps_store* s, uint32_t n, const aps_key* d_keys, int32_
   if (!d_keys || !d_len) return APS_EINVAL;
   DeviceGuard g(s->cfg.device);
   cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-  lookup_kernel<<<(unsigned)(((uint64_t)n * kLookupLanes + kK1Threads - 1) / kK1Threads), kK1Threads, 0, st>>>(s->table, d_keys, n, d_len);
+  {
+    static const uint32_t per_group = [] { const char* e = getenv("APS_LOOKUP_PER_GROUP"); return e ? (uint32_t)std::max(1, atoi(e)) : kLookupPerGroup; }();
+    static const bool wide = [] { const char* e = getenv("APS_LOOKUP_256"); return e ? atoi(e) != 0 : true; }();
+    const uint64_t groups = ((uint64_t)n + per_group - 1) / per_group;  // keys per group of four lanes
+    const unsigned grid = (unsigned)std::max<uint64_t>(1, (groups * kLookupLanes + kK1Threads - 1) / kK1Threads);
+    if (wide) lookup_kernel<true><<<grid, kK1Threads, 0, st>>>(s->table, d_keys, n, d_len);
+    else lookup_kernel<false><<<grid, kK1Threads, 0, st>>>(s->table, d_keys, n, d_len);
+  }
   count_launch(s);
   CUDA_TRY(cudaGetLastError());
   return APS_OK;

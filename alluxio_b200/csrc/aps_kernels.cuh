@@ -1332,27 +1332,45 @@ __global__ void __launch_bounds__(kK1Threads) delete_kernel(Table t, const aps_k
 // so a key gets kLookupLanes lanes that read 8 / kLookupLanes entries each: the per-warp instruction stream (hash,
 // ballots, bookkeeping -- 65 % of the issue slots with eight lanes per key) is shared by more keys.
 constexpr uint32_t kLookupLanes = 4;
+constexpr uint32_t kLookupPerGroup = 8;  // keys a lane group handles one after the other (grid sizing)
+// Each group of four lanes walks a strided list of keys.  A lookup is two dependent DRAM round trips -- the key, then its
+// bucket -- so the next key is fetched while the current bucket is on its way (one exposed round trip per key instead of
+// two), and the counters are summed in registers and reach shared memory once per lane group instead of once per key.
+__device__ __forceinline__ void load_entry256(const Entry* e, uint64_t& k0, uint64_t& k1, uint64_t& k2, uint64_t& meta) {
+  asm volatile("ld.global.cg.v4.u64 {%0,%1,%2,%3}, [%4];" : "=l"(k0), "=l"(k1), "=l"(k2), "=l"(meta) : "l"(e));  // one 256-bit access
+}
+template <bool k256>
 __global__ void __launch_bounds__(kK1Threads) lookup_kernel(Table t, const aps_key* keys, uint32_t n, int32_t* len_out) {
   __shared__ BlockAcct acct;
   acct_init(acct);
   constexpr uint32_t L = kLookupLanes, E = kBucketEntries / L;
-  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t i = gid / L, sub = gid % L, gshift = (threadIdx.x & 31u) & ~(L - 1u), gmask = ((1u << L) - 1u) << gshift;
-  if (i < n) {
-    const aps_key key = keys[i];
+  const uint32_t sub = threadIdx.x % L, gshift = (threadIdx.x & 31u) & ~(L - 1u), gmask = ((1u << L) - 1u) << gshift;
+  const uint32_t groups = gridDim.x * (kK1Threads / L), group = blockIdx.x * (kK1Threads / L) + threadIdx.x / L;
+  uint32_t n_done = 0, n_buckets = 0;
+  aps_key key = group < n ? keys[group] : aps_key{0, 0, 0};
+  for (uint32_t i = group; i < n; i += groups) {
     uint64_t b = hash_key(key) & t.bucket_mask;
+    uint64_t k0[E], k1[E], k2[E], m[E];
+#pragma unroll
+    for (uint32_t q = 0; q < E; ++q) {
+      if (k256) load_entry256(t.entries + b * kBucketEntries + sub * E + q, k0[q], k1[q], k2[q], m[q]);
+      else load_entry(t.entries + b * kBucketEntries + sub * E + q, k0[q], k1[q], k2[q], m[q]);
+    }
+    const aps_key cur = key;
+    if (i + groups < n) key = keys[i + groups];  // in flight together with the bucket
     uint64_t found = 0;
     uint32_t nb = 0;
     for (uint64_t p = 0; p <= t.bucket_mask; ++p) {
-      uint64_t k0[E], k1[E], k2[E], m[E];
+      if (p) {  // beyond the home bucket (about one lookup in a hundred at load 0.5)
 #pragma unroll
-      for (uint32_t q = 0; q < E; ++q) load_entry(t.entries + b * kBucketEntries + sub * E + q, k0[q], k1[q], k2[q], m[q]);
+        for (uint32_t q = 0; q < E; ++q) load_entry(t.entries + b * kBucketEntries + sub * E + q, k0[q], k1[q], k2[q], m[q]);
+      }
       ++nb;
       uint64_t mine = 0;
       bool empty = false;
 #pragma unroll
       for (uint32_t q = 0; q < E; ++q) {
-        if ((m[q] >> 63) && k0[q] == key.file_hi && k1[q] == key.file_lo && k2[q] == key.page_index) mine = m[q];
+        if ((m[q] >> 63) && k0[q] == cur.file_hi && k1[q] == cur.file_lo && k2[q] == cur.page_index) mine = m[q];
         empty |= m[q] == kMetaEmpty;
       }
       const uint32_t bm = (__ballot_sync(gmask, mine != 0) >> gshift) & ((1u << L) - 1u);
@@ -1365,10 +1383,14 @@ __global__ void __launch_bounds__(kK1Threads) lookup_kernel(Table t, const aps_k
       b = (b + 1) & t.bucket_mask;
     }
     if (sub == 0) {
-      acct_add(acct, kCtrLookups, 1ull);
-      acct_add(acct, kCtrProbes, (unsigned long long)nb);
+      ++n_done;
+      n_buckets += nb;
       len_out[i] = found ? (int32_t)meta_len(found) : -1;
     }
+  }
+  if (sub == 0 && n_done) {
+    acct_add(acct, kCtrLookups, (unsigned long long)n_done);
+    acct_add(acct, kCtrProbes, (unsigned long long)n_buckets);
   }
   acct_flush(acct, t);
 }
