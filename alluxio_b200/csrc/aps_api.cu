@@ -582,6 +582,19 @@ int calibrate_sms(aps_store* s) {
   return APS_OK;
 }
 
+// The MD5 kernel stages 2 x 32 x 2 KiB in dynamic shared memory: opt in once per device.
+int md5_prepare(int device) {
+  static std::mutex mu;
+  static bool done[64] = {};
+  std::lock_guard<std::mutex> lk(mu);
+  if (device < 0 || device >= 64) return APS_EINVAL;
+  if (!done[device]) {
+    CUDA_TRY(cudaFuncSetAttribute(md5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMd5DynSmem));
+    done[device] = true;
+  }
+  return APS_OK;
+}
+
 __global__ void corrupt_kernel(Table t, aps_key key, uint32_t off, int* found) {
   const uint32_t sub = threadIdx.x & 7u;
   Probe pr = tile_lookup(t, key, sub, 0);
@@ -1803,7 +1816,8 @@ int aps_md5_batch_dev(int32_t device, uint32_t n_files, const void* const* d_dat
   if (!d_data || !d_len || !d_out) return APS_EINVAL;
   DeviceGuard g(device);
   if (!g.ok) return APS_ECUDA;
-  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, nullptr, nullptr, 1);
+  if (md5_prepare(device) != APS_OK) return APS_ECUDA;
+  md5_kernel<<<(n_files + 31) / 32, 32, kMd5DynSmem, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, nullptr, nullptr, 1);
   count_launch(nullptr);
   CUDA_TRY(cudaGetLastError());
   return APS_OK;
@@ -1816,7 +1830,8 @@ int aps_md5_stream_dev(int32_t device, uint32_t n_files, const void* const* d_da
   if (!d_data || !d_len || !d_state || (finalize && !d_out)) return APS_EINVAL;
   DeviceGuard g(device);
   if (!g.ok) return APS_ECUDA;
-  md5_kernel<<<(n_files + 31) / 32, 32, 0, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, d_state, d_prefix_len,
+  if (md5_prepare(device) != APS_OK) return APS_ECUDA;
+  md5_kernel<<<(n_files + 31) / 32, 32, kMd5DynSmem, (cudaStream_t)stream>>>(n_files, d_data, d_len, d_out, d_state, d_prefix_len,
                                                                     finalize);
   count_launch(nullptr);
   CUDA_TRY(cudaGetLastError());

@@ -1623,19 +1623,21 @@ __global__ void fill_pages_kernel(uint8_t* dst, uint64_t stride, uint32_t page_l
 // stages 512 bytes of each of its 32 files per step with 16-byte cp.async (coalesced per file) into
 // a padded shared tile (row stride 132 words, read back 128 bits at a time without bank conflicts).
 // ------------------------------------------------------------------------------------------------
-constexpr uint32_t kMd5Seg = 512;
-constexpr uint32_t kMd5RowWords = kMd5Seg / 4 + 4;  // 528-byte rows: 16-byte aligned, and a quarter-warp of
+constexpr uint32_t kMd5Seg = 2048;  // bytes of every file staged per step (round 1: 512; the staging loop is per step, so 4x fewer)
+constexpr uint32_t kMd5DynSmem = 2u * 32u * (kMd5Seg / 4 + 4) * 4u;  // two buffers of 32 rows (132 KiB): dynamic shared memory
+constexpr uint32_t kMd5RowWords = kMd5Seg / 4 + 4;  // rows of seg + 16 bytes: 16-byte aligned, and a quarter-warp of
                                                     // 128-bit reads (lane f at f*528) covers all 32 banks
 
 __device__ __forceinline__ uint32_t rotl32(uint32_t x, int s) { return __funnelshift_l(x, x, s); }
 
 // The chain through a step is b -> F(b,c,d) -> (+) -> rotate -> (+b).  a + m + k does not depend on the
 // previous step's result, so it is formed first and kept off that chain (3 dependent ops per step).
-#define APS_MD5_STEP(f, a, b, c, d, m, k, s)          \
-  do {                                                \
-    uint32_t pre_;                                    \
-    asm("add.u32 %0, %1, %2;" : "=r"(pre_) : "r"(a), "r"((m) + (k))); /* opaque: keeps the compiler from re-chaining it */ \
-    a = b + rotl32(f(b, c, d) + pre_, s);             \
+#define APS_MD5_STEP(f, a, b, c, d, m, k, s)                                                       \
+  do {                                                                                             \
+    uint32_t mk_, t_;                                                                              \
+    asm("add.u32 %0, %1, %2;" : "=r"(mk_) : "r"(m), "r"(k)); /* m + k: off the chain, kept apart */  \
+    asm("{\n\t.reg .u32 x;\n\tadd.u32 x, %1, %2;\n\tadd.u32 %0, x, %3;\n\t}" : "=r"(t_) : "r"(f(b, c, d)), "r"(a), "r"(mk_)); \
+    a = b + rotl32(t_, s);                                                                         \
   } while (0)
 #define APS_F1(b, c, d) ((d) ^ ((b) & ((c) ^ (d))))
 #define APS_F2(b, c, d) ((c) ^ ((d) & ((b) ^ (c))))
@@ -1693,7 +1695,8 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* const* data, const uint64_t* len,
                                                  uint8_t (*out)[16], uint32_t (*state)[4], const uint64_t* prefix,
                                                  int finalize) {
-  __shared__ __align__(16) uint32_t tile[2][32 * kMd5RowWords];
+  extern __shared__ __align__(16) uint32_t md5_tile[];
+  uint32_t(*tile)[32 * kMd5RowWords] = reinterpret_cast<uint32_t(*)[32 * kMd5RowWords]>(md5_tile);
   const uint32_t lane = threadIdx.x;
   const uint32_t file = blockIdx.x * 32 + lane;
   const bool have = file < n_files;
@@ -1720,7 +1723,9 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
       const bool fal = __shfl_sync(0xFFFFFFFFu, (int)my_aligned, f);
       if (fal && (seg + 1) * kMd5Seg <= flen) {
         const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(&tile[buf][f * kMd5RowWords]);
-        cp_async16(sbase + lane * 16, base + seg * kMd5Seg + lane * 16);
+#pragma unroll
+        for (uint32_t q = 0; q < kMd5Seg / 512u; ++q)
+          cp_async16(sbase + (q * 32u + lane) * 16u, base + seg * kMd5Seg + (q * 32u + lane) * 16u);
       }
     }
     cp_async_commit();
@@ -1734,19 +1739,29 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
     if (have && (seg + 1) * kMd5Seg <= my_len) {
       if (my_aligned) {
         const uint4* row = reinterpret_cast<const uint4*>(&tile[buf][lane * kMd5RowWords]);
-#pragma unroll 1
-        for (int blk = 0; blk < 8; ++blk) {
-          uint32_t m[16];
+        // the next block's sixteen words are read from shared memory while the current block's chain runs
+        uint32_t m[16], mn[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 v = row[blk * 4 + j];
-            m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+        for (int j = 0; j < 4; ++j) {
+          uint4 v = row[j];
+          m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+        }
+#pragma unroll 1
+        for (int blk = 0; blk < (int)(kMd5Seg / 64u); ++blk) {
+          if (blk + 1 < (int)(kMd5Seg / 64u)) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 v = row[(blk + 1) * 4 + j];
+              mn[4 * j] = v.x; mn[4 * j + 1] = v.y; mn[4 * j + 2] = v.z; mn[4 * j + 3] = v.w;
+            }
           }
           md5_block(h, m);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) m[j] = mn[j];
         }
       } else {
         const uint8_t* g = my + seg * kMd5Seg;
-        for (int blk = 0; blk < 8; ++blk) {
+        for (int blk = 0; blk < (int)(kMd5Seg / 64u); ++blk) {
           uint32_t m[16];
           for (int j = 0; j < 16; ++j) {
             const uint8_t* q = g + blk * 64 + j * 4;
@@ -1759,7 +1774,7 @@ __global__ void __launch_bounds__(32) md5_kernel(uint32_t n_files, const void* c
     __syncwarp();
   }
   if (!have) return;
-  // remainder (< 512 bytes) + padding, straight from global memory
+  // remainder (< one staged segment) + padding, straight from global memory
   uint64_t pos = (my_len / kMd5Seg) * kMd5Seg;
   while (pos + 64 <= my_len) {
     uint32_t m[16];

@@ -38,7 +38,7 @@ def main():
     ap.add_argument("--wave-mib", type=int, default=16)
     ap.add_argument("--check", type=int, default=-1, help="files verified against the oracle (-1 = all)")
     ap.add_argument("--md5sum-files", type=int, default=64, help="files also written to tmpfs and digested by md5sum")
-    ap.add_argument("--e2e-files", type=int, default=64, help="files of the end-to-end leg (pinned host -> digest)")
+    ap.add_argument("--e2e-files", type=int, default=4096, help="files of the end-to-end leg (pinned host -> digest), 1 MiB each")
     args = ap.parse_args()
     L = capi.lib()
     orc.build()
@@ -125,14 +125,17 @@ def main():
 
     # ---- end to end: files in PINNED HOST memory -> digests on the host (H2D copy + kernel + D2H of the digests timed)
     e2e = None
-    ke = min(args.e2e_files, n)
+    ke = args.e2e_files
     if ke:
-        hbuf = torch.empty(ke * wave, dtype=torch.uint8).pin_memory()
+        # as many chains as the main run, 1 MiB per file (a few files would measure one chain's ~0.14 GB/s, not the link)
+        esz = 1 << 20
+        hbuf = torch.empty(ke * esz, dtype=torch.uint8).pin_memory()
+        hnp = hbuf.numpy()
         for f in range(ke):
-            hbuf[f * wave:(f + 1) * wave] = torch.from_numpy(orc.fill_page(SEED, f, 0, wave))
-        dbuf = torch.empty(ke * wave, dtype=torch.uint8, device=dev)
-        eptrs = torch.from_numpy((dbuf.data_ptr() + np.arange(ke, dtype=np.int64) * wave)).to(dev)
-        elens = torch.full((ke,), wave, dtype=torch.int64, device=dev)
+            hnp[f * esz:(f + 1) * esz] = orc.fill_page(SEED, f, 7, esz)
+        dbuf = torch.empty(ke * esz, dtype=torch.uint8, device=dev)
+        eptrs = torch.from_numpy((dbuf.data_ptr() + np.arange(ke, dtype=np.int64) * esz)).to(dev)
+        elens = torch.full((ke,), esz, dtype=torch.int64, device=dev)
         eout = torch.zeros(ke * 16, dtype=torch.uint8, device=dev)
         hout = torch.zeros(ke * 16, dtype=torch.uint8).pin_memory()
 
@@ -147,15 +150,15 @@ def main():
         for _ in range(3):
             once()
         dt = (time.perf_counter() - t0) / 3
-        ok = all(hout.numpy().reshape(ke, 16)[f].tobytes() == orc.md5(orc.fill_page(SEED, f, 0, wave)) for f in (0, ke - 1))
-        e2e = {"value": round(ke * wave / dt / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": ke * wave, "d2h_bytes_per_step": ke * 16,
-               "files": ke, "file_mib": args.wave_mib, "digests_equal_oracle": bool(ok),
-               "note": "PCIe-bound: the files cross the link once; %d files of %d MiB per step" % (ke, args.wave_mib)}
+        ok = all(hout.numpy().reshape(ke, 16)[f].tobytes() == orc.md5(orc.fill_page(SEED, f, 7, esz)) for f in (0, ke // 2, ke - 1))
+        e2e = {"value": round(ke * esz / dt / 1e9, 2), "unit": "GB/s", "h2d_bytes_per_step": ke * esz, "d2h_bytes_per_step": ke * 16,
+               "files": ke, "file_mib": 1, "digests_equal_oracle": bool(ok),
+               "note": "PCIe-bound: the files cross the link once, then one kernel; %d files of 1 MiB in pinned host memory per step" % ke}
 
     gbps = total / (ms * 1e-3) / 1e9
     # the chain inside a file is serial: 64 steps per 64-byte block, each step 3 dependent integer operations
     cycles_per_step = n * (sm_mhz * 1e6) * (ms * 1e-3) / (total / 64 * 64)
-    model_cycles = 12.0  # 3 dependent ops x ~4 cycles of dependent-issue latency
+    model_cycles = 12.28  # the bare LOP3 -> IADD3 -> LEA.HI chain of one step on B200, measured (tools/micro/md5_chain_latency.cu)
     line = {
         "metric": "fs_checksum_md5_GBps", "value": round(gbps, 1), "unit": "GB/s", "n_gpus": 1,
         "config": {"workload": "%d files x %d MiB, one file per lane, %d waves of %d MiB per file (BASELINE configs[3])"
