@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(HERE, "libaps.so")
 (APS_OK, APS_ENOTFOUND, APS_EINVAL, APS_ENOSPC, APS_ECUDA, APS_ECORRUPT, APS_ECLOSED, APS_ENOMEM, APS_EFAULT,
  APS_ELIMIT, APS_EIO, APS_ETIMEOUT) = range(12)
 APS_NOALLOC_MAX_RANGES, APS_NOALLOC_MAX_LEN = 1024, 4 << 20
-APS_FLAG_CRC, APS_FLAG_TMA_COPY, APS_FLAG_STABLE_REQS, APS_FLAG_DEVICE_CLOCK = 1, 2, 4, 8
+APS_FLAG_CRC, APS_FLAG_STABLE_REQS, APS_FLAG_DEVICE_CLOCK = 1, 4, 8
 APS_FAULT_PUT, APS_FAULT_DELETE = 1, 2
 
 

@@ -251,7 +251,7 @@ struct aps_store {
   bool use_table_image = true;  // APS_NO_TABLE_IMAGE=1: build the shared-memory CRC tables with plain loads
   uint32_t prefetch_rows = 48;  // rows a waiting warp prefetches into L2 (APS_PF_ROWS overrides; 0/16/32/48/64/96 rows
                                 // measured 0.892/0.900/0.913/0.9175/0.9165/0.908 of the HBM peak)
-  bool use_tma = false;         // APS_FLAG_TMA_COPY on a store without CRC: the bulk-async form of the copy kernel
+  bool use_tma = false;         // (retired public flag) the bulk-async form of the copy kernel
   // what the store enqueued last: a get may start reading before its predecessor has finished only if that
   // predecessor was a get too (see launch_copy)
   bool last_was_get = false;
@@ -678,7 +678,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   s->use_early = getenv("APS_NO_EARLY") == nullptr;
   s->fused_put = getenv("APS_NO_FUSED_PUT") == nullptr;
   if (const char* pf = getenv("APS_PF_ROWS")) s->prefetch_rows = (uint32_t)std::min(256, std::max(0, atoi(pf)));
-  s->use_tma = (cfg->flags & APS_FLAG_TMA_COPY) != 0 && (cfg->flags & APS_FLAG_CRC) == 0;
+  s->use_tma = false;  // the public flag is retired (aps.h); APS_COPY_VARIANT=tma still selects the bulk-async kernel
   uint64_t slots = cfg->slab_slots;
   if (slots == 0) {
     uint64_t base = (cfg->cache_bytes + cfg->page_size - 1) / cfg->page_size;

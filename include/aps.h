@@ -62,7 +62,9 @@ typedef struct aps_key {
 } aps_key;
 
 #define APS_FLAG_CRC 1u        /* compute CRC32C inside every copy, record it at put, verify whole-page gets */
-#define APS_FLAG_TMA_COPY 2u   /* when CRC is off, move pages with bulk-async (TMA) copies instead of LDG/STG */
+/* (flag bit 2 is retired: it selected a bulk-async (TMA) form of the page copy, which measured slower than the 128-bit
+ * load/store path in every configuration -- DESIGN.md 4.2.  The kernel stays in the library as an experiment, reachable
+ * only through APS_COPY_VARIANT=tma; a store opened with the bit set ignores it.) */
 #define APS_FLAG_STABLE_REQS 4u /* a promise by the caller of the device forms: a request array is complete in HBM before
                                  * the call that uses it is enqueued (it is not produced by earlier work on the same
                                  * stream).  Back-to-back gets on one stream always overlap: a get resolves its pages and
