@@ -218,6 +218,7 @@ struct aps_store {
   Job* d_jobs = nullptr;
   uint32_t* d_acc = nullptr;
   uint32_t* d_rowshift = nullptr;  // x^(8*512*k) for k = 0 .. page_rows
+  uint32_t init_full = 0;          // 0xFFFFFFFF * x^(8 * page size)
   unsigned long long* d_timeline = nullptr;  // aps_debug_timeline
   uint32_t* d_sched = nullptr;               // CTA rank counters of the copy kernel (self-resetting)
   // sharded cache: tables of all shards (own + peers mapped over NVLink), see aps_shard_attach
@@ -327,6 +328,9 @@ int launch_copy(aps_store* s, uint32_t n, const aps_get_req* d_get_reqs, aps_res
   a.tables = s->dc->d_tables;
   a.table_image = s->use_table_image ? (v.group == 4 ? s->dc->d_table_image4 : s->dc->d_table_image) : nullptr;
   a.rowshift = s->d_rowshift;
+  a.init_full = s->init_full;
+  static const uint32_t dbg_flags = [] { const char* e = getenv("APS_COPY_FLAGS"); return e ? (uint32_t)atoi(e) : 0u; }();
+  a.serve_flags = dbg_flags;  // experiments: 4 = no short cut for a job done by one warp
   a.error_flag = s->h_error;
   a.timeline = s->d_timeline;
   a.steal = s->use_steal ? 1 : 0;
@@ -691,6 +695,7 @@ int aps_open(const aps_config* cfg, aps_store** out) {
   s->slots = slots;
   s->n_entries = entries;
   s->page_rows = (stride + kRowBytes - 1) / kRowBytes;
+  s->init_full = gf_mul(0xFFFFFFFFu, host_xpow8(cfg->page_size));
   const uint32_t mb = s->cfg.max_batch;
 
 #define OPEN_TRY(expr)                                                                                    \
@@ -1635,6 +1640,7 @@ int aps_get_batch_push_begin_dev(aps_store* s, uint32_t n, const aps_get_req* d_
   a.tables = s->dc->d_tables;
   a.table_image = s->use_table_image ? s->dc->d_table_image : nullptr;
   a.rowshift = s->d_rowshift;
+  a.init_full = s->init_full;
   a.error_flag = s->h_error;
   a.steal = s->use_steal ? 1 : 0;
   a.sched = p.d_sched;

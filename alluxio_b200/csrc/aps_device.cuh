@@ -217,6 +217,11 @@ __host__ __device__ __forceinline__ uint32_t gf_mul(uint32_t a, uint32_t b) {  /
   return r;
 }
 
+// The same product as a CALL: inlined, its 32 unrolled steps are ~130 instructions at every one of a dozen sites, which
+// made the copy kernel 135 KB of code -- more than the instruction cache holds, and a page-sized task walks through most
+// of it.  None of the sites is in the streaming loop.
+static __device__ __noinline__ uint32_t gf_mul_call(uint32_t a, uint32_t b) { return gf_mul(a, b); }
+
 // x^(8 * 2^k) mod P for k = 0..31 (filled by the host at load time)
 __constant__ uint32_t c_xpow8[32];
 // per-lane constant of the 512-byte row reduction: x^(8 * (500 - 16 * lane))
@@ -225,7 +230,7 @@ __constant__ uint32_t c_lane_shift[32];
 __device__ __forceinline__ uint32_t xpow8(uint32_t nbytes) {  // x^(8 * nbytes) mod P
   uint32_t r = 0x80000000u;                                    // x^0
   for (int k = 0; nbytes; ++k, nbytes >>= 1)
-    if (nbytes & 1u) r = gf_mul(r, c_xpow8[k]);
+    if (nbytes & 1u) r = gf_mul_call(r, c_xpow8[k]);
   return r;
 }
 

@@ -263,7 +263,7 @@ __device__ __forceinline__ uint32_t stream_rows(const uint8_t* src, uint8_t* dst
   }
   // lane words -> one register: t = Z4(Z4(Z4(S0)^S1)^S2)^S3, then shift to the end of the row
   uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
-  return warp_xor(gf_mul(t, c_lane_shift[lane]));
+  return warp_xor(gf_mul_call(t, c_lane_shift[lane]));
 }
 
 // Generic path (tails, unaligned requests): lane l takes the l-th contiguous slice, one byte at a
@@ -279,7 +279,7 @@ __device__ __forceinline__ uint32_t warp_bytes(const uint8_t* src, uint8_t* dst,
     if (kCrc) r = crc_byte_bitwise(r, b);
   }
   if (!kCrc) return 0;
-  return warp_xor(gf_mul(r, xpow8(n - hi)));
+  return warp_xor(gf_mul_call(r, xpow8(n - hi)));
 }
 
 constexpr uint32_t kMaxTasksPerJob = 128;
@@ -345,6 +345,7 @@ struct CopyArgs {
   uint32_t* sched;           // scratch: {fast CTAs ranked, slow CTAs ranked, CTAs arrived}; zero on entry, self-resetting
   const uint8_t* sm_slow;    // per SM id: 1 = this SM streams measurably slower than the median (calibrated at open)
   uint32_t n_slow;           // how many SMs that is
+  uint32_t init_full;        // 0xFFFFFFFF * x^(8 * page size): the init term of a full page's CRC (0 = compute it)
   const PushServe* push;     // kServe: the push transport's maps (device memory)
   uint32_t push_seq;         // kServe: which posting to serve
   uint32_t serve_rows;       // kServe: 512-byte rows of a full page ...
@@ -364,7 +365,7 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // x^(8 * nbytes) from the per-row table plus (ragged lengths only) the sub-row remainder
 __device__ __forceinline__ uint32_t shift_for(const uint32_t* rowshift, uint32_t nbytes) {
   uint32_t sh = __ldg(&rowshift[nbytes >> 9]);
-  if (nbytes & 511u) sh = gf_mul(sh, xpow8(nbytes & 511u));
+  if (nbytes & 511u) sh = gf_mul_call(sh, xpow8(nbytes & 511u));
   return sh;
 }
 
@@ -871,7 +872,8 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
       continue;
     }
     // shift the segment CRC to the end of the job and fold it into the job's accumulator
-    uint32_t contrib = rows_done ? gf_mul(crc, shift_for(a.rowshift, j.n - end_byte)) : 0u;
+    const uint32_t after = j.n - end_byte;  // bytes of the job behind this segment (0: nothing to shift over)
+    uint32_t contrib = rows_done ? (after ? gf_mul_call(crc, shift_for(a.rowshift, after)) : crc) : 0u;
     uint32_t units = rows_done;
     if (tail_mine) {  // the last n % 512 bytes: nothing follows them
       const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
@@ -880,22 +882,36 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     }
     const uint32_t target = (j.n + kRowBytes - 1) / kRowBytes;
     uint32_t prev = 0;
+    // A warp that did the WHOLE job by itself (small pages: one task per page, nothing stolen) holds the job's zero-init
+    // CRC already: no accumulator, no row count, none of their round trips to L2.  (Nobody else has rows of this job, so
+    // the job's accumulator and counter stay untouched at zero.)
+    // Measured (tools/bench_get_sizes.py, same box, A/B): 64 KiB pages 0.845 -> 0.866 of the HBM peak with the short cut,
+    // but 16 KiB pages 0.66 -> 0.60 and 4 KiB pages 0.33 -> 0.29 -- with nothing to wait for at the end of a page the warps
+    // of tiny pages run further ahead of the memory system, which serves them worse.  So: pages of 32 KiB and more only.
+    const bool whole = !kServe && row_lo == 0 && units == target && j.n >= 32768u && !(a.serve_flags & 4u);
     if (kServe && !(a.serve_flags & 1u)) {  // every lane's stores into the requester's memory are ordered before the row count that announces them
       __threadfence_system();
       __syncwarp();
     }
-    if (lane == 0) {
-      atomicXor(&a.acc[job], contrib);
-      __threadfence();
-      prev = atomicAdd(&a.done[job], units);
+    if (!whole) {
+      if (lane == 0) {
+        atomicXor(&a.acc[job], contrib);
+        __threadfence();
+        prev = atomicAdd(&a.done[job], units);
+      }
+      prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
+      if (prev + units != target) continue;
     }
-    prev = __shfl_sync(0xFFFFFFFFu, prev, 0);
-    if (prev + units != target) continue;
     aps_result fin{0, 0};
     if (lane == 0) {  // this segment completed the job
-      __threadfence();
-      const uint32_t x = atomicExch(&a.acc[job], 0u);
-      const uint32_t full = x ^ gf_mul(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
+      uint32_t x = contrib;
+      if (!whole) {
+        __threadfence();
+        x = atomicExch(&a.acc[job], 0u);
+        a.done[job] = 0;
+      }
+      const uint32_t init = (j.n == a.table.max_len && a.init_full) ? a.init_full : gf_mul_call(0xFFFFFFFFu, shift_for(a.rowshift, j.n));
+      const uint32_t full = x ^ init ^ 0xFFFFFFFFu;
       bool corrupt = false;
       if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
       if (j.flags & kJobOutCrc) a.crc_out[job] = full;
@@ -906,7 +922,6 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
       }
       fin = aps_result{corrupt ? -APS_ECORRUPT : (int32_t)j.n, full};
       if (!kServe && a.res) a.res[job] = fin;
-      a.done[job] = 0;
     }
     if (kServe) push_deliver(*a.push, a.push_seq, j.pad, fin, lane, srv_cnt);
   }
@@ -1180,7 +1195,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) tma_copy_kernel(CopyArgs a) {
           APS_FOLD_ROW(w);
         }
         const uint32_t t = z4_word(z4_word(z4_word(S0) ^ S1) ^ S2) ^ S3;
-        crc = warp_xor(gf_mul(t, c_lane_shift[lane]));
+        crc = warp_xor(gf_mul_call(t, c_lane_shift[lane]));
       }
     } else if (d.rows) {  // unaligned job: bytes straight from global memory
       crc = warp_bytes<kCrc>(j.src + byte_lo, j.dst ? j.dst + byte_lo : nullptr, d.rows * kRowBytes, lane);
@@ -1192,7 +1207,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) tma_copy_kernel(CopyArgs a) {
       mbar_arrive(bar_at + st * 16u + 8u);
     }
     uint32_t contrib = 0, units = d.rows;
-    if (kCrc && d.rows) contrib = gf_mul(crc, shift_for(a.rowshift, j.n - (uint32_t)(byte_lo + (size_t)d.rows * kRowBytes)));
+    if (kCrc && d.rows) contrib = gf_mul_call(crc, shift_for(a.rowshift, j.n - (uint32_t)(byte_lo + (size_t)d.rows * kRowBytes)));
     if (d.flags & kDescTail) {
       const uint32_t t0 = (j.n / kRowBytes) * kRowBytes;
       const uint32_t ct = warp_bytes<kCrc>(j.src + t0, j.dst ? j.dst + t0 : nullptr, j.n - t0, lane);
@@ -1208,7 +1223,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1) tma_copy_kernel(CopyArgs a) {
       if (prev + units == target) {
         __threadfence();
         const uint32_t x = atomicExch(&a.acc[job], 0u);
-        const uint32_t full = x ^ gf_mul(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
+        const uint32_t full = x ^ gf_mul_call(0xFFFFFFFFu, shift_for(a.rowshift, j.n)) ^ 0xFFFFFFFFu;
         bool corrupt = false;
         if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
         if (j.flags & kJobOutCrc) a.crc_out[job] = full;
