@@ -559,6 +559,11 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     __syncthreads();
   }
   if (!kServe && a.timeline && threadIdx.x == 0) a.timeline[blockIdx.x * 4 + 1] = globaltimer_ns();
+  uint32_t put_pages = 0, put_tombs_gone = 0;  // kPut: this warp's share of the store's counters (lane 0)
+  unsigned long long put_bytes = 0;             // (a two's complement sum: a replaced page may shrink)
+  uint32_t rec_early = 0;  // kGet: the recorded CRC of the page this warp resolved last (lane 0)
+  uint32_t cnt_lookups = 0, cnt_probes = 0;  // kGet: this warp's share of the store's counters (lane 0)
+  unsigned long long cnt_bytes = 0;
   uint32_t local = warp;  // this warp takes the CTA's fixed tasks local, local + nwarps, ...
   bool surplus_pending = warp == surplus_warp && extra > 0;
 
@@ -640,6 +645,8 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
             j.flags = (a.crc_on && rq.page_off == 0 && j.n == plen && plen > 0) ? kJobVerify : 0u;
             status = (int32_t)j.n;
             if (c == 0 && lane == 0 && tb.slot_ref) tb.slot_ref[j.slot] = 1;  // CLOCK: referenced (a store that commutes)
+            // the CRC recorded at put, asked for now and looked at when the page is done (same warp: see `whole`)
+            if (kCrc && !kServe && lane == 0 && (j.flags & kJobVerify)) rec_early = __ldcg(&tb.slot_crc[j.slot]);
           }
           if (dep_ok || a.trust_reqs) break;
           // Early, but the request array is not promised to be final yet (no APS_FLAG_STABLE_REQS): use what was read
@@ -661,9 +668,11 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
           rq = again;
         }
         if (c == 0 && lane == 0) {
-          atomicAdd(&a.table.counters[kCtrLookups], 1ull);
-          atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)pr.nbuckets);
-          if (j.n) atomicAdd(&a.table.counters[kCtrBytesCopied], (unsigned long long)j.n);
+          // counted in registers and added to the store's counters once per warp, at the end: three atomics per PAGE on
+          // the same three addresses serialise in L2 (65,536 pages of 4 KiB per step: ~60 us of a 265 us step)
+          ++cnt_lookups;
+          cnt_probes += pr.nbuckets;
+          cnt_bytes += (unsigned long long)j.n;
           report = !kCrc || j.n == 0;  // otherwise the finisher reports
           report_status = status;
         }
@@ -722,7 +731,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
                 slot = meta_slot(cl.was);
                 e->meta = meta_make(slot, rq.len);
                 if (t.slot_ref) t.slot_ref[slot] = 1;
-                atomicAdd(&t.counters[kCtrBytes], (unsigned long long)rq.len - (unsigned long long)meta_len(cl.was));
+                put_bytes += (unsigned long long)rq.len - (unsigned long long)meta_len(cl.was);
               } else {
                 const int idx = atomicSub(t.free_top, 1) - 1;
                 if (idx < 0) {
@@ -737,9 +746,9 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
                     t.slot_entry[slot] = cl.entry_idx;
                     t.slot_ref[slot] = 1;
                   }
-                  atomicAdd(&t.counters[kCtrPages], 1ull);
-                  atomicAdd(&t.counters[kCtrBytes], (unsigned long long)rq.len);
-                  if (cl.was == kMetaTomb) atomicAdd(&t.counters[kCtrTombs], ~0ull);
+                  ++put_pages;  // counted in registers, added once per warp at the end (see the get's counters)
+                  put_bytes += (unsigned long long)rq.len;
+                  if (cl.was == kMetaTomb) ++put_tombs_gone;
                 }
               }
             }
@@ -750,7 +759,7 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
           if (lane == 0) {
             if (!err) {
               if (rq.len == 0) t.slot_crc[slot] = 0;  // CRC32C of the empty string
-              else atomicAdd(&t.counters[kCtrBytesCopied], (unsigned long long)rq.len);
+              else cnt_bytes += (unsigned long long)rq.len;
             }
             __threadfence();
             *(volatile unsigned long long*)&a.jslot[job] = word;
@@ -885,10 +894,10 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     // A warp that did the WHOLE job by itself (small pages: one task per page, nothing stolen) holds the job's zero-init
     // CRC already: no accumulator, no row count, none of their round trips to L2.  (Nobody else has rows of this job, so
     // the job's accumulator and counter stay untouched at zero.)
-    // Measured (tools/bench_get_sizes.py, same box, A/B): 64 KiB pages 0.845 -> 0.866 of the HBM peak with the short cut,
-    // but 16 KiB pages 0.66 -> 0.60 and 4 KiB pages 0.33 -> 0.29 -- with nothing to wait for at the end of a page the warps
-    // of tiny pages run further ahead of the memory system, which serves them worse.  So: pages of 32 KiB and more only.
-    const bool whole = !kServe && row_lo == 0 && units == target && j.n >= 32768u && !(a.serve_flags & 4u);
+    // Measured (tools/bench_get_sizes.py, A/B on one box, fractions of the HBM peak): 64 KiB pages 0.845 -> 0.866, 16 KiB 0.70 ->
+    // 0.77, 4 KiB 0.34 -> 0.45 -- once the per-page counter atomics were gone (with them, small pages got SLOWER with the
+    // short cut: warps with nothing to wait for at the end of a page queued up behind the same three addresses in L2).
+    const bool whole = !kServe && row_lo == 0 && units == target && !(a.serve_flags & 4u);
     if (kServe && !(a.serve_flags & 1u)) {  // every lane's stores into the requester's memory are ordered before the row count that announces them
       __threadfence_system();
       __syncwarp();
@@ -916,7 +925,8 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
       if (j.flags & kJobRecord) a.table.slot_crc[j.slot] = full;
       if (j.flags & kJobOutCrc) a.crc_out[job] = full;
       const uint32_t* recorded = (kGet && !kServe && j.pad) ? a.shards[j.pad - 1u].slot_crc : a.table.slot_crc;
-      if ((j.flags & kJobVerify) && __ldcg(&recorded[j.slot]) != full) {
+      // (a page done by the warp that resolved it compares with the value that warp asked for at the start)
+      if ((j.flags & kJobVerify) && ((kGet && !kServe && whole) ? rec_early : __ldcg(&recorded[j.slot])) != full) {
         corrupt = true;
         atomicAdd(&a.table.counters[kCtrCrcMismatch], 1ull);
       }
@@ -926,6 +936,17 @@ __global__ void __launch_bounds__(kServe ? 640 : kThreads, 1) copy_kernel(CopyAr
     if (kServe) push_deliver(*a.push, a.push_seq, j.pad, fin, lane, srv_cnt);
   }
   gate();  // a warp that found nothing to do arrives here without having waited
+  if (kPut && lane == 0) {
+    if (put_pages) atomicAdd(&a.table.counters[kCtrPages], (unsigned long long)put_pages);
+    if (put_bytes) atomicAdd(&a.table.counters[kCtrBytes], put_bytes);
+    if (put_tombs_gone) atomicAdd(&a.table.counters[kCtrTombs], 0ull - (unsigned long long)put_tombs_gone);
+    if (cnt_bytes) atomicAdd(&a.table.counters[kCtrBytesCopied], cnt_bytes);
+  }
+  if (kGet && lane == 0 && cnt_lookups) {
+    atomicAdd(&a.table.counters[kCtrLookups], (unsigned long long)cnt_lookups);
+    atomicAdd(&a.table.counters[kCtrProbes], (unsigned long long)cnt_probes);
+    if (cnt_bytes) atomicAdd(&a.table.counters[kCtrBytesCopied], cnt_bytes);
+  }
   if (kServe) {
     // a requester that asked this owner for nothing still waits for its done word (behind the gate: the previous round's
     // serve kernel has finished, so done words go up in round order)
