@@ -110,6 +110,7 @@ SIGNATURES = {
     "aps_debug_corrupt": (C.c_int, [_vp, C.POINTER(aps_key), _u32]),
     "aps_debug_timeline": (C.c_int, [_vp, C.c_int, _vp, _u32]),
     "aps_debug_crc_constants": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "aps_debug_crc_fold4": (C.c_int, [_vp]),
     "aps_strerror": (C.c_char_p, [C.c_int]),
     "aps_last_cuda_error": (C.c_char_p, []),
     "aps_version": (C.c_char_p, []),

@@ -631,6 +631,11 @@ int aps_debug_crc_constants(uint32_t* fold, uint32_t* z4, uint32_t* xpow8_out, u
   if (lane_shift) memcpy(lane_shift, h.lane_shift, sizeof(h.lane_shift));
   return APS_OK;
 }
+int aps_debug_crc_fold4(uint32_t* fold4) {
+  if (!fold4) return APS_EINVAL;
+  memcpy(fold4, host_crc_consts().tables.fold4, sizeof(host_crc_consts().tables.fold4));
+  return APS_OK;
+}
 const char* aps_last_cuda_error(void) { return tl_cuda_error; }
 uint64_t aps_total_kernel_launches(void) { return g_launches.load(); }
 

@@ -376,6 +376,8 @@ APS_API int aps_debug_corrupt(aps_store* s, const aps_key* key, uint32_t byte_of
  * fold[4][256] (x^(8*512) per byte lane), z4[4][256] (x^32), xpow8[32] (x^(8*2^k)) and
  * lane_shift[32].  tests/test_crc_algebra.py replays the kernel's arithmetic with them on the CPU. */
 APS_API int aps_debug_crc_constants(uint32_t* fold, uint32_t* z4, uint32_t* xpow8, uint32_t* lane_shift);
+/* The same for fold4[4][256] (x^(8*512*4)): the tables of the kernels that fold the four rows of a group independently. */
+APS_API int aps_debug_crc_fold4(uint32_t* fold4);
 
 APS_API const char* aps_strerror(int code);
 APS_API const char* aps_last_cuda_error(void); /* thread-local text of the last failed CUDA call */

@@ -151,3 +151,53 @@ def test_known_answers_through_kernel_arithmetic(consts):
     assert kernel_crc(np.zeros(32, np.uint8), consts) == 0x8A9136AA
     assert kernel_crc(np.full(32, 0xFF, np.uint8), consts) == 0x62A8AB43
     assert kernel_crc(np.arange(32, dtype=np.uint8), consts) == 0x46DD794E
+
+
+def warp_rows_independent(data, consts, fold4, group=4):
+    """stream_rows with kIndep: row u of every group of four goes into its own state, carried forward by a whole group
+    (tables x^(8*512*4)); the states are merged -- Horner with the one-row tables -- at the end of the segment, or just
+    before a last, incomplete group, whose rows then go through the one-row tables."""
+    fold, z4, xp, ls = consts
+    rows = data.size // ROW
+    w = data[:rows * ROW].view("<u4").reshape(rows, 32, 4)
+    chains = [np.zeros((32, 4), np.uint32) for _ in range(group)]
+    merged = None
+    r = 0
+    while r < rows:
+        cnt = min(group, rows - r)
+        if cnt == group:
+            for u in range(group):
+                chains[u] = apply4(fold4, chains[u]) ^ w[r + u]
+        else:
+            merged = chains[0]
+            for u in range(1, group):
+                merged = apply4(fold, merged) ^ chains[u]
+            for u in range(cnt):
+                merged = apply4(fold, merged) ^ w[r + u]
+        r += cnt
+    if merged is None:
+        merged = chains[0]
+        for u in range(1, group):
+            merged = apply4(fold, merged) ^ chains[u]
+    S = merged
+    t = apply4(z4, apply4(z4, apply4(z4, S[:, 0]) ^ S[:, 1]) ^ S[:, 2]) ^ S[:, 3]
+    acc = 0
+    for lane in range(32):
+        acc ^= gf_mul(int(t[lane]), int(ls[lane]))
+    return acc
+
+
+def test_four_independent_states_equal_the_serial_fold(consts):
+    fold4 = np.zeros((4, 256), np.uint32)
+    capi.check(capi.lib().aps_debug_crc_fold4(fold4.ctypes.data))
+    xp = consts[2]
+    for j in range(4):
+        for b in (1, 0x5A, 0xFF):
+            assert int(fold4[j][b]) == gf_mul((b << (8 * j)) & 0xFFFFFFFF, xpow8(4 * 512, xp))
+    rng = np.random.default_rng(4)
+    for rows in (1, 2, 3, 4, 5, 7, 8, 9, 31, 32, 33, 128):
+        data = rng.integers(0, 256, rows * ROW, dtype=np.uint8)
+        got = warp_rows_independent(data, consts, fold4)
+        assert got == warp_rows(data, consts), rows
+        # zero-init CRC of the rows -> the real CRC32C through init / xorout
+        assert got ^ gf_mul(0xFFFFFFFF, xpow8(data.size, xp)) ^ 0xFFFFFFFF == orc.crc32c(data), rows

@@ -179,6 +179,17 @@ def test_get_more_than_stored_returns_minus_one_and_drops_page(env):
     assert env.mgr.get(pid, 100, bytearray(100)) == 0
 
 
+def test_get_of_zero_bytes_returns_minus_one_and_drops_page(env):
+    """LocalCacheManager.get: getPage returns bytesToRead (0), get treats bytesRead <= 0 as a failed read, removes the page
+    from the meta store and returns -1 (CACHE/LocalCacheManager.java:383-395, 540-555).  The page store keeps the file."""
+    assert env.mgr.put(PAGE_ID1, PAGE1)
+    assert env.mgr.get(PAGE_ID1, 0, env.buf) == -1
+    assert env.mgr.pages() == 0 and env.mgr.bytes() == 0
+    assert env.mgr.get(PAGE_ID1, len(PAGE1), env.buf) == 0      # a miss now
+    assert env.mgr.put(PAGE_ID1, PAGE2)                          # re-admitted; the store's file is overwritten
+    assert env.mgr.get(PAGE_ID1, len(PAGE2), env.buf) == len(PAGE2) and bytes(env.buf) == PAGE2
+
+
 def test_delete(env):
     assert not env.mgr.delete(PAGE_ID1)
     env.mgr.put(PAGE_ID1, PAGE1)
