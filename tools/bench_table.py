@@ -125,6 +125,18 @@ def main():
     final = [gu.to_dev(keys_of(resident[rng.permutation(n)[:nb]]))]
     timed(do_lookup, final)
     ok_final = int((lens == page).sum().item())
+    # the table side of an insert alone: empty pages (nothing to copy), fresh ids into the places of a deleted batch
+    ms_ins0 = 0.0
+    for r in range(args.reps):
+        pick = rng.permutation(n)[:nb]
+        timed(do_delete, [gu.to_dev(keys_of(resident[pick]))])
+        new = np.arange(fresh, fresh + nb, dtype=np.uint64)
+        fresh += nb
+        rq = np.zeros(nb, dtype=gu.PUT_REQ)
+        rq["file_lo"], rq["page_index"], rq["len"] = new // 1000, new % 1000, 0
+        rq["src"] = src.data_ptr()
+        ms_ins0 += timed(do_put, [gu.to_dev(rq)])
+        resident[pick] = new
     launches = int(L.aps_total_kernel_launches() - launches0)
     L.aps_close(st)
 
@@ -140,6 +152,9 @@ def main():
         "lookup_hit_Mops": mops(nb * args.reps, ms_hit), "lookup_miss_Mops": mops(nb * args.reps, ms_miss),
         "insert_populate_Mops": mops(n, ms_pop), "insert_churn_Mops": mops(nb * args.reps, ms_ins),
         "erase_Mops": mops(nb * args.reps, ms_del),
+        "insert_empty_pages_Mops": mops(nb * args.reps, ms_ins0),
+        "insert_note": "insert_* put 16-byte pages, so they include a copy-kernel pass in which a whole warp moves 16 bytes; "
+                       "insert_empty_pages is the table side alone (claim an entry, pop a slot, publish)",
         "buckets_per_hit": round(bph, 4), "buckets_per_miss": round(bpm, 4),
         "tombstones_after_churn": int(s3.tombstones), "pages_after_churn": int(s3.pages),
         "checks": {"hits_found": ok_hit == nb, "misses_absent": ok_miss == nb, "resident_after_churn_found": ok_final == nb,
