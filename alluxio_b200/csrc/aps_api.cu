@@ -241,7 +241,6 @@ struct aps_store {
   bool d2h_stage_failed = false;
   cudaStream_t copy_stream = nullptr;  // the copy engine's stream for staged host-destination gets
   cudaEvent_t chunk_ev[8] = {};
-  std::vector<std::pair<const void*, int>> ptr_kind;  // host_ptr_kind's memo
   bool use_d2h_stage = true;       // APS_NO_D2H_STAGE=1: let the kernel store into host memory directly
   uint32_t faults = 0;
   bool use_pdl = true;    // APS_NO_PDL=1 turns programmatic dependent launch off
@@ -900,19 +899,15 @@ int aps_get_batch_sharded(aps_store* s, uint32_t n, const aps_get_req* reqs, aps
   return get_batch_host(s, n, reqs, res, stream, true);
 }
 
-// What kind of memory is `p`?  Asked once per distinct pointer (a reader hands the same few buffers back again and
-// again); the driver call costs microseconds that the batched path does not have to spare.
+// What kind of memory is `p`?  Asked on every call: a memo keyed by address would go stale when the caller frees a
+// pinned buffer and the allocator hands the same address out again as pageable memory (a kernel would then write to
+// memory it cannot reach); the driver call costs about a microsecond of a call that moves megabytes.
 enum PtrKind { kPtrDevice = 0, kPtrPinned = 1, kPtrPageable = 2 };  // device / managed; page-locked host; plain host
-static int host_ptr_kind(aps_store* s, const void* p) {
-  for (const auto& e : s->ptr_kind)
-    if (e.first == p) return e.second;
+static int host_ptr_kind(aps_store*, const void* p) {
   cudaPointerAttributes at{};
   if (cudaPointerGetAttributes(&at, p) != cudaSuccess) cudaGetLastError();
-  const int kind = at.type == cudaMemoryTypeHost ? kPtrPinned
-                   : (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) ? kPtrDevice : kPtrPageable;
-  if (s->ptr_kind.size() >= 16) s->ptr_kind.erase(s->ptr_kind.begin());
-  s->ptr_kind.emplace_back(p, kind);
-  return kind;
+  return at.type == cudaMemoryTypeHost ? kPtrPinned
+         : (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) ? kPtrDevice : kPtrPageable;
 }
 
 // The HBM staging area of the host-array batched calls (one slot per request of the largest batch one call serves),

@@ -743,8 +743,9 @@ def run_ours(args):
         "e2e": {"value": round(e2e_gbps, 2), "unit": UNIT,
                 "h2d_bytes_per_step": BATCH * GET_REQ.itemsize, "d2h_bytes_per_step": step_bytes + BATCH * RESULT.itemsize,
                 "steps": e2e_steps,
-                "path": "aps_get_batch: host request arrays -> pinned host destinations (PCIe-bound; gathered in HBM by the fused "
-                        "kernel in chunks while the copy engine moves the previous chunk)",
+                "path": ("aps_get_batch" if world == 1 else "aps_get_batch_sharded (requester-side kernel reads the owners' slabs)") +
+                        ": host request arrays -> pinned host destinations (PCIe-bound; gathered in HBM by the fused kernel in two "
+                        "pieces, the copy engine moving the first while the second is gathered)",
                 "host_d2h_ceiling_GBps": None if pcie_gbps is None else round(world * pcie_gbps, 2),
                 "host_d2h_ceiling_note": "plain cudaMemcpyAsync of 256 MiB HBM -> pinned host, all ranks at once (barrier), aggregate",
                 "frac_of_host_d2h_ceiling": None if pcie_gbps is None else round(e2e_gbps / (world * pcie_gbps), 4)},
