@@ -364,19 +364,45 @@ def run_ours(args):
         for i, bl in enumerate(blobs):
             C.memmove(C.addressof(arr[i]), bl, 256)
         capi.check(L.aps_shard_attach(h, world, rank, arr), "shard_attach")
+
+    def all_ranks_ok(ok):
+        t = torch.tensor([1 if ok else 0], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    dst = None
     if transport == "push":
-        capi.check(L.aps_push_setup(h, dst_bytes, depth), "push_setup")
+        # set-up is collective; if it fails on any rank (e.g. no room for the landing buffer) every rank falls back to the
+        # pull form, and the line says which transport ran
         ph = capi.aps_push_handle()
-        capi.check(L.aps_push_export(h, C.byref(ph)), "push_export")
-        blobs = [None] * world
-        dist.all_gather_object(blobs, bytes(ph.opaque))
-        parr = (capi.aps_push_handle * world)()
-        for i, bl in enumerate(blobs):
-            C.memmove(C.addressof(parr[i]), bl, 192)
-        capi.check(L.aps_push_attach(h, world, rank, parr), "push_attach")
-        nb = C.c_uint64()
-        dst = raw_tensor(L.aps_push_landing(h, C.byref(nb)), dst_bytes, dev)
-    else:
+        try:
+            capi.check(L.aps_push_setup(h, dst_bytes, depth), "push_setup")
+            capi.check(L.aps_push_export(h, C.byref(ph)), "push_export")
+            ok = True
+        except Exception as e:  # noqa: BLE001
+            print("bench.py: push transport unavailable on rank %d: %r" % (rank, e), file=sys.stderr)
+            ok = False
+        if all_ranks_ok(ok):
+            blobs = [None] * world
+            dist.all_gather_object(blobs, bytes(ph.opaque))
+            parr = (capi.aps_push_handle * world)()
+            for i, bl in enumerate(blobs):
+                C.memmove(C.addressof(parr[i]), bl, 192)
+            try:
+                capi.check(L.aps_push_attach(h, world, rank, parr), "push_attach")
+                ok = True
+            except Exception as e:  # noqa: BLE001
+                print("bench.py: push attach failed on rank %d: %r" % (rank, e), file=sys.stderr)
+                ok = False
+            ok = all_ranks_ok(ok)
+        else:
+            ok = False
+        if ok:
+            nb = C.c_uint64()
+            dst = raw_tensor(L.aps_push_landing(h, C.byref(nb)), dst_bytes, dev)
+        else:
+            transport, depth = "pull", 1
+    if dst is None:
         dst = torch.empty(dst_bytes, dtype=torch.uint8, device=dev)
     if world > 1:
         dist.barrier()
