@@ -136,13 +136,16 @@ def run_reference(args):
     steps, warmup = max(1, min(args.steps, 256)), min(args.warmup, 5)
     dirs = cpu_dirs()
     results = {}
+    head = None  # the timed steps run on the first directory that works (tmpfs when the box has one)
     for label, base, kind in dirs:
         try:
-            results[label] = cpu_config0(base, [threads, 1], step_gets=BATCH, steps=steps if label == dirs[0][0] else 0, warmup=warmup)
+            results[label] = cpu_config0(base, [threads, 1], step_gets=BATCH, steps=0 if head else steps, warmup=warmup)
             results[label]["dir"], results[label]["fs"] = base, kind
+            head = head or results[label]
         except Exception as e:  # noqa: BLE001
             results[label] = {"unavailable": repr(e)[:200], "dir": base, "fs": kind}
-    head = results[dirs[0][0]]
+    if head is None:
+        raise SystemExit("reference arm: no writable directory could hold the file set: %r" % (results,))
     gbps, ms = head["steps"]
     desc = ("%d steps of %d uniform random whole-page gets over BASELINE configs[0]'s file set (%d files x %d pages of 1 MiB = "
             "%.0f GiB under %s [%s], resident in the OS page cache: the reference's best case), %d threads"
@@ -165,8 +168,6 @@ def run_reference(args):
     print(json.dumps(line))
     return 0
 
-
-# ------------------------------------------------------------------------------------------------ clocks
 
 # ------------------------------------------------------------------------------------------------ clocks
 
