@@ -13,13 +13,13 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force=False):
-    """Compile the restatement with the committed Makefile."""
-    if force or not os.path.exists(_LIB_PATH):
-        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    """Compile the restatement with the committed Makefile (make rebuilds what is older than its sources)."""
+    subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
     return _LIB_PATH
 
 
 _lib = None
+EXTERNAL_READ = C.CFUNCTYPE(C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int32)
 
 
 def lib():
@@ -71,6 +71,16 @@ def lib():
             "orc_manager_page_lock_id": (i32, [vp, cp, i64]),
             "orc_manager_bytes": (i64, [vp]),
             "orc_manager_pages": (i64, [vp]),
+            "orc_stream_open": (vp, [vp, cp, i64, i64, EXTERNAL_READ, vp]),
+            "orc_stream_destroy": (None, [vp]),
+            "orc_stream_read": (i32, [vp, vp, i32, i32, i32]),
+            "orc_stream_positioned_read": (i32, [vp, i64, vp, i32, i32, i32]),
+            "orc_stream_skip": (i64, [vp, i64]),
+            "orc_stream_seek": (C.c_int, [vp, i64]),
+            "orc_stream_remaining": (i64, [vp]),
+            "orc_stream_get_pos": (i64, [vp]),
+            "orc_stream_close": (None, [vp]),
+            "orc_stream_counters": (None, [vp, vp]),
             "orc_replay": (i64, [cp, dbl, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), C.POINTER(i64)]),
             "orc_fill_page": (None, [u64, u64, u64, vp, i64]),
             "orc_bench_local_get": (dbl, [cp, i64, i64, i64, C.c_int, i64, u64, u64, i32, C.c_int, C.POINTER(i64)]),
@@ -362,6 +372,82 @@ class LocalCacheManager:
 
     def pages(self):
         return lib().orc_manager_pages(self._h)
+
+
+class LocalCacheFileInStream:
+    """CACHE/LocalCacheFileInStream.java:37-336 over an oracle LocalCacheManager.  `external(pos, n) -> bytes` stands
+    for the external FileInStream (it may return fewer than n bytes; b"" ends the page read).  Exceptions as in the
+    Python mirror of the product: ValueError = IllegalArgumentException, IOError = IOException, RuntimeError =
+    IllegalStateException (closed stream)."""
+
+    def __init__(self, manager, file_id, file_len, external, page_size):
+        def ext(user, file_pos, dst, n):
+            data = external(file_pos, n)
+            C.memmove(dst, data, len(data))
+            return len(data)
+
+        self._manager = manager
+        self._cb = EXTERNAL_READ(ext)
+        self._h = lib().orc_stream_open(manager._h, str(file_id).encode(), file_len, page_size, self._cb, None)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_stream_destroy(self._h)
+            self._h = None
+
+    @staticmethod
+    def _result(r):
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        if r == -3:
+            raise IOError("IOException")
+        return r
+
+    def read(self, b, off=0, length=None):
+        length = len(b) - off if length is None else length
+        cbuf = (C.c_uint8 * max(1, len(b))).from_buffer(b) if len(b) else (C.c_uint8 * 1)()
+        r = lib().orc_stream_read(self._h, C.addressof(cbuf), len(b), off, length)
+        del cbuf
+        return self._result(r)
+
+    def read_byte(self):
+        """int read(): CACHE/LocalCacheFileInStream.java:96-103."""
+        one = bytearray(1)
+        return -1 if self.read(one) == -1 else one[0]
+
+    def positioned_read(self, pos, b, off=0, length=None):
+        length = len(b) - off if length is None else length
+        cbuf = (C.c_uint8 * max(1, len(b))).from_buffer(b) if len(b) else (C.c_uint8 * 1)()
+        r = lib().orc_stream_positioned_read(self._h, pos, C.addressof(cbuf), len(b), off, length)
+        del cbuf
+        return self._result(r)
+
+    def skip(self, n):
+        r = lib().orc_stream_skip(self._h, n)
+        if r == -4:
+            raise RuntimeError("Cannot operate on a closed stream")
+        return r
+
+    def seek(self, pos):
+        r = lib().orc_stream_seek(self._h, pos)
+        if r == -2:
+            raise ValueError("IllegalArgumentException")
+        if r == -4:
+            raise RuntimeError("Cannot operate on a closed stream")
+
+    def remaining(self):
+        return lib().orc_stream_remaining(self._h)
+
+    def get_pos(self):
+        return lib().orc_stream_get_pos(self._h)
+
+    def close(self):
+        lib().orc_stream_close(self._h)
+
+    def counters(self):
+        v = (C.c_int64 * 4)()
+        lib().orc_stream_counters(self._h, v)
+        return dict(zip(("BytesReadCache", "BytesRequestedExternal", "BytesReadExternal", "ExternalReadCalls"), list(v)))
 
 
 def replay(evictor, page_size, cache_size, files, pages, page_lens, lfu_logbase=2.0, victims_cap=None):

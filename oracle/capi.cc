@@ -118,6 +118,36 @@ int32_t orc_manager_page_lock_id(void* m, const char* f, int64_t i) {
 int64_t orc_manager_bytes(void* m) { return ((LocalCacheManager*)m)->meta()->Bytes(); }
 int64_t orc_manager_pages(void* m) { return ((LocalCacheManager*)m)->meta()->Pages(); }
 
+// ---------------------------------------------------------------- stream (CACHE/LocalCacheFileInStream.java)
+// external(user, pos, dst, len) -> bytes read stands for the external FileInStream.
+typedef int32_t (*orc_external_read)(void* user, int64_t pos, uint8_t* dst, int32_t len);
+void* orc_stream_open(void* m, const char* file_id, int64_t file_length, int64_t page_size, orc_external_read external,
+                      void* user) {
+  return new LocalCacheFileInStream(file_id, file_length, page_size, (LocalCacheManager*)m,
+                                    [external, user](int64_t pos, uint8_t* dst, int32_t len) { return external(user, pos, dst, len); });
+}
+void orc_stream_destroy(void* s) { delete (LocalCacheFileInStream*)s; }
+// bytes read; -1 end of file; -2 IllegalArgumentException; -3 IOException
+int32_t orc_stream_read(void* s, uint8_t* b, int32_t b_len, int32_t off, int32_t len) {
+  return ((LocalCacheFileInStream*)s)->Read(b, b_len, off, len);
+}
+int32_t orc_stream_positioned_read(void* s, int64_t pos, uint8_t* b, int32_t b_len, int32_t off, int32_t len) {
+  return ((LocalCacheFileInStream*)s)->PositionedRead(pos, b, b_len, off, len);
+}
+int64_t orc_stream_skip(void* s, int64_t n) { return ((LocalCacheFileInStream*)s)->Skip(n); }  // -4 closed
+int orc_stream_seek(void* s, int64_t pos) { return ((LocalCacheFileInStream*)s)->Seek(pos); }  // 0, -2, -4 closed
+int64_t orc_stream_remaining(void* s) { return ((LocalCacheFileInStream*)s)->Remaining(); }
+int64_t orc_stream_get_pos(void* s) { return ((LocalCacheFileInStream*)s)->GetPos(); }
+void orc_stream_close(void* s) { ((LocalCacheFileInStream*)s)->Close(); }
+// out[0..3] = bytes read from the cache, bytes requested from external, bytes read from external, external read calls
+void orc_stream_counters(void* s, int64_t* out) {
+  auto* st = (LocalCacheFileInStream*)s;
+  out[0] = st->bytesReadCache;
+  out[1] = st->bytesRequestedExternal;
+  out[2] = st->bytesReadExternal;
+  out[3] = st->externalReads;
+}
+
 // ---------------------------------------------------------------- trace replay (BASELINE config 3)
 // Runs the reference read flow for each access: CacheManager.get; on a miss (0) the caller reads
 // the page externally and calls CacheManager.put (CACHE/LocalCacheFileInStream.java:121-143).

@@ -7,6 +7,7 @@
 #include <sys/types.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <cerrno>
 #include <cmath>
 #include <cstring>
@@ -622,6 +623,103 @@ bool LocalCacheManager::Restore() {  // :466-509
     else if (mPageStore->Delete(info.pageId) != kOk) return false;  // :493-497 (exception -> false)
   }
   return true;
+}
+
+// ================================================================================================
+// CACHE/LocalCacheFileInStream.java
+// ================================================================================================
+
+LocalCacheFileInStream::LocalCacheFileInStream(const std::string& fileId, int64_t fileLength, int64_t pageSize,
+                                               LocalCacheManager* manager, ExternalRead external)  // :83-93
+    : mFileId(fileId), mLength(fileLength), mPageSize(pageSize), mCacheManager(manager), mExternal(std::move(external)) {}
+
+// :291-310.  getExternalFileInStream (:256-270) opens the external stream once and seeks it to the start of
+// the page when it is not there already; the callback takes the position instead.
+bool LocalCacheFileInStream::ReadExternalPage(int64_t pos, std::vector<uint8_t>* page) {
+  const int64_t pageStart = pos - (pos % mPageSize);                                     // :292
+  const int32_t pageSize = (int32_t)std::min<int64_t>(mPageSize, mLength - pageStart);   // :294
+  page->assign((size_t)pageSize, 0);                                                     // :295
+  int32_t totalBytesRead = 0;
+  while (totalBytesRead < pageSize) {                                                    // :297-303
+    ++externalReads;
+    const int32_t bytesRead = mExternal(pageStart + totalBytesRead, page->data() + totalBytesRead, pageSize - totalBytesRead);
+    if (bytesRead <= 0) break;
+    totalBytesRead += bytesRead;
+  }
+  bytesReadExternal += totalBytesRead;                                                   // :304
+  return totalBytesRead == pageSize;                                                     // :305-308 IOException
+}
+
+// The loop of read (:120-144) and of positionedRead (:188-212): the same statements over mPosition and over
+// a local currentPosition.
+int32_t LocalCacheFileInStream::ReadLoop(int64_t* position, uint8_t* b, int32_t bLen, int32_t off, int32_t len,
+                                         bool positioned) {
+  int32_t totalBytesRead = 0;
+  const int64_t lengthToRead = std::min<int64_t>(len, mLength - *position);              // :118 / :186
+  std::vector<uint8_t> page;
+  while (totalBytesRead < lengthToRead) {
+    const int64_t currentPage = *position / mPageSize;
+    const int32_t currentPageOffset = (int32_t)(*position % mPageSize);
+    const int32_t bytesLeftInPage = (int32_t)std::min<int64_t>(mPageSize - currentPageOffset, lengthToRead - totalBytesRead);
+    const PageId pageId{mFileId, currentPage};
+    const int32_t bytesRead = mCacheManager->Get(pageId, currentPageOffset, bytesLeftInPage, b, bLen, off + totalBytesRead);
+    if (bytesRead == kGetIllegalArgument) return kGetIllegalArgument;  // thrown out of get(), out of the loop
+    if (bytesRead > 0) {                                                                 // :129-132
+      totalBytesRead += bytesRead;
+      *position += bytesRead;
+      bytesReadCache += bytesRead;
+    } else {                                                                             // :133-143
+      if (!ReadExternalPage(*position, &page)) return kStreamIo;
+      if (!page.empty()) {
+        if (off + totalBytesRead + bytesLeftInPage > bLen) return kGetIllegalArgument;  // System.arraycopy bounds
+        memcpy(b + off + totalBytesRead, page.data() + currentPageOffset, (size_t)bytesLeftInPage);
+        totalBytesRead += bytesLeftInPage;
+        *position += bytesLeftInPage;
+        bytesRequestedExternal += bytesLeftInPage;
+        mCacheManager->Put(pageId, page.data(), (int32_t)page.size());                   // result ignored (:141)
+      }
+    }
+  }
+  // :146-150 / :214-221
+  const int64_t left = positioned ? mLength - *position : Remaining();
+  if (totalBytesRead > len || (totalBytesRead < len && left > 0)) return kStreamIo;
+  return totalBytesRead;
+}
+
+int32_t LocalCacheFileInStream::Read(uint8_t* b, int32_t bLen, int32_t off, int32_t len) {  // :108-152
+  if (!(len >= 0)) return kGetIllegalArgument;                                           // :109
+  if (!(off >= 0)) return kGetIllegalArgument;                                           // :110
+  if (len == 0) return 0;                                                                // :111-113
+  if (mPosition >= mLength) return -1;                                                   // :114-116
+  return ReadLoop(&mPosition, b, bLen, off, len, false);
+}
+
+int32_t LocalCacheFileInStream::PositionedRead(int64_t pos, uint8_t* b, int32_t bLen, int32_t off, int32_t len) {  // :175-223
+  if (!(len >= 0)) return kGetIllegalArgument;                                           // :176
+  if (!(off >= 0)) return kGetIllegalArgument;                                           // :177
+  if (!(pos >= 0)) return kGetIllegalArgument;                                           // :178
+  if (len == 0) return 0;                                                                // :179-181
+  if (pos < 0 || pos >= mLength) return -1;                                              // :182-184
+  int64_t currentPosition = pos;                                                         // :186
+  return ReadLoop(&currentPosition, b, bLen, off, len, true);
+}
+
+int64_t LocalCacheFileInStream::Skip(int64_t n) {  // :154-162
+  if (mClosed) return kStreamClosed;
+  if (n <= 0) return 0;
+  const int64_t toSkip = std::min(Remaining(), n);
+  mPosition += toSkip;
+  return toSkip;
+}
+
+int LocalCacheFileInStream::Seek(int64_t pos) {  // :230-243
+  if (mClosed) return kStreamClosed;
+  if (!(pos >= 0)) return kGetIllegalArgument;
+  if (!(pos <= mLength)) return kGetIllegalArgument;
+  if (pos == mPosition) return 0;
+  if (pos < mPosition) mEOF = false;
+  mPosition = pos;
+  return 0;
 }
 
 }  // namespace orc

@@ -139,4 +139,42 @@ class LocalCacheManager {
   State mState;
 };
 
+// ---- CACHE/LocalCacheFileInStream.java:37-336 ---------------------------------------------------
+// The stream a client reads a file through: page by page out of the cache, whole pages from the external
+// file system on a miss (and offered to the cache).  `ExternalRead(pos, dst, len) -> bytes read` stands for
+// the external FileInStream after getExternalFileInStream() has positioned it (:256-270); <= 0 ends the read
+// loop of readExternalPage (:299-303).  Results follow the Java ones with exceptions turned into codes:
+// kGetIllegalArgument (Preconditions.checkArgument), kStreamIo (IOException), kStreamClosed
+// (IllegalStateException from checkIfClosed).  The meters of :312-335 are process-wide statics in the
+// reference; here they are per stream.
+constexpr int kStreamIo = -3;
+constexpr int kStreamClosed = -4;
+using ExternalRead = std::function<int32_t(int64_t pos, uint8_t* dst, int32_t len)>;
+
+class LocalCacheFileInStream {
+ public:
+  // pageSize = alluxio.user.client.cache.page.size (:86); fileId = URIStatus.getFileIdentifier() (:128).
+  LocalCacheFileInStream(const std::string& fileId, int64_t fileLength, int64_t pageSize, LocalCacheManager* manager,
+                         ExternalRead external);
+  int32_t Read(uint8_t* b, int32_t bLen, int32_t off, int32_t len);                         // :108-152
+  int32_t PositionedRead(int64_t pos, uint8_t* b, int32_t bLen, int32_t off, int32_t len);  // :175-223
+  int64_t Skip(int64_t n);                                                                  // :154-162
+  int Seek(int64_t pos);                                                                    // :230-243
+  int64_t Remaining() const { return mEOF ? 0 : mLength - mPosition; }                      // :170-172
+  int64_t GetPos() const { return mPosition; }                                              // :225-228
+  void Close() { mClosed = true; }  // :164-167 closes the external stream; the tests here only see the flag
+  int64_t bytesReadCache = 0, bytesRequestedExternal = 0, bytesReadExternal = 0;            // :312-320
+  int64_t externalReads = 0;  // calls made on the external stream (not a reference metric; used by the tests)
+ private:
+  // the page loop both reads share; *position is mPosition (read) or a local copy of pos (positionedRead)
+  int32_t ReadLoop(int64_t* position, uint8_t* b, int32_t bLen, int32_t off, int32_t len, bool positioned);
+  bool ReadExternalPage(int64_t pos, std::vector<uint8_t>* page);                           // :291-310
+  std::string mFileId;
+  int64_t mLength, mPageSize;
+  LocalCacheManager* mCacheManager;
+  ExternalRead mExternal;
+  int64_t mPosition = 0;
+  bool mClosed = false, mEOF = false;
+};
+
 }  // namespace orc
