@@ -1001,9 +1001,14 @@ int32_t LocalCacheFileInStream::ReadAt(int64_t* position, void* b, int32_t bLen,
   if (len < 0 || off < 0 || *position < 0) return kGetIllegalArgument;
   if (len == 0) return 0;
   if (*position >= mLength) return -1;
-  if (off > bLen || len > bLen - off) return kGetIllegalArgument;  // Java: ArrayIndexOutOfBounds from the copy
+  // What has to fit into b is what the read delivers -- min(len, bytes left in the file) -- not len: the reference's only
+  // bound is LocalCacheManager.get's bytesToRead <= buffer.length - offsetInBuffer (CACHE/LocalCacheManager.java:364-366),
+  // applied page by page (CTEST/LocalCacheFileInStreamTest.java:215-238 reads with len = 2 * fileSize into a buffer with
+  // 2 * fileSize - 2 bytes of room).  The per-page loop below leaves the check to Get, as the reference does; the two
+  // single-call forms check the whole read here.
+  const int64_t want = std::min<int64_t>(len, mLength - *position);
+  if ((mBypass || mBatched) && want > (int64_t)bLen - off) return kGetIllegalArgument;
   if (mBypass) {  // the delegated file system's own stream
-    const int64_t want = std::min<int64_t>(len, mLength - *position);
     int64_t total = 0;
     while (total < want) {
       const int r = mExternal(mUser, *position + total, (uint8_t*)b + off + total, (int32_t)(want - total));
@@ -1027,6 +1032,7 @@ int32_t LocalCacheFileInStream::ReadAt(int64_t* position, void* b, int32_t bLen,
     const int32_t pageOff = (int32_t)(*position % mPageSize);
     const int32_t inPage = (int32_t)std::min<int64_t>(mPageSize - pageOff, toRead - total);
     const int32_t got = mManager->Get(mFileId, pageIdx, pageOff, inPage, b, bLen, off + total);
+    if (got == kGetIllegalArgument) return kGetIllegalArgument;  // this piece does not fit into b: thrown out of get()
     if (got > 0) {
       total += got;
       *position += got;
