@@ -91,6 +91,12 @@ APS_API int aps_open(const aps_config* cfg, aps_store** out) {
     s->cfg.slab_slots = std::max<uint64_t>(64, need + need / 8);
   }
   if (!s->cfg.max_batch) s->cfg.max_batch = 4096;
+  {  // handles live as long as the process (a closed one is a tombstone, as in the library): keep them reachable
+    static std::mutex mu;
+    static std::vector<aps_store*>* all = new std::vector<aps_store*>();
+    std::lock_guard<std::mutex> lk(mu);
+    all->push_back(s);
+  }
   *out = s;
   return APS_OK;
 }
