@@ -1,5 +1,8 @@
 /* Minimal stand-in for the JDK's jni.h (absent from this image), just enough to type-check integration/jni/aps_jni.c
- * against include/aps.h in tests/test_c_abi.py.  Declares only what the shim uses; not a JNI implementation. */
+ * against include/aps.h in tests/test_c_abi.py, and to RUN it over the mock JNIEnv of fake_env.c (tests/test_jni_shim_runs.py).
+ * Declares only what the shim uses. */
+#ifndef JNI_STUB_H_
+#define JNI_STUB_H_
 #include <stdint.h>
 typedef int32_t jint; typedef int64_t jlong; typedef signed char jbyte; typedef unsigned char jboolean;
 typedef void* jobject; typedef jobject jclass; typedef jobject jstring; typedef jobject jarray; typedef jarray jintArray;
@@ -31,3 +34,4 @@ struct JNINativeInterface_ {
   jobjectArray (*NewObjectArray)(JNIEnv*, jsize, jclass, jobject);
   jclass (*FindClass)(JNIEnv*, const char*);
 };
+#endif
