@@ -241,6 +241,30 @@ def test_time_bound_page_store():
     plain.close()
 
 
+def test_time_bound_store_concurrent_puts_with_a_large_pool():
+    """TimeBoundPageStoreTest.concurrentPutWithLargeThreadPool (:135-144): as many store threads as callers and a store
+    that does not hang -- every put goes through, nothing times out, nothing is rejected."""
+    n = 10
+    m = _manager(cache_size=256 * PS, slab_slots=256, timeout_ms=5000, timeout_threads=n)
+    page = increasing(PS)
+    results = [None] * n
+    barrier = threading.Barrier(n)
+
+    def worker(k):
+        barrier.wait()
+        results[k] = m.put(PID("0L", k), page)
+
+    ts = [threading.Thread(target=worker, args=(k,)) for k in range(n)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert all(results) and m.pages() == n
+    assert m.store_timeouts() == {"put": 0, "get": 0, "delete": 0, "rejected": 0}
+    buf = bytearray(PS)
+    for k in range(n):
+        assert m.get(PID("0L", k), PS, buf) == PS and bytes(buf) == page
+    m.close()
+
+
 def test_async_cache_same_page_is_refused_while_pending():
     """LocalCacheManagerTest.asyncCacheSamePage (:563-580): a put of an id that is still queued returns false and is
     not an async rejection; the first put lands."""
