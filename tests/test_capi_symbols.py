@@ -72,3 +72,26 @@ def test_host_library_exports_and_binds_every_symbol_of_aps_cache_h():
     for name in syms:
         assert hasattr(L, name), name
     assert sorted(cache.SIGNATURES) == syms
+
+
+def test_product_has_no_path_through_the_oracle_or_the_test_double():
+    """The checker and the double are test infrastructure: no source of the product names them, the host library's one
+    dependency for the store entry points is libaps.so itself, and the CUDA library exports none of the double's state."""
+    import subprocess
+    offenders = []
+    for top in ("alluxio_b200", "include", "integration"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, top)):
+            for f in files:
+                if not f.endswith((".py", ".cc", ".cu", ".cuh", ".h", ".c", ".java")):
+                    continue
+                text = open(os.path.join(dirpath, f), errors="replace").read()
+                for line in text.splitlines():
+                    code = line.split("//")[0].split("#")[0] if not line.lstrip().startswith(("*", "/*")) else ""
+                    if re.search(r"\b(import\s+oracle|from\s+oracle|host_double|fake_aps|liboracle|orc_\w+\s*\()", code):
+                        offenders.append((os.path.join(dirpath, f), line.strip()))
+    assert not offenders, offenders
+    from alluxio_b200 import cache
+    needed = subprocess.run(["readelf", "-d", cache.LIB_PATH], capture_output=True, text=True).stdout
+    assert "libaps.so" in needed and "oracle" not in needed and "double" not in needed
+    undefined = subprocess.run(["nm", "-D", "--undefined-only", cache.LIB_PATH], capture_output=True, text=True).stdout
+    assert "aps_open" in undefined and "aps_get_batch" in undefined   # resolved by libaps.so, not defined in the host library
