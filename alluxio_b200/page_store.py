@@ -40,8 +40,8 @@ class PageId:
         return "PageId{FileId=%s, PageIndex=%d}" % (self.file_id, self.page_index)
 
 
-_DEC = re.compile(r"^(0|-?[1-9][0-9]{0,18})$")
-_HEX32 = re.compile(r"^[0-9a-f]{32}$")
+_DEC = re.compile(r"(0|-?[1-9][0-9]{0,18})\Z")   # \Z, not $: "123\n" is not a decimal long (Java's String.matches)
+_HEX32 = re.compile(r"[0-9a-f]{32}\Z")
 _MASK64 = (1 << 64) - 1
 _INTERNED_HI = _MASK64
 

@@ -198,3 +198,48 @@ def test_evictors_follow_the_oracle_through_random_sequences(kind, base):
         assert (va is None) == (vb is None), step
         if va is not None:
             assert (va.file_id, va.page_index) == (vb.file_id, vb.page_index), step
+
+
+def test_three_file_key_codecs_agree_on_edge_cases():
+    """PageId.fileId -> 128-bit key is written three times: Python (page_store.FileKeyCodec), C++ (host FileKeyCodec,
+    apc_file_key_of) and Java (GpuPageStore.fileKey).  The Java one cannot run here, so its two regular expressions are
+    read out of the source and applied with Java's String.matches semantics (the WHOLE string must match).  All three
+    must put every string into the same class -- decimal long, 32-hex, or interned -- with the same key."""
+    import os
+    import re
+    from alluxio_b200.cache import file_key_of
+    src = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "integration", "java", "alluxio",
+                            "client", "file", "cache", "store", "GpuPageStore.java")).read()
+    java_patterns = re.findall(r'fileId\.matches\("([^"]+)"\)', src)
+    assert len(java_patterns) == 2
+    java_dec, java_hex = (re.compile(p) for p in java_patterns)
+    M = (1 << 64) - 1
+
+    def java(s):
+        if java_dec.fullmatch(s):
+            v = int(s)
+            if -(1 << 63) <= v < (1 << 63):          # Long.parseLong; NumberFormatException falls through to interning
+                return 0, v & M
+        if java_hex.fullmatch(s):
+            hi, lo = int(s[:16], 16), int(s[16:], 16)
+            if hi not in (0, M):                      # hi != 0L && hi != -1L
+                return hi, lo
+        return M, None
+
+    corpus = ["0", "-0", "00", "+1", "1", "-1", "007", "9223372036854775807", "9223372036854775808", "-9223372036854775808",
+              "-9223372036854775809", "1" * 19, "9" * 19, "1" * 20, "123\n", "\n123", " 123", "123 ", "12a", "１２３", "",
+              "-", "d41d8cd98f00b204e9800998ecf8427e", "D41D8CD98F00B204E9800998ECF8427E", "d41d8cd98f00b204e9800998ecf8427",
+              "d41d8cd98f00b204e9800998ecf8427e0", "0000000000000000ffffffffffffffff", "ffffffffffffffff0000000000000000",
+              "0000000000000001ffffffffffffffff", "fffffffffffffffe0000000000000000", "d41d8cd98f00b204e9800998ecf8427e\n",
+              "123e4567-e89b-12d3-a456-426614174000", "/a/raw/path", "g" * 32, "0" * 32, "f" * 32]
+    py = FileKeyCodec()
+    for s in corpus:
+        want = java(s)
+        got_py, got_cc = py.encode(s), file_key_of(s)
+        if want[1] is None:
+            assert got_py[0] == M and got_cc[0] == M, (s, got_py, got_cc)
+        else:
+            assert got_py == want and got_cc == want, (s, want, got_py, got_cc)
+    # interned ids are exact: different strings never share a key, equal strings always do
+    keys = [py.encode(s) for s in corpus]
+    assert len(set(keys)) == len(set(corpus)) and [py.encode(s) for s in corpus] == keys
