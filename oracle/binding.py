@@ -56,6 +56,7 @@ def lib():
             "orc_meta_evict": (C.c_int, [vp, vp, C.c_size_t, C.POINTER(i64), C.POINTER(i64)]),
             "orc_store_open_local": (vp, [cp, i64, i64, i32, C.c_int]),
             "orc_store_open_mem": (vp, [i64, i64, C.c_int]),
+            "orc_store_open_external": (vp, [vp, vp, vp, vp, vp, i64]),
             "orc_store_destroy": (None, [vp]),
             "orc_store_put": (C.c_int, [vp, cp, i64, u8p, i32]),
             "orc_store_get": (C.c_int, [vp, cp, i64, i32, i32, u8p, i32, i32, C.POINTER(i32)]),
@@ -280,6 +281,63 @@ class PageStore:
     @classmethod
     def open_mem(cls, page_size, cache_size, keep_bytes=True):
         return cls(lib().orc_store_open_mem(page_size, cache_size, int(keep_bytes)), page_size, cache_size)
+
+    @classmethod
+    def over(cls, impl, page_size, cache_size, make_id=None):
+        """A PageStore implemented by `impl` -- any object with the interface of CACHE/PageStore.java:119-171 as the
+        Python mirrors spell it: put(id, bytes), get(id, bytearray, page_offset, bytes_to_read, buffer_offset) -> n,
+        delete(id), get_pages() -> [(id, size)].  The oracle's LocalCacheManager then drives `impl` exactly as the
+        reference's LocalCacheManager drives a PageStore in the JVM.  Exceptions map as in the reference:
+        *PageNotFoundException -> 1, ValueError (IllegalArgumentException) -> 2, anything else (IOException) -> 3."""
+        make_id = make_id or PageId
+
+        def status(e):
+            if "PageNotFound" in type(e).__name__:
+                return 1
+            return 2 if isinstance(e, ValueError) else 3
+
+        def put(user, f, idx, page, n):
+            try:
+                impl.put(make_id(f.decode(), idx), C.string_at(page, n) if n else b"")
+                return 0
+            except Exception as e:  # noqa: BLE001
+                return status(e)
+
+        def get(user, f, idx, page_offset, bytes_to_read, buffer, buf_len, buffer_offset, bytes_read):
+            try:
+                tmp = bytearray(max(buf_len, 0))
+                n = impl.get(make_id(f.decode(), idx), tmp, page_offset, bytes_to_read, buffer_offset)
+                if n > 0 and buffer:
+                    C.memmove(buffer + buffer_offset, bytes(tmp[buffer_offset:buffer_offset + n]), n)
+                bytes_read[0] = n
+                return 0
+            except Exception as e:  # noqa: BLE001
+                return status(e)
+
+        def delete(user, f, idx):
+            try:
+                impl.delete(make_id(f.decode(), idx))
+                return 0
+            except Exception as e:  # noqa: BLE001
+                return status(e)
+
+        def get_pages(user, emit, emit_user):
+            try:
+                for pid, size in impl.get_pages():
+                    emit(emit_user, 1, str(pid.file_id).encode(), pid.page_index, size)
+                return 0
+            except Exception as e:  # noqa: BLE001
+                return status(e)
+
+        emit_t = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_char_p, C.c_int64, C.c_int64)
+        cbs = (C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_int32)(put),
+               C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_char_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_int32,
+                           C.POINTER(C.c_int32))(get),
+               C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_char_p, C.c_int64)(delete),
+               C.CFUNCTYPE(C.c_int, C.c_void_p, emit_t, C.c_void_p)(get_pages))
+        self = cls(lib().orc_store_open_external(None, *[C.cast(c, C.c_void_p) for c in cbs], cache_size), page_size, cache_size)
+        self._keep = (impl, cbs)
+        return self
 
     def __del__(self):
         if getattr(self, "_h", None):

@@ -74,6 +74,15 @@ void* orc_store_open_local(const char* root, int64_t page_size, int64_t cache_si
 void* orc_store_open_mem(int64_t page_size, int64_t cache_size, int keep_bytes) {
   return OpenMemPageStore(page_size, cache_size, keep_bytes != 0).release();
 }
+// A store implemented by the caller (see ExternalPageStoreCalls): callbacks return 0 ok, 1 PageNotFoundException,
+// 2 IllegalArgumentException, 3 IOException.
+void* orc_store_open_external(void* user, int (*put)(void*, const char*, int64_t, const uint8_t*, int32_t),
+                              int (*get)(void*, const char*, int64_t, int32_t, int32_t, uint8_t*, int32_t, int32_t, int32_t*),
+                              int (*del)(void*, const char*, int64_t),
+                              int (*get_pages)(void*, void (*)(void*, int, const char*, int64_t, int64_t), void*),
+                              int64_t cache_size) {
+  return OpenExternalPageStore(ExternalPageStoreCalls{user, put, get, del, get_pages}, cache_size).release();
+}
 void orc_store_destroy(void* s) { delete (PageStore*)s; }
 int orc_store_put(void* s, const char* f, int64_t i, const uint8_t* page, int32_t len) {
   return ((PageStore*)s)->Put(PageId{f, i}, page, len);

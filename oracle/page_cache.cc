@@ -503,7 +503,53 @@ class MemPageStore : public PageStore {
   bool mKeepBytes;
 };
 
+// See page_cache.h: the store lives outside; fault injection of the ported tests still works from this side.
+class ExternalPageStore : public PageStore {
+ public:
+  ExternalPageStore(const ExternalPageStoreCalls& calls, int64_t cacheSize) : mCalls(calls), mCacheSize(cacheSize) {}
+  StoreStatus Put(const PageId& id, const uint8_t* page, int32_t len) override {
+    if (putFaulty) return kIo;
+    return (StoreStatus)mCalls.put(mCalls.user, id.fileId.c_str(), id.pageIndex, page, len);
+  }
+  StoreStatus Get(const PageId& id, int32_t pageOffset, int32_t bytesToRead, uint8_t* buffer, int32_t bufLen,
+                  int32_t bufferOffset, int32_t* bytesRead) override {
+    *bytesRead = 0;
+    return (StoreStatus)mCalls.get(mCalls.user, id.fileId.c_str(), id.pageIndex, pageOffset, bytesToRead, buffer, bufLen,
+                                   bufferOffset, bytesRead);
+  }
+  StoreStatus Delete(const PageId& id) override {
+    if (deleteFaulty) return kIo;
+    return (StoreStatus)mCalls.del(mCalls.user, id.fileId.c_str(), id.pageIndex);
+  }
+  StoreStatus GetPages(std::vector<std::pair<bool, PageInfo>>* out) override {
+    out->clear();
+    return (StoreStatus)mCalls.get_pages(
+        mCalls.user,
+        [](void* emitUser, int valid, const char* fileId, int64_t pageIndex, int64_t size) {
+          auto* v = static_cast<std::vector<std::pair<bool, PageInfo>>*>(emitUser);
+          v->push_back({valid != 0, PageInfo{PageId{fileId, pageIndex}, size}});
+        },
+        out);
+  }
+  int64_t GetCacheSize() const override { return mCacheSize; }
+  bool RootExists() const override { return true; }
+  StoreStatus Recreate() override {  // PageStore.create over a store that cannot be wiped in place: delete what it lists
+    std::vector<std::pair<bool, PageInfo>> pages;
+    if (GetPages(&pages) != kOk) return kIo;
+    for (auto& e : pages)
+      if (e.first && mCalls.del(mCalls.user, e.second.pageId.fileId.c_str(), e.second.pageId.pageIndex) != kOk) return kIo;
+    return kOk;
+  }
+ private:
+  ExternalPageStoreCalls mCalls;
+  int64_t mCacheSize;
+};
+
 }  // namespace
+
+std::unique_ptr<PageStore> OpenExternalPageStore(const ExternalPageStoreCalls& calls, int64_t cacheSize) {
+  return std::unique_ptr<PageStore>(new ExternalPageStore(calls, cacheSize));
+}
 
 std::unique_ptr<PageStore> OpenLocalPageStore(const std::string& root, int64_t pageSize, int64_t cacheSize,
                                               int32_t fileBuckets, bool wipeFirst) {

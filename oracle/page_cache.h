@@ -111,6 +111,22 @@ std::unique_ptr<PageStore> OpenLocalPageStore(const std::string& root, int64_t p
 // Same contract, pages held in RAM (for replays too large for one-file-per-page on disk).
 std::unique_ptr<PageStore> OpenMemPageStore(int64_t pageSize, int64_t cacheSize, bool keepBytes);
 
+// A PageStore implemented OUTSIDE the oracle, reached through the five calls of the interface
+// (CACHE/PageStore.java:119-171).  This is how the tests put the oracle's LocalCacheManager -- the restatement of the
+// reference's Java -- on top of the store under test, exactly as the JVM puts the real LocalCacheManager on top of
+// GpuPageStore: the manager's own logic is the checker's, only the PageStore behind it is the product.
+// Each callback returns a StoreStatus; get_pages calls emit(emit_user, valid, fileId, pageIndex, size) per page.
+struct ExternalPageStoreCalls {
+  void* user;
+  int (*put)(void* user, const char* fileId, int64_t pageIndex, const uint8_t* page, int32_t len);
+  int (*get)(void* user, const char* fileId, int64_t pageIndex, int32_t pageOffset, int32_t bytesToRead, uint8_t* buffer,
+             int32_t bufLen, int32_t bufferOffset, int32_t* bytesRead);
+  int (*del)(void* user, const char* fileId, int64_t pageIndex);
+  int (*get_pages)(void* user, void (*emit)(void* emitUser, int valid, const char* fileId, int64_t pageIndex, int64_t size),
+                   void* emitUser);
+};
+std::unique_ptr<PageStore> OpenExternalPageStore(const ExternalPageStoreCalls& calls, int64_t cacheSize);
+
 // ---- CACHE/CacheManager.java:34-188, CACHE/LocalCacheManager.java:75-627 ------------------------
 enum State { NOT_IN_USE = 0, READ_ONLY = 1, READ_WRITE = 2 };
 constexpr int kGetIllegalArgument = -2;  // stands for IllegalArgumentException out of get()
