@@ -199,67 +199,6 @@ def test_positioned_read_through_the_cache():
 
 
 @pytest.mark.parametrize("evictor", ["LRU", "LFU", "FIFO"])
-def test_random_operations_equal_the_oracle_manager(evictor):
-    """put / get / delete in random order on a cache under pressure -- pages of every length from empty to full, partial
-    and over-long gets (a short read drops the page), gets of zero bytes, offsets up to and beyond the page size, buffers
-    too small, re-puts of resident pages, deletes of absent ones, and a store that fails its puts or its deletes for a
-    while (FaultyPageStore, CTEST/LocalCacheManagerTest.java:660-691).  Every return value or exception, every byte
-    returned and the cache's page and byte counts must equal the oracle manager's after every step."""
-    rng = np.random.default_rng({"LRU": 1, "LFU": 2, "FIFO": 3}[evictor])
-    ps, cap_pages = 512, 24
-    ostore = orc.PageStore.open_mem(ps, cap_pages * ps)
-    om = orc.LocalCacheManager(ostore, ps, evictor)
-    m = manager(cache_size=cap_pages * ps, evictor=evictor, page_size=ps, slab_slots=4096)
-    lengths = [0, 1, 17, ps // 2, ps - 1, ps, ps, ps, ps, ps]
-    for step in range(3000):
-        f, i = str(int(rng.integers(5))), int(rng.integers(20))
-        op = int(rng.integers(10))
-        if step % 500 == 250:                                   # a stretch with a faulty store, then back to normal
-            fp, fd = bool(rng.integers(2)), bool(rng.integers(2))
-            m.set_store_faulty(put=fp, delete=fd)
-            ostore.set_faulty(put=fp, delete=fd)
-        elif step % 500 == 330:
-            m.set_store_faulty()
-            ostore.set_faulty()
-        if op < 4:
-            n = lengths[int(rng.integers(len(lengths)))]
-            data = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
-            r, ro = m.put(PID(f, i), data), om.put(orc.PageId(f, i), data)
-            assert r == ro, (step, "put", f, i, n, r, ro)
-        elif op < 9:
-            want = int(rng.choice([0, 1, 17, ps // 2, ps - 1, ps, ps]))
-            off = int(rng.choice([0, 0, 0, 1, ps // 2, ps, ps + 1]))
-            room = want if rng.integers(5) else max(0, want - 1)
-            at = int(rng.integers(3))
-            b, bo = bytearray(at + room), bytearray(at + room)
-            out = []
-            for mgr, pid, buf in ((m, PID(f, i), b), (om, orc.PageId(f, i), bo)):
-                try:
-                    out.append(mgr.get(pid, want, buf, offset_in_buffer=at, page_offset=off))
-                except ValueError:
-                    out.append("IllegalArgumentException")
-            assert out[0] == out[1], (step, "get", f, i, want, off, room, at, out)
-            assert b == bo, (step, "get bytes", f, i, want, off)
-        else:
-            r, ro = m.delete(PID(f, i)), om.delete(orc.PageId(f, i))
-            assert r == ro, (step, "delete", f, i, r, ro)
-        assert (m.pages(), m.bytes()) == (om.pages(), om.bytes()), (step, op)
-    mt = m.metrics()
-    assert mt["PagesEvicted"] > 100 and mt["PutStoreWriteErrors"] + mt["PutStoreDeleteErrors"] > 0 and mt["GetErrors"] > 0
-    m.set_store_faulty()
-    ostore.set_faulty()
-    buf, obuf = bytearray(ps), bytearray(ps)
-    for f in range(5):                                          # the same pages are left, with the same bytes
-        for i in range(20):
-            for n in (ps, ps - 1, ps // 2, 17, 1):              # find the stored length: the first n that reads whole
-                r, ro = m.get(PID(str(f), i), n, buf), om.get(orc.PageId(str(f), i), n, obuf)
-                assert r == ro and (r <= 0 or buf[:r] == obuf[:r])
-                if r != -1:
-                    break
-    m.close()
-
-
-@pytest.mark.parametrize("evictor", ["LRU", "LFU", "FIFO"])
 def test_replay_matches_oracle_element_by_element(evictor):
     """BASELINE config 3 in miniature: 64 KiB pages, Zipf(0.99) accesses, capacity << universe; the
     evictor on the host drives GPU table inserts and erases.  Everything observable must equal the

@@ -241,30 +241,6 @@ def test_time_bound_page_store():
     plain.close()
 
 
-def test_time_bound_store_concurrent_puts_with_a_large_pool():
-    """TimeBoundPageStoreTest.concurrentPutWithLargeThreadPool (:135-144): as many store threads as callers and a store
-    that does not hang -- every put goes through, nothing times out, nothing is rejected."""
-    n = 10
-    m = _manager(cache_size=256 * PS, slab_slots=256, timeout_ms=5000, timeout_threads=n)
-    page = increasing(PS)
-    results = [None] * n
-    barrier = threading.Barrier(n)
-
-    def worker(k):
-        barrier.wait()
-        results[k] = m.put(PID("0L", k), page)
-
-    ts = [threading.Thread(target=worker, args=(k,)) for k in range(n)]
-    [t.start() for t in ts]
-    [t.join() for t in ts]
-    assert all(results) and m.pages() == n
-    assert m.store_timeouts() == {"put": 0, "get": 0, "delete": 0, "rejected": 0}
-    buf = bytearray(PS)
-    for k in range(n):
-        assert m.get(PID("0L", k), PS, buf) == PS and bytes(buf) == page
-    m.close()
-
-
 def test_async_cache_same_page_is_refused_while_pending():
     """LocalCacheManagerTest.asyncCacheSamePage (:563-580): a put of an id that is still queued returns false and is
     not an async rejection; the first put lands."""
@@ -301,88 +277,6 @@ def test_oversized_buffers_and_several_files():
         b = bytearray(len(d))
         assert s.read(b) == len(d) and bytes(b) == d
     assert m.pages() == sum((len(d) + PS - 1) // PS for d in files.values())
-    m.close()
-
-
-def test_position_read_oversized_buffer():
-    """CTEST/LocalCacheFileInStreamTest.java:215-238, literally: positionedRead(1, b, 2, 2 * fileSize) with b.length =
-    2 * fileSize asks for more than b has room for behind off -- and is served, because what the file still holds fits
-    (the only bound is LocalCacheManager.get's, page by page)."""
-    file_size = PS
-    data = increasing(file_size)
-    m = _manager()
-    s = m.open_file("/test", file_size, External(data))
-    miss = bytearray(file_size * 2)
-    assert s.positioned_read(1, miss, 2, file_size * 2) == file_size - 1
-    assert bytes(miss[2:file_size + 1]) == data[1:file_size]
-    assert s.counters()["BytesReadCache"] == 0 and m.pages() == 1
-    hit = bytearray(file_size * 2)
-    assert s.positioned_read(1, hit, 2, file_size * 2) == file_size - 1
-    assert bytes(hit[2:file_size + 1]) == data[1:file_size]
-    assert s.counters()["BytesReadCache"] == file_size - 1
-    s.set_batched()                                            # the one-call form: same answer
-    again = bytearray(file_size * 2)
-    assert s.positioned_read(1, again, 2, file_size * 2) == file_size - 1 and again == hit
-    m.close()
-
-
-def test_stream_equals_the_oracle_stream_op_by_op():
-    """Three files read through ONE small cache by the product's stream and by the oracle's restatement of
-    LocalCacheFileInStream (pinned by the reference's own tests, tests/test_oracle_stream.py): the same random sequence
-    of read / positionedRead / seek / skip -- buffers larger and smaller than the read included -- must give the same
-    return values and exceptions, bytes, positions, meters and cache contents after every step."""
-    from oracle import binding as orc
-    cache_pages = 12
-    m = _manager(cache_size=cache_pages * PS)
-    om = orc.LocalCacheManager(orc.PageStore.open_mem(PS, cache_pages * PS), PS, "LRU")
-    rng = np.random.default_rng(77)
-    files = {str(300 + k): rng.integers(0, 256, n, dtype=np.uint8).tobytes() for k, n in enumerate((7 * PS + 13, 3 * PS, 9 * PS - 1))}
-    mine = {f: m.open_file(f, len(d), External(d)) for f, d in files.items()}
-    theirs = {f: orc.LocalCacheFileInStream(om, f, len(d), External(d), PS) for f, d in files.items()}
-
-    def both(f, call):
-        out = []
-        for s in (mine[f], theirs[f]):
-            try:
-                out.append(call(s))
-            except (ValueError, IOError, RuntimeError) as e:
-                out.append(type(e).__name__)
-        assert out[0] == out[1], (f, out)
-        return out[0]
-
-    names = list(files)
-    for step in range(600):
-        f = names[int(rng.integers(len(names)))]
-        n_file = len(files[f])
-        op = int(rng.integers(5))
-        if op == 0:
-            both(f, lambda s, p=int(rng.integers(-2, n_file + 3)): s.seek(p))
-        elif op == 1:
-            both(f, lambda s, n=int(rng.integers(-3, 3 * PS)): s.skip(n))
-        elif op == 2 or op == 3:                                # read; one in four with a buffer that may be too small
-            n, off = int(rng.integers(0, 4 * PS)), int(rng.integers(0, 4))
-            room = n if rng.integers(4) else int(rng.integers(0, n + 1))
-            a, b = bytearray(off + room), bytearray(off + room)
-            bufs = iter((a, b))
-            both(f, lambda s: s.read(next(bufs), off, n))
-            assert a == b, (step, f, n, off, room)
-        else:
-            n, pos = int(rng.integers(0, 4 * PS)), int(rng.integers(-1, n_file + PS))
-            a, b = bytearray(n + 5), bytearray(n + 5)
-            bufs = iter((a, b))
-            both(f, lambda s: s.positioned_read(pos, next(bufs), 5, n))
-            assert a == b, (step, f, n, pos)
-        assert mine[f].get_pos() == theirs[f].get_pos() and mine[f].remaining() == theirs[f].remaining()
-        c, oc = mine[f].counters(), theirs[f].counters()
-        assert all(c[k] == oc[k] for k in c), (step, c, oc)
-        assert (m.pages(), m.bytes()) == (om.pages(), om.bytes()), step
-    assert m.pages() == cache_pages or m.bytes() > (cache_pages - 1) * PS      # the cache was full: evictions took part
-    buf, obuf = bytearray(PS), bytearray(PS)
-    for f, d in files.items():                                  # the same pages are resident, with the same bytes
-        for i in range((len(d) + PS - 1) // PS):
-            want = min(PS, len(d) - i * PS)
-            r, ro = m.get(PID(f, i), want, buf), om.get(orc.PageId(f, i), want, obuf)
-            assert r == ro and (r <= 0 or buf[:r] == obuf[:r]), (f, i, r, ro)
     m.close()
 
 

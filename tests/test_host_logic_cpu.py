@@ -5,7 +5,8 @@ without a GPU.
 How: tests/host_double links the UNCHANGED host layer against a host-memory stand-in for the handful of libaps.so entry
 points it calls (a test double: tests/host_double/fake_aps.cc, built into tests/_build/ and loaded by nothing else).
 The bodies run here are the `-m gpu` tests themselves (tests/test_gpu_cache_manager.py, test_gpu_stream_factory.py,
-test_gpu_sharded_manager.py, test_gpu_reference_manager.py): the same assertions, the same oracle comparisons, over the double here and over the CUDA
+test_gpu_sharded_manager.py, test_gpu_z_reference_manager.py,
+test_gpu_z_host_layer_vs_oracle.py): the same assertions, the same oracle comparisons, over the double here and over the CUDA
 store on the B200.  A case is left to the GPU run only when it drives the CUDA store directly (named below)."""
 import importlib
 
@@ -20,7 +21,8 @@ GPU_ONLY = {
     "test_gpu_cache_manager": set(),
     "test_gpu_stream_factory": set(),
     "test_gpu_sharded_manager": set(),
-    "test_gpu_reference_manager": set(),
+    "test_gpu_z_reference_manager": set(),
+    "test_gpu_z_host_layer_vs_oracle": set(),
 }
 
 
@@ -41,7 +43,7 @@ def _cases():
         mod = importlib.import_module(mod_name)
         for name in sorted(vars(mod)):
             fn = getattr(mod, name)
-            if not (name.startswith("test_") and callable(fn)) or name in skip:
+            if not (name.startswith("test_") and callable(fn)) or name in skip or getattr(fn, "__module__", mod_name) != mod_name:
                 continue
             for params in _param_sets(fn):
                 tag = "-".join("".join(map(str, v)) if isinstance(v, list) else str(v) for v in params.values())
