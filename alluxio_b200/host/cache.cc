@@ -697,7 +697,7 @@ bool LocalCacheManager::Put(const std::string& fileId, int64_t pageIndex, const 
   const int32_t lockId = GetPageLockId(fileId, pageIndex);
   if (!mAsyncCacheExecutor) {
     const bool ok = PutInternal(k, lockId, page, len);
-    if (ok) metrics.bytesWrittenCache += len; else metrics.putErrors++;
+    if (!ok) metrics.putErrors++;
     return ok;
   }
   {
@@ -708,7 +708,7 @@ bool LocalCacheManager::Put(const std::string& fileId, int64_t pageIndex, const 
   auto bytes = std::make_shared<std::vector<uint8_t>>((const uint8_t*)page, (const uint8_t*)page + len);
   const bool accepted = mAsyncCacheExecutor->TrySubmit([this, k, lockId, bytes] {
     const bool ok = PutInternal(k, lockId, bytes->data(), (int32_t)bytes->size());
-    if (ok) metrics.bytesWrittenCache += (int64_t)bytes->size(); else metrics.putErrors++;
+    if (!ok) metrics.putErrors++;
     std::lock_guard<std::mutex> lk(mPendingMu);
     mPendingRequests.erase(k);
   });
@@ -742,7 +742,10 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
       }
     }
     if (enoughSpace) {  // :274-285
-      if (mPageStore->Put(k, page, len) == APS_OK) return true;
+      if (mPageStore->Put(k, page, len) == APS_OK) {
+        metrics.bytesWrittenCache += len;  // :277 -- marked by the store write, so not for a page that was already there
+        return true;
+      }
       UndoAddPage(k);
       metrics.putStoreWriteErrors++;
       return false;
@@ -775,7 +778,10 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
     metrics.putEvictionErrors++;
     return false;
   }
-  if (mPageStore->Put(k, page, len) == APS_OK) return true;
+  if (mPageStore->Put(k, page, len) == APS_OK) {
+    metrics.bytesWrittenCache += len;  // :337
+    return true;
+  }
   UndoAddPage(k);  // :339-344
   metrics.putStoreWriteErrors++;
   return false;
@@ -790,7 +796,10 @@ int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int
                                void* buffer, int32_t bufLen, int32_t offsetInBuffer) {  // :360-399
   if (!(pageOffset <= mPageSize)) return kGetIllegalArgument;
   if (!(bytesToRead <= bufLen - offsetInBuffer)) return kGetIllegalArgument;
-  if (mState.load() == NOT_IN_USE) return -1;
+  if (mState.load() == NOT_IN_USE) {  // :368-372 (GET_NOT_READY_ERRORS has no counter here; GET_ERRORS has)
+    metrics.getErrors++;
+    return -1;
+  }
   const Key k = MakeKey(fileId, pageIndex);
   std::shared_lock<std::shared_mutex> pageLock(mPageLocks[GetPageLockId(fileId, pageIndex)]);
   bool hasPage;

@@ -70,6 +70,7 @@ def lib():
             "orc_manager_delete": (C.c_int, [vp, cp, i64]),
             "orc_manager_state": (C.c_int, [vp]),
             "orc_manager_page_lock_id": (i32, [vp, cp, i64]),
+            "orc_manager_metrics": (None, [vp, vp]),
             "orc_manager_bytes": (i64, [vp]),
             "orc_manager_pages": (i64, [vp]),
             "orc_stream_open": (vp, [vp, cp, i64, i64, EXTERNAL_READ, vp]),
@@ -427,6 +428,17 @@ class LocalCacheManager:
 
     def bytes(self):
         return lib().orc_manager_bytes(self._h)
+
+    METRICS = ("BytesWrittenCache", "BytesEvicted", "PagesEvicted", "GetErrors", "GetNotReadyErrors", "GetStoreReadErrors",
+               "CleanupGetErrors", "PutErrors", "PutNotReadyErrors", "PutEvictionErrors", "PutStoreWriteErrors",
+               "PutStoreDeleteErrors", "PutBenignRacingErrors", "CleanupPutErrors", "DeleteErrors", "DeleteNotReadyErrors",
+               "DeleteNonExistingPageErrors", "DeleteStoreDeleteErrors")
+
+    def metrics(self):
+        """The Client.Cache* counters of LocalCacheManager.Metrics (LocalCacheManager.java:557-627)."""
+        v = (C.c_int64 * len(self.METRICS))()
+        lib().orc_manager_metrics(self._h, v)
+        return dict(zip(self.METRICS, list(v)))
 
     def pages(self):
         return lib().orc_manager_pages(self._h)

@@ -124,6 +124,15 @@ int orc_manager_state(void* m) { return ((LocalCacheManager*)m)->state(); }
 int32_t orc_manager_page_lock_id(void* m, const char* f, int64_t i) {
   return ((LocalCacheManager*)m)->GetPageLockId(PageId{f, i});
 }
+// out[18], in the order of LocalCacheManager::Metrics (page_cache.h)
+void orc_manager_metrics(void* m, int64_t* out) {
+  const LocalCacheManager::Metrics& x = ((LocalCacheManager*)m)->metrics;
+  const int64_t v[18] = {x.bytesWrittenCache, x.bytesEvicted, x.pagesEvicted, x.getErrors, x.getNotReadyErrors,
+                         x.getStoreReadErrors, x.cleanupGetErrors, x.putErrors, x.putNotReadyErrors, x.putEvictionErrors,
+                         x.putStoreWriteErrors, x.putStoreDeleteErrors, x.putBenignRacingErrors, x.cleanupPutErrors,
+                         x.deleteErrors, x.deleteNotReadyErrors, x.deleteNonExistingPageErrors, x.deleteStoreDeleteErrors};
+  memcpy(out, v, sizeof(v));
+}
 int64_t orc_manager_bytes(void* m) { return ((LocalCacheManager*)m)->meta()->Bytes(); }
 int64_t orc_manager_pages(void* m) { return ((LocalCacheManager*)m)->meta()->Pages(); }
 

@@ -579,8 +579,14 @@ int32_t LocalCacheManager::GetPageLockId(const PageId& id) const {  // :172-174
 }
 
 bool LocalCacheManager::Put(const PageId& id, const uint8_t* page, int32_t len) {  // :206-246, sync write
-  if (mState != READ_WRITE) return false;
-  return PutInternal(id, page, len);
+  if (mState != READ_WRITE) {
+    metrics.putNotReadyErrors++;                                       // :209
+    metrics.putErrors++;                                               // :210
+    return false;
+  }
+  const bool ok = PutInternal(id, page, len);
+  if (!ok) metrics.putErrors++;                                        // :216-218
+  return ok;
 }
 
 bool LocalCacheManager::PutInternal(const PageId& id, const uint8_t* page, int32_t len) {  // :249-347
@@ -591,17 +597,25 @@ bool LocalCacheManager::PutInternal(const PageId& id, const uint8_t* page, int32
   if (enoughSpace) {
     mMetaStore->AddPage(id, PageInfo{id, len});                        // :263
   } else {
-    if (!mMetaStore->Evict(&victim)) return false;                     // :265-271
+    if (!mMetaStore->Evict(&victim)) {                                 // :265-271
+      metrics.putEvictionErrors++;                                     // :269
+      return false;
+    }
   }
   if (enoughSpace) {                                                   // :274-285
-    if (mPageStore->Put(id, page, len) == kOk) return true;
+    if (mPageStore->Put(id, page, len) == kOk) {
+      metrics.bytesWrittenCache += len;                                // :277
+      return true;
+    }
     UndoAddPage(id);
+    metrics.putStoreWriteErrors++;                                     // :282
     return false;
   }
   // two-phase commit :288-346
   if (mMetaStore->HasPage(id)) return true;                            // :296-300
   if (!mMetaStore->RemovePage(victim.pageId)) {                        // :301-309
     UndoAddPage(id);
+    metrics.putBenignRacingErrors++;                                   // :307
     return false;
   }
   enoughSpace = mMetaStore->Bytes() + len <= mCacheSize;               // :310
@@ -609,22 +623,38 @@ bool LocalCacheManager::PutInternal(const PageId& id, const uint8_t* page, int32
   StoreStatus del = mPageStore->Delete(victim.pageId);                 // :318-320 ALWAYS
   if (del != kOk) {
     if (enoughSpace) UndoAddPage(id);                                  // :323-326
+    metrics.putStoreDeleteErrors++;                                    // :328
     return false;
   }
+  metrics.bytesEvicted += victim.pageSize;                             // :320
+  metrics.pagesEvicted++;                                              // :321
   evicted.push_back(victim.pageId);
-  if (!enoughSpace) return false;                                      // :331-334 one victim per put
-  if (mPageStore->Put(id, page, len) == kOk) return true;              // :336-338
+  if (!enoughSpace) {                                                  // :331-334 one victim per put
+    metrics.putEvictionErrors++;                                       // :332
+    return false;
+  }
+  if (mPageStore->Put(id, page, len) == kOk) {                         // :336-338
+    metrics.bytesWrittenCache += len;                                  // :337
+    return true;
+  }
   UndoAddPage(id);                                                     // :339-344
+  metrics.putStoreWriteErrors++;                                       // :343
   return false;
 }
 
-void LocalCacheManager::UndoAddPage(const PageId& id) { mMetaStore->RemovePage(id); }  // :349-357
+void LocalCacheManager::UndoAddPage(const PageId& id) {  // :349-357
+  if (!mMetaStore->RemovePage(id)) metrics.cleanupPutErrors++;         // :354 (removePage threw)
+}
 
 int32_t LocalCacheManager::Get(const PageId& id, int32_t pageOffset, int32_t bytesToRead, uint8_t* buffer,
                                int32_t bufLen, int32_t offsetInBuffer) {  // :360-399
   if (!(pageOffset <= mPageSize)) return kGetIllegalArgument;             // :362-363
   if (!(bytesToRead <= bufLen - offsetInBuffer)) return kGetIllegalArgument;  // :364-366
-  if (mState == NOT_IN_USE) return -1;                                    // :368-372
+  if (mState == NOT_IN_USE) {                                             // :368-372
+    metrics.getNotReadyErrors++;
+    metrics.getErrors++;
+    return -1;
+  }
   if (!mMetaStore->HasPage(id)) return 0;                                 // :376-382
   // getPage :540-555
   int32_t ret = 0;
@@ -634,16 +664,31 @@ int32_t LocalCacheManager::Get(const PageId& id, int32_t pageOffset, int32_t byt
   if (st != kOk) bytesRead = -1;
   else bytesRead = (ret != bytesToRead) ? -1 : bytesToRead;                // :544-549
   if (bytesRead <= 0) {                                                   // :384-395
-    mMetaStore->RemovePage(id);
+    metrics.getErrors++;                                                  // :385
+    metrics.getStoreReadErrors++;                                         // :386
+    if (!mMetaStore->RemovePage(id)) metrics.cleanupGetErrors++;          // :389-393
     return -1;
   }
   return bytesRead;
 }
 
 bool LocalCacheManager::Delete(const PageId& id) {  // :402-429
-  if (mState != READ_WRITE) return false;
-  if (!mMetaStore->RemovePage(id)) return false;
-  return mPageStore->Delete(id) == kOk;  // deletePage :530-538
+  if (mState != READ_WRITE) {
+    metrics.deleteNotReadyErrors++;                                       // :405
+    metrics.deleteErrors++;                                               // :406
+    return false;
+  }
+  if (!mMetaStore->RemovePage(id)) {                                      // :411-419
+    metrics.deleteNonExistingPageErrors++;
+    metrics.deleteErrors++;
+    return false;
+  }
+  const bool ok = mPageStore->Delete(id) == kOk;  // deletePage :530-538
+  if (!ok) {                                                              // :422-427
+    metrics.deleteStoreDeleteErrors++;
+    metrics.deleteErrors++;
+  }
+  return ok;
 }
 
 void LocalCacheManager::RestoreOrInit() {  // :441-464

@@ -144,6 +144,14 @@ class LocalCacheManager {
   DefaultMetaStore* meta() { return mMetaStore.get(); }
   // victims evicted so far (pageIndex + fileId), for replay comparison
   std::vector<PageId> evicted;
+  // The Client.Cache* counters of LocalCacheManager.Metrics (:557-627), incremented where the reference increments them
+  // (the line of each increment is cited in page_cache.cc).  Names: MetricKey.CLIENT_CACHE_<NAME>.
+  struct Metrics {
+    int64_t bytesWrittenCache = 0, bytesEvicted = 0, pagesEvicted = 0, getErrors = 0, getNotReadyErrors = 0,
+            getStoreReadErrors = 0, cleanupGetErrors = 0, putErrors = 0, putNotReadyErrors = 0, putEvictionErrors = 0,
+            putStoreWriteErrors = 0, putStoreDeleteErrors = 0, putBenignRacingErrors = 0, cleanupPutErrors = 0,
+            deleteErrors = 0, deleteNotReadyErrors = 0, deleteNonExistingPageErrors = 0, deleteStoreDeleteErrors = 0;
+  } metrics;
  private:
   bool PutInternal(const PageId& id, const uint8_t* page, int32_t len);
   void UndoAddPage(const PageId& id);
