@@ -50,6 +50,7 @@ SIGNATURES = {
     "apc_manager_close": (C.c_int, [_vp]),
     "apc_get_noexcept": (_i32, [_vp, _cp, _i64, _i32, _i32, _vp, _i32, _i32]),
     "apc_metrics_read": (None, [_vp, _vp]),
+    "apc_metrics_read_more": (None, [_vp, _vp]),
     "apc_positioned_read_batched": (_i32, [_vp, _cp, _i64, _i64, _vp, _i32, EXTERNAL_READ, _vp, C.POINTER(_i64),
                                            C.POINTER(_i64)]),
     "apc_put": (C.c_int, [_vp, _cp, _i64, _vp, _i32]),
@@ -309,11 +310,16 @@ class LocalCacheManager:
                     "PagesEvicted", "GetErrors", "PutErrors", "DeleteErrors", "PutEvictionErrors", "PutStoreWriteErrors",
                     "PutStoreDeleteErrors", "GetStoreReadErrors", "DeleteNonExistingPageErrors")
 
+    MORE_METRIC_NAMES = ("GetNotReadyErrors", "DeleteNotReadyErrors", "DeleteStoreDeleteErrors", "PutBenignRacingErrors",
+                         "CleanupGetErrors", "CleanupPutErrors", "PutNotReadyErrors", "PutAsyncRejectionErrors")
+
     def metrics(self):
+        """The Client.Cache* counters of LocalCacheManager.Metrics (CACHE/LocalCacheManager.java:557-627)."""
         import numpy as np
-        v = np.zeros(14, np.int64)
+        v, w = np.zeros(14, np.int64), np.zeros(8, np.int64)
         lib().apc_metrics_read(self._h, v.ctypes.data)
-        return dict(zip(self.METRIC_NAMES, v.tolist()))
+        lib().apc_metrics_read_more(self._h, w.ctypes.data)
+        return dict(zip(self.METRIC_NAMES + self.MORE_METRIC_NAMES, v.tolist() + w.tolist()))
 
     def get_noexcept(self, p, bytes_to_read, buffer, offset_in_buffer=0, page_offset=0):
         cbuf = (C.c_uint8 * max(1, len(buffer))).from_buffer(buffer) if len(buffer) else (C.c_uint8 * 1)()

@@ -760,7 +760,8 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
     std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
     if (mMetaStore->HasPage(k)) return true;  // :296-300 a racing thread inserted it
     if (!mMetaStore->RemovePage(victim)) {     // :301-309 benign race: victim already gone
-      mMetaStore->RemovePage(k);
+      if (!mMetaStore->RemovePage(k)) metrics.cleanupPutErrors++;  // undoAddPage (:349-357)
+      metrics.putBenignRacingErrors++;
       return false;
     }
     enoughSpace = mMetaStore->Bytes() + len <= mCacheSize;                // :310
@@ -789,14 +790,15 @@ bool LocalCacheManager::PutInternal(const Key& k, int32_t lockId, const void* pa
 
 void LocalCacheManager::UndoAddPage(const Key& k) {  // :349-357
   std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
-  mMetaStore->RemovePage(k);
+  if (!mMetaStore->RemovePage(k)) metrics.cleanupPutErrors++;
 }
 
 int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int32_t pageOffset, int32_t bytesToRead,
                                void* buffer, int32_t bufLen, int32_t offsetInBuffer) {  // :360-399
   if (!(pageOffset <= mPageSize)) return kGetIllegalArgument;
   if (!(bytesToRead <= bufLen - offsetInBuffer)) return kGetIllegalArgument;
-  if (mState.load() == NOT_IN_USE) {  // :368-372 (GET_NOT_READY_ERRORS has no counter here; GET_ERRORS has)
+  if (mState.load() == NOT_IN_USE) {  // :368-372
+    metrics.getNotReadyErrors++;
     metrics.getErrors++;
     return -1;
   }
@@ -816,7 +818,7 @@ int32_t LocalCacheManager::Get(const std::string& fileId, int64_t pageIndex, int
   const int32_t bytesRead = (rc != APS_OK || got != bytesToRead) ? -1 : bytesToRead;
   if (bytesRead <= 0) {
     std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
-    mMetaStore->RemovePage(k);
+    if (!mMetaStore->RemovePage(k)) metrics.cleanupGetErrors++;  // :389-393
     metrics.getErrors++;
     metrics.getStoreReadErrors++;
     return -1;
@@ -869,6 +871,7 @@ void LocalCacheManager::GetMany(const std::string& fileId, int64_t firstPage, in
 
 bool LocalCacheManager::Delete(const std::string& fileId, int64_t pageIndex) {  // :402-429
   if (mState.load() != READ_WRITE) {
+    metrics.deleteNotReadyErrors++;
     metrics.deleteErrors++;
     return false;
   }
@@ -883,7 +886,10 @@ bool LocalCacheManager::Delete(const std::string& fileId, int64_t pageIndex) {  
     }
   }
   const bool ok = mPageStore->Delete(k) == APS_OK;
-  if (!ok) metrics.deleteErrors++;
+  if (!ok) {  // :422-427
+    metrics.deleteStoreDeleteErrors++;
+    metrics.deleteErrors++;
+  }
   return ok;
 }
 
@@ -1345,6 +1351,14 @@ void apc_metrics_read(apc_manager* m, int64_t* out14) {
                          c.pagesEvicted, c.getErrors, c.putErrors, c.deleteErrors, c.putEvictionErrors, c.putStoreWriteErrors,
                          c.putStoreDeleteErrors, c.getStoreReadErrors, c.deleteNonExistingPageErrors};
   memcpy(out14, v, sizeof(v));
+}
+
+void apc_metrics_read_more(apc_manager* m, int64_t* out8) {
+  const CacheMetrics& c = m->mgr->metrics;
+  const int64_t v[8] = {c.getNotReadyErrors, c.deleteNotReadyErrors, c.deleteStoreDeleteErrors, c.putBenignRacingErrors,
+                        c.cleanupGetErrors, c.cleanupPutErrors, m->mgr->putNotReadyErrors.load(),
+                        m->mgr->putAsyncRejectionErrors.load()};
+  memcpy(out8, v, sizeof(v));
 }
 
 // Multi-page read in one store call: LocalCacheFileInStream.positionedRead with the per-page

@@ -328,7 +328,9 @@ class TimeBoundPageStore : public PageStore {
 struct CacheMetrics {
   std::atomic<int64_t> bytesReadCache{0}, bytesRequestedExternal{0}, bytesReadExternal{0}, bytesWrittenCache{0},
       bytesEvicted{0}, pagesEvicted{0}, getErrors{0}, putErrors{0}, deleteErrors{0}, putEvictionErrors{0},
-      putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0};
+      putStoreWriteErrors{0}, putStoreDeleteErrors{0}, getStoreReadErrors{0}, deleteNonExistingPageErrors{0},
+      getNotReadyErrors{0}, deleteNotReadyErrors{0}, deleteStoreDeleteErrors{0}, putBenignRacingErrors{0},
+      cleanupGetErrors{0}, cleanupPutErrors{0};
 };
 
 // ---- CACHE/LocalCacheManager.java:75-627 -----------------------------------------------------------------

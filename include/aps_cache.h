@@ -120,6 +120,10 @@ APS_API int32_t apc_get_noexcept(apc_manager* m, const char* file_id, int64_t pa
  * PutEvictionErrors, PutStoreWriteErrors, PutStoreDeleteErrors, GetStoreReadErrors, DeleteNonExistingPageErrors
  * (core/common/src/main/java/alluxio/metrics/MetricKey.java:778-995). */
 APS_API void apc_metrics_read(apc_manager* m, int64_t* out14);
+/* The rest of LocalCacheManager.Metrics (CACHE/LocalCacheManager.java:557-627), in this order: GetNotReadyErrors,
+ * DeleteNotReadyErrors, DeleteStoreDeleteErrors, PutBenignRacingErrors, CleanupGetErrors, CleanupPutErrors,
+ * PutNotReadyErrors, PutAsyncRejectionErrors. */
+APS_API void apc_metrics_read_more(apc_manager* m, int64_t* out8);
 /* CacheManager.delete(PageId) -> boolean, CACHE/LocalCacheManager.java:402-429 */
 APS_API int apc_delete(apc_manager* m, const char* file_id, int64_t page_index);
 APS_API int apc_state(apc_manager* m);

@@ -65,7 +65,7 @@ def test_random_operations_equal_the_oracle_manager(evictor):
         if step % 50 == 49:                                     # the Client.Cache* counters both sides keep (LocalCacheManager.Metrics)
             mt, omt = m.metrics(), om.metrics()
             common = [k for k in omt if k in mt]
-            assert len(common) >= 11 and {k: mt[k] for k in common} == {k: omt[k] for k in common}, step
+            assert len(common) == len(omt) == 18 and {k: mt[k] for k in common} == omt, step
     mt = m.metrics()
     assert mt["PagesEvicted"] > 100 and mt["PutStoreWriteErrors"] + mt["PutStoreDeleteErrors"] > 0 and mt["GetErrors"] > 0
     m.set_store_faulty()
