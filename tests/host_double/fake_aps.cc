@@ -11,7 +11,7 @@
 //
 // Contract followed: include/aps.h, entry by entry (status codes, the length rule of aps_get, distinct keys in put and
 // delete batches, n <= max_batch, fault injection on the single-page calls only, idempotent close).  What it does not
-// model: CRC32C (results carry crc = 0; the host layer never reads it), device / pinned / pageable distinctions (all memory is host memory), the batch size of
+// model: CRC32C VERIFICATION (results carry the CRC32C of the bytes moved, nothing is checked against a recorded one), device / pinned / pageable distinctions (all memory is host memory), the batch size of
 // aps_iterate's walk order (here: insertion-independent map order; the real store walks its hash table).
 #include <algorithm>
 #include <cstdlib>
@@ -27,6 +27,19 @@ namespace {
 
 using KeyT = std::tuple<uint64_t, uint64_t, uint64_t>;
 KeyT K(const aps_key& k) { return KeyT(k.file_hi, k.file_lo, k.page_index); }
+
+// CRC-32C (RFC 3720) of the bytes a call moves, as the library reports it in aps_result.crc (SSE4.2 crc32 instruction).
+__attribute__((target("sse4.2"))) uint32_t crc32c(const uint8_t* p, size_t n) {
+  uint64_t c = 0xFFFFFFFFu;
+  size_t i = 0;
+  for (; i + 8 <= n; i += 8) {
+    uint64_t w;
+    memcpy(&w, p + i, 8);
+    c = __builtin_ia32_crc32di(c, w);
+  }
+  for (; i < n; ++i) c = __builtin_ia32_crc32qi((uint32_t)c, p[i]);
+  return ~(uint32_t)c;
+}
 
 uint64_t mix64(uint64_t z) {
   z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -57,7 +70,7 @@ aps_result get_one(aps_store* s, const aps_get_req& r) {
   if (r.page_off > page.size()) return aps_result{-APS_EINVAL, 0};
   const uint32_t n = (uint32_t)std::min<uint64_t>(page.size() - r.page_off, r.nbytes);
   if (n) memcpy(r.dst, page.data() + r.page_off, n);
-  return aps_result{(int32_t)n, 0};
+  return aps_result{(int32_t)n, (s->cfg.flags & APS_FLAG_CRC) ? crc32c(page.data() + r.page_off, n) : 0u};
 }
 
 aps_result put_one(aps_store* s, const aps_put_req& r) {
@@ -66,8 +79,9 @@ aps_result put_one(aps_store* s, const aps_put_req& r) {
   if (it == s->pages.end() && s->pages.size() >= s->cfg.slab_slots) return aps_result{-APS_ENOSPC, 0};
   const uint8_t* src = static_cast<const uint8_t*>(r.src);
   std::vector<uint8_t> bytes(src, src + r.len);
+  const uint32_t crc = (s->cfg.flags & APS_FLAG_CRC) ? crc32c(bytes.data(), bytes.size()) : 0u;
   s->pages[K(r.key)] = std::move(bytes);
-  return aps_result{(int32_t)r.len, 0};
+  return aps_result{(int32_t)r.len, crc};
 }
 
 template <typename KeyOf>

@@ -23,6 +23,9 @@ GPU_ONLY = {
     "test_gpu_sharded_manager": set(),
     "test_gpu_z_reference_manager": set(),
     "test_gpu_z_host_layer_vs_oracle": set(),
+    # the PageStore contract cases (PageStoreTest ports, random ops against the oracle's LocalPageStore): over the double
+    # they show that the stand-in itself follows the contract the GPU store is tested against
+    "test_gpu_page_store": {"test_crc_detects_a_flipped_byte"},   # flips a byte in the HBM slab
 }
 
 
@@ -55,11 +58,18 @@ def _cases():
 def test_gpu_case_over_the_double(mod_name, name, params, request):
     fn = getattr(importlib.import_module(mod_name), name)
     kwargs = dict(params)
-    for arg in fn.__code__.co_varnames[:fn.__code__.co_argcount]:
-        if arg not in kwargs:
-            kwargs[arg] = request.getfixturevalue(arg)
     with host_double.host_layer_over_double():
+        for arg in fn.__code__.co_varnames[:fn.__code__.co_argcount]:
+            if arg in kwargs:
+                continue
+            if arg == "store":                                   # the fixture of test_gpu_page_store.py, made over the double
+                from alluxio_b200.page_store import GpuPageStore
+                kwargs[arg] = GpuPageStore(page_size=1024, cache_size=65536, slab_slots=256)
+            else:
+                kwargs[arg] = request.getfixturevalue(arg)
         fn(**kwargs)
+        if "store" in kwargs:
+            kwargs["store"].close()
 
 
 def test_the_double_routes_like_the_library():
