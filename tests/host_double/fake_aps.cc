@@ -285,6 +285,8 @@ APS_API int aps_snapshot_save_names(aps_store*, const char*, uint32_t, const cha
 APS_API int aps_snapshot_names(const char*, aps_name_cb, void*) { return APS_EIO; }
 APS_API int aps_snapshot_load(aps_store*, const char*, uint64_t*, uint64_t*) { return APS_EIO; }
 
+APS_API const char* aps_last_cuda_error(void) { return ""; }
+
 APS_API const char* aps_strerror(int code) {
   static const char* const names[] = {"ok", "page not found", "invalid argument", "no space", "CUDA error", "corrupt page",
                                       "store closed", "out of memory", "injected fault", "limit", "I/O error", "timeout"};

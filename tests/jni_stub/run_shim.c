@@ -4,7 +4,8 @@
  * under test is the shim's own code: argument unpacking, which array is written back and which is released with
  * JNI_ABORT, every Get paired with a Release, statuses and per-request results reaching the Java arrays, the direct-buffer
  * offsets of the batched calls.  Built with AddressSanitizer + UBSan by tests/test_jni_shim_runs.py.
- * aps_md5_batch is answered by the oracle's RFC 1321 MD5 here (the kernel is tested in tests/test_gpu_md5.py). */
+ * aps_md5_batch is answered by the oracle's RFC 1321 MD5 here (tests/host_double/md5_via_oracle.c; the kernel is tested in
+ * tests/test_gpu_md5.py). */
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -12,13 +13,7 @@
 #include "fake_env.h"
 #include "../../integration/jni/aps_jni.c" /* the shim itself, compiled into this test */
 
-void orc_md5(const void* data, size_t n, uint8_t out[16]); /* oracle/checksums.c */
-int aps_md5_batch(int32_t device, uint32_t n_files, const void* const* data, const uint64_t* len, uint8_t (*out)[16]) {
-  uint32_t i;
-  (void)device;
-  for (i = 0; i < n_files; ++i) orc_md5(data[i], (size_t)len[i], out[i]);
-  return APS_OK;
-}
+void orc_md5(const void* data, size_t n, uint8_t out[16]); /* oracle/checksums.c; aps_md5_batch: tests/host_double/md5_via_oracle.c */
 
 static int g_failures = 0;
 #define CHECK(cond, ...)                                     \
