@@ -185,3 +185,24 @@ def test_time_bound_store_concurrent_puts_with_a_large_pool():
     for k in range(n):
         assert m.get(PID("0L", k), PS, buf) == PS and bytes(buf) == page
     m.close()
+
+
+def test_async_restore_with_more_pages_than_capacity():
+    """LocalCacheManagerTest.asyncRestoreWithMorePagesThanCapacity (:513-529): the restore thread adopts what fits and
+    deletes the rest from the store; the manager is READ_WRITE afterwards."""
+    from alluxio_b200.cache import LocalCacheManager
+    from alluxio_b200.page_store import GpuPageStore
+    store = GpuPageStore(page_size=PS, cache_size=2 * PS, slab_slots=16)
+    for i in range(3):
+        store.put(PID("5", i), increasing(i, PS))
+    m = LocalCacheManager.create(PS, 2 * PS, over=store, async_restore=True)
+    m.wait_async()
+    assert m.state() == m.READ_WRITE and (m.pages(), m.bytes()) == (2, 2 * PS)
+    assert len(store.get_pages()) == 2
+    buf = bytearray(PS)
+    hits = [i for i in range(3) if m.get(PID("5", i), PS, buf) == PS and bytes(buf) == increasing(i, PS)]
+    assert len(hits) == 2
+    assert m.put(PID("6", 0), increasing(PS))                  # room is made the usual way: one victim
+    assert (m.pages(), m.bytes()) == (2, 2 * PS)
+    m.close()
+    store.close()
