@@ -206,3 +206,33 @@ def test_async_restore_with_more_pages_than_capacity():
     assert (m.pages(), m.bytes()) == (2, 2 * PS)
     m.close()
     store.close()
+
+
+def test_positioned_reads_through_the_manager_equal_the_oracle_stream():
+    """apc_positioned_read -- LocalCacheFileInStream.positionedRead as a call on the manager (CACHE/LocalCacheFileInStream
+    .java:175-223) -- against the oracle's stream over the oracle's manager, two files sharing a cache under pressure:
+    bytes, end-of-file answers, how many bytes came from the cache and from outside, and the cache's size after every call."""
+    cap = 10
+    m = _manager(cache_size=cap * PS)
+    om = orc.LocalCacheManager(orc.PageStore.open_mem(PS, cap * PS), PS, "LRU")
+    rng = np.random.default_rng(31)
+    files = {"811": rng.integers(0, 256, 13 * PS + 5, dtype=np.uint8).tobytes(), "812": rng.integers(0, 256, 4 * PS, dtype=np.uint8).tobytes()}
+    ostreams = {f: orc.LocalCacheFileInStream(om, f, len(d), (lambda d: lambda pos, n: d[pos:pos + n])(d), PS) for f, d in files.items()}
+    for step in range(300):
+        f = "811" if rng.integers(3) else "812"
+        d = files[f]
+        pos, n = int(rng.integers(0, len(d) + PS)), int(rng.integers(0, 4 * PS))
+        before = ostreams[f].counters()
+        got, from_cache, from_external = m.positioned_read(f, len(d), pos, n, lambda p, k: d[p:p + k])
+        b = bytearray(n)
+        r = ostreams[f].positioned_read(pos, b)
+        after = ostreams[f].counters()
+        if r < 0:
+            assert got is None, (step, f, pos, n)
+        else:
+            assert got == bytes(b[:r]) == d[pos:pos + n], (step, f, pos, n)
+            assert from_cache == after["BytesReadCache"] - before["BytesReadCache"], (step, f, pos, n)
+            assert from_external == after["BytesRequestedExternal"] - before["BytesRequestedExternal"], (step, f, pos, n)
+        assert (m.pages(), m.bytes()) == (om.pages(), om.bytes()), step
+    assert m.pages() == cap
+    m.close()
