@@ -895,11 +895,37 @@ bool LocalCacheManager::Delete(const std::string& fileId, int64_t pageIndex) {  
 
 void LocalCacheManager::RestoreOrInit() {  // :441-464
   if (!Restore()) {
-    mMetaStore->Reset();
-    mState = NOT_IN_USE;  // a GPU store cannot be "re-created in place"; the caller falls back (FileSystem.java:156-158)
-    return;
+    {
+      std::unique_lock<std::shared_mutex> metaLock(mMetaLock);
+      mMetaStore->Reset();
+    }
+    // The reference closes the store and creates it anew (PageStore.create wipes the cache directory) and goes on
+    // READ_WRITE with an empty cache; only if that fails is the cache NOT_IN_USE and the caller falls back
+    // (FileSystem.java:156-158).  A GPU store is emptied in place.
+    if (!WipeStore()) {
+      mState = NOT_IN_USE;
+      return;
+    }
   }
   mState = READ_WRITE;
+}
+
+bool LocalCacheManager::WipeStore() {
+  std::vector<std::pair<Key, int64_t>> pages;
+  if (mPageStore->GetPages(&pages) != APS_OK) return false;
+  constexpr size_t kChunk = 1024;  // well below any store's max_batch
+  std::vector<aps_key> keys;
+  std::vector<aps_result> res;
+  for (size_t lo = 0; lo < pages.size(); lo += kChunk) {
+    const size_t n = std::min(kChunk, pages.size() - lo);
+    keys.clear();
+    for (size_t i = 0; i < n; ++i) keys.push_back(aps_key{pages[lo + i].first.hi, pages[lo + i].first.lo, pages[lo + i].first.idx});
+    res.assign(n, aps_result{0, 0});
+    if (mPageStore->DeleteBatch((uint32_t)n, keys.data(), res.data()) != APS_OK) return false;
+    for (const aps_result& r : res)
+      if (r.len < 0 && r.len != -APS_ENOTFOUND) return false;
+  }
+  return true;
 }
 
 bool LocalCacheManager::Restore() {  // :466-509

@@ -377,6 +377,7 @@ class LocalCacheManager {
   void UndoAddPage(const Key& k);
   void RestoreOrInit();
   bool Restore();
+  bool WipeStore();  // PageStore.create over a store that is emptied in place (the reference wipes the cache directory)
   ManagerOptions mOptions;
   std::unique_ptr<HandOffPool> mAsyncCacheExecutor;
   std::thread mInitService;

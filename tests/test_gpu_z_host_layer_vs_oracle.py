@@ -236,3 +236,31 @@ def test_positioned_reads_through_the_manager_equal_the_oracle_stream():
         assert (m.pages(), m.bytes()) == (om.pages(), om.bytes()), step
     assert m.pages() == cap
     m.close()
+
+
+def test_a_failed_restore_wipes_the_store_and_the_cache_goes_on_empty():
+    """restoreOrInit (CACHE/LocalCacheManager.java:441-464): when restore fails, the meta store is reset, the page store
+    is created anew (emptied) and the cache is READ_WRITE and empty -- LocalCacheManagerTest.syncRestoreUnknownFile
+    (:402-420) ends that way.  A GPU store holds no unknown files, so the failure is injected where the reference's
+    FaultyPageStore injects it: the delete of the page that does not fit (:493-497)."""
+    from alluxio_b200.cache import LocalCacheManager
+    from alluxio_b200.page_store import GpuPageStore
+    store = GpuPageStore(page_size=PS, cache_size=2 * PS, slab_slots=16)
+    ref_store = orc.PageStore.open_mem(PS, 2 * PS)
+    for i in range(3):                                         # three pages, room for two
+        store.put(PID("5", i), increasing(i, PS))
+        ref_store.put(orc.PageId("5", i), increasing(i, PS))
+    store.set_faulty(delete=True)
+    ref_store.set_faulty(delete=True)
+    m = LocalCacheManager.over_store(store, PS, "LRU")
+    om = orc.LocalCacheManager(ref_store, PS, "LRU")
+    assert m.state() == om.state() == m.READ_WRITE
+    assert (m.pages(), m.bytes()) == (om.pages(), om.bytes()) == (0, 0)
+    assert store.get_pages() == [] and ref_store.get_pages() == []
+    store.set_faulty()
+    ref_store.set_faulty()
+    buf = bytearray(PS)
+    assert m.get(PID("5", 0), PS, buf) == om.get(orc.PageId("5", 0), PS, bytearray(PS)) == 0
+    assert m.put(PID("5", 0), increasing(9, PS)) and m.get(PID("5", 0), PS, buf) == PS and bytes(buf) == increasing(9, PS)
+    m.close()
+    store.close()
