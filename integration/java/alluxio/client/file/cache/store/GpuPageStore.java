@@ -36,7 +36,8 @@ public class GpuPageStore implements PageStore {
   private static final int ENOTFOUND = 1;
   private static final int EINVAL = 2;
 
-  private final long mHandle;
+  /** One native store per GPU; a page lives in the store of GPU nativeShardOf(key, mHandles.length). */
+  private final long[] mHandles;
   private final long mCacheSize;
   private final int mPageSize;
   /** Interned file ids that are neither decimal longs nor 32-hex strings (exact, never hashed). */
@@ -52,21 +53,54 @@ public class GpuPageStore implements PageStore {
   public GpuPageStore(GpuPageStoreOptions options) throws IOException {
     mCacheSize = options.getCacheSize();
     mPageSize = (int) options.getPageSize();
-    long[] handle = new long[1];
-    int rc = nativeOpen(options.getDevice(), mPageSize, mCacheSize, options.getSlabSlots(),
-        options.getTableCapacity(), options.getMaxBatch(), options.isCrcEnabled() ? 1 : 0, handle);
-    if (rc != OK) {
-      throw new IOException("aps_open failed: " + nativeStrError(rc));
+    // alluxio.user.client.cache.gpu.device: a CUDA ordinal, or -1 for one shard of the cache on every visible GPU.
+    // The cache stays ONE cache: LocalCacheManager, its meta store, its evictor and its byte budget are untouched.
+    int[] devices;
+    if (options.getDevice() >= 0) {
+      devices = new int[] {options.getDevice()};
+    } else {
+      devices = new int[Math.max(1, nativeDeviceCount())];
+      for (int d = 0; d < devices.length; d++) {
+        devices[d] = d;
+      }
     }
-    mHandle = handle[0];
+    int shards = devices.length;
+    long pages = (mCacheSize + mPageSize - 1) / mPageSize;
+    // hash routing balances only on average: every shard gets its share of the budget plus a quarter plus 64 slots
+    long share = (pages + shards - 1) / shards;
+    long slots = options.getSlabSlots() != 0 || shards == 1 ? options.getSlabSlots() : share + share / 4 + 64;
+    long shardBytes = shards == 1 ? mCacheSize : slots * (long) mPageSize;
+    mHandles = new long[shards];
+    for (int i = 0; i < shards; i++) {
+      long[] handle = new long[1];
+      int rc = nativeOpen(devices[i], mPageSize, shardBytes, slots, options.getTableCapacity(),
+          options.getMaxBatch(), options.isCrcEnabled() ? 1 : 0, handle);
+      if (rc != OK) {
+        for (int j = 0; j < i; j++) {
+          nativeClose(mHandles[j]);
+        }
+        throw new IOException("aps_open failed on GPU " + devices[i] + ": " + nativeStrError(rc));
+      }
+      mHandles[i] = handle[0];
+    }
+    for (int i = 0; shards > 1 && i < shards; i++) {
+      int rc = nativeShardAttachLocal(mHandles, i); // lets a batched get of shard 0 read every owner over NVLink
+      if (rc != OK) {
+        for (long handle : mHandles) {
+          nativeClose(handle);
+        }
+        throw new IOException("aps_shard_attach_local failed: " + nativeStrError(rc));
+      }
+    }
     mStaging = ThreadLocal.withInitial(() -> allocPinned(mPageSize));
-    mSnapshotPath = options.getSnapshotPath();
+    // a snapshot is one file per store; with several shards the cache simply starts cold
+    mSnapshotPath = shards == 1 ? options.getSnapshotPath() : null;
     if (mSnapshotPath != null && new java.io.File(mSnapshotPath).exists()) {
       // warm restart: getPages() then lists these pages and LocalCacheManager.restore adopts them.  Ids that are neither
       // decimal nor 32-hex were interned by the process that wrote the snapshot: take its table over first.
       String[] names = nativeSnapshotNames(mSnapshotPath);
       long[] counts = new long[2];
-      rc = names == null ? EINVAL : OK;
+      int rc = names == null ? EINVAL : OK;
       if (rc == OK) {
         synchronized (mInternedNames) {
           for (String name : names) {
@@ -74,7 +108,7 @@ public class GpuPageStore implements PageStore {
             mInternedNames.add(name);
           }
         }
-        rc = nativeSnapshotLoad(mHandle, mSnapshotPath, counts);
+        rc = nativeSnapshotLoad(mHandles[0], mSnapshotPath, counts);
       }
       if (rc != OK) {
         LOG.warn("ignoring snapshot {}: {}", mSnapshotPath, nativeStrError(rc));
@@ -119,6 +153,12 @@ public class GpuPageStore implements PageStore {
     return new long[] {-1L, n};
   }
 
+  /** The store that owns the page: hash(PageId) mod shards, the same routing the native side uses. */
+  private long handleOf(long[] k, long pageIndex) {
+    return mHandles.length == 1 ? mHandles[0]
+        : mHandles[nativeShardOf(k[0], k[1], pageIndex, mHandles.length)];
+  }
+
   @Override
   public void put(PageId pageId, byte[] page) throws IOException {
     if (page.length > mPageSize) {
@@ -128,7 +168,8 @@ public class GpuPageStore implements PageStore {
     ByteBuffer staging = mStaging.get();
     staging.clear();
     staging.put(page);
-    int rc = nativePut(mHandle, k[0], k[1], pageId.getPageIndex(), staging, page.length);
+    int rc = nativePut(handleOf(k, pageId.getPageIndex()), k[0], k[1], pageId.getPageIndex(), staging,
+        page.length);
     if (rc != OK) {
       throw new IOException("Failed to put page " + pageId + ": " + nativeStrError(rc));
     }
@@ -144,7 +185,7 @@ public class GpuPageStore implements PageStore {
     ByteBuffer staging = mStaging.get();
     int room = Math.min(buffer.length - bufferOffset, mPageSize);
     int[] outLen = new int[1];
-    int rc = nativeGet(mHandle, k[0], k[1], pageId.getPageIndex(), pageOffset,
+    int rc = nativeGet(handleOf(k, pageId.getPageIndex()), k[0], k[1], pageId.getPageIndex(), pageOffset,
         Math.max(0, bytesToRead), staging, room, outLen);
     if (rc == ENOTFOUND) {
       throw new PageNotFoundException(pageId.toString());
@@ -163,7 +204,7 @@ public class GpuPageStore implements PageStore {
   @Override
   public void delete(PageId pageId) throws IOException, PageNotFoundException {
     long[] k = fileKey(pageId.getFileId());
-    int rc = nativeDelete(mHandle, k[0], k[1], pageId.getPageIndex());
+    int rc = nativeDelete(handleOf(k, pageId.getPageIndex()), k[0], k[1], pageId.getPageIndex());
     if (rc == ENOTFOUND) {
       throw new PageNotFoundException(pageId.toString());
     }
@@ -175,11 +216,18 @@ public class GpuPageStore implements PageStore {
   @Override
   public Stream<PageInfo> getPages() throws IOException {
     // long[3n + ...]: (fileHi, fileLo, pageIndex, length) per resident page
-    long[] flat = nativeIterate(mHandle);
-    if (flat == null) {
-      throw new IOException("Failed to list the pages of the GPU store");
+    List<PageInfo> pages = new ArrayList<>();
+    for (long handle : mHandles) {
+      long[] flat = nativeIterate(handle);
+      if (flat == null) {
+        throw new IOException("Failed to list the pages of the GPU store");
+      }
+      addPages(flat, pages);
     }
-    List<PageInfo> pages = new ArrayList<>(flat.length / 4);
+    return pages.stream();
+  }
+
+  private void addPages(long[] flat, List<PageInfo> pages) {
     for (int i = 0; i + 3 < flat.length; i += 4) {
       String fileId;
       if (flat[i] == 0L) {
@@ -193,7 +241,6 @@ public class GpuPageStore implements PageStore {
       }
       pages.add(new PageInfo(new PageId(fileId, flat[i + 2]), flat[i + 3]));
     }
-    return pages.stream();
   }
 
   @Override
@@ -211,12 +258,16 @@ public class GpuPageStore implements PageStore {
       synchronized (mInternedNames) {
         names = mInternedNames.toArray(new String[0]);
       }
-      int rc = nativeSnapshotSave(mHandle, mSnapshotPath, names);
+      int rc = nativeSnapshotSave(mHandles[0], mSnapshotPath, names);
       if (rc != OK) {
         LOG.warn("could not save snapshot {}: {}", mSnapshotPath, nativeStrError(rc));
       }
     }
-    nativeClose(mHandle);
+    for (long handle : mHandles) {
+      if (handle != 0) {
+        nativeClose(handle);
+      }
+    }
     synchronized (mPinned) {
       for (ByteBuffer b : mPinned) {
         nativeFreePinned(b);
@@ -239,6 +290,27 @@ public class GpuPageStore implements PageStore {
     return keys;
   }
 
+  /** Owner shard of every request (3 longs each in keys). */
+  private int[] ownersOf(long[] keys) {
+    int[] owners = new int[keys.length / 3];
+    for (int i = 0; mHandles.length > 1 && i < owners.length; i++) {
+      owners[i] = nativeShardOf(keys[3 * i], keys[3 * i + 1], keys[3 * i + 2], mHandles.length);
+    }
+    return owners;
+  }
+
+  /** Positions of the requests whose page lives on the given shard. */
+  private static int[] ownedBy(int[] owners, int shard) {
+    int[] mine = new int[owners.length];
+    int count = 0;
+    for (int i = 0; i < owners.length; i++) {
+      if (owners[i] == shard) {
+        mine[count++] = i;
+      }
+    }
+    return java.util.Arrays.copyOf(mine, count);
+  }
+
   /**
    * Reads bytesToRead[i] bytes of page ids[i] from pageOffsets[i] into dst at dstOffsets[i], all in one call.
    *
@@ -252,7 +324,10 @@ public class GpuPageStore implements PageStore {
     int n = ids.length;
     int[] outLen = new int[n];
     int[] crc = outCrc != null ? outCrc : new int[n];
-    int rc = nativeGetBatch(mHandle, n, keysOf(ids), pageOffsets, bytesToRead, dst, dstOffsets, outLen, crc);
+    // several shards: ONE kernel on shard 0 that probes every owner's table and reads its slab in place (NVLink)
+    int rc = mHandles.length == 1
+        ? nativeGetBatch(mHandles[0], n, keysOf(ids), pageOffsets, bytesToRead, dst, dstOffsets, outLen, crc)
+        : nativeGetBatchSharded(mHandles[0], n, keysOf(ids), pageOffsets, bytesToRead, dst, dstOffsets, outLen, crc);
     if (rc != OK) {
       throw new IOException("Failed to read " + n + " pages: " + nativeStrError(rc));
     }
@@ -269,9 +344,29 @@ public class GpuPageStore implements PageStore {
     Preconditions.checkArgument(src.isDirect(), "the source must be a direct buffer");
     int n = ids.length;
     int[] status = new int[n];
-    int rc = nativePutBatch(mHandle, n, keysOf(ids), src, srcOffsets, lengths, status, new int[n]);
-    if (rc != OK) {
-      throw new IOException("Failed to put " + n + " pages: " + nativeStrError(rc));
+    long[] keys = keysOf(ids);
+    int[] owners = ownersOf(keys);
+    for (int shard = 0; shard < mHandles.length; shard++) { // puts go to the owner: one call per shard that owns any
+      int[] mine = ownedBy(owners, shard);
+      if (mine.length == 0) {
+        continue;
+      }
+      long[] k = new long[3 * mine.length];
+      long[] off = new long[mine.length];
+      int[] len = new int[mine.length];
+      int[] st = new int[mine.length];
+      for (int j = 0; j < mine.length; j++) {
+        System.arraycopy(keys, 3 * mine[j], k, 3 * j, 3);
+        off[j] = srcOffsets[mine[j]];
+        len[j] = lengths[mine[j]];
+      }
+      int rc = nativePutBatch(mHandles[shard], mine.length, k, src, off, len, st, new int[mine.length]);
+      if (rc != OK) {
+        throw new IOException("Failed to put " + mine.length + " pages: " + nativeStrError(rc));
+      }
+      for (int j = 0; j < mine.length; j++) {
+        status[mine[j]] = st[j];
+      }
     }
     for (int i = 0; i < n; i++) {
       if (status[i] != OK) {
@@ -284,9 +379,25 @@ public class GpuPageStore implements PageStore {
   public boolean[] deleteBatch(PageId[] ids) throws IOException {
     int n = ids.length;
     int[] status = new int[n];
-    int rc = nativeDeleteBatch(mHandle, n, keysOf(ids), status);
-    if (rc != OK) {
-      throw new IOException("Failed to delete " + n + " pages: " + nativeStrError(rc));
+    long[] keys = keysOf(ids);
+    int[] owners = ownersOf(keys);
+    for (int shard = 0; shard < mHandles.length; shard++) {
+      int[] mine = ownedBy(owners, shard);
+      if (mine.length == 0) {
+        continue;
+      }
+      long[] k = new long[3 * mine.length];
+      int[] st = new int[mine.length];
+      for (int j = 0; j < mine.length; j++) {
+        System.arraycopy(keys, 3 * mine[j], k, 3 * j, 3);
+      }
+      int rc = nativeDeleteBatch(mHandles[shard], mine.length, k, st);
+      if (rc != OK) {
+        throw new IOException("Failed to delete " + mine.length + " pages: " + nativeStrError(rc));
+      }
+      for (int j = 0; j < mine.length; j++) {
+        status[mine[j]] = st[j];
+      }
     }
     boolean[] present = new boolean[n];
     for (int i = 0; i < n; i++) {
@@ -335,4 +446,9 @@ public class GpuPageStore implements PageStore {
   private static native int nativeMd5Batch(int device, int n, ByteBuffer pinned, long[] offsets, long[] lengths,
       byte[] digests);
   private static native int nativeSnapshotLoad(long handle, String path, long[] loadedAndRejected);
+  private static native int nativeDeviceCount();
+  private static native int nativeShardOf(long fileHi, long fileLo, long pageIndex, int shards);
+  private static native int nativeShardAttachLocal(long[] handles, int myShard);
+  private static native int nativeGetBatchSharded(long handle, int n, long[] keys, int[] pageOffsets, int[] bytesToRead,
+      ByteBuffer buffer, long[] offsets, int[] outLen, int[] outCrc);
 }

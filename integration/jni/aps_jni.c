@@ -98,8 +98,8 @@ JNIEXPORT jlongArray JNICALL JFN(nativeIterate)(JNIEnv* env, jclass cls, jlong h
 
 /* ---- batched calls: ONE aps_*_batch call per JNI call; pages move through one direct ByteBuffer ------------------
  * (GetDirectBufferAddress: no copy, no pinning by the JVM).  The marshalling itself is in aps_marshal.h. */
-JNIEXPORT jint JNICALL JFN(nativeGetBatch)(JNIEnv* env, jclass cls, jlong handle, jint n, jlongArray keys, jintArray page_off,
-                                           jintArray nbytes, jobject buffer, jlongArray off, jintArray out_len, jintArray out_crc) {
+static jint get_batch(JNIEnv* env, int sharded, jlong handle, jint n, jlongArray keys, jintArray page_off, jintArray nbytes,
+                      jobject buffer, jlongArray off, jintArray out_len, jintArray out_crc) {
   jlong* k = (*env)->GetLongArrayElements(env, keys, NULL);
   jint* po = (*env)->GetIntArrayElements(env, page_off, NULL);
   jint* nb = (*env)->GetIntArrayElements(env, nbytes, NULL);
@@ -108,16 +108,56 @@ JNIEXPORT jint JNICALL JFN(nativeGetBatch)(JNIEnv* env, jclass cls, jlong handle
   jint* oc = (*env)->GetIntArrayElements(env, out_crc, NULL);
   void* base = (*env)->GetDirectBufferAddress(env, buffer);
   int rc = (k && po && nb && of && ol && oc && base)
-               ? aps_marshal_get_batch((aps_store*)(intptr_t)handle, n, (const int64_t*)k, (const int32_t*)po, (const int32_t*)nb, base,
-                                       (const int64_t*)of, (int32_t*)ol, (int32_t*)oc)
+               ? aps_marshal_get_batch_ex((aps_store*)(intptr_t)handle, sharded, n, (const int64_t*)k, (const int32_t*)po,
+                                          (const int32_t*)nb, base, (const int64_t*)of, (int32_t*)ol, (int32_t*)oc)
                : APS_EINVAL;
-  (void)cls;
   if (oc) (*env)->ReleaseIntArrayElements(env, out_crc, oc, 0);
   if (ol) (*env)->ReleaseIntArrayElements(env, out_len, ol, 0);
   if (of) (*env)->ReleaseLongArrayElements(env, off, of, JNI_ABORT);
   if (nb) (*env)->ReleaseIntArrayElements(env, nbytes, nb, JNI_ABORT);
   if (po) (*env)->ReleaseIntArrayElements(env, page_off, po, JNI_ABORT);
   if (k) (*env)->ReleaseLongArrayElements(env, keys, k, JNI_ABORT);
+  return rc;
+}
+JNIEXPORT jint JNICALL JFN(nativeGetBatch)(JNIEnv* env, jclass cls, jlong handle, jint n, jlongArray keys, jintArray page_off,
+                                           jintArray nbytes, jobject buffer, jlongArray off, jintArray out_len, jintArray out_crc) {
+  (void)cls;
+  return get_batch(env, 0, handle, n, keys, page_off, nbytes, buffer, off, out_len, out_crc);
+}
+/* The same over a cache sharded across the GPUs of the box: `handle` is shard 0, every page comes from its owner. */
+JNIEXPORT jint JNICALL JFN(nativeGetBatchSharded)(JNIEnv* env, jclass cls, jlong handle, jint n, jlongArray keys,
+                                                  jintArray page_off, jintArray nbytes, jobject buffer, jlongArray off,
+                                                  jintArray out_len, jintArray out_crc) {
+  (void)cls;
+  return get_batch(env, 1, handle, n, keys, page_off, nbytes, buffer, off, out_len, out_crc);
+}
+
+/* ---- one cache over several GPUs: a page lives in the store of GPU aps_shard_of(key, shards) ---------------------- */
+JNIEXPORT jint JNICALL JFN(nativeDeviceCount)(JNIEnv* env, jclass cls) {
+  int n = 0;
+  (void)env;
+  (void)cls;
+  return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+JNIEXPORT jint JNICALL JFN(nativeShardOf)(JNIEnv* env, jclass cls, jlong hi, jlong lo, jlong idx, jint shards) {
+  aps_key k = {(uint64_t)hi, (uint64_t)lo, (uint64_t)idx};
+  (void)env;
+  (void)cls;
+  return (jint)aps_shard_of(&k, (uint32_t)shards);
+}
+/* handles = the stores of all shards (GpuPageStore.mHandles); lets shard my_shard read the others in place. */
+JNIEXPORT jint JNICALL JFN(nativeShardAttachLocal)(JNIEnv* env, jclass cls, jlongArray handles, jint my_shard) {
+  jsize n = (*env)->GetArrayLength(env, handles), i;
+  jlong* h = (*env)->GetLongArrayElements(env, handles, NULL);
+  aps_store** stores = h ? (aps_store**)calloc((size_t)n, sizeof(*stores)) : NULL;
+  int rc = APS_ENOMEM;
+  (void)cls;
+  if (stores) {
+    for (i = 0; i < n; ++i) stores[i] = (aps_store*)(intptr_t)h[i];
+    rc = my_shard >= 0 && my_shard < n ? aps_shard_attach_local(stores[my_shard], (uint32_t)n, (uint32_t)my_shard, stores) : APS_EINVAL;
+  }
+  free(stores);
+  if (h) (*env)->ReleaseLongArrayElements(env, handles, h, JNI_ABORT);
   return rc;
 }
 

@@ -15,8 +15,10 @@
 
 #include "aps.h"
 
-static int aps_marshal_get_batch(aps_store* s, int32_t n, const int64_t* keys, const int32_t* page_off, const int32_t* nbytes,
-                                 void* base, const int64_t* off, int32_t* out_len, int32_t* out_crc) {
+/* sharded != 0: the store is shard 0 of a set attached with aps_shard_attach_local; every request is served from the store
+ * that owns its key (aps_get_batch_sharded). */
+static inline int aps_marshal_get_batch_ex(aps_store* s, int sharded, int32_t n, const int64_t* keys, const int32_t* page_off,
+                                    const int32_t* nbytes, void* base, const int64_t* off, int32_t* out_len, int32_t* out_crc) {
   aps_get_req* rq;
   aps_result* rs;
   int32_t i;
@@ -37,7 +39,7 @@ static int aps_marshal_get_batch(aps_store* s, int32_t n, const int64_t* keys, c
     rq[i].nbytes = (uint32_t)nbytes[i];
     rq[i].dst = (unsigned char*)base + off[i];
   }
-  rc = aps_get_batch(s, (uint32_t)n, rq, rs, NULL);
+  rc = sharded ? aps_get_batch_sharded(s, (uint32_t)n, rq, rs, NULL) : aps_get_batch(s, (uint32_t)n, rq, rs, NULL);
   for (i = 0; i < n && rc == APS_OK; ++i) {
     out_len[i] = rs[i].len;
     if (out_crc) out_crc[i] = (int32_t)rs[i].crc;
@@ -47,7 +49,12 @@ static int aps_marshal_get_batch(aps_store* s, int32_t n, const int64_t* keys, c
   return rc;
 }
 
-static int aps_marshal_put_batch(aps_store* s, int32_t n, const int64_t* keys, const void* base, const int64_t* off,
+static inline int aps_marshal_get_batch(aps_store* s, int32_t n, const int64_t* keys, const int32_t* page_off, const int32_t* nbytes,
+                                 void* base, const int64_t* off, int32_t* out_len, int32_t* out_crc) {
+  return aps_marshal_get_batch_ex(s, 0, n, keys, page_off, nbytes, base, off, out_len, out_crc);
+}
+
+static inline int aps_marshal_put_batch(aps_store* s, int32_t n, const int64_t* keys, const void* base, const int64_t* off,
                                  const int32_t* len, int32_t* out_status, int32_t* out_crc) {
   aps_put_req* rq;
   aps_result* rs;
@@ -79,7 +86,7 @@ static int aps_marshal_put_batch(aps_store* s, int32_t n, const int64_t* keys, c
   return rc;
 }
 
-static int aps_marshal_delete_batch(aps_store* s, int32_t n, const int64_t* keys, int32_t* out_status) {
+static inline int aps_marshal_delete_batch(aps_store* s, int32_t n, const int64_t* keys, int32_t* out_status) {
   aps_key* k;
   aps_result* rs;
   int32_t i;
@@ -105,7 +112,7 @@ static int aps_marshal_delete_batch(aps_store* s, int32_t n, const int64_t* keys
 }
 
 /* `alluxio fs checksum` for n files whose bytes lie in one direct buffer: digests (16 bytes each) into out. */
-static int aps_marshal_md5_batch(int32_t device, int32_t n, const void* base, const int64_t* off, const int64_t* len,
+static inline int aps_marshal_md5_batch(int32_t device, int32_t n, const void* base, const int64_t* off, const int64_t* len,
                                  unsigned char* out) {
   const void** data;
   uint64_t* l;

@@ -215,6 +215,75 @@ int main(void) {
     fake_free(text); fake_free(path); fake_free(names); fake_free(counts);
   }
 
+  /* ---- gpu.device = -1: one cache over every GPU.  GpuPageStore opens a store per device, attaches them to each other,
+   * routes put / delete by nativeShardOf and reads any page through ONE sharded batch on shard 0. */
+  {
+    enum { M = 40 };
+    jint shards = JFN(nativeDeviceCount)(env, NULL);
+    jlong hs[8];
+    jlongArray jhandles;
+    jobject pinned = JFN(nativeAllocPinned)(env, NULL, M * PAGE);
+    unsigned char* p = (unsigned char*)fake_data(pinned);
+    jlong keys[3 * M], offs[M];
+    jint po[M], nb[M], owner_pages[8] = {0};
+    jlongArray jkeys, joffs;
+    jintArray jpo, jnb, jout_len, jcrc;
+    CHECK(shards == 2, "nativeDeviceCount = %d", shards);
+    for (i = 0; i < shards; ++i) {
+      CHECK(JFN(nativeOpen)(env, NULL, i, PAGE, 64 * PAGE, 128, 0, 0, 1, handle_out) == APS_OK, "nativeOpen shard %d", i);
+      hs[i] = ((jlong*)fake_data(handle_out))[0];
+    }
+    jhandles = longs(hs, shards);
+    for (i = 0; i < shards; ++i) CHECK(JFN(nativeShardAttachLocal)(env, NULL, jhandles, i) == APS_OK, "attach shard %d", i);
+    CHECK(JFN(nativeShardAttachLocal)(env, NULL, jhandles, shards) == APS_EINVAL, "attach beyond the set");
+    BALANCED();
+    for (i = 0; i < M; ++i) {                      /* put: to the owner */
+      const jint owner = JFN(nativeShardOf)(env, NULL, 0, 31, i, shards);
+      jobject one = fake_new_direct_buffer(p + (size_t)i * PAGE, PAGE);
+      CHECK(owner >= 0 && owner < shards, "owner %d", owner);
+      ++owner_pages[owner];
+      for (k = 0; k < len_of(i); ++k) p[(size_t)i * PAGE + k] = byte_of(31, i, k);
+      CHECK(JFN(nativePut)(env, NULL, hs[owner], 0, 31, i, one, len_of(i)) == APS_OK, "put to owner");
+      fake_free(one);
+      keys[3 * i] = 0; keys[3 * i + 1] = 31; keys[3 * i + 2] = i;
+      offs[i] = (jlong)i * PAGE;
+      po[i] = 0;
+      nb[i] = PAGE;
+    }
+    CHECK(owner_pages[0] > 0 && owner_pages[1] > 0, "routing put everything on one shard");
+    memset(p, 0xEE, (size_t)M * PAGE);
+    jkeys = longs(keys, 3 * M);
+    joffs = longs(offs, M);
+    jpo = ints(po, M);
+    jnb = ints(nb, M);
+    jout_len = ints(NULL, M);
+    jcrc = ints(NULL, M);
+    CHECK(JFN(nativeGetBatchSharded)(env, NULL, hs[0], M, jkeys, jpo, jnb, pinned, joffs, jout_len, jcrc) == APS_OK, "sharded get");
+    for (i = 0; i < M; ++i) {
+      CHECK(((jint*)fake_data(jout_len))[i] == len_of(i), "sharded get %d: %d bytes", i, ((jint*)fake_data(jout_len))[i]);
+      for (k = 0; k < len_of(i); ++k)
+        if (p[(size_t)i * PAGE + k] != byte_of(31, i, k)) {
+          CHECK(0, "sharded get %d byte %d", i, k);
+          break;
+        }
+    }
+    /* the plain batched get on shard 0 sees only shard 0's pages */
+    CHECK(JFN(nativeGetBatch)(env, NULL, hs[0], M, jkeys, jpo, jnb, pinned, joffs, jout_len, jcrc) == APS_OK, "local get");
+    for (i = 0, k = 0; i < M; ++i) k += ((jint*)fake_data(jout_len))[i] >= 0;
+    CHECK(k == owner_pages[0], "shard 0 answered %d pages, owns %d", k, owner_pages[0]);
+    BALANCED();
+    for (i = 0; i < shards; ++i) {                 /* getPages(): the shards' listings add up */
+      jlongArray listed = JFN(nativeIterate)(env, NULL, hs[i]);
+      CHECK(listed != NULL && ((fake_obj*)listed)->n == 4 * owner_pages[i], "shard %d lists %d longs", i, listed ? ((fake_obj*)listed)->n : -1);
+      fake_free(listed);
+      CHECK(JFN(nativeClose)(env, NULL, hs[i]) == APS_OK, "close shard %d", i);
+    }
+    JFN(nativeFreePinned)(env, NULL, pinned);
+    fake_free(pinned); fake_free(jhandles); fake_free(jkeys); fake_free(joffs); fake_free(jpo); fake_free(jnb);
+    fake_free(jout_len); fake_free(jcrc);
+    BALANCED();
+  }
+
   /* ---- close() is idempotent; a closed store answers APS_ECLOSED, and getPages() reports the failure as null */
   CHECK(JFN(nativeClose)(env, NULL, h) == APS_OK && JFN(nativeClose)(env, NULL, h) == APS_OK, "nativeClose twice");
   CHECK(JFN(nativeDelete)(env, NULL, h, 0, 7, 1) == APS_ECLOSED, "delete on a closed store");
