@@ -33,3 +33,57 @@ def test_every_native_method_has_its_jni_function():
     # and nothing in the shim that the class does not declare
     for n in re.findall(r"JFN\((native\w+)\)", shim):
         assert n in natives, "%s has no declaration in GpuPageStore.java" % n
+
+
+def _strip_java(text):
+    """Java source without comments, string and char literals (enough for bracket counting)."""
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", "", text)
+    text = re.sub(r'"(\\.|[^"\\])*"', '""', text)
+    return re.sub(r"'(\\.|[^'\\])'", "''", text)
+
+
+@pytest.mark.parametrize("name", ["GpuPageStore.java", "GpuPageStoreOptions.java"])
+def test_java_sources_are_well_formed_as_far_as_can_be_told_without_a_compiler(name):
+    """No JDK here: what can be checked is structure -- brackets balance and nest, every statement-looking line ends, every
+    native the class CALLS is declared with that many parameters, and the JNI function takes the same number (+ env, cls)."""
+    java = _strip_java(open(os.path.join(ROOT, "integration", "java", "alluxio", "client", "file", "cache", "store", name)).read())
+    stack, pairs = [], {")": "(", "]": "[", "}": "{"}
+    for ch in java:
+        if ch in "([{":
+            stack.append(ch)
+        elif ch in pairs:
+            assert stack and stack.pop() == pairs[ch], "unbalanced %s in %s" % (ch, name)
+    assert not stack, "unclosed %s in %s" % (stack, name)
+    if name != "GpuPageStore.java":
+        return
+    shim = open(os.path.join(ROOT, "integration", "jni", "aps_jni.c")).read()
+
+    def arity(args):
+        depth, n, seen = 0, 0, False
+        for ch in args:
+            if ch in "([{":
+                depth += 1
+            elif ch in ")]}":
+                depth -= 1
+            elif ch == "," and depth == 0:
+                n += 1
+            seen = seen or not ch.isspace()
+        return n + 1 if seen else 0
+
+    def call_args(text, start):
+        depth, i = 1, start
+        while depth:
+            depth += {"(": 1, ")": -1}.get(text[i], 0)
+            i += 1
+        return text[start:i - 1]
+
+    declared = {}
+    for m in re.finditer(r"private static native [\w\[\]<>]+ (native\w+)\(", java):
+        declared[m.group(1)] = arity(call_args(java, m.end()))
+    for m in re.finditer(r"(?<!native )(?<![\w\]>] )\b(native\w+)\(", java):
+        name_, n = m.group(1), arity(call_args(java, m.end()))
+        assert name_ in declared, "%s is called but not declared" % name_
+        assert n == declared[name_], "%s is called with %d arguments, declared with %d" % (name_, n, declared[name_])
+    for m in re.finditer(r"JFN\((native\w+)\)\(", shim):
+        assert arity(call_args(shim, m.end())) == declared[m.group(1)] + 2, "%s: JNI parameters do not match the declaration" % m.group(1)
