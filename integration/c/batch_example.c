@@ -35,6 +35,10 @@ int main(void) {
   int64_t keys[3 * (N + 1)], off[N + 1];
   int32_t len[N + 1], page_off[N + 1], nbytes[N + 1], status[N + 1], out_len[N + 1], crc_put[N + 1], crc_get[N + 1];
   int i, rc;
+  if (!src || !dst) {
+    fprintf(stderr, "out of memory\n");
+    return 2;
+  }
   memset(&cfg, 0, sizeof(cfg));
   cfg.device = 0;
   cfg.page_size = PAGE;

@@ -38,6 +38,10 @@ int main(void) {
   }
   page = (unsigned char*)malloc(cfg.page_size);
   back = (unsigned char*)malloc(cfg.page_size);
+  if (!page || !back) {
+    fprintf(stderr, "out of memory\n");
+    return 2;
+  }
   for (i = 0; i < cfg.page_size; ++i) page[i] = (unsigned char)(i * 31u + (i >> 8));
   rc = aps_put(store, &key, page, cfg.page_size);
   if (rc == APS_OK) rc = aps_get(store, &key, 0, cfg.page_size, back, cfg.page_size, &got, &crc);
