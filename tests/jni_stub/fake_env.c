@@ -16,6 +16,7 @@ int fake_env_outstanding(void) { return g_outstanding; }
 
 static fake_obj* new_obj(int kind, jsize n, size_t elem) {
   fake_obj* o = (fake_obj*)calloc(1, sizeof(*o));
+  if (!o) abort();
   o->kind = kind;
   o->n = n;
   o->elem = elem;
