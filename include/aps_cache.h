@@ -38,7 +38,9 @@ typedef struct apc_meta apc_meta;       /* DefaultMetaStore */
 APS_API int apc_manager_create(const aps_config* cfg, const char* evictor, double lfu_logbase, apc_manager** out);
 /* LocalCacheManager.create(conf, metaStore, pageStore) over a store that already holds pages: the restore
  * path (CACHE/LocalCacheManager.java:466-509) adopts them in getPages() order while they fit the cache size
- * and deletes the rest from the store.  The store stays the caller's (apc_manager_close does not close it). */
+ * and deletes the rest from the store.  If that restore fails (a delete that fails, a listing that fails) the store is
+ * emptied and the cache goes on READ_WRITE and empty, as restoreOrInit does (:441-464); only if emptying fails too is the
+ * manager NOT_IN_USE.  The store stays the caller's (apc_manager_close does not close it). */
 APS_API int apc_manager_create_over(aps_store* store, uint32_t page_size, const char* evictor, double lfu_logbase,
                                     apc_manager** out);
 /* Warm restart through the manager.  apc_manager_snapshot_save writes the store's pages together with
