@@ -87,3 +87,65 @@ def test_java_sources_are_well_formed_as_far_as_can_be_told_without_a_compiler(n
         assert n == declared[name_], "%s is called with %d arguments, declared with %d" % (name_, n, declared[name_])
     for m in re.finditer(r"JFN\((native\w+)\)\(", shim):
         assert arity(call_args(shim, m.end())) == declared[m.group(1)] + 2, "%s: JNI parameters do not match the declaration" % m.group(1)
+
+
+def test_patched_reference_files_are_well_formed(tmp_path):
+    """Applies both patches for real to copies of the files they touch and checks the results as far as can be done without
+    a compiler: brackets balance, and the calls the patched LocalCacheManager makes into GpuPageStore have the arity of the
+    methods GpuPageStore.java declares."""
+    if not os.path.isdir(os.path.join(REFERENCE, "core")) or not shutil.which("patch"):
+        pytest.skip("reference tree or patch(1) not available here")
+    touched = set()
+    for name in PATCHES:
+        for line in open(os.path.join(ROOT, "integration", "patches", name)):
+            if line.startswith("+++ b/"):
+                touched.add(line[6:].split("\t")[0].strip())
+    assert len(touched) == 8
+    for rel in touched:
+        os.makedirs(os.path.dirname(tmp_path / rel), exist_ok=True)
+        shutil.copy(os.path.join(REFERENCE, rel), tmp_path / rel)
+    for name in PATCHES:
+        out = subprocess.run(["patch", "-p1", "-d", str(tmp_path), "-i", os.path.join(ROOT, "integration", "patches", name)],
+                             capture_output=True, text=True)
+        assert out.returncode == 0, out.stdout + out.stderr
+    pairs = {")": "(", "]": "[", "}": "{"}
+    for rel in touched:
+        java, stack = _strip_java(open(tmp_path / rel).read()), []
+        for ch in java:
+            if ch in "([{":
+                stack.append(ch)
+            elif ch in pairs:
+                assert stack and stack.pop() == pairs[ch], "unbalanced %s in patched %s" % (ch, rel)
+        assert not stack, "unclosed %s in patched %s" % (stack, rel)
+    store = _strip_java(open(os.path.join(ROOT, "integration", "java", "alluxio", "client", "file", "cache", "store", "GpuPageStore.java")).read())
+    manager = _strip_java(open(tmp_path / "core/client/fs/src/main/java/alluxio/client/file/cache/LocalCacheManager.java").read())
+
+    def params(text, name):
+        m = re.search(r"public [\w\[\]<>]+ %s\(" % name, text)
+        depth, i = 1, m.end()
+        while depth:
+            depth += {"(": 1, ")": -1}.get(text[i], 0)
+            i += 1
+        return text[m.end():i - 1].count(",") + 1
+
+    for method in ("getBatch", "allocPinned"):
+        call = re.search(r"store\.%s\(([^;]*)\);" % method, manager)
+        assert call, "the patched LocalCacheManager no longer calls GpuPageStore.%s" % method
+        depth = n = 0
+        for ch in call.group(1):
+            depth += {"(": 1, ")": -1}.get(ch, 0)
+            n += ch == "," and depth == 0
+        assert n + 1 == params(store, method), "GpuPageStore.%s is called with %d arguments" % (method, n + 1)
+    # the registration patch and the options class agree on the setters it calls
+    options = open(os.path.join(ROOT, "integration", "java", "alluxio", "client", "file", "cache", "store", "GpuPageStoreOptions.java")).read()
+    created = open(tmp_path / "core/client/fs/src/main/java/alluxio/client/file/cache/store/PageStoreOptions.java").read()
+    gpu_case = created[created.index("case GPU:"):]
+    gpu_case = gpu_case[:gpu_case.index("break;")]
+    setters = re.findall(r"\.(set\w+)\(", gpu_case)
+    assert len(setters) >= 4
+    for setter in setters:
+        assert re.search(r"public GpuPageStoreOptions %s\(" % setter, options), setter
+    # every key the patch reads is defined by the patch
+    keys = open(tmp_path / "core/common/src/main/java/alluxio/conf/PropertyKey.java").read()
+    for key in set(re.findall(r"PropertyKey\.(USER_CLIENT_CACHE_GPU_\w+)", created)):
+        assert re.search(r"public static final PropertyKey %s =" % key, keys) and re.search(r"public static final String %s =" % key, keys), key
