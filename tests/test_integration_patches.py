@@ -100,7 +100,7 @@ def test_patched_reference_files_are_well_formed(tmp_path):
         for line in open(os.path.join(ROOT, "integration", "patches", name)):
             if line.startswith("+++ b/"):
                 touched.add(line[6:].split("\t")[0].strip())
-    assert len(touched) == 8
+    assert len(touched) == 9
     for rel in touched:
         os.makedirs(os.path.dirname(tmp_path / rel), exist_ok=True)
         shutil.copy(os.path.join(REFERENCE, rel), tmp_path / rel)
