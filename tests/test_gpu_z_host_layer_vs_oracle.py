@@ -264,3 +264,38 @@ def test_a_failed_restore_wipes_the_store_and_the_cache_goes_on_empty():
     assert m.put(PID("5", 0), increasing(9, PS)) and m.get(PID("5", 0), PS, buf) == PS and bytes(buf) == increasing(9, PS)
     m.close()
     store.close()
+
+
+def test_load_cache_and_evict():
+    """LocalCacheManagerIntegrationTest.loadCacheAndEvict (:117-144): a cache is filled, its manager closed and a new
+    one created over the same store; the restored pages then take part in eviction like any others -- putting half a
+    cache of new pages evicts exactly half of the restored ones."""
+    from alluxio_b200.cache import LocalCacheManager
+    from alluxio_b200.page_store import GpuPageStore
+    count = 32
+    page = increasing(PS)
+    store = GpuPageStore(page_size=PS, cache_size=count * PS, slab_slots=128)
+    m = LocalCacheManager.over_store(store, PS, "LRU")
+    buf = bytearray(PS)
+    for i in range(count):                                     # loadFullCache
+        assert m.put(PID("0", i), page)
+    for i in range(count):
+        assert m.get(PID("0", i), PS, buf) == PS and bytes(buf) == page
+    m.close()                                                  # the store outlives its manager, as the cache directory does
+    m = LocalCacheManager.over_store(store, PS, "LRU")
+    assert m.state() == m.READ_WRITE and m.pages() == count
+    for i in range(count // 2):
+        assert m.put(PID("1", i), page)
+    evicted = 0
+    for i in range(count):
+        ret = m.get(PID("0", i), PS, buf)
+        if ret <= 0:
+            evicted += 1
+            continue
+        assert ret == PS and bytes(buf) == page
+    assert evicted == count // 2
+    for i in range(count // 2):
+        assert m.get(PID("1", i), PS, buf) == PS and bytes(buf) == page
+    assert len(store.get_pages()) == count
+    m.close()
+    store.close()

@@ -304,3 +304,54 @@ def test_replay_matches_step_by_step_manager(tmp_path):
                 assert mgr.put(pid, bytes(int(lens[k]))) == bool(r["put_ok"][k])
         assert mgr.pages() == r["final_pages"] and mgr.bytes() == r["final_bytes"]
         assert r["n_victims"] > 0
+
+
+# ---- tests/src/test/java/alluxio/client/fs/LocalCacheManagerIntegrationTest.java: a cache that is closed and created again
+
+IT_PAGE_COUNT = 32
+
+
+def _load_full_cache(tmp_path, evictor="LRU"):
+    """loadFullCache (:249-257): 32 pages of 1 KB into a 32 KB cache, all readable."""
+    e = Env(tmp_path, cache_size=IT_PAGE_COUNT * PAGE_SIZE, evictor=evictor)
+    for i in range(IT_PAGE_COUNT):
+        assert e.mgr.put(page_id(0, i), PAGE1)
+    for i in range(IT_PAGE_COUNT):
+        assert e.mgr.get(page_id(0, i), PAGE_SIZE, e.buf) == PAGE_SIZE and bytes(e.buf) == PAGE1
+    return e
+
+
+def test_load_cache_and_evict(tmp_path):
+    """loadCacheAndEvict (:117-144): the restored pages take part in eviction like any others."""
+    _load_full_cache(tmp_path)
+    e = Env(tmp_path, cache_size=IT_PAGE_COUNT * PAGE_SIZE, evictor="LRU", wipe=False)   # close + create again
+    for i in range(IT_PAGE_COUNT // 2):
+        assert e.mgr.put(page_id(1, i), PAGE1)
+    evicted = 0
+    for i in range(IT_PAGE_COUNT):
+        ret = e.mgr.get(page_id(0, i), PAGE_SIZE, e.buf)
+        if ret <= 0:
+            evicted += 1
+            continue
+        assert ret == PAGE_SIZE and bytes(e.buf) == PAGE1
+    assert evicted == IT_PAGE_COUNT // 2
+    for i in range(IT_PAGE_COUNT // 2):
+        assert e.mgr.get(page_id(1, i), PAGE_SIZE, e.buf) == PAGE_SIZE and bytes(e.buf) == PAGE1
+
+
+def test_load_cache_smaller_new_cache_size(tmp_path):
+    """loadCacheSmallerNewCacheSizeLocal (:183-205): half the budget keeps (at least) half of the pages."""
+    _load_full_cache(tmp_path)
+    e = Env(tmp_path, cache_size=IT_PAGE_COUNT * PAGE_SIZE // 2, evictor="LRU", wipe=False)
+    assert e.mgr.state() == orc.LocalCacheManager.READ_WRITE
+    hits = sum(e.mgr.get(page_id(0, i), PAGE_SIZE, e.buf) == PAGE_SIZE for i in range(IT_PAGE_COUNT))
+    assert hits == IT_PAGE_COUNT // 2 and e.mgr.pages() == hits
+    assert len(e.store.get_pages()) == hits          # the pages that did not fit were deleted from the store (:493-497)
+
+
+def test_load_cache_larger_new_cache_size(tmp_path):
+    """loadCacheLargerNewCacheSize (:218-222)."""
+    e = Env(tmp_path, cache_size=IT_PAGE_COUNT * PAGE_SIZE)
+    assert e.mgr.put(PAGE_ID1, PAGE1)
+    e = Env(tmp_path, cache_size=2 * IT_PAGE_COUNT * PAGE_SIZE, wipe=False)
+    assert e.mgr.get(PAGE_ID1, PAGE_SIZE, e.buf) == PAGE_SIZE and bytes(e.buf) == PAGE1
