@@ -102,3 +102,83 @@ def test_oracle_manager_equals_the_independent_model(history):
         else:
             assert om.delete(pid) == model.delete(op[1]), op
         assert (om.pages(), om.bytes()) == (len(model.meta), model.bytes()), op
+
+
+# ---- LFUCacheEvictor (CACHE/evictor/LFUCacheEvictor.java:61-153), stated again and independently ---------------------
+
+import math
+
+
+class LfuModel:
+    """Counts per page, buckets by (int)(ln(count) / ln(base)), LRU inside a bucket, and mMinBucket maintained exactly
+    as the Java does (a page that leaves the minimum bucket empty takes mMinBucket along to its new bucket, :117-119;
+    a delete that empties it walks upwards, :143-149)."""
+
+    def __init__(self, base):
+        self.divisor = math.log(base)
+        self.count, self.buckets, self.min_bucket = {}, {}, -1
+
+    def bucket_of(self, count):
+        return int(math.log(count) / self.divisor)
+
+    def update(self, pid):                                     # updateOnGet = updateOnPut (:108-133)
+        new_count = self.count[pid] = self.count.get(pid, 0) + 1
+        new_bucket = self.bucket_of(new_count)
+        if new_count > 1:
+            old_bucket = self.bucket_of(new_count - 1)
+            if new_bucket != old_bucket:
+                pages = self.buckets.get(old_bucket)
+                if pages is not None:
+                    pages.pop(pid, None)
+                    if not pages:
+                        del self.buckets[old_bucket]
+                        if old_bucket == self.min_bucket:
+                            self.min_bucket = new_bucket
+                self.buckets.setdefault(new_bucket, OrderedDict())[pid] = True
+            elif pid in self.buckets.get(new_bucket, {}):
+                self.buckets[new_bucket].move_to_end(pid)      # LinkedHashMap in access order: get() touches
+        else:
+            self.min_bucket = new_bucket
+            self.buckets.setdefault(new_bucket, OrderedDict())[pid] = True
+
+    def delete(self, pid):                                     # :135-151
+        count = self.count.pop(pid, None)
+        if count is None:
+            return
+        bucket = self.bucket_of(count)
+        pages = self.buckets.get(bucket)
+        if pages is not None:
+            pages.pop(pid, None)
+            if not pages:
+                del self.buckets[bucket]
+                if bucket == self.min_bucket and self.buckets:
+                    while self.min_bucket not in self.buckets:
+                        self.min_bucket += 1
+
+    def evict(self):                                           # :153-164: the eldest page of bucket mMinBucket, or null
+        pages = self.buckets.get(self.min_bucket)
+        return next(iter(pages)) if pages else None
+
+
+evictor_ops = st.lists(st.tuples(st.sampled_from(["get", "get", "put", "delete", "evict", "evict_and_delete"]), st.integers(0, 7)),
+                       min_size=5, max_size=300)
+
+
+@settings(max_examples=300, deadline=None)
+@given(evictor_ops, st.sampled_from([2.0, 1.1, 1.5, 3.0, 10.0]))
+def test_oracle_lfu_evictor_equals_the_independent_model(history, base):
+    model, oe = LfuModel(base), orc.Evictor("LFU", base)
+    for op, k in history:
+        pid = orc.PageId("f", k)
+        if op in ("get", "put"):
+            model.update(k)
+            (oe.update_on_get if op == "get" else oe.update_on_put)(pid)
+        elif op == "delete":
+            model.delete(k)
+            oe.update_on_delete(pid)
+        else:
+            want, got = model.evict(), oe.evict()
+            assert (None if got is None else got.page_index) == want, (op, k, base)
+            if op == "evict_and_delete" and want is not None:  # what DefaultMetaStore.evict's caller does next
+                model.delete(want)
+                oe.update_on_delete(orc.PageId("f", want))
