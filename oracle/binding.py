@@ -12,9 +12,28 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 
+_SOURCES = ("checksums.c", "page_cache.cc", "page_cache.h", "capi.cc", "Makefile")
+
+
+def _stale():
+    if not os.path.exists(_LIB_PATH):
+        return True
+    built = os.path.getmtime(_LIB_PATH)
+    return any(os.path.getmtime(os.path.join(_HERE, f)) > built for f in _SOURCES)
+
+
 def build(force=False):
-    """Compile the restatement with the committed Makefile (make rebuilds what is older than its sources)."""
-    subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    """Compile the restatement with the committed Makefile when the library is missing or older than a source.  Several
+    processes may get here at once (bench.py under torchrun: every rank checks its pages against the oracle), so the
+    build runs under a file lock: one builds, the others wait and then find it up to date."""
+    if not force and not _stale():
+        return _LIB_PATH
+    import fcntl
+    with open(os.path.join(_HERE, ".build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if force or _stale():
+            subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+            os.utime(_LIB_PATH)  # make may have had nothing to do (objects newer than sources): mark the library current
     return _LIB_PATH
 
 
