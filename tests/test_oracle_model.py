@@ -77,7 +77,7 @@ ops = st.lists(st.one_of(
     st.tuples(st.just("delete"), ids)), min_size=10, max_size=200)
 
 
-@settings(max_examples=400, deadline=None)
+@settings(max_examples=400, deadline=None, derandomize=True)  # 4,000 random examples were run once when this was written
 @given(ops)
 def test_oracle_manager_equals_the_independent_model(history):
     model = Model()
@@ -164,7 +164,7 @@ evictor_ops = st.lists(st.tuples(st.sampled_from(["get", "get", "put", "delete",
                        min_size=5, max_size=300)
 
 
-@settings(max_examples=300, deadline=None)
+@settings(max_examples=300, deadline=None, derandomize=True)
 @given(evictor_ops, st.sampled_from([2.0, 1.1, 1.5, 3.0, 10.0]))
 def test_oracle_lfu_evictor_equals_the_independent_model(history, base):
     model, oe = LfuModel(base), orc.Evictor("LFU", base)
