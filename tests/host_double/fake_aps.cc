@@ -174,6 +174,10 @@ APS_API int aps_iterate(aps_store* s, aps_iter_cb cb, void* user) {
     for (const auto& e : s->pages)
       all.push_back({aps_key{std::get<0>(e.first), std::get<1>(e.first), std::get<2>(e.first)}, (uint32_t)e.second.size()});
   }
+  // The real store walks its hash table: callers must not depend on the order.  APS_DOUBLE_ITERATE=reverse lets the
+  // CPU suite run every case under a second order (tests/test_host_logic_cpu.py does).
+  const char* order = getenv("APS_DOUBLE_ITERATE");
+  if (order && !strcmp(order, "reverse")) std::reverse(all.begin(), all.end());
   for (const auto& e : all)
     if (cb(user, &e.first, e.second)) break;
   return APS_OK;
